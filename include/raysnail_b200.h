@@ -1,0 +1,281 @@
+/*
+ * raysnail_b200.h — C ABI of the B200 (sm_100a) path-tracing backend for Raysnail.
+ *
+ * This is the drop-in boundary for ONE hot path of the reference renderer: the per-pixel
+ * Monte-Carlo sample loop that `TakePhotoSettings::shot_to_target` (reference
+ * src/camera.rs:261-287) hands to `Painter::draw` (src/painter.rs:307-336).  A host (the
+ * reference's Rust crate through `extern "C"`, or the C++/Python host in this repository)
+ * flattens its scene graph into the plain SoA/AoS buffers below, uploads them once, and
+ * calls `rs_render*`; the library returns exactly what `shot_to_target` returns: a row-major
+ * `[f32;4]` image (src/painter.rs:154-187, src/prelude/vec3.rs:227-240).
+ *
+ * Rules of the boundary:
+ *   - plain C: pointers, sizes, PODs; no exceptions cross it; every call returns an rs_status;
+ *   - the caller owns every host buffer; `rs_upload_scene` copies what it needs;
+ *   - one rs_ctx is bound to one CUDA device and is used by one host thread at a time;
+ *   - there is no CPU fallback: if no CUDA device is usable, rs_create fails.
+ *
+ * All geometry is f64 (the reference's Vec3 is f64, src/prelude/vec3.rs:14-19); colours are
+ * f32 (src/prelude/color.rs:10-16).
+ */
+#ifndef RAYSNAIL_B200_H
+#define RAYSNAIL_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RS_ABI_VERSION 1
+
+typedef enum rs_status {
+    RS_OK = 0,
+    RS_ERR_INVALID_ARGUMENT = 1,
+    RS_ERR_CUDA = 2,
+    RS_ERR_NO_DEVICE = 3,
+    RS_ERR_NO_SCENE = 4,
+    RS_ERR_UNSUPPORTED = 5,
+    RS_ERR_OUT_OF_MEMORY = 6,
+    RS_ERR_PARSE = 7,
+    RS_ERR_IO = 8
+} rs_status;
+
+/* ------------------------------------------------------------------------------------------
+ * Scene graph nodes.  One node per reference `Hittable` object (src/hittable/hit.rs:80-112).
+ * ---------------------------------------------------------------------------------------- */
+typedef enum rs_node_type {
+    RS_NODE_SPHERE = 0,       /* src/hittable/geometry/sphere.rs   p: cx cy cz r vx vy vz          */
+    RS_NODE_BOX = 1,          /* src/hittable/geometry/box.rs      p: minx miny minz maxx maxy maxz */
+    RS_NODE_RECT = 2,         /* src/hittable/geometry/rect.rs     p: k a0 a1 b0 b1 ; rect_axis     */
+    RS_NODE_QUADRIC = 3,      /* src/hittable/geometry/quadric.rs  p: qa qb qc qd qe qf qg qh qi qj */
+    RS_NODE_DIFFERENCE = 4,   /* src/hittable/csg/difference.rs    child0 = plus, child1 = minus    */
+    RS_NODE_INTERSECTION = 5, /* src/hittable/csg/intersection.rs  child0 = o1,   child1 = o2       */
+    RS_NODE_TRANSFORM = 6,    /* src/hittable/transform/tf_facade.rs child0; xforms[first..first+n) */
+    RS_NODE_MEDIUM = 7        /* src/hittable/medium/constant.rs   child0 = boundary; p[0]=density;
+                                 material = the Isotropic material                                  */
+} rs_node_type;
+
+/* rect_axis: which AARect constructor built it (src/hittable/geometry/rect.rs:56-78) */
+#define RS_RECT_XY 0 /* axis = (0,1,2) */
+#define RS_RECT_XZ 1 /* axis = (0,2,1) */
+#define RS_RECT_YZ 2 /* axis = (1,2,0) */
+
+typedef struct rs_node {
+    int32_t type;        /* rs_node_type */
+    int32_t material;    /* index into materials, -1 = None (Option<Arc<dyn Material>>) */
+    int32_t child0;
+    int32_t child1;
+    int32_t first_xform; /* RS_NODE_TRANSFORM: first entry of its TransformStack */
+    int32_t n_xform;     /* RS_NODE_TRANSFORM: number of stack entries           */
+    int32_t rect_axis;   /* RS_NODE_RECT */
+    int32_t reserved;
+    double p[10];
+} rs_node;
+
+/* One TransformStack entry: `Transform{matrix, inverse}`, row-major 4x4
+ * (src/hittable/transform/transform.rs:8-13). */
+typedef struct rs_xform {
+    double m[16];
+    double inv[16];
+} rs_xform;
+
+/* ------------------------------------------------------------------------------------------
+ * Materials (src/material/) and textures (src/texture/).
+ * ---------------------------------------------------------------------------------------- */
+typedef enum rs_material_type {
+    RS_MAT_LAMBERTIAN = 0,    /* lambertian.rs    texture                                      */
+    RS_MAT_METAL = 1,         /* metal.rs:86-127  texture                                      */
+    RS_MAT_DIFFUSE_METAL = 2, /* metal.rs:22-84   texture, a = exponent                        */
+    RS_MAT_DIELECTRIC = 3,    /* dielectric.rs    color, a = refractive, has_curve (Glass)     */
+    RS_MAT_DIFFUSE_LIGHT = 4, /* light.rs         texture, a = multiplier                      */
+    RS_MAT_ISOTROPIC = 5,     /* isotropic.rs     color                                        */
+    RS_MAT_BLINN_PHONG = 6,   /* blinn_phong.rs   texture, a = k_specular, b = exponent        */
+    RS_MAT_MIXED = 7          /* mixed_material.rs mat1, mat2, a = probability_1               */
+} rs_material_type;
+
+typedef struct rs_material {
+    int32_t type;           /* rs_material_type */
+    int32_t texture;        /* index into textures, -1 if unused */
+    int32_t mat1;           /* RS_MAT_MIXED */
+    int32_t mat2;           /* RS_MAT_MIXED */
+    int32_t has_curve;      /* RS_MAT_DIELECTRIC: 1 = Glass Schlick curve (dielectric.rs:17-25) */
+    int32_t phong_exponent; /* CommonMaterialSettings (material/mod.rs:41-55), default 1 */
+    double phong_factor;    /* default 0 */
+    double a;
+    double b;
+    float color[4];
+} rs_material;
+
+typedef enum rs_texture_type {
+    RS_TEX_SOLID = 0,   /* prelude/color.rs:61-65 */
+    RS_TEX_CHECKER = 1, /* texture/checker.rs     */
+    RS_TEX_IMAGE = 2,   /* texture/image.rs       */
+    RS_TEX_PERLIN = 3   /* texture/noise.rs       */
+} rs_texture_type;
+
+typedef struct rs_texture {
+    int32_t type;          /* rs_texture_type */
+    int32_t odd;           /* CHECKER: texture id used when the sign product is < 0 */
+    int32_t even;          /* CHECKER */
+    int32_t width;         /* IMAGE */
+    int32_t height;        /* IMAGE */
+    int32_t texel_offset;  /* IMAGE: byte offset into texels (RGBA8, row-major, row 0 = top) */
+    int32_t perlin_kind;   /* PERLIN: 0 Normal, 1 Turbulence, 2 Marble (noise.rs:10-15) */
+    int32_t perlin_depth;  /* PERLIN: turbulence depth */
+    int32_t perlin_smooth; /* PERLIN: 0 None, 1 LinearInterpolate, 2 HermitianCubic */
+    int32_t perlin_vector; /* PERLIN: 1 = unit-vector lattice, 0 = float lattice */
+    int32_t point_count;   /* PERLIN: power of two */
+    int32_t perm_offset;   /* PERLIN: offset (in int32) into perlin_perm: perm_x, perm_y, perm_z */
+    int32_t value_offset;  /* PERLIN: offset (in double) into perlin_values: point_count*(vector?3:1) */
+    int32_t reserved;
+    double scale;          /* CHECKER, PERLIN */
+    float color[4];        /* SOLID */
+} rs_texture;
+
+/* ------------------------------------------------------------------------------------------
+ * The flattened `World` (src/hittable/collection/world.rs:25-53).
+ *
+ * roots[i] >= 0  : node index of the i-th object of the world's HittableList;
+ * roots[i] <  0  : triangle ~roots[i] (src/hittable/geometry/triangle_mesh.rs:17-149).
+ * The position i in `roots` is the object id reported by the parity probes.
+ * root_bbox[6*i..] = the object's `Hittable::bbox` as the reference computes it
+ * (min xyz, max xyz); the host already has it.  An object only counts as hit when the ray
+ * passes `AABB::hit` on this box (src/prelude/aabb.rs:20-38): that reproduces the clipping the
+ * reference gets from e.g. the fixed +-100 quadric box and the Intersection bbox quirk
+ * (src/hittable/csg/intersection.rs:102-118).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct rs_scene_desc {
+    const rs_node* nodes;
+    int32_t n_nodes;
+    const int32_t* roots;
+    const double* root_bbox;
+    int32_t n_roots;
+    const int32_t* lights; /* node indices of `World.lights` in list order */
+    int32_t n_lights;
+    const rs_xform* xforms;
+    int32_t n_xforms;
+    const double* tri_verts;     /* n_tris * 9: p0 p1 p2                     */
+    const double* tri_normals;   /* n_tris * 9: normal0 normal1 normal2      */
+    const int32_t* tri_material; /* n_tris, -1 = None                        */
+    int32_t n_tris;
+    const rs_material* materials;
+    int32_t n_materials;
+    const rs_texture* textures;
+    int32_t n_textures;
+    const uint8_t* texels;
+    int64_t n_texel_bytes;
+    const int32_t* perlin_perm;
+    int32_t n_perlin_perm;
+    const double* perlin_values;
+    int32_t n_perlin_values;
+    int32_t default_material; /* World.default_material (world.rs:29,51): white Lambertian */
+    /* Background closure restricted to the one form every shipped caller uses:
+     * bg0.gradient(bg1, 0.5*(dir.y+1))  (raysnail.rs:364-367, rtow_13_1.rs:38-41, world.rs:20-23) */
+    float bg0[4];
+    float bg1[4];
+} rs_scene_desc;
+
+/* `Camera` after `Camera::new` (src/camera.rs:18-73). */
+typedef struct rs_camera {
+    double origin[3];
+    double lb[3];
+    double horizontal_full[3];
+    double vertical_full[3];
+    double horizontal_unit[3];
+    double vertical_unit[3];
+    double aperture;
+    double shutter_speed;
+    int32_t width;
+    int32_t height;
+} rs_camera;
+
+/* `Painter` + `TakePhotoSettings` (src/painter.rs:66-130, src/camera.rs:103-154). */
+typedef struct rs_render_params {
+    int32_t sqrt_spp;          /* Painter::samples: floor(sqrt(samples_requested)) */
+    int32_t depth;             /* TakePhotoSettings::depth, default 8 */
+    int32_t gamma;             /* 1 = sqrt per channel (vec3.rs:229-233) */
+    int32_t stratum_row_begin; /* render strata rows s_j in [begin, end); whole image: 0..sqrt_spp */
+    int32_t stratum_row_end;
+    int32_t max_wave_paths;    /* 0 = library default; upper bound on paths in flight */
+    uint64_t seed;             /* Philox4x32-10 key */
+    uint32_t flags;            /* RS_FLAG_* */
+    uint32_t reserved;
+} rs_render_params;
+
+#define RS_FLAG_PIXEL_CENTRE 1u  /* probes only: no jitter, no lens, time 0 (u,v at stratum centre) */
+#define RS_FLAG_KERNEL_TIMING 2u /* record CUDA events around every kernel; fills rs_stats.ms_* (syncs the stream) */
+
+typedef struct rs_stats {
+    uint64_t n_samples;        /* camera paths started */
+    uint64_t n_segments;       /* closest-hit queries (ray segments) */
+    uint64_t n_launches;       /* kernels launched by the last render call */
+    double ms_raygen, ms_extend, ms_shade, ms_accumulate; /* CUDA-event time of last render */
+    double ms_total;
+} rs_stats;
+
+typedef struct rs_ctx rs_ctx;
+
+/* ---- life cycle --------------------------------------------------------------------------*/
+int rs_abi_version(void);
+/* Bind a context to CUDA device `device`.  Fails (RS_ERR_NO_DEVICE) without a GPU. */
+int rs_create(rs_ctx** out, int device);
+void rs_destroy(rs_ctx* ctx);
+/* Message of the last failed call on this context (or of a failed rs_create when ctx == NULL). */
+const char* rs_last_error(const rs_ctx* ctx);
+
+/* ---- scene: replaces `World::new` (world.rs:40-53) + `BVH::new` (bvh.rs:47-112) -----------*/
+int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* scene);
+
+/* ---- the hot path: replaces `shot_to_target` (camera.rs:261-287) ---------------------------*/
+/* Renders into a host image: out_rgba = W*H*[f32;4]; pixel_mask (nullable, W*H bytes) is the
+ * flattened `PixelController::calculate_pixel` (painter.rs:204-210): 0 -> [0,0,0,0]. */
+int rs_render(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* params,
+              const uint8_t* pixel_mask, float* out_rgba);
+
+/* Device-resident variant used for multi-GPU sharding: ADDS the linear per-pixel radiance sums
+ * of strata rows [begin,end) into d_accum (device, W*H float4, xyz = sum, w = sample count).
+ * d_pixel_mask: device pointer or NULL.  `stream` is a cudaStream_t (0 = legacy default). */
+int rs_render_accumulate(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* params,
+                         const uint8_t* d_pixel_mask, float* d_accum, void* stream);
+
+/* `Vec3::into_color` (vec3.rs:227-240) over a summed buffer: out = [sqrt(sum/n)..., 1] or
+ * [0,0,0,0] where masked.  All pointers are device pointers. n_samples = sqrt_spp^2. */
+int rs_finalize(rs_ctx* ctx, const float* d_accum, const uint8_t* d_pixel_mask, float* d_out_rgba,
+                int32_t width, int32_t height, int32_t n_samples, int32_t gamma, void* stream);
+
+/* ---- passes logic of the CLI (src/bin/raysnail.rs:157-208, 379-427); device pointers -------*/
+/* combine_pixel: new == (0,0,0,0) ? old : (old*pass + new)/(pass+1)   (raysnail.rs:176-193) */
+int rs_combine_passes(rs_ctx* ctx, const float* d_old, const float* d_new, float* d_out,
+                      int64_t n_pixels, float pass, void* stream);
+/* calc_noise (raysnail.rs:157-173), including its `x = y` indexing quirk when quirk != 0. */
+int rs_noise_map(rs_ctx* ctx, const float* d_pixels, float* d_noise, int32_t width, int32_t height,
+                 int32_t quirk, void* stream);
+/* PNG quantisation (raysnail.rs:437-441): (clamp(c,0,1)*255.5) as u8; out = W*H*3 bytes. */
+int rs_quantize_rgb8(rs_ctx* ctx, const float* d_pixels, uint8_t* d_rgb, int64_t n_pixels,
+                     void* stream);
+
+/* ---- parity probes (host output buffers, one entry per pixel) ------------------------------*/
+/* Primary ray of sample `sample_index` (= s_j*sqrt_spp + s_i) of every pixel: closest hit.
+ * obj_id: index into roots or -1; t: hit.t1; normal/point: HitRecord fields; front: hit.outside;
+ * material: resolved material index (default material substituted). Any pointer may be NULL. */
+int rs_debug_primary(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* params,
+                     int32_t sample_index, int32_t* obj_id, double* t, double* normal3,
+                     double* point3, int32_t* front, int32_t* material, double* ray_od6);
+
+/* One bounce: the primary hit is shaded once (camera.rs:165-250).
+ * kind: 0 miss, 1 no scatter (emitted only), 2 skip_pdf specular, 3 light branch, 4 pdf branch.
+ * next_od6: scattered ray origin+direction; weight3: colour factor applied to the recursive
+ * ray_color (srec.color * light_multi * pdf_multiplicator); emitted3: radiance added here
+ * (emitted, or the background colour on a miss). */
+int rs_debug_scatter(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* params,
+                     int32_t sample_index, int32_t* kind, double* next_od6, double* weight3,
+                     double* emitted3);
+
+int rs_get_stats(const rs_ctx* ctx, rs_stats* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAYSNAIL_B200_H */

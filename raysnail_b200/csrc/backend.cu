@@ -1,0 +1,792 @@
+// Host orchestration of the CUDA backend: the C ABI of include/raysnail_b200.h.
+//
+//   rs_upload_scene   validates the flat scene, pre-multiplies TransformStacks, builds the
+//                     world BVH (binned SAH, replaces BVH::new of the reference,
+//                     src/hittable/collection/bvh.rs:47-112 — any topology returns the same
+//                     closest hit) and copies everything to HBM.
+//   rs_render*        drives the wavefront: raygen -> depth x (extend, shade) -> accumulate
+//                     per wave of (pixel range x sample range); replaces Painter::draw
+//                     (src/painter.rs:256-336).
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/raysnail_b200.h"
+#include "device/kernels.cuh"
+
+using namespace rsd;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    cudaError_t ensure(size_t n) {
+        if (n <= bytes) return cudaSuccess;
+        release();
+        cudaError_t e = cudaMalloc(&p, n ? n : 16);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    template <class T>
+    T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct HostBvhNode {  // two children with f64 boxes
+    double box[2][6];
+    int child[2];
+};
+
+}  // namespace
+
+struct rs_ctx {
+    int device = 0;
+    int sm_count = 148;
+    std::string error;
+    bool has_scene = false;
+
+    // scene (device)
+    DevBuf d_nodes, d_xf, d_bvh, d_root_node, d_root_kind, d_root_sphere, d_root_bbox, d_root_gate;
+    DevBuf d_tri_geom, d_tri_normals, d_tri_material, d_lights, d_materials, d_textures, d_texels, d_perm, d_values;
+    DScene scene{};
+    // scene (host side, kept to re-pad the f32 boxes when the camera moves far away)
+    std::vector<HostBvhNode> bvh_host;
+    int bvh_root = 0;
+    double scene_omax = 0.0, padded_omax = -1.0;
+    int n_lights = 0;
+
+    // wave state
+    DevBuf d_pa[2], d_pb[2], d_pc[2], d_pd[2], d_pe[2], d_hit, d_hit_end, d_cq, d_contrib, d_ctr, d_stats;
+    uint32_t capacity = 0;
+    WaveState ws{};
+    int extend_grid = 148, shade_grid = 148;
+
+    // scratch for rs_render / probes
+    DevBuf d_accum, d_out, d_mask, d_dbg[11];
+
+    // timing
+    std::vector<cudaEvent_t> events;
+    rs_stats stats{};
+};
+
+namespace {
+
+int fail(rs_ctx* ctx, int code, const std::string& msg) {
+    if (ctx) ctx->error = msg;
+    else g_create_error = msg;
+    return code;
+}
+
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess) return fail(ctx, RS_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+    } while (0)
+
+template <class T>
+int upload(rs_ctx* ctx, DevBuf& buf, const T* src, size_t n) {
+    CK(buf.ensure(std::max<size_t>(n, 1) * sizeof(T)));
+    if (n) CK(cudaMemcpy(buf.p, src, n * sizeof(T), cudaMemcpyHostToDevice));
+    return RS_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// BVH build: binned SAH over the reference bounding boxes of the world objects
+// ---------------------------------------------------------------------------------------------
+struct BuildPrim {
+    double lo[3], hi[3], c[3];
+    int root;
+};
+
+double half_area(const double* lo, const double* hi) {
+    double dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+void box_of(const std::vector<BuildPrim>& prims, size_t lo, size_t hi, double* out) {
+    for (int a = 0; a < 3; ++a) { out[a] = DBL_MAX; out[3 + a] = -DBL_MAX; }
+    for (size_t i = lo; i < hi; ++i)
+        for (int a = 0; a < 3; ++a) {
+            out[a] = std::min(out[a], prims[i].lo[a]);
+            out[3 + a] = std::max(out[3 + a], prims[i].hi[a]);
+        }
+}
+
+// returns child reference: >= 0 inner node index, < 0 leaf ~root
+int build_bvh(std::vector<BuildPrim>& prims, size_t lo, size_t hi, int depth, std::vector<HostBvhNode>& nodes) {
+    if (hi - lo == 1) return ~prims[lo].root;
+    size_t mid = lo + (hi - lo) / 2;
+    int axis = 0;
+    bool split_done = false;
+    if (depth < 24) {
+        double cb[6];
+        for (int a = 0; a < 3; ++a) { cb[a] = DBL_MAX; cb[3 + a] = -DBL_MAX; }
+        for (size_t i = lo; i < hi; ++i)
+            for (int a = 0; a < 3; ++a) { cb[a] = std::min(cb[a], prims[i].c[a]); cb[3 + a] = std::max(cb[3 + a], prims[i].c[a]); }
+        constexpr int NB = 16;
+        double best_cost = DBL_MAX;
+        int best_axis = -1, best_bin = -1;
+        for (int a = 0; a < 3; ++a) {
+            double ext = cb[3 + a] - cb[a];
+            if (!(ext > 0.0)) continue;
+            double blo[NB][3], bhi[NB][3];
+            int cnt[NB] = {0};
+            for (int b = 0; b < NB; ++b)
+                for (int k = 0; k < 3; ++k) { blo[b][k] = DBL_MAX; bhi[b][k] = -DBL_MAX; }
+            double scale = NB / ext;
+            for (size_t i = lo; i < hi; ++i) {
+                int b = std::min(NB - 1, std::max(0, (int)((prims[i].c[a] - cb[a]) * scale)));
+                cnt[b]++;
+                for (int k = 0; k < 3; ++k) { blo[b][k] = std::min(blo[b][k], prims[i].lo[k]); bhi[b][k] = std::max(bhi[b][k], prims[i].hi[k]); }
+            }
+            double rarea[NB];
+            int rcnt[NB];
+            double rl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, rh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+            int rc = 0;
+            for (int b = NB - 1; b > 0; --b) {
+                for (int k = 0; k < 3; ++k) { rl[k] = std::min(rl[k], blo[b][k]); rh[k] = std::max(rh[k], bhi[b][k]); }
+                rc += cnt[b];
+                rarea[b] = rc ? half_area(rl, rh) : 0.0;
+                rcnt[b] = rc;
+            }
+            double ll[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, lh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+            int lc = 0;
+            for (int b = 0; b < NB - 1; ++b) {
+                for (int k = 0; k < 3; ++k) { ll[k] = std::min(ll[k], blo[b][k]); lh[k] = std::max(lh[k], bhi[b][k]); }
+                lc += cnt[b];
+                if (lc == 0 || rcnt[b + 1] == 0) continue;
+                double cost = half_area(ll, lh) * lc + rarea[b + 1] * rcnt[b + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = b; }
+            }
+        }
+        if (best_axis >= 0) {
+            axis = best_axis;
+            double ext = cb[3 + axis] - cb[axis], scale = NB / ext;
+            auto it = std::partition(prims.begin() + lo, prims.begin() + hi, [&](const BuildPrim& p) {
+                int b = std::min(NB - 1, std::max(0, (int)((p.c[axis] - cb[axis]) * scale)));
+                return b <= best_bin;
+            });
+            mid = (size_t)(it - prims.begin());
+            split_done = mid > lo && mid < hi;
+        }
+    }
+    if (!split_done) {  // median split on the widest centroid axis
+        double cb[6];
+        for (int a = 0; a < 3; ++a) { cb[a] = DBL_MAX; cb[3 + a] = -DBL_MAX; }
+        for (size_t i = lo; i < hi; ++i)
+            for (int a = 0; a < 3; ++a) { cb[a] = std::min(cb[a], prims[i].c[a]); cb[3 + a] = std::max(cb[3 + a], prims[i].c[a]); }
+        axis = 0;
+        for (int a = 1; a < 3; ++a)
+            if (cb[3 + a] - cb[a] > cb[3 + axis] - cb[axis]) axis = a;
+        mid = lo + (hi - lo) / 2;
+        std::nth_element(prims.begin() + lo, prims.begin() + mid, prims.begin() + hi,
+                         [&](const BuildPrim& a, const BuildPrim& b) { return a.c[axis] < b.c[axis]; });
+    }
+    int idx = (int)nodes.size();
+    nodes.emplace_back();
+    double b0[6], b1[6];
+    box_of(prims, lo, mid, b0);
+    box_of(prims, mid, hi, b1);
+    int c0 = build_bvh(prims, lo, mid, depth + 1, nodes);
+    int c1 = build_bvh(prims, mid, hi, depth + 1, nodes);
+    HostBvhNode& n = nodes[idx];
+    std::memcpy(n.box[0], b0, sizeof(b0));
+    std::memcpy(n.box[1], b1, sizeof(b1));
+    n.child[0] = c0;
+    n.child[1] = c1;
+    return idx;
+}
+
+float f32_down(double v) {
+    float f = (float)v;
+    if ((double)f > v) f = std::nextafterf(f, -FLT_MAX);
+    return f;
+}
+float f32_up(double v) {
+    float f = (float)v;
+    if ((double)f < v) f = std::nextafterf(f, FLT_MAX);
+    return f;
+}
+
+// f32 node boxes padded outward so that the f32 slab test never rejects a box the f64 ray
+// enters: the absolute pad covers the rounding of the ray origin (|o| <= omax) and of the
+// bound itself (DESIGN.md "conservative f32 traversal").
+int upload_bvh(rs_ctx* ctx, double omax) {
+    std::vector<BvhNode> dev(std::max<size_t>(ctx->bvh_host.size(), 1));
+    const double k = 1.0 / 2097152.0;  // 2^-21
+    for (size_t i = 0; i < ctx->bvh_host.size(); ++i) {
+        const HostBvhNode& h = ctx->bvh_host[i];
+        float lo[2][3], hi[2][3];
+        for (int c = 0; c < 2; ++c)
+            for (int a = 0; a < 3; ++a) {
+                double l = h.box[c][a], u = h.box[c][3 + a];
+                lo[c][a] = f32_down(l - k * (omax + std::fabs(l)) - 1e-7);
+                hi[c][a] = f32_up(u + k * (omax + std::fabs(u)) + 1e-7);
+            }
+        BvhNode& d = dev[i];
+        d.bx = make_float4(lo[0][0], hi[0][0], lo[0][1], hi[0][1]);
+        d.by = make_float4(lo[1][0], hi[1][0], lo[1][1], hi[1][1]);
+        d.bz = make_float4(lo[0][2], hi[0][2], lo[1][2], hi[1][2]);
+        d.ch = make_int4(h.child[0], h.child[1], 0, 0);
+    }
+    int rc = upload(ctx, ctx->d_bvh, dev.data(), dev.size());
+    if (rc != RS_OK) return rc;
+    ctx->scene.bvh = ctx->d_bvh.as<BvhNode>();
+    ctx->padded_omax = omax;
+    return RS_OK;
+}
+
+int tree_depth(const rs_scene_desc* s, int ni) {
+    const rs_node& n = s->nodes[ni];
+    switch (n.type) {
+        case RS_NODE_DIFFERENCE:
+        case RS_NODE_INTERSECTION: return 1 + std::max(tree_depth(s, n.child0), tree_depth(s, n.child1));
+        case RS_NODE_TRANSFORM:
+        case RS_NODE_MEDIUM: return 1 + tree_depth(s, n.child0);
+        default: return 1;
+    }
+}
+
+void mat3x4_mul(const long double* a, const double* b16, long double* out) {  // out = b(4x4 affine) * a(3x4 affine)
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) {
+            long double s = 0;
+            for (int k = 0; k < 3; ++k) s += (long double)b16[4 * r + k] * a[4 * k + c];
+            if (c == 3) s += (long double)b16[4 * r + 3];
+            out[4 * r + c] = s;
+        }
+}
+
+int ensure_wave(rs_ctx* ctx, uint32_t cap) {
+    if (cap <= ctx->capacity) return RS_OK;
+    for (int b = 0; b < 2; ++b) {
+        CK(ctx->d_pa[b].ensure((size_t)cap * sizeof(double2)));
+        CK(ctx->d_pb[b].ensure((size_t)cap * sizeof(double2)));
+        CK(ctx->d_pc[b].ensure((size_t)cap * sizeof(double2)));
+        CK(ctx->d_pd[b].ensure((size_t)cap * sizeof(double2)));
+        CK(ctx->d_pe[b].ensure((size_t)cap * sizeof(uint4)));
+        ctx->ws.buf[b].a = ctx->d_pa[b].as<double2>();
+        ctx->ws.buf[b].b = ctx->d_pb[b].as<double2>();
+        ctx->ws.buf[b].c = ctx->d_pc[b].as<double2>();
+        ctx->ws.buf[b].d = ctx->d_pd[b].as<double2>();
+        ctx->ws.buf[b].e = ctx->d_pe[b].as<uint4>();
+    }
+    CK(ctx->d_hit.ensure((size_t)cap * sizeof(HitA)));
+    CK(ctx->d_hit_end.ensure((size_t)cap * sizeof(double)));
+    CK(ctx->d_cq.ensure((size_t)cap * RS_NUM_CLASSES * sizeof(uint32_t)));
+    CK(ctx->d_contrib.ensure((size_t)cap * sizeof(float4)));
+    CK(ctx->d_ctr.ensure(sizeof(WaveCounters)));
+    CK(ctx->d_stats.ensure(sizeof(DeviceStats)));
+    ctx->ws.hit = ctx->d_hit.as<HitA>();
+    ctx->ws.hit_end = ctx->d_hit_end.as<double>();
+    ctx->ws.class_queue = ctx->d_cq.as<uint32_t>();
+    ctx->ws.contrib = ctx->d_contrib.as<float4>();
+    ctx->ws.ctr = ctx->d_ctr.as<WaveCounters>();
+    ctx->ws.stats = ctx->d_stats.as<DeviceStats>();
+    ctx->ws.capacity = cap;
+    ctx->capacity = cap;
+    return RS_OK;
+}
+
+int check_render_args(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p) {
+    if (!ctx) return RS_ERR_INVALID_ARGUMENT;
+    if (!ctx->has_scene) return fail(ctx, RS_ERR_NO_SCENE, "no scene uploaded");
+    if (!cam || !p) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "null camera or params");
+    if (cam->width <= 0 || cam->height <= 0 || (int64_t)cam->width * cam->height > (int64_t)1 << 30)
+        return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad image size");
+    if (p->sqrt_spp <= 0 || p->sqrt_spp > 46340) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "sqrt_spp must be in 1..46340");
+    if (p->depth < 0 || p->depth > RS_MAX_DEPTH) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "depth must be in 0..64");
+    if (p->stratum_row_begin < 0 || p->stratum_row_end > p->sqrt_spp || p->stratum_row_begin > p->stratum_row_end)
+        return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad stratum row range");
+    if (ctx->n_lights == 0)
+        return fail(ctx, RS_ERR_INVALID_ARGUMENT, "world.lights is empty (the reference panics in HittableList::random)");
+    return RS_OK;
+}
+
+FrameParams make_frame(const rs_camera* cam, const rs_render_params* p) {
+    FrameParams fp;
+    std::memset(&fp, 0, sizeof(fp));
+    fp.cam = *cam;
+    fp.sqrt_spp = p->sqrt_spp;
+    fp.depth = p->depth;
+    fp.stratum_row_begin = p->stratum_row_begin;
+    fp.flags = p->flags;
+    fp.key = make_uint2((uint32_t)p->seed, (uint32_t)(p->seed >> 32));
+    return fp;
+}
+
+int prepare_camera(rs_ctx* ctx, const rs_camera* cam) {
+    double om = ctx->scene_omax;
+    for (int a = 0; a < 3; ++a) om = std::max(om, std::fabs(cam->origin[a]) + std::fabs(cam->aperture) + 1e-3);
+    if (om > ctx->padded_omax) return upload_bvh(ctx, om * 1.25);
+    return RS_OK;
+}
+
+struct Timing {
+    rs_ctx* ctx;
+    cudaStream_t stream;
+    bool on;
+    size_t used = 0;
+    std::vector<int> tags;  // category of the interval that starts at event i
+    void mark(int tag) {
+        if (!on) return;
+        if (used == ctx->events.size()) {
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            ctx->events.push_back(e);
+        }
+        cudaEventRecord(ctx->events[used++], stream);
+        tags.push_back(tag);
+    }
+};
+
+// the wavefront loop
+int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, const unsigned char* d_mask, float4* d_accum,
+                cudaStream_t stream, bool timing) {
+    const uint32_t np = (uint32_t)cam->width * (uint32_t)cam->height;
+    const uint32_t s_total = (uint32_t)(p->stratum_row_end - p->stratum_row_begin) * (uint32_t)p->sqrt_spp;
+    ctx->stats = rs_stats{};
+    if (s_total == 0 || np == 0) return RS_OK;
+    uint32_t cap = p->max_wave_paths > 0 ? (uint32_t)p->max_wave_paths : (1u << 23);
+    cap = std::max(cap, 1024u);
+    const uint32_t P = std::min(np, cap);
+    const uint32_t K = std::max(1u, std::min(s_total, cap / P));
+    int rc = ensure_wave(ctx, P * K);
+    if (rc != RS_OK) return rc;
+    rc = prepare_camera(ctx, cam);
+    if (rc != RS_OK) return rc;
+    FrameParams fp = make_frame(cam, p);
+    fp.mask = d_mask;
+    CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), stream));
+    Timing tm{ctx, stream, timing};
+    uint64_t launches = 0;
+    for (uint32_t pixel0 = 0; pixel0 < np; pixel0 += P) {
+        fp.pixel0 = pixel0;
+        fp.n_pixels = std::min(P, np - pixel0);
+        for (uint32_t sample0 = 0; sample0 < s_total; sample0 += K) {
+            fp.sample0 = sample0;
+            fp.n_samples = std::min(K, s_total - sample0);
+            CK(cudaMemsetAsync(ctx->ws.ctr, 0, sizeof(WaveCounters), stream));
+            tm.mark(0);
+            launch_raygen(fp, ctx->ws, stream);
+            ++launches;
+            for (int b = 0; b < p->depth; ++b) {
+                tm.mark(1);
+                launch_extend(ctx->scene, fp, ctx->ws, b, ctx->extend_grid, stream);
+                tm.mark(2);
+                launch_shade(ctx->scene, fp, ctx->ws, b, ctx->shade_grid, nullptr, stream);
+                launches += 2;
+            }
+            tm.mark(3);
+            launch_accumulate(fp, ctx->ws, d_accum, stream);
+            ++launches;
+        }
+    }
+    tm.mark(4);
+    CK(cudaGetLastError());
+    ctx->stats.n_launches = launches;
+    if (timing) {
+        CK(cudaStreamSynchronize(stream));
+        double ms[5] = {0, 0, 0, 0, 0};
+        for (size_t i = 0; i + 1 < tm.used; ++i) {
+            float e = 0.f;
+            cudaEventElapsedTime(&e, ctx->events[i], ctx->events[i + 1]);
+            ms[tm.tags[i]] += e;
+        }
+        float total = 0.f;
+        if (tm.used >= 2) cudaEventElapsedTime(&total, ctx->events[0], ctx->events[tm.used - 1]);
+        ctx->stats.ms_raygen = ms[0];
+        ctx->stats.ms_extend = ms[1];
+        ctx->stats.ms_shade = ms[2];
+        ctx->stats.ms_accumulate = ms[3];
+        ctx->stats.ms_total = total;
+    }
+    return RS_OK;
+}
+
+int fetch_device_stats(rs_ctx* ctx, cudaStream_t stream) {
+    DeviceStats ds;
+    CK(cudaMemcpyAsync(&ds, ctx->ws.stats, sizeof(ds), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    ctx->stats.n_samples = ds.n_samples;
+    ctx->stats.n_segments = ds.n_segments;
+    return RS_OK;
+}
+
+}  // namespace
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+int rs_abi_version(void) { return RS_ABI_VERSION; }
+
+int rs_create(rs_ctx** out, int device) {
+    if (!out) return RS_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, RS_ERR_NO_DEVICE, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                                                   " (this backend has no CPU fallback)");
+    if (device < 0 || device >= count) return fail(nullptr, RS_ERR_INVALID_ARGUMENT, "device index out of range");
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(nullptr, RS_ERR_CUDA, cudaGetErrorString(e));
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return fail(nullptr, RS_ERR_CUDA, cudaGetErrorString(e));
+    if (prop.major < 10)
+        return fail(nullptr, RS_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is not sm_100-class; this library is built for sm_100a only");
+    rs_ctx* ctx = new rs_ctx();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm();
+    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm();
+    *out = ctx;
+    return RS_OK;
+}
+
+void rs_destroy(rs_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
+    delete ctx;
+}
+
+const char* rs_last_error(const rs_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
+    if (!ctx || !s) return RS_ERR_INVALID_ARGUMENT;
+    CK(cudaSetDevice(ctx->device));
+    ctx->has_scene = false;
+    // ---- validation -------------------------------------------------------------------------
+    if (s->n_nodes < 0 || s->n_roots < 0 || s->n_tris < 0 || s->n_materials <= 0 || s->n_textures < 0)
+        return fail(ctx, RS_ERR_INVALID_ARGUMENT, "negative counts / no materials");
+    if (s->n_materials > 65535) return fail(ctx, RS_ERR_UNSUPPORTED, "more than 65535 materials");
+    if (s->default_material < 0 || s->default_material >= s->n_materials) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad default material");
+    for (int i = 0; i < s->n_textures; ++i) {
+        const rs_texture& t = s->textures[i];
+        if (t.type < RS_TEX_SOLID || t.type > RS_TEX_PERLIN) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad texture type");
+        if (t.type == RS_TEX_CHECKER && (t.odd < 0 || t.odd >= i || t.even < 0 || t.even >= i)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "checker children must precede it");
+        if (t.type == RS_TEX_IMAGE && (t.width <= 0 || t.height <= 0 || t.texel_offset < 0 || (int64_t)t.texel_offset + (int64_t)t.width * t.height * 4 > s->n_texel_bytes))
+            return fail(ctx, RS_ERR_INVALID_ARGUMENT, "image texture out of range");
+        if (t.type == RS_TEX_PERLIN) {
+            int pc = t.point_count;
+            if (pc <= 0 || (pc & (pc - 1)) || t.perm_offset < 0 || t.perm_offset + 3 * pc > s->n_perlin_perm || t.value_offset < 0 ||
+                t.value_offset + pc * (t.perlin_vector ? 3 : 1) > s->n_perlin_values)
+                return fail(ctx, RS_ERR_INVALID_ARGUMENT, "perlin tables out of range");
+        }
+    }
+    for (int i = 0; i < s->n_materials; ++i) {
+        const rs_material& m = s->materials[i];
+        if (m.type < RS_MAT_LAMBERTIAN || m.type > RS_MAT_MIXED) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad material type");
+        bool needs_tex = m.type == RS_MAT_LAMBERTIAN || m.type == RS_MAT_METAL || m.type == RS_MAT_DIFFUSE_METAL || m.type == RS_MAT_DIFFUSE_LIGHT || m.type == RS_MAT_BLINN_PHONG;
+        if (needs_tex && (m.texture < 0 || m.texture >= s->n_textures)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "material texture out of range");
+        if (m.type == RS_MAT_MIXED && (m.mat1 < 0 || m.mat1 >= i || m.mat2 < 0 || m.mat2 >= i)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "mixed material children must precede it");
+    }
+    std::vector<rs_node> nodes(s->nodes, s->nodes + s->n_nodes);
+    std::vector<XformPre> xf;
+    for (int i = 0; i < s->n_nodes; ++i) {
+        rs_node& n = nodes[i];
+        if (n.type < RS_NODE_SPHERE || n.type > RS_NODE_MEDIUM) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad node type");
+        if (n.material >= s->n_materials) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "node material out of range");
+        bool two = n.type == RS_NODE_DIFFERENCE || n.type == RS_NODE_INTERSECTION, one = n.type == RS_NODE_TRANSFORM || n.type == RS_NODE_MEDIUM;
+        if ((two || one) && (n.child0 < 0 || n.child0 >= i)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "child0 must precede its parent");
+        if (two && (n.child1 < 0 || n.child1 >= i)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "child1 must precede its parent");
+        if (n.type == RS_NODE_MEDIUM && n.material < 0) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "medium needs its isotropic material");
+        if (n.type == RS_NODE_RECT && (n.rect_axis < 0 || n.rect_axis > 2)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad rect axis");
+        if (n.type == RS_NODE_TRANSFORM) {
+            if (n.first_xform < 0 || n.n_xform < 0 || n.first_xform + n.n_xform > s->n_xforms) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "transform stack out of range");
+            // pre-multiply the stack (transform.rs:133-157): forward applies entry 0 first,
+            // inverse applies the inverses from the last entry to the first
+            long double F[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0}, J[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0}, T[12];
+            for (int k = 0; k < n.n_xform; ++k) { mat3x4_mul(F, s->xforms[n.first_xform + k].m, T); std::memcpy(F, T, sizeof(T)); }
+            // the reference applies inv_{n-1} first: composite = inv_0 * inv_1 * ... * inv_{n-1}
+            for (int k = n.n_xform - 1; k >= 0; --k) { mat3x4_mul(J, s->xforms[n.first_xform + k].inv, T); std::memcpy(J, T, sizeof(T)); }
+            XformPre x;
+            for (int k = 0; k < 12; ++k) { x.fwd[k] = (double)F[k]; x.inv[k] = (double)J[k]; }
+            n.first_xform = (int)xf.size();
+            n.n_xform = 1;
+            xf.push_back(x);
+        }
+    }
+    for (int i = 0; i < s->n_roots; ++i) {
+        int r = s->roots[i];
+        if (r >= 0 ? r >= s->n_nodes : ~r >= s->n_tris) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "root out of range");
+        if (r >= 0 && tree_depth(s, r) > RS_MAX_TREE_DEPTH) return fail(ctx, RS_ERR_UNSUPPORTED, "object tree deeper than RS_MAX_TREE_DEPTH (8)");
+    }
+    for (int i = 0; i < s->n_lights; ++i) {
+        int r = s->lights[i];
+        if (r < 0 || r >= s->n_nodes) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "light out of range");
+        if (tree_depth(s, r) > RS_MAX_TREE_DEPTH) return fail(ctx, RS_ERR_UNSUPPORTED, "light object tree too deep");
+    }
+    for (int i = 0; i < s->n_tris; ++i)
+        if (s->tri_material[i] >= s->n_materials) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "triangle material out of range");
+
+    // ---- root tables + BVH ------------------------------------------------------------------
+    std::vector<int> root_kind(s->n_roots);
+    std::vector<double> root_sphere((size_t)s->n_roots * 4, 0.0);
+    std::vector<unsigned char> root_gate(s->n_roots, 0);
+    std::vector<BuildPrim> prims;
+    prims.reserve(s->n_roots);
+    double omax = 1.0;
+    for (int i = 0; i < s->n_roots; ++i) {
+        int r = s->roots[i];
+        const double* bb = s->root_bbox + 6 * (size_t)i;
+        if (r < 0) {
+            root_kind[i] = ROOT_TRIANGLE;
+        } else {
+            const rs_node& n = nodes[r];
+            bool static_sphere = n.type == RS_NODE_SPHERE && n.p[4] == 0.0 && n.p[5] == 0.0 && n.p[6] == 0.0;
+            if (static_sphere) {
+                root_kind[i] = ROOT_SPHERE;
+                for (int k = 0; k < 4; ++k) root_sphere[4 * (size_t)i + k] = n.p[k];
+            } else {
+                root_kind[i] = ROOT_GENERIC;
+                // spheres / boxes / rects always lie inside their reference bbox; everything
+                // else is clipped by it the way the reference's BVH leaf clips it
+                root_gate[i] = !(n.type == RS_NODE_SPHERE || n.type == RS_NODE_BOX || n.type == RS_NODE_RECT);
+            }
+        }
+        BuildPrim p;
+        bool degenerate = false;
+        for (int a = 0; a < 3; ++a) {
+            double lo = bb[a], hi = bb[3 + a];
+            if (!(lo == lo) || !(hi == hi)) degenerate = true;
+            lo = std::max(lo, -1e30);
+            hi = std::min(hi, 1e30);
+            // AABB::hit rejects t_max <= t_min (aabb.rs:33): a box with no thickness on an axis
+            // (e.g. an axis-aligned triangle, triangle_mesh.rs:43-45) is never hit
+            if (!(hi > lo)) degenerate = true;
+            p.lo[a] = lo;
+            p.hi[a] = hi;
+            p.c[a] = 0.5 * (lo + hi);
+        }
+        if (degenerate) continue;
+        for (int a = 0; a < 3; ++a) omax = std::max(omax, std::max(std::fabs(p.lo[a]), std::fabs(p.hi[a])));
+        p.root = i;
+        prims.push_back(p);
+    }
+    ctx->bvh_host.clear();
+    int bvh_root = 0x7fffffff;
+    if (!prims.empty()) bvh_root = build_bvh(prims, 0, prims.size(), 0, ctx->bvh_host);
+    ctx->scene_omax = omax;
+
+    // triangles: p0, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56)
+    std::vector<double> tri_geom((size_t)s->n_tris * 9);
+    for (int i = 0; i < s->n_tris; ++i) {
+        const double* v = s->tri_verts + 9 * (size_t)i;
+        double* g = &tri_geom[9 * (size_t)i];
+        g[0] = v[0]; g[1] = v[1]; g[2] = v[2];
+        g[3] = v[0] - v[3]; g[4] = v[1] - v[4]; g[5] = v[2] - v[5];
+        g[6] = v[0] - v[6]; g[7] = v[1] - v[7]; g[8] = v[2] - v[8];
+    }
+
+    // ---- upload -------------------------------------------------------------------------------
+    int rc;
+    if ((rc = upload(ctx, ctx->d_nodes, nodes.data(), nodes.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_xf, xf.data(), xf.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_root_node, s->roots, (size_t)s->n_roots)) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_root_kind, root_kind.data(), root_kind.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_root_sphere, root_sphere.data(), root_sphere.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_root_bbox, s->root_bbox, (size_t)s->n_roots * 6)) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_root_gate, root_gate.data(), root_gate.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_tri_geom, tri_geom.data(), tri_geom.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_tri_normals, s->tri_normals, (size_t)s->n_tris * 9)) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_tri_material, s->tri_material, (size_t)s->n_tris)) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_lights, s->lights, (size_t)s->n_lights)) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_materials, s->materials, (size_t)s->n_materials)) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_textures, s->textures, (size_t)s->n_textures)) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_texels, s->texels, (size_t)s->n_texel_bytes)) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_perm, s->perlin_perm, (size_t)s->n_perlin_perm)) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_values, s->perlin_values, (size_t)s->n_perlin_values)) != RS_OK) return rc;
+
+    DScene& S = ctx->scene;
+    S.nodes = ctx->d_nodes.as<rs_node>();
+    S.xf = ctx->d_xf.as<XformPre>();
+    S.bvh_root = prims.empty() ? 0 : bvh_root;
+    S.n_roots = prims.empty() ? 0 : s->n_roots;
+    S.root_node = ctx->d_root_node.as<int>();
+    S.root_kind = ctx->d_root_kind.as<int>();
+    S.root_sphere = ctx->d_root_sphere.as<double4>();
+    S.root_bbox = ctx->d_root_bbox.as<double>();
+    S.root_gate = ctx->d_root_gate.as<unsigned char>();
+    S.tri_geom = ctx->d_tri_geom.as<double>();
+    S.tri_normals = ctx->d_tri_normals.as<double>();
+    S.tri_material = ctx->d_tri_material.as<int>();
+    S.lights = ctx->d_lights.as<int>();
+    S.n_lights = s->n_lights;
+    S.materials = ctx->d_materials.as<rs_material>();
+    S.textures = ctx->d_textures.as<rs_texture>();
+    S.texels = ctx->d_texels.as<unsigned char>();
+    S.perlin_perm = ctx->d_perm.as<int>();
+    S.perlin_values = ctx->d_values.as<double>();
+    S.default_material = s->default_material;
+    S.bg0 = make_float4(s->bg0[0], s->bg0[1], s->bg0[2], s->bg0[3]);
+    S.bg1 = make_float4(s->bg1[0], s->bg1[1], s->bg1[2], s->bg1[3]);
+    ctx->n_lights = s->n_lights;
+    ctx->padded_omax = -1.0;
+    if ((rc = upload_bvh(ctx, omax * 1.25)) != RS_OK) return rc;
+    ctx->has_scene = true;
+    return RS_OK;
+}
+
+int rs_render_accumulate(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, const uint8_t* d_mask, float* d_accum, void* stream) {
+    int rc = check_render_args(ctx, cam, p);
+    if (rc != RS_OK) return rc;
+    if (!d_accum) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "null accumulation buffer");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = render_into(ctx, cam, p, d_mask, reinterpret_cast<float4*>(d_accum), st, (p->flags & RS_FLAG_KERNEL_TIMING) != 0);
+    if (rc != RS_OK) return rc;
+    return RS_OK;
+}
+
+int rs_finalize(rs_ctx* ctx, const float* d_accum, const uint8_t* d_mask, float* d_out, int32_t width, int32_t height, int32_t n_samples,
+                int32_t gamma, void* stream) {
+    if (!ctx || !d_accum || !d_out || width <= 0 || height <= 0 || n_samples <= 0) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad finalize arguments");
+    CK(cudaSetDevice(ctx->device));
+    launch_finalize(reinterpret_cast<const float4*>(d_accum), d_mask, reinterpret_cast<float4*>(d_out), (int64_t)width * height, n_samples, gamma,
+                    (cudaStream_t)stream);
+    CK(cudaGetLastError());
+    return RS_OK;
+}
+
+int rs_render(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, const uint8_t* pixel_mask, float* out_rgba) {
+    int rc = check_render_args(ctx, cam, p);
+    if (rc != RS_OK) return rc;
+    if (!out_rgba) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "null output image");
+    CK(cudaSetDevice(ctx->device));
+    const size_t np = (size_t)cam->width * cam->height;
+    CK(ctx->d_accum.ensure(np * sizeof(float4)));
+    CK(ctx->d_out.ensure(np * sizeof(float4)));
+    const unsigned char* d_mask = nullptr;
+    if (pixel_mask) {
+        CK(ctx->d_mask.ensure(np));
+        CK(cudaMemcpyAsync(ctx->d_mask.p, pixel_mask, np, cudaMemcpyHostToDevice, 0));
+        d_mask = ctx->d_mask.as<unsigned char>();
+    }
+    CK(cudaMemsetAsync(ctx->d_accum.p, 0, np * sizeof(float4), 0));
+    rc = render_into(ctx, cam, p, d_mask, ctx->d_accum.as<float4>(), 0, (p->flags & RS_FLAG_KERNEL_TIMING) != 0);
+    if (rc != RS_OK) return rc;
+    const int n = (p->stratum_row_end - p->stratum_row_begin) * p->sqrt_spp;
+    launch_finalize(ctx->d_accum.as<float4>(), d_mask, ctx->d_out.as<float4>(), (int64_t)np, std::max(n, 1), p->gamma, 0);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out_rgba, ctx->d_out.p, np * sizeof(float4), cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return fetch_device_stats(ctx, 0);
+}
+
+int rs_combine_passes(rs_ctx* ctx, const float* d_old, const float* d_new, float* d_out, int64_t n, float pass, void* stream) {
+    if (!ctx || !d_old || !d_new || !d_out || n < 0) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad combine arguments");
+    CK(cudaSetDevice(ctx->device));
+    launch_combine(reinterpret_cast<const float4*>(d_old), reinterpret_cast<const float4*>(d_new), reinterpret_cast<float4*>(d_out), n, pass, (cudaStream_t)stream);
+    CK(cudaGetLastError());
+    return RS_OK;
+}
+
+int rs_noise_map(rs_ctx* ctx, const float* d_pixels, float* d_noise, int32_t width, int32_t height, int32_t quirk, void* stream) {
+    if (!ctx || !d_pixels || !d_noise || width <= 0 || height <= 0) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad noise arguments");
+    CK(cudaSetDevice(ctx->device));
+    launch_noise(reinterpret_cast<const float4*>(d_pixels), d_noise, width, height, quirk, (cudaStream_t)stream);
+    CK(cudaGetLastError());
+    return RS_OK;
+}
+
+int rs_quantize_rgb8(rs_ctx* ctx, const float* d_pixels, uint8_t* d_rgb, int64_t n, void* stream) {
+    if (!ctx || !d_pixels || !d_rgb || n < 0) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad quantize arguments");
+    CK(cudaSetDevice(ctx->device));
+    launch_quantize(reinterpret_cast<const float4*>(d_pixels), d_rgb, n, (cudaStream_t)stream);
+    CK(cudaGetLastError());
+    return RS_OK;
+}
+
+static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, int32_t sample_index, bool shade, void* host_out[11],
+                     const size_t elem_bytes[11]) {
+    int rc = check_render_args(ctx, cam, p);
+    if (rc != RS_OK) return rc;
+    if (sample_index < 0 || sample_index >= p->sqrt_spp * p->sqrt_spp) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "sample index out of range");
+    if (p->depth < 1) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "probes need depth >= 1");
+    CK(cudaSetDevice(ctx->device));
+    const uint32_t np = (uint32_t)cam->width * (uint32_t)cam->height;
+    rc = ensure_wave(ctx, np);
+    if (rc != RS_OK) return rc;
+    rc = prepare_camera(ctx, cam);
+    if (rc != RS_OK) return rc;
+    FrameParams fp = make_frame(cam, p);
+    fp.mask = nullptr;
+    fp.pixel0 = 0;
+    fp.n_pixels = np;
+    // local sample index such that s_j * sqrt_spp + s_i == sample_index
+    fp.stratum_row_begin = 0;
+    fp.sample0 = (uint32_t)sample_index;
+    fp.n_samples = 1;
+    void* dev[11];
+    for (int i = 0; i < 11; ++i) {
+        dev[i] = nullptr;
+        if (host_out[i]) {
+            CK(ctx->d_dbg[i].ensure((size_t)np * elem_bytes[i]));
+            CK(cudaMemsetAsync(ctx->d_dbg[i].p, 0, (size_t)np * elem_bytes[i], 0));
+            dev[i] = ctx->d_dbg[i].p;
+        }
+    }
+    DebugOut dbg;
+    dbg.obj_id = (int*)dev[0]; dbg.t = (double*)dev[1]; dbg.normal3 = (double*)dev[2]; dbg.point3 = (double*)dev[3];
+    dbg.front = (int*)dev[4]; dbg.material = (int*)dev[5]; dbg.ray_od6 = (double*)dev[6];
+    dbg.kind = (int*)dev[7]; dbg.next_od6 = (double*)dev[8]; dbg.weight3 = (double*)dev[9]; dbg.emitted3 = (double*)dev[10];
+    CK(cudaMemsetAsync(ctx->ws.ctr, 0, sizeof(WaveCounters), 0));
+    CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), 0));
+    launch_raygen(fp, ctx->ws, 0);
+    launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_grid, 0);
+    if (shade) launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_grid, &dbg, 0);
+    else launch_probe_primary(ctx->scene, fp, ctx->ws, dbg, 0);
+    CK(cudaGetLastError());
+    for (int i = 0; i < 11; ++i)
+        if (host_out[i]) CK(cudaMemcpyAsync(host_out[i], dev[i], (size_t)np * elem_bytes[i], cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return RS_OK;
+}
+
+int rs_debug_primary(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, int32_t sample_index, int32_t* obj_id, double* t,
+                     double* normal3, double* point3, int32_t* front, int32_t* material, double* ray_od6) {
+    void* host[11] = {obj_id, t, normal3, point3, front, material, ray_od6, nullptr, nullptr, nullptr, nullptr};
+    const size_t eb[11] = {4, 8, 24, 24, 4, 4, 48, 4, 48, 24, 24};
+    return run_probe(ctx, cam, p, sample_index, false, host, eb);
+}
+
+int rs_debug_scatter(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, int32_t sample_index, int32_t* kind, double* next_od6,
+                     double* weight3, double* emitted3) {
+    void* host[11] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, kind, next_od6, weight3, emitted3};
+    const size_t eb[11] = {4, 8, 24, 24, 4, 4, 48, 4, 48, 24, 24};
+    return run_probe(ctx, cam, p, sample_index, true, host, eb);
+}
+
+int rs_get_stats(const rs_ctx* ctx, rs_stats* out) {
+    if (!ctx || !out) return RS_ERR_INVALID_ARGUMENT;
+    rs_ctx* c = const_cast<rs_ctx*>(ctx);
+    if (c->capacity) {
+        cudaSetDevice(c->device);
+        DeviceStats ds;
+        if (cudaMemcpy(&ds, c->ws.stats, sizeof(ds), cudaMemcpyDeviceToHost) == cudaSuccess) {
+            c->stats.n_samples = ds.n_samples;
+            c->stats.n_segments = ds.n_segments;
+        }
+    }
+    *out = c->stats;
+    return RS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,815 @@
+// sm_100a kernels of the wavefront path tracer.
+//
+//   raygen      replaces Painter::render_pixel's strata loop + Camera::ray
+//               (reference src/painter.rs:154-187, src/camera.rs:77-85)
+//   extend      replaces World::hit -> BVH::hit -> leaf Hittable::hit
+//               (src/hittable/collection/bvh.rs:173-192 and every geometry/*.rs, csg/*.rs ...)
+//   shade       replaces the body of TakePhotoSettings::ray_color (src/camera.rs:156-255),
+//               Material::scatter/emitted (src/material/*.rs), the PDFs (src/prelude/pdf.rs)
+//               and the textures (src/texture/*.rs)
+//   accumulate  replaces the f64 `color_vec` sum (painter.rs:163-176)
+//   finalize    replaces Vec3::into_color (src/prelude/vec3.rs:227-240)
+//   combine / noise / quantize: the CLI's passes logic (src/bin/raysnail.rs:157-208,437-441)
+//
+// Scheduling: extend and shade are persistent kernels (grid = SMs x resident blocks); each
+// warp fetches 32 work items at a time with one atomicAdd on a cursor in global memory.
+// extend buckets its hits by resolved material class with __match_any_sync so that every
+// warp of shade runs one material's code; shade compacts the surviving paths into the other
+// ping-pong buffer with __ballot_sync-aggregated atomics.
+#include <cfloat>
+
+#include "kernels.cuh"
+
+namespace rsd {
+
+#define RS_BLOCK 256
+#define RS_TMIN 0.0001
+#define RS_STACK 48
+// relative slack for the f32 slab test: covers the rounding of 1/d, the FMA and the f64->f32
+// conversions of the ray; the absolute part (origin rounding) is folded into the padded boxes.
+#define RS_SLAB_EPS 9.5367431640625e-07f  // 2^-20
+
+__device__ __forceinline__ double pack_f2(float a, float b) {
+    return __hiloint2double(__float_as_int(b), __float_as_int(a));
+}
+__device__ __forceinline__ void unpack_f2(double d, float& a, float& b) {
+    a = __int_as_float(__double2loint(d));
+    b = __int_as_float(__double2hiint(d));
+}
+
+struct PathRec {
+    Ray ray;
+    float3 T;
+    uint32_t slot, pixel, sample;
+};
+
+__device__ __forceinline__ void store_path(const PathBuf& B, uint32_t i, const PathRec& p) {
+    B.a[i] = make_double2(p.ray.o.x, p.ray.o.y);
+    B.b[i] = make_double2(p.ray.o.z, p.ray.time);
+    B.c[i] = make_double2(p.ray.d.x, p.ray.d.y);
+    B.d[i] = make_double2(p.ray.d.z, pack_f2(p.T.x, p.T.y));
+    B.e[i] = make_uint4(__float_as_uint(p.T.z), p.slot, p.pixel, p.sample);
+}
+__device__ __forceinline__ void load_path(const PathBuf& B, uint32_t i, PathRec& p) {
+    double2 a = B.a[i], b = B.b[i], c = B.c[i], d = B.d[i];
+    uint4 e = B.e[i];
+    p.ray.o = v3(a.x, a.y, b.x);
+    p.ray.time = b.y;
+    p.ray.d = v3(c.x, c.y, d.x);
+    unpack_f2(d.y, p.T.x, p.T.y);
+    p.T.z = __uint_as_float(e.x);
+    p.slot = e.y;
+    p.pixel = e.z;
+    p.sample = e.w;
+}
+__device__ __forceinline__ void load_ray_only(const PathBuf& B, uint32_t i, Ray& r, uint32_t& pixel, uint32_t& sample) {
+    double2 a = B.a[i], b = B.b[i], c = B.c[i], d = B.d[i];
+    uint4 e = B.e[i];
+    r.o = v3(a.x, a.y, b.x);
+    r.time = b.y;
+    r.d = v3(c.x, c.y, d.x);
+    pixel = e.z;
+    sample = e.w;
+}
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
+
+// warp-aggregated append: returns this lane's position; `counter` is bumped once per warp
+__device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
+    uint32_t mask = __ballot_sync(0xffffffffu, pred);
+    if (mask == 0) return 0;
+    uint32_t leader = __ffs(mask) - 1, base = 0;
+    if (lane_id() == leader) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + __popc(mask & ((1u << lane_id()) - 1u));
+}
+
+// =============================================================================================
+// raygen
+// =============================================================================================
+__device__ __forceinline__ Ray camera_ray(const FrameParams& fp, int row, int col, int s_i, int s_j, RngCtx& rng) {
+    const rs_camera& c = fp.cam;
+    uint4 w = rng_words(rng, P_PIXEL, 0);
+    double jx = u01(w.x), jy = u01(w.y), jt = u01(w.z);
+    const bool centre = (fp.flags & RS_FLAG_PIXEL_CENTRE) != 0;
+    if (centre) { jx = 0.5; jy = 0.5; jt = 0.0; }
+    // painter.rs:169-172, 133-139
+    double xo = (double)col + ((double)s_i + jx) / (double)fp.sqrt_spp;
+    double yo = (double)row + ((double)s_j + jy) / (double)fp.sqrt_spp;
+    double h = (double)c.height;
+    double u = xo / (double)c.width;
+    double v = (h - 1.0 - yo) / h;
+    // camera.rs:77-85
+    double aperture = centre ? 0.0 : c.aperture;
+    V3 p = v3(0.0, 0.0, 0.0);
+    if (aperture != 0.0) {  // with aperture 0 the disk sample is multiplied by 0: skip the draws
+        for (uint32_t k = 0;; ++k) {
+            double a, b;
+            rng_pair(rng, P_LENS, 0, k, a, b);
+            p = v3(-1.0 + a * 2.0, -1.0 + b * 2.0, 0.0);
+            if (length_squared(p) < 1.0) break;
+        }
+    }
+    V3 rd = (aperture / 2.0) * p;
+    V3 hu = v3(c.horizontal_unit[0], c.horizontal_unit[1], c.horizontal_unit[2]);
+    V3 vu = v3(c.vertical_unit[0], c.vertical_unit[1], c.vertical_unit[2]);
+    V3 offset = hu * rd.x + vu * rd.y;
+    Ray r;
+    r.o = v3(c.origin[0], c.origin[1], c.origin[2]) + offset;
+    V3 hf = v3(c.horizontal_full[0], c.horizontal_full[1], c.horizontal_full[2]);
+    V3 vf = v3(c.vertical_full[0], c.vertical_full[1], c.vertical_full[2]);
+    V3 dir = v3(c.lb[0], c.lb[1], c.lb[2]) + u * hf + v * vf - r.o;
+    r.d = unit(dir);
+    r.time = c.shutter_speed * jt;
+    return r;
+}
+
+__global__ void __launch_bounds__(RS_BLOCK) raygen_kernel(const __grid_constant__ FrameParams fp, const __grid_constant__ WaveState ws) {
+    const uint32_t total = fp.n_pixels * fp.n_samples;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    // every thread of a warp iterates the same number of times (warp_append is collective)
+    for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += stride) {
+        uint32_t i = base + threadIdx.x;
+        bool live = i < total;
+        PathRec p;
+        if (live) {
+            uint32_t p_local = i % fp.n_pixels, k_local = i / fp.n_pixels;
+            uint32_t pixel = fp.pixel0 + p_local;
+            ws.contrib[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (fp.mask && fp.mask[pixel] == 0) {
+                live = false;
+            } else {
+                int row = (int)(pixel / (uint32_t)fp.cam.width), col = (int)(pixel % (uint32_t)fp.cam.width);
+                uint32_t j = fp.sample0 + k_local;
+                int s_j = fp.stratum_row_begin + (int)(j / (uint32_t)fp.sqrt_spp), s_i = (int)(j % (uint32_t)fp.sqrt_spp);
+                RngCtx rng;
+                rng.key = fp.key;
+                rng.pixel = pixel;
+                rng.sample = (uint32_t)(s_j * fp.sqrt_spp + s_i);
+                rng.depth = 0;
+                p.ray = camera_ray(fp, row, col, s_i, s_j, rng);
+                p.T = make_float3(1.f, 1.f, 1.f);
+                p.slot = i;
+                p.pixel = pixel;
+                p.sample = rng.sample;
+            }
+        }
+        uint32_t pos = warp_append(&ws.ctr->n_rays[0], live);
+        if (live) store_path(ws.buf[0], pos, p);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_samples, (unsigned long long)total);
+}
+
+// =============================================================================================
+// extend
+// =============================================================================================
+struct Closest {
+    double t;        // current limit end / best t
+    double end_then; // limit the winning generic object was evaluated under
+    int root;
+    int material;
+};
+
+__device__ __forceinline__ void test_root(const DScene& S, int root, const Ray& ray, const RngCtx& rng, Closest& best) {
+    const int kind = __ldg(&S.root_kind[root]);
+    if (kind == ROOT_SPHERE) {
+        const double2* sp = reinterpret_cast<const double2*>(S.root_sphere + root);
+        double2 c01 = __ldg(sp), c23 = __ldg(sp + 1);  // two 128-bit ld.global.nc
+        double t1, t2;
+        if (sphere_roots(v3(c01.x, c01.y, c23.x), c23.y * c23.y, ray, RS_TMIN, best.t, t1, t2)) {
+            best.t = t1;
+            best.root = root;
+        }
+    } else if (kind == ROOT_TRIANGLE) {
+        const int tri = ~__ldg(&S.root_node[root]);
+        double t, beta, gamma;
+        if (triangle_test(S.tri_geom + 9 * (size_t)tri, ray, RS_TMIN, best.t, t, beta, gamma)) {
+            best.t = t;
+            best.root = root;
+        }
+    } else {
+        if (__ldg(&S.root_gate[root])) {
+            const double inf = __longlong_as_double(0x7ff0000000000000LL);
+            if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
+        }
+        HitRec h;
+        if (TreeTop::hit(S, __ldg(&S.root_node[root]), ray, RS_TMIN, best.t, rng, h)) {
+            best.end_then = best.t;
+            best.t = h.t1;
+            best.root = root;
+            best.material = h.material;
+        }
+    }
+}
+
+__device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); }
+
+__device__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, Closest& best) {
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    best.t = inf;
+    best.end_then = inf;
+    best.root = -1;
+    best.material = -1;
+    if (S.n_roots == 0) return;
+    if (S.bvh_root < 0) {  // single object
+        test_root(S, ~S.bvh_root, ray, rng, best);
+        return;
+    }
+    // f32 copy of the ray for the slab tests
+    const float ox = (float)ray.o.x, oy = (float)ray.o.y, oz = (float)ray.o.z;
+    float dx = (float)ray.d.x, dy = (float)ray.d.y, dz = (float)ray.d.z;
+    const float tiny = 1e-20f;
+    dx = fabsf(dx) > tiny ? dx : copysignf(tiny, dx);
+    dy = fabsf(dy) > tiny ? dy : copysignf(tiny, dy);
+    dz = fabsf(dz) > tiny ? dz : copysignf(tiny, dz);
+    const float idx = 1.0f / dx, idy = 1.0f / dy, idz = 1.0f / dz;
+    const float oodx = ox * idx, oody = oy * idy, oodz = oz * idz;
+    const float tmin_f = (float)RS_TMIN * (1.0f - 2.0f * RS_SLAB_EPS);
+    float tmax_f = FLT_MAX;
+
+    int stack[RS_STACK];
+    int sp = 0;
+    int node = S.bvh_root;
+    while (true) {
+        if (node >= 0) {
+            const float4* np = reinterpret_cast<const float4*>(S.bvh + node);
+            const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
+            const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+            float a0 = fmaf(bx.x, idx, -oodx), a1 = fmaf(bx.y, idx, -oodx);
+            float b0 = fmaf(bx.z, idy, -oody), b1 = fmaf(bx.w, idy, -oody);
+            float c0 = fmaf(bz.x, idz, -oodz), c1 = fmaf(bz.y, idz, -oodz);
+            float near0 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), tmin_f));
+            float far0 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), tmax_f));
+            a0 = fmaf(by.x, idx, -oodx); a1 = fmaf(by.y, idx, -oodx);
+            b0 = fmaf(by.z, idy, -oody); b1 = fmaf(by.w, idy, -oody);
+            c0 = fmaf(bz.z, idz, -oodz); c1 = fmaf(bz.w, idz, -oodz);
+            float near1 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), tmin_f));
+            float far1 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), tmax_f));
+            const bool h0 = near0 <= up(up(far0)), h1 = near1 <= up(up(far1));
+            if (h0 && h1) {
+                const bool swap = near1 < near0;
+                const int first = swap ? ch.y : ch.x, second = swap ? ch.x : ch.y;
+                if (sp < RS_STACK) stack[sp++] = second;
+                node = first;
+                continue;
+            } else if (h0) {
+                node = ch.x;
+                continue;
+            } else if (h1) {
+                node = ch.y;
+                continue;
+            }
+        } else {
+            test_root(S, ~node, ray, rng, best);
+            // shrink the f32 limit (rounded up) so farther boxes are culled
+            tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+}
+
+__device__ __forceinline__ int root_material(const DScene& S, const Closest& best) {
+    const int kind = S.root_kind[best.root];
+    int m;
+    if (kind == ROOT_SPHERE) m = S.nodes[S.root_node[best.root]].material;
+    else if (kind == ROOT_TRIANGLE) m = S.tri_material[~S.root_node[best.root]];
+    else m = best.material;
+    return m < 0 ? S.default_material : m;
+}
+
+// MixedMaterial::scatter (mixed_material.rs:43-51) resolved ahead of shading, so that the
+// class buckets hold concrete materials.  Level 0 uses word 2 of the P_SCATTER call.
+__device__ __forceinline__ int resolve_mixed(const DScene& S, int m, const RngCtx& rng) {
+    for (uint32_t level = 0; level < 8 && S.materials[m].type == RS_MAT_MIXED; ++level) {
+        const rs_material& mm = S.materials[m];
+        uint32_t word = level == 0 ? rng_words(rng, P_SCATTER, 0).z : rng_words(rng, P_MIXED, level).x;
+        m = ((double)word < 4294967295.0 * mm.a) ? mm.mat1 : mm.mat2;
+    }
+    return m;
+}
+
+__global__ void __launch_bounds__(RS_BLOCK) extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+                                                          const __grid_constant__ WaveState ws, const int bounce) {
+    const uint32_t n = ws.ctr->n_rays[bounce];
+    const PathBuf& in = ws.buf[bounce & 1];
+    uint32_t* head = &ws.ctr->extend_head[bounce];
+    uint32_t* class_count = ws.ctr->class_count[bounce];
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_segments, (unsigned long long)n);
+    while (true) {
+        uint32_t base = 0;
+        if (lane_id() == 0) base = atomicAdd(head, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const uint32_t i = base + lane_id();
+        const bool live = i < n;
+        int cls = -1;
+        if (live) {
+            Ray ray;
+            RngCtx rng;
+            rng.key = fp.key;
+            load_ray_only(in, i, ray, rng.pixel, rng.sample);
+            rng.depth = (uint32_t)bounce + 1;
+            Closest best;
+            closest_hit(S, ray, rng, best);
+            HitA h;
+            h.t = best.t;
+            h.root = best.root;
+            h.matinfo = 0;
+            cls = 0;
+            if (best.root >= 0) {
+                int top = root_material(S, best);
+                int leaf = resolve_mixed(S, top, rng);
+                h.matinfo = (uint32_t)leaf | ((uint32_t)top << 16);
+                cls = 1 + S.materials[leaf].type;
+                if (S.root_kind[best.root] == ROOT_GENERIC) ws.hit_end[i] = best.end_then;
+            }
+            ws.hit[i] = h;
+        }
+        // material-coherent bucketing
+        const uint32_t active = __ballot_sync(0xffffffffu, live);
+        if (live) {
+            const uint32_t peers = __match_any_sync(active, cls);
+            const uint32_t leader = __ffs(peers) - 1;
+            uint32_t qbase = 0;
+            if (lane_id() == leader) qbase = atomicAdd(&class_count[cls], __popc(peers));
+            qbase = __shfl_sync(peers, qbase, leader);
+            const uint32_t rank = __popc(peers & ((1u << lane_id()) - 1u));
+            ws.class_queue[(size_t)cls * ws.capacity + qbase + rank] = i;
+        }
+    }
+}
+
+// =============================================================================================
+// shade
+// =============================================================================================
+__device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, const RngCtx& rng, const HitA& ha, double end_then,
+                                            bool want_uv, HitRec& h) {
+    const int kind = S.root_kind[ha.root];
+    const int rn = S.root_node[ha.root];
+    if (kind == ROOT_SPHERE) {
+        const rs_node& n = S.nodes[rn];
+        sphere_record(n.p, n.material, ray, ha.t, ha.t, want_uv, h);
+    } else if (kind == ROOT_TRIANGLE) {
+        double t, beta, gamma;
+        const double inf = __longlong_as_double(0x7ff0000000000000LL);
+        triangle_test(S.tri_geom + 9 * (size_t)(~rn), ray, -inf, inf, t, beta, gamma);
+        triangle_record(S, ~rn, ray, ha.t, beta, gamma, h);
+    } else {
+        // same limit as in extend => bit-identical record
+        if (!TreeTop::hit(S, rn, ray, RS_TMIN, end_then, rng, h)) {
+            h.point = ray_at(ray, ha.t);
+            h.normal = v3(0.0, 1.0, 0.0);
+            h.t1 = ha.t; h.t2 = ha.t; h.u = 0.0; h.v = 0.0; h.material = -1; h.outside = true;
+        }
+    }
+}
+
+// camera.rs:94-100
+__device__ __forceinline__ double phong_highlight(V3 dir_to_light, V3 ray_dir, V3 normal, int exponent, double factor) {
+    V3 reflected = dir_to_light - (2.0 * dot(dir_to_light, normal)) * normal;
+    double base = fmax(dot(reflected, -ray_dir), 0.0);
+    double specular = pow(base, (double)exponent);
+    return specular * factor;
+}
+
+struct PdfState {  // the `Box<dyn PDF>` of a ScatterRecord, flattened
+    int kind;      // 0 Cosine, 1 Reflection, 2 BlinnPhong, 3 Sphere
+    V3 n_w;        // onb_normal.axis[2]
+    V3 r_w;        // onb_reflected.axis[2]
+    V3 r_in;
+    double exponent, k_specular;
+};
+
+__device__ __forceinline__ double pdf_value(const PdfState& P, V3 dir) {
+    switch (P.kind) {
+        case 0: {  // pdf.rs:36-43
+            double c = dot(dir, P.n_w);
+            return c < 0.0 ? 0.0 : c / RS_PI;
+        }
+        case 1: {  // pdf.rs:114-122
+            double v = dot(dir, P.r_w) / RS_PI;
+            return v < 0.0 ? 0.0 : v;
+        }
+        case 2: {  // pdf.rs:177-192
+            double cosine = dot(dir, P.n_w);
+            V3 random_normal = unit((-P.r_in) + dir);
+            double cosine_specular = fmax(dot(random_normal, P.n_w), 0.0);
+            double normal_pdf = (P.exponent + 1.0) / (2.0 * RS_PI) * pow(cosine_specular, P.exponent);
+            return fmax(cosine / RS_PI, 0.0) * (1.0 - P.k_specular) + normal_pdf / (4.0 * dot(P.r_in * -1.0, random_normal)) * P.k_specular;
+        }
+        default: return 1.0 / (4.0 * RS_PI);  // pdf.rs:226-228
+    }
+}
+
+__device__ __noinline__ V3 pdf_generate(const PdfState& P, V3 normal, V3 reflected, const RngCtx& rng) {
+    switch (P.kind) {
+        case 0: {  // pdf.rs:45-47
+            uint4 w = rng_words(rng, P_BRDF, 0);
+            ONB onb = onb_build(normal);
+            return onb_local(onb, cosine_direction(u01(w.x), u01(w.y)));
+        }
+        case 1: {  // pdf.rs:124-140
+            ONB onb = onb_build(reflected);
+            V3 dir = v3(0.0, 0.0, 0.0);
+            for (uint32_t k = 0; k < 4096; ++k) {
+                double r1, xi2;
+                rng_pair(rng, P_BRDF, 0, k, r1, xi2);
+                dir = onb_local(onb, cosine_direction_exponent(P.exponent, r1, xi2));
+                if (dot(dir, P.n_w) > 0.0) break;
+            }
+            return dir;
+        }
+        case 2: {  // pdf.rs:195-209
+            uint4 w = rng_words(rng, P_BRDF, 0);
+            if (u01(w.x) < P.k_specular) {
+                ONB onb = onb_build(reflected);
+                V3 dir = v3(0.0, 0.0, 0.0);
+                for (uint32_t k = 0; k < 4096; ++k) {
+                    double r1, xi2;
+                    rng_pair(rng, P_BRDF, 1, k, r1, xi2);
+                    dir = onb_local(onb, cosine_direction_exponent(P.exponent, r1, xi2));
+                    if (dot(dir, P.n_w) > 0.0) break;
+                }
+                return dir;
+            }
+            ONB onb = onb_build(normal);
+            return onb_local(onb, cosine_direction(u01(w.y), u01(w.z)));
+        }
+        default: {  // vec3.rs:91-96
+            uint4 w = rng_words(rng, P_BRDF, 0);
+            double a = u01(w.x) * (2.0 * RS_PI);
+            double z = -1.0 + u01(w.y) * 2.0;
+            double r = sqrt(1.0 - z * z);
+            double s, c;
+            sincos(a, &s, &c);
+            return v3(r * c, r * s, z);
+        }
+    }
+}
+
+__device__ __forceinline__ void dbg_store3(double* p, uint32_t i, V3 v) {
+    if (p) { p[3 * (size_t)i] = v.x; p[3 * (size_t)i + 1] = v.y; p[3 * (size_t)i + 2] = v.z; }
+}
+
+__global__ void __launch_bounds__(RS_BLOCK) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+                                                         const __grid_constant__ WaveState ws, const int bounce,
+                                                         const __grid_constant__ DebugOut dbg, const int has_dbg) {
+    const PathBuf& in = ws.buf[bounce & 1];
+    const PathBuf& out = ws.buf[(bounce + 1) & 1];
+    const uint32_t* class_count = ws.ctr->class_count[bounce];
+    uint32_t* head = &ws.ctr->shade_head[bounce];
+    uint32_t* out_count = &ws.ctr->n_rays[bounce + 1];
+    const bool last_bounce = bounce + 1 >= fp.depth;
+
+    // virtual index space: each class padded to a multiple of 32 so a warp never mixes classes
+    uint32_t cls_begin[RS_NUM_CLASSES + 1];
+    cls_begin[0] = 0;
+#pragma unroll
+    for (int c = 0; c < RS_NUM_CLASSES; ++c) cls_begin[c + 1] = cls_begin[c] + ((class_count[c] + 31u) & ~31u);
+    const uint32_t total = cls_begin[RS_NUM_CLASSES];
+
+    while (true) {
+        uint32_t base = 0;
+        if (lane_id() == 0) base = atomicAdd(head, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= total) break;
+        int cls = 0;
+#pragma unroll
+        for (int c = 1; c < RS_NUM_CLASSES; ++c)
+            if (base >= cls_begin[c]) cls = c;
+        const uint32_t qi = base - cls_begin[cls] + lane_id();
+        const bool live = qi < class_count[cls];
+
+        bool survive = false;
+        PathRec p;
+        if (live) {
+            const uint32_t i = ws.class_queue[(size_t)cls * ws.capacity + qi];
+            load_path(in, i, p);
+            const HitA ha = ws.hit[i];
+            RngCtx rng;
+            rng.key = fp.key;
+            rng.pixel = p.pixel;
+            rng.sample = p.sample;
+            rng.depth = (uint32_t)bounce + 1;
+
+            float3 add = make_float3(0.f, 0.f, 0.f);  // radiance added at this vertex (before T)
+            int kind = 0;
+            V3 next_o = v3(0, 0, 0), next_d = v3(0, 0, 0);
+            double w_r = 0.0, w_g = 0.0, w_b = 0.0;
+
+            if (cls == 0) {
+                // miss: world.background(ray) (camera.rs:253-254)
+                float4 bg = background(S, p.ray.d);
+                add = make_float3(bg.x, bg.y, bg.z);
+            } else {
+                const rs_material& mat = S.materials[ha.matinfo & 0xffffu];
+                const rs_material& smat = S.materials[ha.matinfo >> 16];
+                const bool want_uv = mat.texture >= 0 && texture_needs_uv(S, mat.texture);
+                HitRec h;
+                const double end_then = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_end[i] : 0.0;
+                rebuild_hit(S, p.ray, rng, ha, end_then, want_uv, h);
+
+                float4 col = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (mat.type == RS_MAT_DIELECTRIC || mat.type == RS_MAT_ISOTROPIC) col = make_float4(mat.color[0], mat.color[1], mat.color[2], mat.color[3]);
+                else col = texture_color(S, mat.texture, h.u, h.v, h.point);
+
+                kind = 1;
+                bool scattered = false, specular = false;
+                PdfState P;
+                P.kind = 0;
+                V3 reflected = v3(0, 0, 0);
+                switch (mat.type) {
+                    case RS_MAT_DIFFUSE_LIGHT: {  // light.rs:33-35: emitted = colour * multiplier, no scatter
+                        add = make_float3((float)((double)col.x * mat.a), (float)((double)col.y * mat.a), (float)((double)col.z * mat.a));
+                        break;
+                    }
+                    case RS_MAT_LAMBERTIAN: {  // lambertian.rs:39-50
+                        scattered = true;
+                        P.kind = 0;
+                        break;
+                    }
+                    case RS_MAT_METAL:            // metal.rs:104-118
+                    case RS_MAT_DIFFUSE_METAL: {  // metal.rs:54-68
+                        reflected = p.ray.d - (2.0 * dot(p.ray.d, h.normal)) * h.normal;
+                        if (dot(reflected, h.normal) > 0.0) {
+                            scattered = true;
+                            if (mat.type == RS_MAT_METAL) {
+                                specular = true;
+                                next_o = h.point;
+                                next_d = reflected;
+                            } else {
+                                P.kind = 1;
+                                P.exponent = mat.a;
+                            }
+                        }
+                        break;
+                    }
+                    case RS_MAT_DIELECTRIC: {  // dielectric.rs:55-93
+                        scattered = true;
+                        specular = true;
+                        next_o = h.point;
+                        double cos_theta = dot(-p.ray.d, h.normal);
+                        double sin_theta = sqrt(1.0 - cos_theta * cos_theta);
+                        double refractive = h.outside ? mat.b : mat.a;
+                        bool refracted = false;
+                        if (!(refractive * sin_theta > 1.0)) {
+                            double reflect_prob = 0.0;
+                            if (mat.has_curve) {  // Glass::reflect_prob (dielectric.rs:20-24)
+                                double r0 = (1.0 - refractive) / (1.0 + refractive);
+                                r0 = r0 * r0;
+                                double x = 1.0 - cos_theta;
+                                reflect_prob = fma(1.0 - r0, x * x * x * x * x, r0);
+                            }
+                            uint4 w = rng_words(rng, P_SCATTER, 0);
+                            if (!(u01(w.w) < reflect_prob)) {
+                                V3 r_parallel = refractive * (p.ray.d + cos_theta * h.normal);
+                                V3 r_perp = (-sqrt(1.0 - length_squared(r_parallel))) * h.normal;
+                                next_d = r_parallel + r_perp;
+                                refracted = true;
+                            }
+                        }
+                        if (!refracted) next_d = p.ray.d - (2.0 * dot(p.ray.d, h.normal)) * h.normal;
+                        break;
+                    }
+                    case RS_MAT_ISOTROPIC: {  // isotropic.rs:26-33
+                        scattered = true;
+                        P.kind = 3;
+                        break;
+                    }
+                    case RS_MAT_BLINN_PHONG: {  // blinn_phong.rs:32-42
+                        scattered = true;
+                        P.kind = 2;
+                        P.k_specular = mat.a;
+                        P.exponent = mat.b;
+                        reflected = p.ray.d - (2.0 * dot(p.ray.d, h.normal)) * h.normal;  // vec3.rs:171-173
+                        break;
+                    }
+                    default: break;
+                }
+
+                if (scattered && specular) {
+                    // skip_pdf: emitted + srec.color * ray_color(srec.ray) (camera.rs:178-182)
+                    kind = 2;
+                    w_r = (double)col.x; w_g = (double)col.y; w_b = (double)col.z;
+                } else if (scattered) {
+                    P.n_w = unit(h.normal);
+                    P.r_in = p.ray.d;
+                    P.r_w = (P.kind == 1 || P.kind == 2) ? unit(reflected) : v3(0, 0, 0);
+                    double light_multi = 1.0, pdf_val;
+                    uint4 w = rng_words(rng, P_SCATTER, 0);
+                    if (u01(w.x) < 0.5) {  // camera.rs:198-213
+                        kind = 3;
+                        pdf_val = 0.3183098861837907;
+                        const int light_node = S.lights[w.y % (uint32_t)S.n_lights];  // list.rs:49-52
+                        V3 dir_to_light = unit(TreeTop::random(S, light_node, h.point, rng));
+                        if (smat.phong_factor > 0.0)
+                            light_multi += phong_highlight(-dir_to_light, p.ray.d, h.normal, smat.phong_exponent, smat.phong_factor);
+                        next_o = ray_at(p.ray, h.t1 - 0.0002);
+                        next_d = dir_to_light;
+                    } else {  // camera.rs:214-218
+                        kind = 4;
+                        next_d = pdf_generate(P, h.normal, reflected, rng);
+                        pdf_val = pdf_value(P, next_d);
+                        next_o = h.point;
+                    }
+                    if (pdf_val <= 0.0 || pdf_val != pdf_val) pdf_val = 1e-5;  // camera.rs:236-238
+                    const double scattering_pdf_val = pdf_value(P, next_d);
+                    const double mult = light_multi * (scattering_pdf_val / pdf_val);
+                    w_r = (double)col.x * mult; w_g = (double)col.y * mult; w_b = (double)col.z * mult;
+                }
+            }
+
+            if (add.x != 0.f || add.y != 0.f || add.z != 0.f) {
+                float4 c = ws.contrib[p.slot];
+                c.x += p.T.x * add.x; c.y += p.T.y * add.y; c.z += p.T.z * add.z;
+                ws.contrib[p.slot] = c;
+            }
+            if (has_dbg) {
+                if (dbg.kind) dbg.kind[p.pixel] = kind;
+                if (dbg.next_od6) {
+                    double* o = dbg.next_od6 + 6 * (size_t)p.pixel;
+                    o[0] = next_o.x; o[1] = next_o.y; o[2] = next_o.z; o[3] = next_d.x; o[4] = next_d.y; o[5] = next_d.z;
+                }
+                dbg_store3(dbg.weight3, p.pixel, v3(w_r, w_g, w_b));
+                dbg_store3(dbg.emitted3, p.pixel, v3((double)add.x, (double)add.y, (double)add.z));
+            }
+            if (kind >= 2 && !last_bounce) {
+                survive = true;
+                p.ray.o = next_o;
+                p.ray.d = next_d;
+                p.T.x *= (float)w_r; p.T.y *= (float)w_g; p.T.z *= (float)w_b;
+            }
+        }
+        const uint32_t pos = warp_append(out_count, survive);
+        if (survive) store_path(out, pos, p);
+    }
+}
+
+// =============================================================================================
+// parity probe: primary hit of every pixel (no shading)
+// =============================================================================================
+__global__ void __launch_bounds__(RS_BLOCK) probe_primary_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+                                                                 const __grid_constant__ WaveState ws, const __grid_constant__ DebugOut dbg) {
+    const uint32_t n = ws.ctr->n_rays[0];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        PathRec p;
+        load_path(ws.buf[0], i, p);
+        const HitA ha = ws.hit[i];
+        const uint32_t px = p.pixel;
+        if (dbg.ray_od6) {
+            double* o = dbg.ray_od6 + 6 * (size_t)px;
+            o[0] = p.ray.o.x; o[1] = p.ray.o.y; o[2] = p.ray.o.z; o[3] = p.ray.d.x; o[4] = p.ray.d.y; o[5] = p.ray.d.z;
+        }
+        if (dbg.obj_id) dbg.obj_id[px] = ha.root;
+        if (ha.root < 0) {
+            if (dbg.t) dbg.t[px] = 0.0;
+            dbg_store3(dbg.normal3, px, v3(0, 0, 0));
+            dbg_store3(dbg.point3, px, v3(0, 0, 0));
+            if (dbg.front) dbg.front[px] = 0;
+            if (dbg.material) dbg.material[px] = -1;
+            continue;
+        }
+        RngCtx rng;
+        rng.key = fp.key; rng.pixel = p.pixel; rng.sample = p.sample; rng.depth = 1;
+        HitRec h;
+        const double end_then = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_end[i] : 0.0;
+        rebuild_hit(S, p.ray, rng, ha, end_then, true, h);
+        if (dbg.t) dbg.t[px] = h.t1;
+        dbg_store3(dbg.normal3, px, h.normal);
+        dbg_store3(dbg.point3, px, h.point);
+        if (dbg.front) dbg.front[px] = h.outside ? 1 : 0;
+        if (dbg.material) dbg.material[px] = (int)(ha.matinfo >> 16);
+    }
+}
+
+// =============================================================================================
+// accumulate / finalize / passes
+// =============================================================================================
+// One thread per pixel of the wave; contrib is sample-major so consecutive threads read
+// consecutive float4s (coalesced 128-bit loads), and the read-modify-write of `accum` is a
+// float4 too.  No atomics: the sum order is fixed, the image is reproducible.
+__global__ void __launch_bounds__(RS_BLOCK) accumulate_kernel(const __grid_constant__ FrameParams fp, const __grid_constant__ WaveState ws,
+                                                              float4* __restrict__ accum) {
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < fp.n_pixels; p += gridDim.x * blockDim.x) {
+        const uint32_t pixel = fp.pixel0 + p;
+        if (fp.mask && fp.mask[pixel] == 0) continue;
+        float sx = 0.f, sy = 0.f, sz = 0.f;
+        for (uint32_t k = 0; k < fp.n_samples; ++k) {
+            const float4 c = ws.contrib[(size_t)k * fp.n_pixels + p];
+            sx += c.x; sy += c.y; sz += c.z;
+        }
+        float4 a = accum[pixel];
+        a.x += sx; a.y += sy; a.z += sz; a.w += (float)fp.n_samples;
+        accum[pixel] = a;
+    }
+}
+
+// Vec3::into_color (vec3.rs:227-240) + the [0,0,0,0] of masked pixels (painter.rs:208-210)
+__global__ void finalize_kernel(const float4* __restrict__ accum, const unsigned char* __restrict__ mask, float4* __restrict__ out,
+                                int64_t n, float inv_n, int gamma) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (mask && mask[i] == 0) { out[i] = make_float4(0.f, 0.f, 0.f, 0.f); continue; }
+        float4 a = accum[i];
+        float r = a.x * inv_n, g = a.y * inv_n, b = a.z * inv_n;
+        if (gamma) { r = sqrtf(r); g = sqrtf(g); b = sqrtf(b); }
+        out[i] = make_float4(r, g, b, 1.0f);
+    }
+}
+
+// combine_pixel (raysnail.rs:176-193)
+__global__ void combine_kernel(const float4* __restrict__ old_px, const float4* __restrict__ new_px, float4* __restrict__ out, int64_t n, float pass) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 o = old_px[i], w = new_px[i];
+        if (w.x == 0.0f && w.y == 0.0f && w.z == 0.0f && w.w == 0.0f) { out[i] = o; continue; }
+        const float d = pass + 1.0f;
+        out[i] = make_float4(__fdiv_rn(__fadd_rn(__fmul_rn(o.x, pass), w.x), d), __fdiv_rn(__fadd_rn(__fmul_rn(o.y, pass), w.y), d),
+                             __fdiv_rn(__fadd_rn(__fmul_rn(o.z, pass), w.z), d), __fdiv_rn(__fadd_rn(__fmul_rn(o.w, pass), w.w), d));
+    }
+}
+
+// calc_noise (raysnail.rs:138-173); quirk keeps its `let x = y as i32;`
+__global__ void noise_kernel(const float4* __restrict__ px, float* __restrict__ noise, int w, int h, int quirk) {
+    const int64_t n = (int64_t)w * h;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int y0 = (int)(i / w), x0 = (int)(i % w);
+        const float4 def = px[i];
+        const int x = quirk ? y0 : x0, y = y0;
+        float diff = 0.0f;
+        for (int yy = y - 2; yy < y + 3; ++yy)
+            for (int xx = x - 2; xx < x + 3; ++xx) {
+                float4 q = def;
+                if (xx >= 0 && yy >= 0 && xx < w && yy < h) q = px[(int64_t)yy * w + xx];
+                const float rd = def.x - q.x, gd = def.y - q.y, bd = def.z - q.z;
+                diff = __fadd_rn(diff, __fadd_rn(__fadd_rn(__fmul_rn(rd, rd), __fmul_rn(gd, gd)), __fmul_rn(bd, bd)));
+            }
+        noise[i] = diff;
+    }
+}
+
+// (clamp(c,0,1) * 255.5) as u8 (raysnail.rs:437-439)
+__device__ __forceinline__ unsigned char quant(float c) {
+    double v = (double)c;
+    double cl = (0.0 > v) ? 0.0 : (v > 1.0 ? 1.0 : v);
+    double s = cl * 255.5;
+    if (s != s) return 0;
+    return (unsigned char)(s < 0.0 ? 0.0 : (s > 255.0 ? 255.0 : s));
+}
+__global__ void quantize_kernel(const float4* __restrict__ px, unsigned char* __restrict__ rgb, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 c = px[i];
+        rgb[3 * i] = quant(c.x); rgb[3 * i + 1] = quant(c.y); rgb[3 * i + 2] = quant(c.z);
+    }
+}
+
+// =============================================================================================
+// launchers
+// =============================================================================================
+static int grid_for(int64_t n) {
+    int64_t b = (n + RS_BLOCK - 1) / RS_BLOCK;
+    if (b < 1) b = 1;
+    if (b > 148 * 16) b = 148 * 16;
+    return (int)b;
+}
+
+void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s) {
+    raygen_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(fp, ws);
+}
+void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int grid, cudaStream_t s) {
+    extend_kernel<<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce);
+}
+void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int grid, const DebugOut* dbg, cudaStream_t s) {
+    DebugOut d = {};
+    if (dbg) d = *dbg;
+    shade_kernel<<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+}
+void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s) {
+    probe_primary_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(S, fp, ws, dbg);
+}
+void launch_accumulate(const FrameParams& fp, const WaveState& ws, float4* accum, cudaStream_t s) {
+    accumulate_kernel<<<grid_for(fp.n_pixels), RS_BLOCK, 0, s>>>(fp, ws, accum);
+}
+void launch_finalize(const float4* accum, const unsigned char* mask, float4* out, int64_t n, int n_samples, int gamma, cudaStream_t s) {
+    finalize_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(accum, mask, out, n, 1.0f / (float)n_samples, gamma);
+}
+void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s) {
+    combine_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(old_px, new_px, out, n, pass);
+}
+void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s) {
+    noise_kernel<<<grid_for((int64_t)w * h), RS_BLOCK, 0, s>>>(px, noise, w, h, quirk);
+}
+void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s) {
+    quantize_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(px, rgb, n);
+}
+int extend_blocks_per_sm() {
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_kernel, RS_BLOCK, 0);
+    return n > 0 ? n : 1;
+}
+int shade_blocks_per_sm() {
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel, RS_BLOCK, 0);
+    return n > 0 ? n : 1;
+}
+
+}  // namespace rsd

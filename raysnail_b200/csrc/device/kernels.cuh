@@ -1,0 +1,99 @@
+// Shared declarations between kernels.cu (device code) and backend.cu (host orchestration).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_scene.cuh"
+
+namespace rsd {
+
+#define RS_MAX_DEPTH 64   // TakePhotoSettings::depth upper bound supported by the counter block
+#define RS_NUM_CLASSES 8  // 0 = miss, 1 + rs_material_type for the resolved (non-mixed) material
+
+// One path record is five 16-byte SoA elements (80 B), so every load/store is a full
+// 128-bit transaction and linear queues coalesce perfectly:
+//   a = (o.x, o.y)  b = (o.z, time)  c = (d.x, d.y)  d = (d.z, bits(T.r, T.g))
+//   e = (bits T.b, slot, pixel, sample)
+struct PathBuf {
+    double2* a;
+    double2* b;
+    double2* c;
+    double2* d;
+    uint4* e;
+};
+
+// closest-hit record written by extend, read by shade (16 B) + the limit the object was
+// evaluated under (only meaningful for ROOT_GENERIC)
+struct __align__(16) HitA {
+    double t;
+    int root;          // -1 = miss
+    uint32_t matinfo;  // resolved material | (settings material << 16)
+};
+
+struct WaveCounters {
+    uint32_t n_rays[RS_MAX_DEPTH + 1];            // live paths entering bounce b
+    uint32_t class_count[RS_MAX_DEPTH][RS_NUM_CLASSES];
+    uint32_t extend_head[RS_MAX_DEPTH];           // persistent-thread work cursors
+    uint32_t shade_head[RS_MAX_DEPTH];
+};
+
+struct DeviceStats {
+    unsigned long long n_samples;
+    unsigned long long n_segments;
+};
+
+struct WaveState {
+    PathBuf buf[2];
+    HitA* hit;
+    double* hit_end;
+    uint32_t* class_queue;  // RS_NUM_CLASSES * capacity
+    float4* contrib;        // per slot: radiance of the finished path
+    WaveCounters* ctr;
+    DeviceStats* stats;
+    uint32_t capacity;
+};
+
+struct FrameParams {
+    rs_camera cam;
+    int sqrt_spp;
+    int depth;
+    int stratum_row_begin;
+    uint32_t flags;
+    uint2 key;
+    // wave
+    uint32_t pixel0;     // first pixel of the wave
+    uint32_t n_pixels;   // P
+    uint32_t sample0;    // first local sample index (0 .. S)
+    uint32_t n_samples;  // K
+    const unsigned char* mask;
+};
+
+struct DebugOut {  // all device pointers, indexed by pixel; any may be null
+    int* obj_id;
+    double* t;
+    double* normal3;
+    double* point3;
+    int* front;
+    int* material;
+    double* ray_od6;
+    int* kind;
+    double* next_od6;
+    double* weight3;
+    double* emitted3;
+};
+
+// launchers (kernels.cu)
+void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s);
+void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int grid, cudaStream_t s);
+void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int grid, const DebugOut* dbg, cudaStream_t s);
+void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s);
+void launch_accumulate(const FrameParams& fp, const WaveState& ws, float4* accum, cudaStream_t s);
+void launch_finalize(const float4* accum, const unsigned char* mask, float4* out, int64_t n, int n_samples, int gamma, cudaStream_t s);
+void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s);
+void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s);
+void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);
+int extend_blocks_per_sm();
+int shade_blocks_per_sm();
+
+}  // namespace rsd

@@ -1,0 +1,546 @@
+// Device-side scene: flat buffers + the intersection / containment / sampling routines for
+// every Hittable of the reference, textures and material helpers.  Used by the extend, shade
+// and probe kernels (kernels.cu).
+//
+// Object expression trees (CSG, TfFacade, ConstantMedium) are evaluated by depth-templated,
+// non-inlined functions (eval<D> calls eval<D-1>): a static call graph instead of device
+// recursion, so ptxas can size the stack.  RS_MAX_TREE_DEPTH bounds the nesting; the host
+// rejects deeper scenes at upload.
+#pragma once
+
+#include "../../../include/raysnail_b200.h"
+#include "rt_math.cuh"
+
+namespace rsd {
+
+#define RS_MAX_TREE_DEPTH 8
+
+// 64-byte BVH node, two children with their boxes (f32, padded outward on the host):
+//   bx = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)   by = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
+//   bz = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)   ch = (child0, child1, -, -)
+// child >= 0: inner node index; child < 0: leaf holding root object ~child.
+struct __align__(64) BvhNode {
+    float4 bx, by, bz;
+    int4 ch;
+};
+
+// pre-multiplied TransformStack of one TfFacade node: 3x4 forward, 3x4 inverse (row-major)
+struct __align__(16) XformPre {
+    double fwd[12];
+    double inv[12];
+};
+
+enum RootKind : int { ROOT_SPHERE = 0, ROOT_TRIANGLE = 1, ROOT_GENERIC = 2 };
+
+struct DScene {
+    const rs_node* nodes;
+    const XformPre* xf;          // indexed by rs_node.first_xform (rewritten at upload)
+    const BvhNode* bvh;
+    int bvh_root;                // >= 0 node, < 0 single leaf, INT_MIN-ish sentinel when empty
+    int n_roots;
+    const int* root_node;        // node index or ~triangle
+    const int* root_kind;        // RootKind
+    const double4* root_sphere;  // ROOT_SPHERE: (cx, cy, cz, r)
+    const double* root_bbox;     // 6 per root (reference bbox, for the gate)
+    const unsigned char* root_gate;
+    const double* tri_geom;      // 9 per triangle: p0.xyz, (a,b,c) = p0-p1, (d,e,f) = p0-p2
+    const double* tri_normals;   // 9 per triangle
+    const int* tri_material;
+    const int* lights;
+    int n_lights;
+    const rs_material* materials;
+    const rs_texture* textures;
+    const unsigned char* texels;
+    const int* perlin_perm;
+    const double* perlin_values;
+    int default_material;
+    float4 bg0, bg1;
+};
+
+struct HitRec {
+    V3 point, normal;
+    double t1, t2, u, v;
+    int material;  // -1 = None
+    bool outside;
+};
+
+// [start, end) like std::ops::Range<f64>::contains
+__device__ __forceinline__ bool in_range(double t, double lo, double hi) { return t >= lo && t < hi; }
+
+// aabb.rs:20-38 in f64 (the gate for roots whose reference bbox does not contain them)
+__device__ __forceinline__ bool aabb_hit_f64(const double* b, const Ray& r, double lo, double hi) {
+    double t_min = lo, t_max = hi;
+    {
+        double inv = 1.0 / r.d.x, t0 = (b[0] - r.o.x) * inv, t1 = (b[3] - r.o.x) * inv;
+        if (inv < 0.0) { double s = t0; t0 = t1; t1 = s; }
+        t_min = fmax(t_min, t0); t_max = fmin(t_max, t1);
+        if (t_max <= t_min) return false;
+    }
+    {
+        double inv = 1.0 / r.d.y, t0 = (b[1] - r.o.y) * inv, t1 = (b[4] - r.o.y) * inv;
+        if (inv < 0.0) { double s = t0; t0 = t1; t1 = s; }
+        t_min = fmax(t_min, t0); t_max = fmin(t_max, t1);
+        if (t_max <= t_min) return false;
+    }
+    {
+        double inv = 1.0 / r.d.z, t0 = (b[2] - r.o.z) * inv, t1 = (b[5] - r.o.z) * inv;
+        if (inv < 0.0) { double s = t0; t0 = t1; t1 = s; }
+        t_min = fmax(t_min, t0); t_max = fmin(t_max, t1);
+        if (t_max <= t_min) return false;
+    }
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Primitives
+// ---------------------------------------------------------------------------------------------
+// sphere.rs:83-109 — returns the accepted root (t1) and the far root (t2)
+__device__ __forceinline__ bool sphere_roots(V3 c, double r2, const Ray& ray, double lo, double hi, double& t1, double& t2) {
+    V3 l = ray.o - c;
+    double half_b = dot(ray.d, l);
+    double a = length_squared(ray.d);
+    double cc = length_squared(l) - r2;
+    double delta = half_b * half_b - a * cc;
+    if (delta < 0.0) return false;
+    double sq = sqrt(delta);
+    double ta = (-half_b - sq) / a;
+    double tb = (-half_b + sq) / a;
+    if (in_range(ta, lo, hi)) { t1 = ta; t2 = tb; return true; }
+    if (in_range(tb, lo, hi)) { t1 = tb; t2 = tb; return true; }
+    return false;
+}
+
+// sphere.rs:64-71
+__device__ __forceinline__ void sphere_uv(V3 center, V3 point, double& u, double& v) {
+    V3 p = unit(point - center);
+    double phi = atan2(-p.z, p.x);
+    double theta = asin(p.y);
+    u = phi / 2.0 / RS_PI + 0.5;
+    v = theta / RS_PI + 0.5;
+}
+
+// HitRecord::new for a sphere (hit.rs:32-53, sphere.rs:56-58: static centre)
+__device__ __forceinline__ void sphere_record(const double* p, int material, const Ray& ray, double t1, double t2, bool want_uv, HitRec& h) {
+    V3 c = v3(p[0], p[1], p[2]);
+    h.point = ray_at(ray, t1);
+    V3 n = vdiv(h.point - c, p[3]);
+    h.outside = dot(ray.d, n) < 0.0;
+    h.normal = h.outside ? n : -n;
+    h.material = material;
+    h.t1 = t1;
+    h.t2 = t2;
+    h.u = 0.0;
+    h.v = 0.0;
+    if (want_uv) sphere_uv(c, h.point, h.u, h.v);
+}
+
+__device__ __forceinline__ bool hit_sphere_node(const rs_node& n, const Ray& ray, double lo, double hi, HitRec& h) {
+    V3 c = v3(n.p[0], n.p[1], n.p[2]);
+    if (n.p[4] != 0.0 || n.p[5] != 0.0 || n.p[6] != 0.0) c = c + v3(n.p[4], n.p[5], n.p[6]) * ray.time;  // center_at
+    double t1, t2;
+    if (!sphere_roots(c, n.p[3] * n.p[3], ray, lo, hi, t1, t2)) return false;
+    sphere_record(n.p, n.material, ray, t1, t2, true, h);
+    return true;
+}
+
+__device__ __forceinline__ void rect_axes(int kind, int& a, int& b, int& c) {
+    if (kind == RS_RECT_XY) { a = 0; b = 1; c = 2; }
+    else if (kind == RS_RECT_XZ) { a = 0; b = 2; c = 1; }
+    else { a = 1; b = 2; c = 0; }
+}
+
+// rect.rs:102-120 + HitRecord::new
+__device__ __forceinline__ bool hit_rect(int kind, double k, double a0, double a1, double b0, double b1, int material,
+                                         const Ray& ray, double lo, double hi, HitRec& h) {
+    int ax0, ax1, ax2;
+    rect_axes(kind, ax0, ax1, ax2);
+    double dk = comp(ray.d, ax2);
+    double t1 = (k - comp(ray.o, ax2)) / dk;
+    if (!in_range(t1, lo, hi)) return false;
+    double a = fma(t1, comp(ray.d, ax0), comp(ray.o, ax0));
+    if (a < a0 || a > a1) return false;
+    double b = fma(t1, comp(ray.d, ax1), comp(ray.o, ax1));
+    if (b < b0 || b > b1) return false;
+    h.point = ray_at(ray, t1);
+    h.outside = dk < 0.0;  // dot(d, +axis) < 0
+    V3 n = v3(0.0, 0.0, 0.0);
+    set_comp(n, ax2, h.outside ? 1.0 : -1.0);
+    h.normal = n;
+    h.material = material;
+    h.t1 = t1;
+    h.t2 = RS_F64_MAX;
+    h.u = (comp(h.point, ax0) - a0) / (a1 - a0);
+    h.v = (comp(h.point, ax1) - b0) / (b1 - b0);
+    return true;
+}
+
+// box.rs:125-150: six faces in the order back, front, left, right, down, up
+static __device__ __noinline__ bool hit_box(const rs_node& n, const Ray& ray, double lo, double hi, HitRec& h) {
+    const double mnx = n.p[0], mny = n.p[1], mnz = n.p[2], mxx = n.p[3], mxy = n.p[4], mxz = n.p[5];
+    HitRec first, second;
+    int count = 0;
+    HitRec cur;
+#define RS_BOX_FACE(kind, k, a0, a1, b0, b1)                                   \
+    if (count < 2 && hit_rect(kind, k, a0, a1, b0, b1, n.material, ray, lo, hi, cur)) { \
+        if (count == 0) first = cur; else second = cur;                          \
+        ++count;                                                                 \
+    }
+    RS_BOX_FACE(RS_RECT_XY, mnz, mnx, mxx, mny, mxy)
+    RS_BOX_FACE(RS_RECT_XY, mxz, mnx, mxx, mny, mxy)
+    RS_BOX_FACE(RS_RECT_YZ, mnx, mny, mxy, mnz, mxz)
+    RS_BOX_FACE(RS_RECT_YZ, mxx, mny, mxy, mnz, mxz)
+    RS_BOX_FACE(RS_RECT_XZ, mny, mnx, mxx, mnz, mxz)
+    RS_BOX_FACE(RS_RECT_XZ, mxy, mnx, mxx, mnz, mxz)
+#undef RS_BOX_FACE
+    if (count == 0) return false;
+    if (count == 1) { h = first; return true; }
+    // two hits: HitRecord::with_normal -> outside = true, t2 = the other face
+    if (first.t1 < second.t1) { h = first; h.t2 = second.t1; }
+    else { h = second; h.t2 = first.t1; }
+    h.outside = true;
+    return true;
+}
+
+// quadric.rs:67-100
+__device__ __forceinline__ V3 quadric_normal(const double* q, V3 p) {
+    double x = 2.0 * q[0] * p.x + q[1] * p.y + q[2] * p.z + q[3];
+    double y = q[1] * p.x + 2.0 * q[4] * p.y + q[5] * p.z + q[6];
+    double z = q[2] * p.x + q[5] * p.y + 2.0 * q[7] * p.z + q[8];
+    V3 r = v3(x, y, z);
+    double len = length(r);
+    if (len == 0.0) return v3(1.0, 0.0, 0.0);
+    return vdiv(r, len);
+}
+
+// quadric.rs:112-182
+static __device__ __noinline__ bool hit_quadric(const rs_node& n, const Ray& ray, double lo, double hi, HitRec& h) {
+    const double qa = n.p[0], qb = n.p[1], qc = n.p[2], qd = n.p[3], qe = n.p[4], qf = n.p[5], qg = n.p[6], qh = n.p[7], qi = n.p[8], qj = n.p[9];
+    const double xo = ray.o.x, yo = ray.o.y, zo = ray.o.z, xd = ray.d.x, yd = ray.d.y, zd = ray.d.z;
+    double a = xd * (qa * xd + qb * yd + qc * zd) + yd * (qe * yd + qf * zd) + zd * qh * zd;
+    double b = xd * (qa * xo + 0.5 * (qb * yo + qc * zo + qd)) + yd * (qe * yo + 0.5 * (qb * xo + qf * zo + qg)) +
+               zd * (qh * zo + 0.5 * (qc * xo + qf * yo + qi));
+    double c = xo * (qa * xo + qb * yo + qc * zo + qd) + yo * (qe * yo + qf * zo + qg) + zo * (qh * zo + qi) + qj;
+    double t1, t2;
+    if (a == 0.0) {
+        if (b == 0.0) return false;
+        t1 = -0.5 * c / b;
+        t2 = RS_F64_MAX;
+        if (!in_range(t1, lo, hi)) return false;
+    } else {
+        double d = b * b - a * c;
+        if (d <= 0.0) return false;
+        double dr = sqrt(d);
+        double ta = (-b - dr) / a, tb = (-b + dr) / a;
+        if (in_range(ta, lo, hi)) { t1 = ta; t2 = tb; }
+        else if (in_range(tb, lo, hi)) { t1 = tb; t2 = RS_F64_MAX; }
+        else return false;
+    }
+    h.point = ray_at(ray, t1);
+    V3 nn = quadric_normal(n.p, h.point);
+    h.outside = dot(ray.d, nn) < 0.0;
+    h.normal = h.outside ? nn : -nn;
+    h.material = n.material;
+    h.t1 = t1;
+    h.t2 = t2;
+    h.u = 0.0;
+    h.v = 0.0;
+    return true;
+}
+
+// triangle_mesh.rs:85-131.  g = p0,(a,b,c),(d,e,f).  Returns t, beta, gamma.
+__device__ __forceinline__ bool triangle_test(const double* g, const Ray& ray, double lo, double hi, double& t, double& beta, double& gamma) {
+    const double a = g[3], b = g[4], c = g[5], d = g[6], e = g[7], f = g[8];
+    const double gg = ray.d.x, hh = ray.d.y, ii = ray.d.z;
+    const double j = g[0] - ray.o.x, k = g[1] - ray.o.y, l = g[2] - ray.o.z;
+    double eihf = e * ii - hh * f, gfdi = gg * f - d * ii, dheg = d * hh - e * gg;
+    double denom = a * eihf + b * gfdi + c * dheg;
+    beta = (j * eihf + k * gfdi + l * dheg) / denom;
+    if (beta < 0.0 || beta >= 1.0) return false;
+    double akjb = a * k - j * b, jcal = j * c - a * l, blkc = b * l - k * c;
+    gamma = (ii * akjb + hh * jcal + gg * blkc) / denom;
+    if (gamma <= 0.0 || beta + gamma >= 1.0) return false;
+    t = -(f * akjb + e * jcal + d * blkc) / denom;
+    return t >= lo && t <= hi;  // inclusive on both ends (triangle_mesh.rs:114)
+}
+
+__device__ __forceinline__ void triangle_record(const DScene& S, int tri, const Ray& ray, double t, double beta, double gamma, HitRec& h) {
+    const double* nn = S.tri_normals + 9 * (size_t)tri;
+    V3 n0 = v3(nn[0], nn[1], nn[2]), n1 = v3(nn[3], nn[4], nn[5]), n2 = v3(nn[6], nn[7], nn[8]);
+    h.normal = n0 * (1.0 - beta - gamma) + n1 * beta + n2 * gamma;  // not normalised, not face-forwarded
+    h.point = ray_at(ray, t);
+    h.material = S.tri_material[tri];
+    h.t1 = t;
+    h.t2 = RS_F64_MAX;
+    h.u = 0.0;
+    h.v = 0.0;
+    h.outside = true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Expression trees
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ V3 xf_apply(const double* m, V3 p, double w) {
+    return v3(m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3] * w, m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7] * w,
+              m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11] * w);
+}
+
+template <int D>
+struct Tree {
+    // `Hittable::contains`
+    static __device__ __noinline__ bool contains(const DScene& S, int ni, V3 p) {
+        const rs_node& n = S.nodes[ni];
+        switch (n.type) {
+            case RS_NODE_SPHERE: {  // sphere.rs:111-115
+                V3 r = v3(n.p[0], n.p[1], n.p[2]) - p;
+                return length_squared(r) < n.p[3] * n.p[3];
+            }
+            case RS_NODE_BOX:  // box.rs:152-157
+                return p.x >= n.p[0] && p.x <= n.p[3] && p.y >= n.p[1] && p.y <= n.p[4] && p.z >= n.p[2] && p.z <= n.p[5];
+            case RS_NODE_QUADRIC: {  // quadric.rs:184-189
+                const double* q = n.p;
+                return (p.x * (q[0] * p.x + q[1] * p.y + q[3]) + p.y * (q[4] * p.y + q[5] * p.z + q[6]) + p.z * (q[7] * p.z + q[2] * p.x + q[8]) + q[9]) <= 0.0;
+            }
+            case RS_NODE_DIFFERENCE: return Tree<D - 1>::contains(S, n.child0, p) && !Tree<D - 1>::contains(S, n.child1, p);
+            case RS_NODE_INTERSECTION: return Tree<D - 1>::contains(S, n.child0, p) && Tree<D - 1>::contains(S, n.child1, p);
+            case RS_NODE_TRANSFORM: return Tree<D - 1>::contains(S, n.child0, xf_apply(S.xf[n.first_xform].inv, p, 1.0));
+            default: return false;  // rect, medium
+        }
+    }
+
+    // `Hittable::hit`
+    static __device__ __noinline__ bool hit(const DScene& S, int ni, const Ray& ray, double lo, double hi, const RngCtx& rng, HitRec& h) {
+        const rs_node& n = S.nodes[ni];
+        switch (n.type) {
+            case RS_NODE_SPHERE: return hit_sphere_node(n, ray, lo, hi, h);
+            case RS_NODE_BOX: return hit_box(n, ray, lo, hi, h);
+            case RS_NODE_RECT: return hit_rect(n.rect_axis, n.p[0], n.p[1], n.p[2], n.p[3], n.p[4], n.material, ray, lo, hi, h);
+            case RS_NODE_QUADRIC: return hit_quadric(n, ray, lo, hi, h);
+            case RS_NODE_DIFFERENCE: {  // difference.rs:57-107
+                HitRec hp, hm;
+                bool has_p = Tree<D - 1>::hit(S, n.child0, ray, lo, hi, rng, hp);
+                if (!has_p) return false;
+                bool has_m = Tree<D - 1>::hit(S, n.child1, ray, lo, hi, rng, hm);
+                if (!has_m) { h = hp; return true; }
+                if (hp.t1 < hm.t1) {
+                    if (!Tree<D - 1>::contains(S, n.child1, hp.point)) {
+                        h = hp;
+                        if (h.material < 0) h.material = n.material;
+                        return true;
+                    }
+                    return false;
+                }
+                if (hm.t2 < hp.t1) {
+                    h = hp;
+                    if (h.material < 0) h.material = n.material;
+                    return true;
+                }
+                if (hm.t2 < hp.t2) {
+                    const rs_node& m = S.nodes[n.child1];
+                    V3 p = ray_at(ray, hm.t2);
+                    // minus.normal(p) / minus.material(): only primitives implement them
+                    V3 nn = v3(0.0, 0.0, 0.0);
+                    int mm = -1;
+                    if (m.type == RS_NODE_SPHERE) { nn = vdiv(p - v3(m.p[0], m.p[1], m.p[2]), m.p[3]); mm = m.material; }
+                    else if (m.type == RS_NODE_BOX) { nn = v3(0.0, 1.0, 0.0); mm = m.material; }
+                    else if (m.type == RS_NODE_RECT) { int a, b, c; rect_axes(m.rect_axis, a, b, c); set_comp(nn, c, 1.0); mm = m.material; }
+                    else if (m.type == RS_NODE_QUADRIC) { nn = quadric_normal(m.p, p); mm = m.material; }
+                    h.point = p;
+                    h.normal = -nn;
+                    h.material = mm >= 0 ? mm : n.material;
+                    h.u = 0.0; h.v = 0.0;
+                    h.t1 = hm.t2; h.t2 = hp.t2;
+                    h.outside = true;
+                    return true;
+                }
+                return false;
+            }
+            case RS_NODE_INTERSECTION: {  // intersection.rs:58-96
+                HitRec h1, h2;
+                if (!Tree<D - 1>::hit(S, n.child0, ray, lo, hi, rng, h1)) return false;
+                if (!Tree<D - 1>::hit(S, n.child1, ray, lo, hi, rng, h2)) return false;
+                bool first_is_1 = h1.t1 < h2.t1;
+                const HitRec& near = first_is_1 ? h1 : h2;
+                const HitRec& far = first_is_1 ? h2 : h1;
+                int obj_near = first_is_1 ? n.child0 : n.child1, obj_far = first_is_1 ? n.child1 : n.child0;
+                if (Tree<D - 1>::contains(S, obj_far, near.point)) h = near;
+                else if (Tree<D - 1>::contains(S, obj_near, far.point)) h = far;
+                else return false;
+                if (h.material < 0) h.material = n.material;
+                return true;
+            }
+            case RS_NODE_TRANSFORM: {  // tf_facade.rs:41-56: only the hit point goes back to world space
+                const XformPre& x = S.xf[n.first_xform];
+                Ray r;
+                r.o = xf_apply(x.inv, ray.o, 1.0);
+                r.d = xf_apply(x.inv, ray.d, 0.0);
+                r.time = ray.time;
+                if (!Tree<D - 1>::hit(S, n.child0, r, lo, hi, rng, h)) return false;
+                h.point = xf_apply(x.fwd, h.point, 1.0);
+                return true;
+            }
+            case RS_NODE_MEDIUM: {  // constant.rs:42-80
+                HitRec r1, r2;
+                const double inf = __longlong_as_double(0x7ff0000000000000LL);
+                if (!Tree<D - 1>::hit(S, n.child0, ray, -inf, inf, rng, r1)) return false;
+                if (!Tree<D - 1>::hit(S, n.child0, ray, r1.t1 + 0.0001, inf, rng, r2)) return false;
+                if (r1.t1 < lo) r1.t1 = lo;
+                if (r2.t1 > hi) r2.t1 = hi;
+                if (r1.t1 >= r2.t1) return false;
+                if (r1.t1 < 0.0) r1.t1 = 0.0;
+                double length_per_unit = length(ray.d);
+                double distance_inside = (r2.t1 - r1.t1) * length_per_unit;
+                uint4 w = rng_words(rng, P_MEDIUM, (uint32_t)ni);
+                double hit_distance = (-1.0 / n.p[0]) * log(u01(w.x));
+                if (hit_distance > distance_inside) return false;
+                double t = r1.t1 + hit_distance / length_per_unit;
+                h.point = ray_at(ray, t);
+                h.normal = v3(1.0, 0.0, 0.0);
+                h.material = n.material;
+                h.t1 = t; h.t2 = t; h.u = 0.0; h.v = 0.0;
+                h.outside = false;
+                return true;
+            }
+            default: return false;
+        }
+    }
+
+    // `Hittable::random` (light sampling)
+    static __device__ __noinline__ V3 random(const DScene& S, int ni, V3 origin, const RngCtx& rng) {
+        const rs_node& n = S.nodes[ni];
+        switch (n.type) {
+            case RS_NODE_SPHERE: {  // sphere.rs:149-164: quarter disk of radius 1 about the centre
+                V3 c = v3(n.p[0], n.p[1], n.p[2]);
+                ONB uvw = onb_build(c - origin);
+                for (uint32_t k = 0;; ++k) {
+                    double a, b;
+                    rng_pair(rng, P_LIGHT, 0, k, a, b);
+                    V3 uv = uvw.u * a + uvw.v * b;
+                    if (length_squared(uv) < 1.0) return (uv + c) - origin;
+                }
+            }
+            case RS_NODE_RECT: {  // rect.rs:141-153: xz only, returns origin - root
+                uint4 w = rng_words(rng, P_LIGHT, 0);
+                V3 root = v3(n.p[1] + u01(w.x) * (n.p[2] - n.p[1]), n.p[0], n.p[3] + u01(w.y) * (n.p[4] - n.p[3]));
+                return origin - root;
+            }
+            case RS_NODE_QUADRIC: return -origin;  // quadric.rs:202-205
+            case RS_NODE_DIFFERENCE:
+            case RS_NODE_INTERSECTION: return Tree<D - 1>::random(S, n.child0, origin, rng);
+            case RS_NODE_TRANSFORM: return Tree<D - 1>::random(S, n.child0, xf_apply(S.xf[n.first_xform].inv, origin, 1.0), rng);
+            default: return v3(1.0, 0.0, 0.0);  // box, medium
+        }
+    }
+};
+
+template <>
+struct Tree<0> {
+    static __device__ __forceinline__ bool contains(const DScene&, int, V3) { return false; }
+    static __device__ __forceinline__ bool hit(const DScene&, int, const Ray&, double, double, const RngCtx&, HitRec&) { return false; }
+    static __device__ __forceinline__ V3 random(const DScene&, int, V3, const RngCtx&) { return v3(1.0, 0.0, 0.0); }
+};
+
+using TreeTop = Tree<RS_MAX_TREE_DEPTH>;
+
+// ---------------------------------------------------------------------------------------------
+// Textures
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t f64_as_u32_sat(double d) {  // Rust `as u32`
+    if (!(d > 0.0)) return 0u;
+    if (d >= 4294967295.0) return 4294967295u;
+    return (uint32_t)d;
+}
+
+static __device__ __noinline__ double perlin_noise(const DScene& S, const rs_texture& t, V3 p) {  // noise.rs:100-137,156-189
+    const int pc = t.point_count;
+    const long long mask = pc - 1;
+    const int* perm = S.perlin_perm + t.perm_offset;
+    const double* val = S.perlin_values + t.value_offset;
+    if (t.perlin_smooth == 0) {
+        int i = (int)(((long long)(4.0 * p.x)) & mask), j = (int)(((long long)(4.0 * p.y)) & mask), k = (int)(((long long)(4.0 * p.z)) & mask);
+        int idx = perm[i] ^ perm[pc + j] ^ perm[2 * pc + k];
+        return t.perlin_vector ? val[3 * idx] : val[idx];
+    }
+    long long i = (long long)floor(p.x), j = (long long)floor(p.y), k = (long long)floor(p.z);
+    double u = p.x - (double)i, v = p.y - (double)j, w = p.z - (double)k;
+    double uu = u, vv = v, ww = w;
+    if (t.perlin_smooth == 2) {
+        uu = u * u * (3.0 - 2.0 * u);
+        vv = v * v * (3.0 - 2.0 * v);
+        ww = w * w * (3.0 - 2.0 * w);
+    }
+    double sum_i = 0.0;
+    for (int di = 0; di < 2; ++di) {
+        double sum_j = 0.0;
+        for (int dj = 0; dj < 2; ++dj) {
+            double sum_k = 0.0;
+            for (int dk = 0; dk < 2; ++dk) {
+                int xi = (int)((i + di) & mask), yi = (int)((j + dj) & mask), zi = (int)((k + dk) & mask);
+                int idx = perm[xi] ^ perm[pc + yi] ^ perm[2 * pc + zi];
+                double lat;
+                if (t.perlin_vector) lat = dot(v3(val[3 * idx], val[3 * idx + 1], val[3 * idx + 2]), v3(u - (double)di, v - (double)dj, w - (double)dk));
+                else lat = val[idx];
+                sum_k += fma((double)di, uu, (double)(1 - di) * (1.0 - uu)) * fma((double)dj, vv, (double)(1 - dj) * (1.0 - vv)) *
+                         fma((double)dk, ww, (double)(1 - dk) * (1.0 - ww)) * lat;
+            }
+            sum_j += sum_k;
+        }
+        sum_i += sum_j;
+    }
+    return sum_i;
+}
+
+static __device__ __noinline__ float4 texture_color(const DScene& S, int ti, double u, double v, V3 p) {
+    // Checker nests arbitrary textures (checker.rs: generic T1, T2): iterate instead of recursing
+    for (int guard = 0; guard < 16; ++guard) {
+        const rs_texture& t = S.textures[ti];
+        if (t.type == RS_TEX_SOLID) return make_float4(t.color[0], t.color[1], t.color[2], t.color[3]);
+        if (t.type == RS_TEX_CHECKER) {  // checker.rs:22-29
+            double value = sin(t.scale * p.x) * sin(t.scale * p.y) * sin(t.scale * p.z);
+            ti = value < 0.0 ? t.odd : t.even;
+            continue;
+        }
+        if (t.type == RS_TEX_IMAGE) {  // image.rs:36-49
+            double vv = 1.0 - v;
+            uint32_t px = f64_as_u32_sat(u * (double)t.width), py = f64_as_u32_sat(vv * (double)t.height);
+            if (px >= (uint32_t)t.width) px = (uint32_t)t.width - 1;
+            if (py >= (uint32_t)t.height) py = (uint32_t)t.height - 1;
+            const unsigned char* c = S.texels + t.texel_offset + 4 * ((size_t)py * t.width + px);
+            return make_float4((float)c[0] / 255.0f, (float)c[1] / 255.0f, (float)c[2] / 255.0f, 1.0f);
+        }
+        // RS_TEX_PERLIN (noise.rs:192-210)
+        double f;
+        if (t.perlin_kind == 0) {
+            f = perlin_noise(S, t, p * t.scale);
+            if (t.perlin_vector) f = 0.5 * (f + 1.0);
+        } else {
+            V3 q = p;
+            double weight = 1.0, sum = 0.0;
+            for (int i = 0; i < t.perlin_depth; ++i) {
+                sum += weight * perlin_noise(S, t, q);
+                weight *= 0.5;
+                q = q * 2.0;
+            }
+            f = fabs(sum);
+            if (t.perlin_kind == 2) f = (sin(fma(t.scale, p.z, 10.0 * f)) + 1.0) * 0.5;
+        }
+        float ff = (float)f;  // Color * f64 (color.rs:99-108): each channel times `rhs as f32`
+        return make_float4(1.0f * ff, 1.0f * ff, 1.0f * ff, 1.0f);
+    }
+    return make_float4(0.f, 0.f, 0.f, 1.f);
+}
+
+__device__ __forceinline__ bool texture_needs_uv(const DScene& S, int ti) {
+    // only image lookups read (u, v); a checker may nest one
+    const rs_texture& t = S.textures[ti];
+    return t.type == RS_TEX_IMAGE || t.type == RS_TEX_CHECKER;
+}
+
+// color.rs:50-58 + world background closures
+__device__ __forceinline__ float4 background(const DScene& S, V3 dir) {
+    double slide = (dir.y + 1.0) * 0.5;
+    float a = (float)fmin(fmax(slide, 0.0), 1.0);
+    float b = 1.0f - a;
+    return make_float4(S.bg0.x * b + S.bg1.x * a, S.bg0.y * b + S.bg1.y * a, S.bg0.z * b + S.bg1.z * a, 1.0f);
+}
+
+}  // namespace rsd
