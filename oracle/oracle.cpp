@@ -23,6 +23,8 @@
 //    collection/bvh.rs:62-69), whose bbox test uses [limit.start, +inf) so that the result
 //    does not depend on traversal order when a reference bbox does not contain its object
 //    (quadric +-100 box, Intersection::bbox z quirk).
+//  * Exact ties in t between two world objects: the reference keeps whichever its (randomly
+//    built) BVH visits first (collection/bvh.rs:184-191); here the lower object id wins.
 //  * `assert!`s that abort the reference (pdf.rs:38 etc., box.rs:129) do not abort here.
 #include <algorithm>
 #include <atomic>
@@ -938,6 +940,15 @@ struct MediumObj : Hittable {  // medium/constant.rs
     Vec3 random(const Vec3&, const Rng&) const override { return Vec3(1.0, 0.0, 0.0); }
 };
 
+inline double next_up(double x) {
+    if (!(x < INF) || !(x > 0.0)) return x;
+    uint64_t b;
+    std::memcpy(&b, &x, 8);
+    b += 1;
+    std::memcpy(&x, &b, 8);
+    return x;
+}
+
 // collection/bvh.rs
 struct BVHNode : Hittable {
     AABB box;
@@ -958,8 +969,19 @@ struct BVHNode : Hittable {
         int id_left = -1;
         bool has_l = left && left->hit(ray, limit, rng, hl);
         if (has_l) id_left = take_leaf_hit();
-        Range right_limit{limit.start, has_l ? hl.t1 : limit.end};
+        // bvh.rs:184-187 shrinks the right limit to `..left.t1`, so on an EXACT tie whichever
+        // subtree is visited first wins — and the reference's tree order is random
+        // (bvh.rs:91).  Canonical, order-independent tie rule used by oracle and GPU alike:
+        // the limit admits t == left.t1 and the lower object id wins.
+        Range right_limit{limit.start, has_l ? next_up(hl.t1) : limit.end};
         bool has_r = right && right->hit(ray, right_limit, rng, hr);
+        if (has_r && has_l) {
+            int id_right = take_leaf_hit();
+            bool right_wins = hr.t1 < hl.t1 || (hr.t1 == hl.t1 && id_right < id_left);
+            if (right_wins) { out = hr; last_leaf_hit(id_right); }
+            else { out = hl; last_leaf_hit(id_left); }
+            return true;
+        }
         if (has_r) { out = hr; return true; }  // hit_right.or(hit_left)
         if (has_l) { out = hl; last_leaf_hit(id_left); return true; }
         return false;

@@ -170,20 +170,29 @@ struct Closest {
     int material;
 };
 
+// smallest double above x (x > 0); +inf stays +inf
+__device__ __forceinline__ double next_up(double x) {
+    return x < __longlong_as_double(0x7ff0000000000000LL) ? __longlong_as_double(__double_as_longlong(x) + 1) : x;
+}
+
+// Closest-hit update.  The reference shrinks the limit to `..best.t` (bvh.rs:184-187), so on an
+// exact tie the object its randomly-built tree visits first wins; the canonical rule here (and
+// in the oracle) is order-independent: the limit admits t == best.t and the lower id wins.
 __device__ __forceinline__ void test_root(const DScene& S, int root, const Ray& ray, const RngCtx& rng, Closest& best) {
     const int kind = __ldg(&S.root_kind[root]);
     if (kind == ROOT_SPHERE) {
         const double2* sp = reinterpret_cast<const double2*>(S.root_sphere + root);
         double2 c01 = __ldg(sp), c23 = __ldg(sp + 1);  // two 128-bit ld.global.nc
         double t1, t2;
-        if (sphere_roots(v3(c01.x, c01.y, c23.x), c23.y * c23.y, ray, RS_TMIN, best.t, t1, t2)) {
+        if (sphere_roots(v3(c01.x, c01.y, c23.x), c23.y * c23.y, ray, RS_TMIN, next_up(best.t), t1, t2) &&
+            (t1 < best.t || root < best.root)) {
             best.t = t1;
             best.root = root;
         }
     } else if (kind == ROOT_TRIANGLE) {
         const int tri = ~__ldg(&S.root_node[root]);
         double t, beta, gamma;
-        if (triangle_test(S.tri_geom + 9 * (size_t)tri, ray, RS_TMIN, best.t, t, beta, gamma)) {
+        if (triangle_test(S.tri_geom + 9 * (size_t)tri, ray, RS_TMIN, best.t, t, beta, gamma) && (t < best.t || root < best.root)) {
             best.t = t;
             best.root = root;
         }
@@ -193,8 +202,9 @@ __device__ __forceinline__ void test_root(const DScene& S, int root, const Ray& 
             if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
         }
         HitRec h;
-        if (TreeTop::hit(S, __ldg(&S.root_node[root]), ray, RS_TMIN, best.t, rng, h)) {
-            best.end_then = best.t;
+        const double hi = next_up(best.t);
+        if (TreeTop::hit(S, __ldg(&S.root_node[root]), ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || root < best.root)) {
+            best.end_then = hi;
             best.t = h.t1;
             best.root = root;
             best.material = h.material;
