@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the raysnail hot path on B200.
+
+Workload (BASELINE.json configs[1]): the book-1 final scene of examples/rtow_13_1.rs
+(seed 7, ~480 spheres, BVH) at 1920x1080, 1024 spp (sqrt_spp 32), depth 8.
+One "step" = one full render of that image (2.12 G camera paths).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+N > 1 is launched by torchrun (one rank per GPU, NCCL): the stratum rows are split across the
+ranks (fixed total work = strong scaling), the per-GPU float4 accumulation buffers are
+summed onto rank 0 with one NCCL reduce, rank 0 finalizes.  Rank 0 prints ONE JSON line.
+
+`--impl reference` times the reference's CPU implementation of the same path.  The Rust
+reference cannot be built in this environment (no cargo/rustc), so that arm runs the C++
+restatement under oracle/ ("kind": "port") with all host threads on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WIDTH, HEIGHT, SQRT_SPP, DEPTH, SCENE_SEED = 1920, 1080, 32, 8, 7
+WORKLOAD = "rtow_13_1 book-1 final scene (seed 7, 477 spheres + light, BVH), 1920x1080, 1024 spp, depth 8"
+METRIC = "path samples/sec"
+UNIT = "samples/s"
+
+# algorithmic bytes per ray segment of the wavefront: 160 B/segment split by
+# kernel (extend: ray read 32 + hit write 16; shade: hit read 16 + state r/w 64 + ray write 32)
+BYTES_PER_SEGMENT = {"extend": 48.0, "shade": 112.0}
+BYTES_PER_SAMPLE = 32.0
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    def __init__(self, index):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(kernel):
+    """per-launch dram bytes of the dominant kernel from the committed ncu capture, if any"""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(kernel)
+        except Exception:
+            return None
+    return None
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the oracle (C++ restatement of the reference's CPU path)
+# ---------------------------------------------------------------------------------------------
+def cpu_render_sample(sqrt_spp_sample, steps=1, warmup=0):
+    """Times the CPU path on the same scene/resolution with a reduced sqrt_spp (samples/s is
+    spp-independent).  Thread partition = painter.rs: hardware threads + 1, interleaved rows."""
+    from oracle_binding import OracleWorld
+    from raysnail_b200 import Scene, make_params
+    scene = Scene.builtin("rtow_final", SCENE_SEED)
+    world = OracleWorld(scene)
+    cam = scene.camera(WIDTH, HEIGHT)
+    params = make_params(sqrt_spp=sqrt_spp_sample, depth=DEPTH)
+    cores = os.cpu_count() or 1
+    times, samples, segments = [], 0, 0
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        _, st = world.render(cam, params, threads=cores + 1)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+            samples, segments = int(st.n_samples), int(st.n_segments)
+    total = sum(times)
+    return {"samples_per_s": samples * len(times) / total, "mrays_per_s": segments * len(times) / total / 1e6, "ms_per_step": 1e3 * total / len(times),
+            "cores": cores, "sample": f"same scene and 1920x1080 frame at {sqrt_spp_sample * sqrt_spp_sample} spp ({samples} paths per step)"}
+
+
+def run_reference(args):
+    rank = env_int("RANK", 0)
+    if rank != 0:
+        return
+    r = cpu_render_sample(1, steps=max(args.steps, 1), warmup=args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["samples_per_s"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "mrays_per_s": r["mrays_per_s"],
+        "config": {"workload": WORKLOAD, "note": "CPU arm: C++ restatement of the Rust reference (no Rust toolchain here); bounded sample per step"},
+        "cpu_baseline": {"value": r["samples_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": r["samples_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def scene_bytes(desc):
+    import ctypes as C
+    from raysnail_b200 import _abi
+    d = desc.contents
+    return (d.n_nodes * C.sizeof(_abi.RsNode) + d.n_roots * (4 + 48) + d.n_lights * 4 + d.n_xforms * C.sizeof(_abi.RsXform) + d.n_tris * (72 + 72 + 4) +
+            d.n_materials * C.sizeof(_abi.RsMaterial) + d.n_textures * C.sizeof(_abi.RsTexture) + d.n_texel_bytes + d.n_perlin_perm * 4 + d.n_perlin_values * 8)
+
+
+def run_gpu(args):
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from raysnail_b200 import RS_FLAG_KERNEL_TIMING, Renderer, Scene, make_params
+
+    world_size, rank, local_rank = env_int("WORLD_SIZE", 1), env_int("RANK", 0), env_int("LOCAL_RANK", 0)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world_size > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    width, height, q, depth = args.width, args.height, args.sqrt_spp, DEPTH
+    scene = Scene.builtin("rtow_final", SCENE_SEED)
+    renderer = Renderer(local_rank)
+    renderer.upload(scene)
+    cam = scene.camera(width, height)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    # strata rows of this rank: contiguous, balanced
+    r0, r1 = (q * rank) // world_size, (q * (rank + 1)) // world_size
+    params = make_params(sqrt_spp=q, depth=depth, rows=(r0, r1), max_wave_paths=args.wave)
+    params_t = make_params(sqrt_spp=q, depth=depth, rows=(r0, r1), max_wave_paths=args.wave, flags=RS_FLAG_KERNEL_TIMING)
+    accum = torch.zeros((height, width, 4), dtype=torch.float32, device=dev)
+    out = torch.empty_like(accum)
+
+    def step(p):
+        accum.zero_()
+        renderer.render_accumulate(cam, p, None, accum.data_ptr(), stream)
+        if world_size > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            renderer.finalize(accum.data_ptr(), None, out.data_ptr(), width, height, q * q, True, stream)
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step(params)
+    barrier()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        step(params)
+    ev1.record()
+    barrier()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    st = renderer.stats()
+    seg = torch.tensor([float(st.n_segments), float(st.n_samples), float(st.n_launches)], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(seg, op=dist.ReduceOp.SUM)
+    n_segments, n_samples, n_launches = [float(x) for x in seg.tolist()]
+
+    # per-kernel CUDA-event timing (events on the launching stream), one extra step
+    barrier()
+    step(params_t)
+    barrier()
+    kt = renderer.stats()
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- e2e through the public API with host buffers -------------------------------------
+    host_img = torch.empty((height, width, 4), dtype=torch.float32).pin_memory()
+    host_mask = torch.ones((height, width), dtype=torch.uint8).pin_memory()
+    d_mask = torch.empty((height, width), dtype=torch.uint8, device=dev)
+    h2d = scene_bytes(scene.desc) + height * width + C.sizeof(type(cam)) + C.sizeof(type(params))
+    d2h = height * width * 16 if rank == 0 else 0
+
+    def e2e_step():
+        renderer.upload(scene)                       # host scene buffers -> HBM (incl. BVH build)
+        d_mask.copy_(host_mask, non_blocking=True)   # pixel mask from pinned host memory
+        accum.zero_()
+        renderer.render_accumulate(cam, params, d_mask.data_ptr(), accum.data_ptr(), stream)
+        if world_size > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            renderer.finalize(accum.data_ptr(), d_mask.data_ptr(), out.data_ptr(), width, height, q * q, True, stream)
+            host_img.copy_(out, non_blocking=True)   # the image the caller gets back
+        torch.cuda.synchronize()
+
+    e2e_steps = max(1, min(args.steps, 3))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    total_samples_per_step = float(width * height * q * q)
+    e2e_value = total_samples_per_step * e2e_steps / (float(e2e_ms.item()) / 1e3)
+
+    if rank == 0:
+        value = total_samples_per_step * args.steps / (ms_total / 1e3)
+        peak, peak_src = measured_peak_gbs()
+        # dominant kernel by CUDA-event time on rank 0's stream
+        shares = {"extend": kt.ms_extend, "shade": kt.ms_shade, "raygen": kt.ms_raygen, "accumulate": kt.ms_accumulate}
+        dom = max(("extend", "shade"), key=lambda k: shares[k])
+        waves = max(1, int(kt.n_launches) // (2 * depth + 2))  # per wave: raygen + depth x (extend, shade) + accumulate
+        n_dom_launches = float(waves * depth)
+        seg_rank0 = float(kt.n_segments)
+        alg_bytes_per_launch = BYTES_PER_SEGMENT[dom] * seg_rank0 / n_dom_launches
+        avg_ms = shares[dom] / n_dom_launches
+        achieved = alg_bytes_per_launch / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+        pipeline_bytes = 160.0 * n_segments + BYTES_PER_SAMPLE * n_samples
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD if (width, height, q) == (WIDTH, HEIGHT, SQRT_SPP) else f"rtow final scene {width}x{height} {q * q} spp (reduced: not the headline workload)",
+                       "parallelism": f"strata-rows x{world_size}", "l2": "path/ray/hit buffers of one wave (>1.5 GB) exceed the 126 MB L2; no flush needed",
+                       "wave_paths": args.wave or (1 << 23)},
+            "mrays_per_s": n_segments / (ms_total / args.steps / 1e3) / 1e6,
+            "segments_per_sample": n_segments / max(n_samples, 1.0),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": int(n_launches * args.steps),
+            "roofline": {"bound": "hbm", "kernel": dom + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": ncu_traffic(dom), "peak_source": peak_src, "avg_launch_ms": avg_ms,
+                         "algorithmic_bytes_per_launch": alg_bytes_per_launch,
+                         "pipeline": {"bytes_per_step": pipeline_bytes, "achieved": pipeline_bytes / (ms_total / args.steps / 1e3) / 1e9 / world_size,
+                                      "frac": pipeline_bytes / (ms_total / args.steps / 1e3) / 1e9 / world_size / peak},
+                         "kernel_ms_per_step": shares},
+            "clocks": clocks,
+        }
+        if world_size == 1 and not args.no_cpu:
+            c = cpu_render_sample(2)
+            line["cpu_baseline"] = {"value": c["samples_per_s"], "unit": UNIT, "cores": c["cores"], "kind": "port", "sample": c["sample"],
+                                    "mrays_per_s": c["mrays_per_s"]}
+        print(json.dumps(line), flush=True)
+    if world_size > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=WIDTH)
+    ap.add_argument("--height", type=int, default=HEIGHT)
+    ap.add_argument("--sqrt-spp", type=int, default=SQRT_SPP)
+    ap.add_argument("--wave", type=int, default=0, help="max paths in flight per wave (0 = library default)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()
