@@ -63,7 +63,10 @@ struct rs_ctx {
     DScene scene{};
     // scene (host side, kept to re-pad the f32 boxes when the camera moves far away)
     std::vector<HostBvhNode> bvh_host;
+    std::vector<int> root_kind_host;
     int bvh_root = 0;
+    int extend_mode = 2;     // 0 static spheres only, 1 + triangles, 2 everything
+    bool shade_generic = true;
     double scene_omax = 0.0, padded_omax = -1.0;
     int n_lights = 0;
 
@@ -239,7 +242,9 @@ int upload_bvh(rs_ctx* ctx, double omax) {
         d.bx = make_float4(lo[0][0], hi[0][0], lo[0][1], hi[0][1]);
         d.by = make_float4(lo[1][0], hi[1][0], lo[1][1], hi[1][1]);
         d.bz = make_float4(lo[0][2], hi[0][2], lo[1][2], hi[1][2]);
-        d.ch = make_int4(h.child[0], h.child[1], 0, 0);
+        // leaf references carry the root kind in their low bits: ~(root << 2 | kind)
+        auto enc = [&](int c) { return c >= 0 ? c : ~((~c << 2) | ctx->root_kind_host[~c]); };
+        d.ch = make_int4(enc(h.child[0]), enc(h.child[1]), 0, 0);
     }
     int rc = upload(ctx, ctx->d_bvh, dev.data(), dev.size());
     if (rc != RS_OK) return rc;
@@ -384,9 +389,9 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
             ++launches;
             for (int b = 0; b < p->depth; ++b) {
                 tm.mark(1);
-                launch_extend(ctx->scene, fp, ctx->ws, b, ctx->extend_grid, stream);
+                launch_extend(ctx->scene, fp, ctx->ws, b, ctx->extend_mode, ctx->extend_grid, stream);
                 tm.mark(2);
-                launch_shade(ctx->scene, fp, ctx->ws, b, ctx->shade_grid, nullptr, stream);
+                launch_shade(ctx->scene, fp, ctx->ws, b, ctx->shade_generic ? 1 : 0, ctx->shade_grid, nullptr, stream);
                 launches += 2;
             }
             tm.mark(3);
@@ -453,8 +458,8 @@ int rs_create(rs_ctx** out, int device) {
     rs_ctx* ctx = new rs_ctx();
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
-    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm();
-    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm();
+    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(2);
+    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(1);
     *out = ctx;
     return RS_OK;
 }
@@ -581,9 +586,26 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
         prims.push_back(p);
     }
     ctx->bvh_host.clear();
+    ctx->root_kind_host = root_kind;
     int bvh_root = 0x7fffffff;
     if (!prims.empty()) bvh_root = build_bvh(prims, 0, prims.size(), 0, ctx->bvh_host);
+    if (!prims.empty() && bvh_root < 0) bvh_root = ~((~bvh_root << 2) | root_kind[~bvh_root]);  // single object
     ctx->scene_omax = omax;
+    // which kernel specialisations this scene needs
+    bool any_tri = false, any_generic = false;
+    for (const BuildPrim& p : prims) {
+        any_tri |= root_kind[p.root] == ROOT_TRIANGLE;
+        any_generic |= root_kind[p.root] == ROOT_GENERIC;
+    }
+    ctx->extend_mode = any_generic ? 2 : (any_tri ? 1 : 0);
+    bool lights_simple = true;  // lights the lean shade kernel samples inline: plain spheres and rects
+    for (int i = 0; i < s->n_lights; ++i) {
+        const rs_node& n = nodes[s->lights[i]];
+        lights_simple &= (n.type == RS_NODE_SPHERE || n.type == RS_NODE_RECT);
+    }
+    ctx->shade_generic = any_generic || !lights_simple;
+    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode);
+    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic ? 1 : 0);
 
     // triangles: p0, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56)
     std::vector<double> tri_geom((size_t)s->n_tris * 9);
@@ -750,8 +772,8 @@ static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     CK(cudaMemsetAsync(ctx->ws.ctr, 0, sizeof(WaveCounters), 0));
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), 0));
     launch_raygen(fp, ctx->ws, 0);
-    launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_grid, 0);
-    if (shade) launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_grid, &dbg, 0);
+    launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->extend_grid, 0);
+    if (shade) launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic ? 1 : 0, ctx->shade_grid, &dbg, 0);
     else launch_probe_primary(ctx->scene, fp, ctx->ws, dbg, 0);
     CK(cudaGetLastError());
     for (int i = 0; i < 11; ++i)

@@ -178,25 +178,29 @@ __device__ __forceinline__ double next_up(double x) {
 // Closest-hit update.  The reference shrinks the limit to `..best.t` (bvh.rs:184-187), so on an
 // exact tie the object its randomly-built tree visits first wins; the canonical rule here (and
 // in the oracle) is order-independent: the limit admits t == best.t and the lower id wins.
-__device__ __forceinline__ void test_root(const DScene& S, int root, const Ray& ray, const RngCtx& rng, Closest& best) {
-    const int kind = __ldg(&S.root_kind[root]);
+// MODE selects what a leaf may hold, so that scenes made of plain spheres (and triangles) get a
+// lean kernel without the expression-tree code: 0 = static spheres, 1 = + triangles, 2 = all.
+// `ref` is the decoded leaf reference (root << 2 | kind).
+template <int MODE>
+__device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& ray, const RngCtx& rng, Closest& best) {
+    const int kind = MODE == 0 ? (int)ROOT_SPHERE : (ref & 3);
+    const int root = ref >> 2;
     if (kind == ROOT_SPHERE) {
         const double2* sp = reinterpret_cast<const double2*>(S.root_sphere + root);
         double2 c01 = __ldg(sp), c23 = __ldg(sp + 1);  // two 128-bit ld.global.nc
-        double t1, t2;
-        if (sphere_roots(v3(c01.x, c01.y, c23.x), c23.y * c23.y, ray, RS_TMIN, next_up(best.t), t1, t2) &&
-            (t1 < best.t || root < best.root)) {
+        double t1;
+        if (sphere_nearest(v3(c01.x, c01.y, c23.x), c23.y * c23.y, ray, RS_TMIN, next_up(best.t), t1) && (t1 < best.t || root < best.root)) {
             best.t = t1;
             best.root = root;
         }
-    } else if (kind == ROOT_TRIANGLE) {
+    } else if (MODE >= 1 && kind == ROOT_TRIANGLE) {
         const int tri = ~__ldg(&S.root_node[root]);
         double t, beta, gamma;
         if (triangle_test(S.tri_geom + 9 * (size_t)tri, ray, RS_TMIN, best.t, t, beta, gamma) && (t < best.t || root < best.root)) {
             best.t = t;
             best.root = root;
         }
-    } else {
+    } else if (MODE >= 2) {
         if (__ldg(&S.root_gate[root])) {
             const double inf = __longlong_as_double(0x7ff0000000000000LL);
             if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
@@ -214,17 +218,20 @@ __device__ __forceinline__ void test_root(const DScene& S, int root, const Ray& 
 
 __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); }
 
-__device__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, Closest& best) {
+#define RS_BVH_SENTINEL ((int)0x80000000)
+#define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) == 2 ? 2 : 3)
+
+// while-while traversal: every lane first walks inner nodes until it holds a leaf (or is done),
+// the warp reconverges, then the lanes holding leaves run the (expensive, f64) object test
+// together.
+template <int MODE>
+__device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, Closest& best) {
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     best.t = inf;
     best.end_then = inf;
     best.root = -1;
     best.material = -1;
     if (S.n_roots == 0) return;
-    if (S.bvh_root < 0) {  // single object
-        test_root(S, ~S.bvh_root, ray, rng, best);
-        return;
-    }
     // f32 copy of the ray for the slab tests
     const float ox = (float)ray.o.x, oy = (float)ray.o.y, oz = (float)ray.o.z;
     float dx = (float)ray.d.x, dy = (float)ray.d.y, dz = (float)ray.d.z;
@@ -239,9 +246,10 @@ __device__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, 
 
     int stack[RS_STACK];
     int sp = 0;
-    int node = S.bvh_root;
+    stack[sp++] = RS_BVH_SENTINEL;
+    int node = S.bvh_root;  // may itself be a leaf (single object)
     while (true) {
-        if (node >= 0) {
+        while (node >= 0) {
             const float4* np = reinterpret_cast<const float4*>(S.bvh + node);
             const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
             const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
@@ -261,20 +269,18 @@ __device__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, 
                 const int first = swap ? ch.y : ch.x, second = swap ? ch.x : ch.y;
                 if (sp < RS_STACK) stack[sp++] = second;
                 node = first;
-                continue;
             } else if (h0) {
                 node = ch.x;
-                continue;
             } else if (h1) {
                 node = ch.y;
-                continue;
+            } else {
+                node = stack[--sp];
             }
-        } else {
-            test_root(S, ~node, ray, rng, best);
-            // shrink the f32 limit (rounded up) so farther boxes are culled
-            tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
         }
-        if (sp == 0) break;
+        if (node == RS_BVH_SENTINEL) break;
+        test_root<MODE>(S, ~node, ray, rng, best);
+        // shrink the f32 limit (rounded up) so farther boxes are culled
+        tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
         node = stack[--sp];
     }
 }
@@ -299,8 +305,9 @@ __device__ __forceinline__ int resolve_mixed(const DScene& S, int m, const RngCt
     return m;
 }
 
-__global__ void __launch_bounds__(RS_BLOCK) extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
-                                                          const __grid_constant__ WaveState ws, const int bounce) {
+template <int MODE>
+__global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+                                                                                     const __grid_constant__ WaveState ws, const int bounce) {
     const uint32_t n = ws.ctr->n_rays[bounce];
     const PathBuf& in = ws.buf[bounce & 1];
     uint32_t* head = &ws.ctr->extend_head[bounce];
@@ -321,7 +328,7 @@ __global__ void __launch_bounds__(RS_BLOCK) extend_kernel(const __grid_constant_
             load_ray_only(in, i, ray, rng.pixel, rng.sample);
             rng.depth = (uint32_t)bounce + 1;
             Closest best;
-            closest_hit(S, ray, rng, best);
+            closest_hit<MODE>(S, ray, rng, best);
             HitA h;
             h.t = best.t;
             h.root = best.root;
@@ -353,6 +360,9 @@ __global__ void __launch_bounds__(RS_BLOCK) extend_kernel(const __grid_constant_
 // =============================================================================================
 // shade
 // =============================================================================================
+// GENERIC = false: the scene holds only static spheres and triangles and its lights are plain
+// spheres/rects, so no expression-tree code is compiled into the kernel.
+template <bool GENERIC>
 __device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, const RngCtx& rng, const HitA& ha, double end_then,
                                             bool want_uv, HitRec& h) {
     const int kind = S.root_kind[ha.root];
@@ -365,7 +375,7 @@ __device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, con
         const double inf = __longlong_as_double(0x7ff0000000000000LL);
         triangle_test(S.tri_geom + 9 * (size_t)(~rn), ray, -inf, inf, t, beta, gamma);
         triangle_record(S, ~rn, ray, ha.t, beta, gamma, h);
-    } else {
+    } else if (GENERIC) {
         // same limit as in extend => bit-identical record
         if (!TreeTop::hit(S, rn, ray, RS_TMIN, end_then, rng, h)) {
             h.point = ray_at(ray, ha.t);
@@ -462,9 +472,10 @@ __device__ __forceinline__ void dbg_store3(double* p, uint32_t i, V3 v) {
     if (p) { p[3 * (size_t)i] = v.x; p[3 * (size_t)i + 1] = v.y; p[3 * (size_t)i + 2] = v.z; }
 }
 
-__global__ void __launch_bounds__(RS_BLOCK) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
-                                                         const __grid_constant__ WaveState ws, const int bounce,
-                                                         const __grid_constant__ DebugOut dbg, const int has_dbg) {
+template <bool GENERIC>
+__global__ void __launch_bounds__(RS_BLOCK, 2) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+                                                            const __grid_constant__ WaveState ws, const int bounce,
+                                                            const __grid_constant__ DebugOut dbg, const int has_dbg) {
     const PathBuf& in = ws.buf[bounce & 1];
     const PathBuf& out = ws.buf[(bounce + 1) & 1];
     const uint32_t* class_count = ws.ctr->class_count[bounce];
@@ -518,7 +529,7 @@ __global__ void __launch_bounds__(RS_BLOCK) shade_kernel(const __grid_constant__
                 const bool want_uv = mat.texture >= 0 && texture_needs_uv(S, mat.texture);
                 HitRec h;
                 const double end_then = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_end[i] : 0.0;
-                rebuild_hit(S, p.ray, rng, ha, end_then, want_uv, h);
+                rebuild_hit<GENERIC>(S, p.ray, rng, ha, end_then, want_uv, h);
 
                 float4 col = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (mat.type == RS_MAT_DIELECTRIC || mat.type == RS_MAT_ISOTROPIC) col = make_float4(mat.color[0], mat.color[1], mat.color[2], mat.color[3]);
@@ -612,7 +623,14 @@ __global__ void __launch_bounds__(RS_BLOCK) shade_kernel(const __grid_constant__
                         kind = 3;
                         pdf_val = 0.3183098861837907;
                         const int light_node = S.lights[w.y % (uint32_t)S.n_lights];  // list.rs:49-52
-                        V3 dir_to_light = unit(TreeTop::random(S, light_node, h.point, rng));
+                        V3 to_light;
+                        if (GENERIC) {
+                            to_light = TreeTop::random(S, light_node, h.point, rng);
+                        } else {
+                            const rs_node& ln = S.nodes[light_node];
+                            to_light = ln.type == RS_NODE_SPHERE ? sphere_random(ln, h.point, rng) : rect_random(ln, h.point, rng);
+                        }
+                        V3 dir_to_light = unit(to_light);
                         if (smat.phong_factor > 0.0)
                             light_multi += phong_highlight(-dir_to_light, p.ray.d, h.normal, smat.phong_exponent, smat.phong_factor);
                         next_o = ray_at(p.ray, h.t1 - 0.0002);
@@ -684,7 +702,7 @@ __global__ void __launch_bounds__(RS_BLOCK) probe_primary_kernel(const __grid_co
         rng.key = fp.key; rng.pixel = p.pixel; rng.sample = p.sample; rng.depth = 1;
         HitRec h;
         const double end_then = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_end[i] : 0.0;
-        rebuild_hit(S, p.ray, rng, ha, end_then, true, h);
+        rebuild_hit<true>(S, p.ray, rng, ha, end_then, true, h);
         if (dbg.t) dbg.t[px] = h.t1;
         dbg_store3(dbg.normal3, px, h.normal);
         dbg_store3(dbg.point3, px, h.point);
@@ -785,13 +803,16 @@ static int grid_for(int64_t n) {
 void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s) {
     raygen_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(fp, ws);
 }
-void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int grid, cudaStream_t s) {
-    extend_kernel<<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce);
+void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int grid, cudaStream_t s) {
+    if (mode == 0) extend_kernel<0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce);
+    else if (mode == 1) extend_kernel<1><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce);
+    else extend_kernel<2><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce);
 }
-void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int grid, const DebugOut* dbg, cudaStream_t s) {
+void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int grid, const DebugOut* dbg, cudaStream_t s) {
     DebugOut d = {};
     if (dbg) d = *dbg;
-    shade_kernel<<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    if (generic) shade_kernel<true><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else shade_kernel<false><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
 }
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s) {
     probe_primary_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(S, fp, ws, dbg);
@@ -811,14 +832,17 @@ void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaS
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s) {
     quantize_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(px, rgb, n);
 }
-int extend_blocks_per_sm() {
+int extend_blocks_per_sm(int mode) {
     int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_kernel, RS_BLOCK, 0);
+    if (mode == 0) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_kernel<0>, RS_BLOCK, 0);
+    else if (mode == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_kernel<1>, RS_BLOCK, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_kernel<2>, RS_BLOCK, 0);
     return n > 0 ? n : 1;
 }
-int shade_blocks_per_sm() {
+int shade_blocks_per_sm(int generic) {
     int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel, RS_BLOCK, 0);
+    if (generic) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<true>, RS_BLOCK, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<false>, RS_BLOCK, 0);
     return n > 0 ? n : 1;
 }
 

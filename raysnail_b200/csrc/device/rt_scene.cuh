@@ -110,6 +110,22 @@ __device__ __forceinline__ bool sphere_roots(V3 c, double r2, const Ray& ray, do
     return false;
 }
 
+// root-level variant: only the accepted root is needed (the far root t2 matters to CSG only)
+__device__ __forceinline__ bool sphere_nearest(V3 c, double r2, const Ray& ray, double lo, double hi, double& t) {
+    V3 l = ray.o - c;
+    double half_b = dot(ray.d, l);
+    double a = length_squared(ray.d);
+    double cc = length_squared(l) - r2;
+    double delta = half_b * half_b - a * cc;
+    if (delta < 0.0) return false;
+    double sq = sqrt(delta);
+    double ta = (-half_b - sq) / a;
+    if (in_range(ta, lo, hi)) { t = ta; return true; }
+    double tb = (-half_b + sq) / a;
+    if (in_range(tb, lo, hi)) { t = tb; return true; }
+    return false;
+}
+
 // sphere.rs:64-71
 __device__ __forceinline__ void sphere_uv(V3 center, V3 point, double& u, double& v) {
     V3 p = unit(point - center);
@@ -276,6 +292,25 @@ __device__ __forceinline__ void triangle_record(const DScene& S, int tri, const 
     h.outside = true;
 }
 
+// `Hittable::random` of the two primitives that act as lights in the shipped scenes
+// sphere.rs:149-164: quarter disk of radius 1 about the centre
+__device__ __forceinline__ V3 sphere_random(const rs_node& n, V3 origin, const RngCtx& rng) {
+    V3 c = v3(n.p[0], n.p[1], n.p[2]);
+    ONB uvw = onb_build(c - origin);
+    for (uint32_t k = 0;; ++k) {
+        double a, b;
+        rng_pair(rng, P_LIGHT, 0, k, a, b);
+        V3 uv = uvw.u * a + uvw.v * b;
+        if (length_squared(uv) < 1.0) return (uv + c) - origin;
+    }
+}
+// rect.rs:141-153: xz only, returns origin - root
+__device__ __forceinline__ V3 rect_random(const rs_node& n, V3 origin, const RngCtx& rng) {
+    uint4 w = rng_words(rng, P_LIGHT, 0);
+    V3 root = v3(n.p[1] + u01(w.x) * (n.p[2] - n.p[1]), n.p[0], n.p[3] + u01(w.y) * (n.p[4] - n.p[3]));
+    return origin - root;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Expression trees
 // ---------------------------------------------------------------------------------------------
@@ -408,21 +443,8 @@ struct Tree {
     static __device__ __noinline__ V3 random(const DScene& S, int ni, V3 origin, const RngCtx& rng) {
         const rs_node& n = S.nodes[ni];
         switch (n.type) {
-            case RS_NODE_SPHERE: {  // sphere.rs:149-164: quarter disk of radius 1 about the centre
-                V3 c = v3(n.p[0], n.p[1], n.p[2]);
-                ONB uvw = onb_build(c - origin);
-                for (uint32_t k = 0;; ++k) {
-                    double a, b;
-                    rng_pair(rng, P_LIGHT, 0, k, a, b);
-                    V3 uv = uvw.u * a + uvw.v * b;
-                    if (length_squared(uv) < 1.0) return (uv + c) - origin;
-                }
-            }
-            case RS_NODE_RECT: {  // rect.rs:141-153: xz only, returns origin - root
-                uint4 w = rng_words(rng, P_LIGHT, 0);
-                V3 root = v3(n.p[1] + u01(w.x) * (n.p[2] - n.p[1]), n.p[0], n.p[3] + u01(w.y) * (n.p[4] - n.p[3]));
-                return origin - root;
-            }
+            case RS_NODE_SPHERE: return sphere_random(n, origin, rng);
+            case RS_NODE_RECT: return rect_random(n, origin, rng);
             case RS_NODE_QUADRIC: return -origin;  // quadric.rs:202-205
             case RS_NODE_DIFFERENCE:
             case RS_NODE_INTERSECTION: return Tree<D - 1>::random(S, n.child0, origin, rng);
