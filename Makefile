@@ -5,7 +5,8 @@ NVCC      ?= /usr/local/cuda/bin/nvcc
 CXX       ?= g++
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := -std=c++17 -O3 -lineinfo $(ARCH) -Xcompiler -fPIC,-O3 -Xptxas -v --expt-relaxed-constexpr
-CXXFLAGS  := -std=c++17 -O2 -fPIC -Wall -Wextra -march=x86-64-v3
+# -ffp-contract=off: Rust never fuses a*b+c on its own, so neither does the host layer
+CXXFLAGS  := -std=c++17 -O2 -fPIC -Wall -Wextra -march=x86-64-v3 -ffp-contract=off
 BUILD     := build
 CSRC      := raysnail_b200/csrc
 LIB       := raysnail_b200/libraysnail_b200.so

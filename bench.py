@@ -168,6 +168,7 @@ def run_gpu(args):
     import torch
     import torch.distributed as dist
     from raysnail_b200 import RS_FLAG_KERNEL_TIMING, Renderer, Scene, make_params
+    from raysnail_b200.distributed import reduce_accum, stratum_rows
 
     world_size, rank, local_rank = env_int("WORLD_SIZE", 1), env_int("RANK", 0), env_int("LOCAL_RANK", 0)
     if not torch.cuda.is_available():
@@ -186,7 +187,7 @@ def run_gpu(args):
     stream = torch.cuda.current_stream().cuda_stream
 
     # strata rows of this rank: contiguous, balanced
-    r0, r1 = (q * rank) // world_size, (q * (rank + 1)) // world_size
+    r0, r1 = stratum_rows(rank, world_size, q)
     params = make_params(sqrt_spp=q, depth=depth, rows=(r0, r1), max_wave_paths=args.wave)
     params_t = make_params(sqrt_spp=q, depth=depth, rows=(r0, r1), max_wave_paths=args.wave, flags=RS_FLAG_KERNEL_TIMING)
     accum = torch.zeros((height, width, 4), dtype=torch.float32, device=dev)
@@ -195,8 +196,7 @@ def run_gpu(args):
     def step(p):
         accum.zero_()
         renderer.render_accumulate(cam, p, None, accum.data_ptr(), stream)
-        if world_size > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        reduce_accum(accum, 0)
         if rank == 0:
             renderer.finalize(accum.data_ptr(), None, out.data_ptr(), width, height, q * q, True, stream)
 
@@ -248,8 +248,7 @@ def run_gpu(args):
         d_mask.copy_(host_mask, non_blocking=True)   # pixel mask from pinned host memory
         accum.zero_()
         renderer.render_accumulate(cam, params, d_mask.data_ptr(), accum.data_ptr(), stream)
-        if world_size > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        reduce_accum(accum, 0)
         if rank == 0:
             renderer.finalize(accum.data_ptr(), d_mask.data_ptr(), out.data_ptr(), width, height, q * q, True, stream)
             host_img.copy_(out, non_blocking=True)   # the image the caller gets back

@@ -219,6 +219,10 @@ typedef struct rs_ctx rs_ctx;
 
 /* ---- life cycle --------------------------------------------------------------------------*/
 int rs_abi_version(void);
+/* sizeof() of the ABI structs as this library was compiled, so a binding (cgo, ctypes, Rust
+ * #[repr(C)]) can verify its layout: 0 rs_node, 1 rs_xform, 2 rs_material, 3 rs_texture,
+ * 4 rs_scene_desc, 5 rs_camera, 6 rs_render_params, 7 rs_stats; -1 for anything else. */
+int rs_abi_struct_size(int which);
 /* Bind a context to CUDA device `device`.  Fails (RS_ERR_NO_DEVICE) without a GPU. */
 int rs_create(rs_ctx** out, int device);
 void rs_destroy(rs_ctx* ctx);

@@ -439,6 +439,20 @@ extern "C" {
 
 int rs_abi_version(void) { return RS_ABI_VERSION; }
 
+int rs_abi_struct_size(int which) {
+    switch (which) {
+        case 0: return (int)sizeof(rs_node);
+        case 1: return (int)sizeof(rs_xform);
+        case 2: return (int)sizeof(rs_material);
+        case 3: return (int)sizeof(rs_texture);
+        case 4: return (int)sizeof(rs_scene_desc);
+        case 5: return (int)sizeof(rs_camera);
+        case 6: return (int)sizeof(rs_render_params);
+        case 7: return (int)sizeof(rs_stats);
+        default: return -1;
+    }
+}
+
 int rs_create(rs_ctx** out, int device) {
     if (!out) return RS_ERR_INVALID_ARGUMENT;
     *out = nullptr;
