@@ -163,6 +163,19 @@ def scene_bytes(desc):
             d.n_materials * C.sizeof(_abi.RsMaterial) + d.n_textures * C.sizeof(_abi.RsTexture) + d.n_texel_bytes + d.n_perlin_perm * 4 + d.n_perlin_values * 8)
 
 
+def load_bench_scene(name):
+    """rtow_final (the headline workload) or another BASELINE.json config: an .sdl file name under
+    tests/golden/sdl (example, quadric, csg, declares, transforms), cornell, mesh:<grid>, mesh_blinn:<grid>."""
+    from raysnail_b200 import Scene
+    sdl = os.path.join(ROOT, "tests", "golden", "sdl", name + ".sdl")
+    if os.path.exists(sdl):
+        return Scene.from_sdl(sdl)
+    if name.startswith("mesh"):
+        kind, _, grid = name.partition(":")
+        return Scene.builtin(kind, SCENE_SEED, int(grid or 708))
+    return Scene.builtin(name, SCENE_SEED)
+
+
 def run_gpu(args):
     import ctypes as C
     import torch
@@ -180,7 +193,7 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=dev)
 
     width, height, q, depth = args.width, args.height, args.sqrt_spp, DEPTH
-    scene = Scene.builtin("rtow_final", SCENE_SEED)
+    scene = load_bench_scene(args.scene)
     renderer = Renderer(local_rank)
     renderer.upload(scene)
     cam = scene.camera(width, height)
@@ -284,7 +297,8 @@ def run_gpu(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD if (width, height, q) == (WIDTH, HEIGHT, SQRT_SPP) else f"rtow final scene {width}x{height} {q * q} spp (reduced: not the headline workload)",
+            "config": {"workload": WORKLOAD if (args.scene, width, height, q) == ("rtow_final", WIDTH, HEIGHT, SQRT_SPP)
+                       else f"{args.scene} {width}x{height} {q * q} spp depth 8 (not the headline workload)",
                        "parallelism": f"strata-rows x{world_size}", "l2": "path/ray/hit buffers of one wave (>1.5 GB) exceed the 126 MB L2; no flush needed",
                        "wave_paths": args.wave or (1 << 23)},
             "mrays_per_s": n_segments / (ms_total / args.steps / 1e3) / 1e6,
@@ -320,6 +334,7 @@ def main():
     ap.add_argument("--sqrt-spp", type=int, default=SQRT_SPP)
     ap.add_argument("--wave", type=int, default=0, help="max paths in flight per wave (0 = library default)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--scene", default="rtow_final", help="other BASELINE.json configs (see load_bench_scene); default = headline")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
