@@ -4,12 +4,17 @@
 NVCC      ?= /usr/local/cuda/bin/nvcc
 CXX       ?= g++
 ARCH      := -gencode arch=compute_100a,code=sm_100a
-NVFLAGS   := -std=c++17 -O3 -lineinfo $(ARCH) -Xcompiler -fPIC,-O3 -Xptxas -v --expt-relaxed-constexpr
+# TUNE: extra -D flags for kernel tuning experiments; VARIANT: suffix for an experimental build
+# (make VARIANT=_t1 TUNE="-DRS_TUNE_SHADE_LEAN=3" builds raysnail_b200/libraysnail_b200_t1.so,
+#  selected at run time with RAYSNAIL_B200_LIB=<path>)
+TUNE      ?=
+VARIANT   ?=
+NVFLAGS   := -std=c++17 -O3 -lineinfo $(ARCH) -Xcompiler -fPIC,-O3 -Xptxas -v --expt-relaxed-constexpr $(TUNE)
 # -ffp-contract=off: Rust never fuses a*b+c on its own, so neither does the host layer
 CXXFLAGS  := -std=c++17 -O2 -fPIC -Wall -Wextra -march=x86-64-v3 -ffp-contract=off
-BUILD     := build
+BUILD     := build$(VARIANT)
 CSRC      := raysnail_b200/csrc
-LIB       := raysnail_b200/libraysnail_b200.so
+LIB       := raysnail_b200/libraysnail_b200$(VARIANT).so
 
 HOST_SRCS := $(CSRC)/host/scene.cpp $(CSRC)/host/sdl_parser.cpp $(CSRC)/host/recipes.cpp \
              $(CSRC)/host/image_io.cpp $(CSRC)/host/host_api.cpp

@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libraysnail_b200.so")
+# RAYSNAIL_B200_LIB selects an experimental build of the same library (kernel tuning variants)
+LIB_PATH = os.environ.get("RAYSNAIL_B200_LIB") or os.path.join(_HERE, "libraysnail_b200.so")
 
 RS_OK = 0
 RS_FLAG_PIXEL_CENTRE = 1

@@ -44,9 +44,14 @@ struct DevBuf {
     T* as() const { return reinterpret_cast<T*>(p); }
 };
 
-struct HostBvhNode {  // two children with f64 boxes
+struct HostBvhNode {  // binary SAH tree: two children with f64 boxes
     double box[2][6];
     int child[2];
+};
+struct HostBvhNode4 {  // collapsed 4-wide tree (what the device traverses)
+    double box[4][6];
+    int child[4];
+    int n;
 };
 
 }  // namespace
@@ -63,6 +68,7 @@ struct rs_ctx {
     DScene scene{};
     // scene (host side, kept to re-pad the f32 boxes when the camera moves far away)
     std::vector<HostBvhNode> bvh_host;
+    std::vector<HostBvhNode4> bvh4_host;
     std::vector<int> root_kind_host;
     int bvh_root = 0;
     int extend_mode = 2;     // 0 static spheres only, 1 + triangles, 2 everything
@@ -227,30 +233,86 @@ float f32_up(double v) {
 // enters: the absolute pad covers the rounding of the ray origin (|o| <= omax) and of the
 // bound itself (DESIGN.md "conservative f32 traversal").
 int upload_bvh(rs_ctx* ctx, double omax) {
-    std::vector<BvhNode> dev(std::max<size_t>(ctx->bvh_host.size(), 1));
+    std::vector<BvhNode4> dev(std::max<size_t>(ctx->bvh4_host.size(), 1));
     const double k = 1.0 / 2097152.0;  // 2^-21
-    for (size_t i = 0; i < ctx->bvh_host.size(); ++i) {
-        const HostBvhNode& h = ctx->bvh_host[i];
-        float lo[2][3], hi[2][3];
-        for (int c = 0; c < 2; ++c)
+    for (size_t i = 0; i < ctx->bvh4_host.size(); ++i) {
+        const HostBvhNode4& h = ctx->bvh4_host[i];
+        float lo[4][3], hi[4][3];
+        int child[4];
+        for (int c = 0; c < 4; ++c) {
+            if (c >= h.n) {  // unused slot: a degenerate box at +FLT_MAX on every axis: t_near > t_far for any ray
+                for (int a = 0; a < 3; ++a) { lo[c][a] = FLT_MAX; hi[c][a] = FLT_MAX; }
+                // should a pathological axis-parallel ray ever "hit" it, re-visiting slot 0 is harmless
+                child[c] = child[0];
+                continue;
+            }
             for (int a = 0; a < 3; ++a) {
                 double l = h.box[c][a], u = h.box[c][3 + a];
                 lo[c][a] = f32_down(l - k * (omax + std::fabs(l)) - 1e-7);
                 hi[c][a] = f32_up(u + k * (omax + std::fabs(u)) + 1e-7);
             }
-        BvhNode& d = dev[i];
-        d.bx = make_float4(lo[0][0], hi[0][0], lo[0][1], hi[0][1]);
-        d.by = make_float4(lo[1][0], hi[1][0], lo[1][1], hi[1][1]);
-        d.bz = make_float4(lo[0][2], hi[0][2], lo[1][2], hi[1][2]);
-        // leaf references carry the root kind in their low bits: ~(root << 2 | kind)
-        auto enc = [&](int c) { return c >= 0 ? c : ~((~c << 2) | ctx->root_kind_host[~c]); };
-        d.ch = make_int4(enc(h.child[0]), enc(h.child[1]), 0, 0);
+            // leaf references carry the root kind in their low bits: ~(root << 2 | kind)
+            const int r = h.child[c];
+            child[c] = r >= 0 ? r : ~((~r << 2) | ctx->root_kind_host[~r]);
+        }
+        BvhNode4& d = dev[i];
+        d.lox = make_float4(lo[0][0], lo[1][0], lo[2][0], lo[3][0]);
+        d.hix = make_float4(hi[0][0], hi[1][0], hi[2][0], hi[3][0]);
+        d.loy = make_float4(lo[0][1], lo[1][1], lo[2][1], lo[3][1]);
+        d.hiy = make_float4(hi[0][1], hi[1][1], hi[2][1], hi[3][1]);
+        d.loz = make_float4(lo[0][2], lo[1][2], lo[2][2], lo[3][2]);
+        d.hiz = make_float4(hi[0][2], hi[1][2], hi[2][2], hi[3][2]);
+        d.child = make_int4(child[0], child[1], child[2], child[3]);
+        d.pad = make_int4(0, 0, 0, 0);
     }
     int rc = upload(ctx, ctx->d_bvh, dev.data(), dev.size());
     if (rc != RS_OK) return rc;
-    ctx->scene.bvh = ctx->d_bvh.as<BvhNode>();
+    ctx->scene.bvh = ctx->d_bvh.as<BvhNode4>();
     ctx->padded_omax = omax;
     return RS_OK;
+}
+
+// Collapse the binary SAH tree into the 4-wide QBVH: a node adopts its grandchildren, always
+// opening the inner child with the largest surface area first.  Returns the wide node index
+// and the stack entries a traversal may need below it (3 pushes per level at most).
+int collapse_bvh4(const std::vector<HostBvhNode>& bin, int bi, std::vector<HostBvhNode4>& out, int& need) {
+    struct Entry { double box[6]; int ref; };
+    Entry e[4];
+    int n = 2;
+    for (int c = 0; c < 2; ++c) { std::memcpy(e[c].box, bin[bi].box[c], sizeof(e[c].box)); e[c].ref = bin[bi].child[c]; }
+    while (n < 4) {
+        int best = -1;
+        double best_area = -1.0;
+        for (int c = 0; c < n; ++c)
+            if (e[c].ref >= 0) {
+                double a = half_area(e[c].box, e[c].box + 3);
+                if (a > best_area) { best_area = a; best = c; }
+            }
+        if (best < 0) break;
+        const HostBvhNode& b = bin[e[best].ref];
+        std::memcpy(e[best].box, b.box[0], sizeof(e[best].box));
+        e[best].ref = b.child[0];
+        std::memcpy(e[n].box, b.box[1], sizeof(e[n].box));
+        e[n].ref = b.child[1];
+        ++n;
+    }
+    const int idx = (int)out.size();
+    out.emplace_back();
+    int child[4], deepest = 0;
+    for (int c = 0; c < n; ++c) {
+        if (e[c].ref >= 0) {
+            int sub = 0;
+            child[c] = collapse_bvh4(bin, e[c].ref, out, sub);
+            deepest = std::max(deepest, sub);
+        } else {
+            child[c] = e[c].ref;
+        }
+    }
+    HostBvhNode4& w = out[idx];
+    w.n = n;
+    for (int c = 0; c < n; ++c) { std::memcpy(w.box[c], e[c].box, sizeof(e[c].box)); w.child[c] = child[c]; }
+    need = 3 + deepest;
+    return idx;
 }
 
 int tree_depth(const rs_scene_desc* s, int ni) {
@@ -603,7 +665,15 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     ctx->root_kind_host = root_kind;
     int bvh_root = 0x7fffffff;
     if (!prims.empty()) bvh_root = build_bvh(prims, 0, prims.size(), 0, ctx->bvh_host);
-    if (!prims.empty() && bvh_root < 0) bvh_root = ~((~bvh_root << 2) | root_kind[~bvh_root]);  // single object
+    ctx->bvh4_host.clear();
+    if (!prims.empty() && bvh_root < 0) {
+        bvh_root = ~((~bvh_root << 2) | root_kind[~bvh_root]);  // single object
+    } else if (!prims.empty()) {
+        int need = 0;
+        bvh_root = collapse_bvh4(ctx->bvh_host, bvh_root, ctx->bvh4_host, need);
+        if (need + 1 > RS_TRAVERSAL_STACK) return fail(ctx, RS_ERR_UNSUPPORTED, "world BVH too deep for the traversal stack");
+    }
+    std::vector<HostBvhNode>().swap(ctx->bvh_host);  // only the collapsed tree is kept
     ctx->scene_omax = omax;
     // which kernel specialisations this scene needs
     bool any_tri = false, any_generic = false;

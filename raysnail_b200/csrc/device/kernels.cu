@@ -24,7 +24,7 @@ namespace rsd {
 
 #define RS_BLOCK 256
 #define RS_TMIN 0.0001
-#define RS_STACK 48
+#define RS_STACK 96  // must match RS_TRAVERSAL_STACK in kernels.cuh (the host checks the tree against it)
 // relative slack for the f32 slab test: covers the rounding of 1/d, the FMA and the f64->f32
 // conversions of the ray; the absolute part (origin rounding) is folded into the padded boxes.
 #define RS_SLAB_EPS 9.5367431640625e-07f  // 2^-20
@@ -219,7 +219,21 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
 __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); }
 
 #define RS_BVH_SENTINEL ((int)0x80000000)
-#define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) == 2 ? 2 : 3)
+// resident 256-thread blocks per SM the kernels are compiled for (register budget); tunable
+// at build time (make TUNE="-DRS_TUNE_EXTEND_LEAN=4 ...")
+#ifndef RS_TUNE_EXTEND_LEAN
+#define RS_TUNE_EXTEND_LEAN 3
+#endif
+#ifndef RS_TUNE_EXTEND_GENERIC
+#define RS_TUNE_EXTEND_GENERIC 2
+#endif
+#ifndef RS_TUNE_SHADE_LEAN
+#define RS_TUNE_SHADE_LEAN 2
+#endif
+#ifndef RS_TUNE_SHADE_GENERIC
+#define RS_TUNE_SHADE_GENERIC 2
+#endif
+#define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) == 2 ? RS_TUNE_EXTEND_GENERIC : RS_TUNE_EXTEND_LEAN)
 
 // while-while traversal: every lane first walks inner nodes until it holds a leaf (or is done),
 // the warp reconverges, then the lanes holding leaves run the (expensive, f64) object test
@@ -248,34 +262,44 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
     int sp = 0;
     stack[sp++] = RS_BVH_SENTINEL;
     int node = S.bvh_root;  // may itself be a leaf (single object)
+    const float slack = (1.0f + RS_SLAB_EPS) * (1.0f + RS_SLAB_EPS);
     while (true) {
         while (node >= 0) {
+            // one 128-byte QBVH node: seven 128-bit ld.global.nc
             const float4* np = reinterpret_cast<const float4*>(S.bvh + node);
-            const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
-            const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
-            float a0 = fmaf(bx.x, idx, -oodx), a1 = fmaf(bx.y, idx, -oodx);
-            float b0 = fmaf(bx.z, idy, -oody), b1 = fmaf(bx.w, idy, -oody);
-            float c0 = fmaf(bz.x, idz, -oodz), c1 = fmaf(bz.y, idz, -oodz);
-            float near0 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), tmin_f));
-            float far0 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), tmax_f));
-            a0 = fmaf(by.x, idx, -oodx); a1 = fmaf(by.y, idx, -oodx);
-            b0 = fmaf(by.z, idy, -oody); b1 = fmaf(by.w, idy, -oody);
-            c0 = fmaf(bz.z, idz, -oodz); c1 = fmaf(bz.w, idz, -oodz);
-            float near1 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), tmin_f));
-            float far1 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), tmax_f));
-            const bool h0 = near0 <= up(up(far0)), h1 = near1 <= up(up(far1));
-            if (h0 && h1) {
-                const bool swap = near1 < near0;
-                const int first = swap ? ch.y : ch.x, second = swap ? ch.x : ch.y;
-                if (sp < RS_STACK) stack[sp++] = second;
-                node = first;
-            } else if (h0) {
-                node = ch.x;
-            } else if (h1) {
-                node = ch.y;
-            } else {
-                node = stack[--sp];
+            const float4 lox = __ldg(np), hix = __ldg(np + 1), loy = __ldg(np + 2), hiy = __ldg(np + 3), loz = __ldg(np + 4), hiz = __ldg(np + 5);
+            const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 6));
+            // slab test of child k; hits become sortable keys: (bits(t_near) & ~3) | k  (t_near > 0)
+#define RS_SLAB4(k, C)                                                                                         \
+            uint32_t key##k;                                                                                       \
+            {                                                                                                      \
+                const float x0 = fmaf(lox.C, idx, -oodx), x1 = fmaf(hix.C, idx, -oodx);                            \
+                const float y0 = fmaf(loy.C, idy, -oody), y1 = fmaf(hiy.C, idy, -oody);                            \
+                const float z0 = fmaf(loz.C, idz, -oodz), z1 = fmaf(hiz.C, idz, -oodz);                            \
+                const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin_f));         \
+                const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax_f));         \
+                key##k = (tn <= tf * slack) ? ((__float_as_uint(tn) & ~3u) | (uint32_t)k) : 0xffffffffu;           \
             }
+            RS_SLAB4(0, x)
+            RS_SLAB4(1, y)
+            RS_SLAB4(2, z)
+            RS_SLAB4(3, w)
+#undef RS_SLAB4
+            // 5-comparator sorting network: key0 = nearest hit ... misses (0xffffffff) last
+#define RS_CSWAP(a, b) { const uint32_t lo_ = min(a, b), hi_ = max(a, b); a = lo_; b = hi_; }
+            RS_CSWAP(key0, key1) RS_CSWAP(key2, key3) RS_CSWAP(key0, key2) RS_CSWAP(key1, key3) RS_CSWAP(key1, key2)
+#undef RS_CSWAP
+#define RS_CHILD(key) (((key) & 3u) == 0u ? ch.x : (((key) & 3u) == 1u ? ch.y : (((key) & 3u) == 2u ? ch.z : ch.w)))
+            if (key0 == 0xffffffffu) {
+                node = stack[--sp];
+            } else {
+                // push the farther hits (farthest first) so that the nearest is popped first
+                if (key3 != 0xffffffffu && sp < RS_STACK) stack[sp++] = RS_CHILD(key3);
+                if (key2 != 0xffffffffu && sp < RS_STACK) stack[sp++] = RS_CHILD(key2);
+                if (key1 != 0xffffffffu && sp < RS_STACK) stack[sp++] = RS_CHILD(key1);
+                node = RS_CHILD(key0);
+            }
+#undef RS_CHILD
         }
         if (node == RS_BVH_SENTINEL) break;
         test_root<MODE>(S, ~node, ray, rng, best);
@@ -313,11 +337,14 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
     uint32_t* head = &ws.ctr->extend_head[bounce];
     uint32_t* class_count = ws.ctr->class_count[bounce];
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_segments, (unsigned long long)n);
+    // the cursor bump for the NEXT batch is issued before the current batch is processed, so the
+    // atomic's round trip to L2 overlaps with the traversal instead of heading every batch
+    uint32_t next_base = 0;
+    if (lane_id() == 0) next_base = atomicAdd(head, 32u);
     while (true) {
-        uint32_t base = 0;
-        if (lane_id() == 0) base = atomicAdd(head, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
+        const uint32_t base = __shfl_sync(0xffffffffu, next_base, 0);
         if (base >= n) break;
+        if (lane_id() == 0) next_base = atomicAdd(head, 32u);
         const uint32_t i = base + lane_id();
         const bool live = i < n;
         int cls = -1;
@@ -473,7 +500,7 @@ __device__ __forceinline__ void dbg_store3(double* p, uint32_t i, V3 v) {
 }
 
 template <bool GENERIC>
-__global__ void __launch_bounds__(RS_BLOCK, 2) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+__global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS_TUNE_SHADE_LEAN) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                             const __grid_constant__ WaveState ws, const int bounce,
                                                             const __grid_constant__ DebugOut dbg, const int has_dbg) {
     const PathBuf& in = ws.buf[bounce & 1];
@@ -490,17 +517,26 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) shade_kernel(const __grid_constan
     for (int c = 0; c < RS_NUM_CLASSES; ++c) cls_begin[c + 1] = cls_begin[c] + ((class_count[c] + 31u) & ~31u);
     const uint32_t total = cls_begin[RS_NUM_CLASSES];
 
+    uint32_t next_base = 0;
+    if (lane_id() == 0) next_base = atomicAdd(head, 32u);
     while (true) {
-        uint32_t base = 0;
-        if (lane_id() == 0) base = atomicAdd(head, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
+        const uint32_t base = __shfl_sync(0xffffffffu, next_base, 0);
         if (base >= total) break;
+        if (lane_id() == 0) next_base = atomicAdd(head, 32u);
         int cls = 0;
 #pragma unroll
         for (int c = 1; c < RS_NUM_CLASSES; ++c)
             if (base >= cls_begin[c]) cls = c;
         const uint32_t qi = base - cls_begin[cls] + lane_id();
         const bool live = qi < class_count[cls];
+
+        // Lambertian / Dielectric / Isotropic / BlinnPhong always scatter: their slot in the output
+        // queue can be reserved before the shading math, so the atomic's latency is hidden;
+        // miss / light never continue; Metal / DiffuseMetal may absorb and reserve afterwards.
+        const bool always = cls == 1 + RS_MAT_LAMBERTIAN || cls == 1 + RS_MAT_DIELECTRIC || cls == 1 + RS_MAT_ISOTROPIC || cls == 1 + RS_MAT_BLINN_PHONG;
+        const bool never = cls == 0 || cls == 1 + RS_MAT_DIFFUSE_LIGHT || last_bounce;
+        uint32_t pos = 0;
+        if (always && !never) pos = warp_append(out_count, live);
 
         bool survive = false;
         PathRec p;
@@ -649,9 +685,12 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) shade_kernel(const __grid_constan
             }
 
             if (add.x != 0.f || add.y != 0.f || add.z != 0.f) {
-                float4 c = ws.contrib[p.slot];
-                c.x += p.T.x * add.x; c.y += p.T.y * add.y; c.z += p.T.z * add.z;
-                ws.contrib[p.slot] = c;
+                // the path owns its slot; result-less atomics compile to RED (fire and forget), so
+                // nothing waits on the read-modify-write
+                float* c = reinterpret_cast<float*>(ws.contrib + p.slot);
+                atomicAdd(c + 0, p.T.x * add.x);
+                atomicAdd(c + 1, p.T.y * add.y);
+                atomicAdd(c + 2, p.T.z * add.z);
             }
             if (has_dbg) {
                 if (dbg.kind) dbg.kind[p.pixel] = kind;
@@ -669,7 +708,7 @@ __global__ void __launch_bounds__(RS_BLOCK, 2) shade_kernel(const __grid_constan
                 p.T.x *= (float)w_r; p.T.y *= (float)w_g; p.T.z *= (float)w_b;
             }
         }
-        const uint32_t pos = warp_append(out_count, survive);
+        if (!always && !never) pos = warp_append(out_count, survive);
         if (survive) store_path(out, pos, p);
     }
 }

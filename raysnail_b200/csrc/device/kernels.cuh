@@ -9,6 +9,7 @@
 namespace rsd {
 
 #define RS_MAX_DEPTH 64   // TakePhotoSettings::depth upper bound supported by the counter block
+#define RS_TRAVERSAL_STACK 96  // per-thread QBVH traversal stack entries (3 pushes per level at most)
 #define RS_NUM_CLASSES 8  // 0 = miss, 1 + rs_material_type for the resolved (non-mixed) material
 
 // One path record is five 16-byte SoA elements (80 B), so every load/store is a full

@@ -24,6 +24,16 @@ struct __align__(64) BvhNode {
     int4 ch;
 };
 
+// 128-byte QBVH node (the world accelerator): four children, boxes as SoA float4s (component
+// k = child k; f32, padded outward on the host), loaded with seven 128-bit ld.global.nc.
+// child >= 0: inner node index; child < 0: leaf ~(object << 2 | kind).  Unused slots hold a
+// degenerate box at +FLT_MAX (lo = hi), which no ray can hit (t_near = +inf or t_far = -inf).
+struct __align__(128) BvhNode4 {
+    float4 lox, hix, loy, hiy, loz, hiz;
+    int4 child;
+    int4 pad;
+};
+
 // pre-multiplied TransformStack of one TfFacade node: 3x4 forward, 3x4 inverse (row-major)
 struct __align__(16) XformPre {
     double fwd[12];
@@ -35,8 +45,8 @@ enum RootKind : int { ROOT_SPHERE = 0, ROOT_TRIANGLE = 1, ROOT_GENERIC = 2 };
 struct DScene {
     const rs_node* nodes;
     const XformPre* xf;          // indexed by rs_node.first_xform (rewritten at upload)
-    const BvhNode* bvh;
-    int bvh_root;                // >= 0 node, < 0 single leaf, INT_MIN-ish sentinel when empty
+    const BvhNode4* bvh;
+    int bvh_root;                // >= 0 node, < 0 single leaf ref
     int n_roots;
     const int* root_node;        // node index or ~triangle
     const int* root_kind;        // RootKind
