@@ -195,6 +195,7 @@ def run_gpu(args):
     width, height, q, depth = args.width, args.height, args.sqrt_spp, DEPTH
     scene = load_bench_scene(args.scene)
     renderer = Renderer(local_rank)
+    renderer.set_bvh_width(args.bvh_width)
     renderer.upload(scene)
     cam = scene.camera(width, height)
     stream = torch.cuda.current_stream().cuda_stream
@@ -334,6 +335,7 @@ def main():
     ap.add_argument("--sqrt-spp", type=int, default=SQRT_SPP)
     ap.add_argument("--wave", type=int, default=0, help="max paths in flight per wave (0 = library default)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--bvh-width", type=int, default=2, choices=[2, 4], help="world BVH: 2 = binary (default), 4 = QBVH")
     ap.add_argument("--scene", default="rtow_final", help="other BASELINE.json configs (see load_bench_scene); default = headline")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -229,6 +229,12 @@ void rs_destroy(rs_ctx* ctx);
 /* Message of the last failed call on this context (or of a failed rs_create when ctx == NULL). */
 const char* rs_last_error(const rs_ctx* ctx);
 
+/* Tuning options; set before rs_upload_scene.  RS_OPT_BVH_WIDTH: 2 (default) = binary world BVH of
+ * 64-byte nodes, 4 = QBVH of 128-byte nodes (both give identical hits; see DESIGN.md for the
+ * measured trade-off).  */
+#define RS_OPT_BVH_WIDTH 1
+int rs_set_option(rs_ctx* ctx, int option, int value);
+
 /* ---- scene: replaces `World::new` (world.rs:40-53) + `BVH::new` (bvh.rs:47-112) -----------*/
 int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* scene);
 

@@ -19,7 +19,7 @@ RS_FLAG_KERNEL_TIMING = 2
 
 # every symbol include/raysnail_b200.h declares
 CORE_SYMBOLS = [
-    "rs_abi_version", "rs_abi_struct_size", "rs_create", "rs_destroy", "rs_last_error", "rs_upload_scene", "rs_render",
+    "rs_abi_version", "rs_abi_struct_size", "rs_set_option", "rs_create", "rs_destroy", "rs_last_error", "rs_upload_scene", "rs_render",
     "rs_render_accumulate", "rs_finalize", "rs_combine_passes", "rs_noise_map", "rs_quantize_rgb8",
     "rs_debug_primary", "rs_debug_scatter", "rs_get_stats",
 ]
@@ -119,6 +119,7 @@ def load() -> C.CDLL:
 
     proto("rs_abi_version", C.c_int)
     proto("rs_abi_struct_size", C.c_int, C.c_int)
+    proto("rs_set_option", C.c_int, vp, C.c_int, C.c_int)
     proto("rs_create", C.c_int, P(vp), C.c_int)
     proto("rs_destroy", None, vp)
     proto("rs_last_error", C.c_char_p, vp)

@@ -286,6 +286,12 @@ class Renderer:
         if rc != 0:
             raise RaysnailError(f"{what} failed ({rc}): {self._lib.rs_last_error(self._ctx).decode()}")
 
+    def set_bvh_width(self, width: int):
+        """2 = binary world BVH (default), 4 = QBVH; takes effect at the next upload."""
+        self._ck(self._lib.rs_set_option(self._ctx, 1, int(width)), "rs_set_option")
+        if self._scene is not None:
+            self.upload(self._scene)
+
     def upload(self, scene: Scene):
         self._ck(self._lib.rs_upload_scene(self._ctx, scene.desc), "rs_upload_scene")
         self._scene = scene  # keep the host buffers alive

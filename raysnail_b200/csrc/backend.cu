@@ -71,6 +71,7 @@ struct rs_ctx {
     std::vector<HostBvhNode4> bvh4_host;
     std::vector<int> root_kind_host;
     int bvh_root = 0;
+    int bvh_width = 2;       // RS_OPT_BVH_WIDTH: 2 = binary 64-byte nodes (default), 4 = QBVH 128-byte nodes
     int extend_mode = 2;     // 0 static spheres only, 1 + triangles, 2 everything
     bool shade_generic = true;
     double scene_omax = 0.0, padded_omax = -1.0;
@@ -233,8 +234,34 @@ float f32_up(double v) {
 // enters: the absolute pad covers the rounding of the ray origin (|o| <= omax) and of the
 // bound itself (DESIGN.md "conservative f32 traversal").
 int upload_bvh(rs_ctx* ctx, double omax) {
-    std::vector<BvhNode4> dev(std::max<size_t>(ctx->bvh4_host.size(), 1));
     const double k = 1.0 / 2097152.0;  // 2^-21
+    if (ctx->bvh_width != 4) {  // binary tree, 64-byte nodes
+        std::vector<BvhNode> dev2(std::max<size_t>(ctx->bvh_host.size(), 1));
+        for (size_t i = 0; i < ctx->bvh_host.size(); ++i) {
+            const HostBvhNode& h = ctx->bvh_host[i];
+            float lo[2][3], hi[2][3];
+            for (int c = 0; c < 2; ++c)
+                for (int a = 0; a < 3; ++a) {
+                    double l = h.box[c][a], u = h.box[c][3 + a];
+                    lo[c][a] = f32_down(l - k * (omax + std::fabs(l)) - 1e-7);
+                    hi[c][a] = f32_up(u + k * (omax + std::fabs(u)) + 1e-7);
+                }
+            BvhNode& d = dev2[i];
+            d.bx = make_float4(lo[0][0], hi[0][0], lo[0][1], hi[0][1]);
+            d.by = make_float4(lo[1][0], hi[1][0], lo[1][1], hi[1][1]);
+            d.bz = make_float4(lo[0][2], hi[0][2], lo[1][2], hi[1][2]);
+            // leaf references carry the root kind in their low bits: ~(root << 2 | kind)
+            auto enc = [&](int c) { return c >= 0 ? c : ~((~c << 2) | ctx->root_kind_host[~c]); };
+            d.ch = make_int4(enc(h.child[0]), enc(h.child[1]), 0, 0);
+        }
+        int rc2 = upload(ctx, ctx->d_bvh, dev2.data(), dev2.size());
+        if (rc2 != RS_OK) return rc2;
+        ctx->scene.bvh2 = ctx->d_bvh.as<BvhNode>();
+        ctx->scene.bvh = nullptr;
+        ctx->padded_omax = omax;
+        return RS_OK;
+    }
+    std::vector<BvhNode4> dev(std::max<size_t>(ctx->bvh4_host.size(), 1));
     for (size_t i = 0; i < ctx->bvh4_host.size(); ++i) {
         const HostBvhNode4& h = ctx->bvh4_host[i];
         float lo[4][3], hi[4][3];
@@ -268,6 +295,7 @@ int upload_bvh(rs_ctx* ctx, double omax) {
     int rc = upload(ctx, ctx->d_bvh, dev.data(), dev.size());
     if (rc != RS_OK) return rc;
     ctx->scene.bvh = ctx->d_bvh.as<BvhNode4>();
+    ctx->scene.bvh2 = nullptr;
     ctx->padded_omax = omax;
     return RS_OK;
 }
@@ -451,7 +479,7 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
             ++launches;
             for (int b = 0; b < p->depth; ++b) {
                 tm.mark(1);
-                launch_extend(ctx->scene, fp, ctx->ws, b, ctx->extend_mode, ctx->extend_grid, stream);
+                launch_extend(ctx->scene, fp, ctx->ws, b, ctx->extend_mode, ctx->bvh_width == 4, ctx->extend_grid, stream);
                 tm.mark(2);
                 launch_shade(ctx->scene, fp, ctx->ws, b, ctx->shade_generic ? 1 : 0, ctx->shade_grid, nullptr, stream);
                 launches += 2;
@@ -534,7 +562,7 @@ int rs_create(rs_ctx** out, int device) {
     rs_ctx* ctx = new rs_ctx();
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
-    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(2);
+    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(2, 0);
     ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(1);
     *out = ctx;
     return RS_OK;
@@ -548,6 +576,16 @@ void rs_destroy(rs_ctx* ctx) {
 }
 
 const char* rs_last_error(const rs_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int rs_set_option(rs_ctx* ctx, int option, int value) {
+    if (!ctx) return RS_ERR_INVALID_ARGUMENT;
+    if (option == RS_OPT_BVH_WIDTH && (value == 2 || value == 4)) {
+        if (ctx->bvh_width != value) ctx->has_scene = false;  // the tree must be rebuilt by the next upload
+        ctx->bvh_width = value;
+        return RS_OK;
+    }
+    return fail(ctx, RS_ERR_INVALID_ARGUMENT, "unknown option or value");
+}
 
 int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if (!ctx || !s) return RS_ERR_INVALID_ARGUMENT;
@@ -668,12 +706,13 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     ctx->bvh4_host.clear();
     if (!prims.empty() && bvh_root < 0) {
         bvh_root = ~((~bvh_root << 2) | root_kind[~bvh_root]);  // single object
-    } else if (!prims.empty()) {
+    } else if (!prims.empty() && ctx->bvh_width == 4) {
         int need = 0;
         bvh_root = collapse_bvh4(ctx->bvh_host, bvh_root, ctx->bvh4_host, need);
         if (need + 1 > RS_TRAVERSAL_STACK) return fail(ctx, RS_ERR_UNSUPPORTED, "world BVH too deep for the traversal stack");
+        std::vector<HostBvhNode>().swap(ctx->bvh_host);  // only the collapsed tree is kept
     }
-    std::vector<HostBvhNode>().swap(ctx->bvh_host);  // only the collapsed tree is kept
+    // (binary tree: depth <= 24 SAH levels + log2(n) median levels, one push per level: fits)
     ctx->scene_omax = omax;
     // which kernel specialisations this scene needs
     bool any_tri = false, any_generic = false;
@@ -688,7 +727,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
         lights_simple &= (n.type == RS_NODE_SPHERE || n.type == RS_NODE_RECT);
     }
     ctx->shade_generic = any_generic || !lights_simple;
-    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode);
+    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4);
     ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic ? 1 : 0);
 
     // triangles: p0, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56)
@@ -856,7 +895,7 @@ static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     CK(cudaMemsetAsync(ctx->ws.ctr, 0, sizeof(WaveCounters), 0));
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), 0));
     launch_raygen(fp, ctx->ws, 0);
-    launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->extend_grid, 0);
+    launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->bvh_width == 4, ctx->extend_grid, 0);
     if (shade) launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic ? 1 : 0, ctx->shade_grid, &dbg, 0);
     else launch_probe_primary(ctx->scene, fp, ctx->ws, dbg, 0);
     CK(cudaGetLastError());

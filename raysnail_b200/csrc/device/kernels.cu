@@ -238,7 +238,9 @@ __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); 
 // while-while traversal: every lane first walks inner nodes until it holds a leaf (or is done),
 // the warp reconverges, then the lanes holding leaves run the (expensive, f64) object test
 // together.
-template <int MODE>
+// WIDE = false: binary tree of 64-byte nodes (the default: fewest instructions per ray on
+// these cache-resident scenes); WIDE = true: the 4-wide QBVH of 128-byte nodes.
+template <int MODE, bool WIDE>
 __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, Closest& best) {
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     best.t = inf;
@@ -258,13 +260,52 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
     const float tmin_f = (float)RS_TMIN * (1.0f - 2.0f * RS_SLAB_EPS);
     float tmax_f = FLT_MAX;
 
-    int stack[RS_STACK];
+    // stack entries carry the entry distance of the child (its sort key) next to the reference,
+    // so entries that fell behind the closest hit found meanwhile are dropped when popped —
+    // most stacked entries are leaves, and a leaf costs an f64 object test
+    unsigned long long stack[RS_STACK];
     int sp = 0;
-    stack[sp++] = RS_BVH_SENTINEL;
+    stack[sp++] = (unsigned long long)(uint32_t)RS_BVH_SENTINEL;  // key 0: never dropped
     int node = S.bvh_root;  // may itself be a leaf (single object)
     const float slack = (1.0f + RS_SLAB_EPS) * (1.0f + RS_SLAB_EPS);
+#define RS_POP()                                                                   \
+    do {                                                                           \
+        const unsigned long long e_ = stack[--sp];                                 \
+        node = (int)(uint32_t)e_;                                                  \
+        if (!(__uint_as_float((uint32_t)(e_ >> 32) & ~3u) > tmax_f)) break;        \
+    } while (true)
     while (true) {
-        while (node >= 0) {
+        while (!WIDE && node >= 0) {
+            // one 64-byte node: two children with their boxes, four 128-bit ld.global.nc
+            const float4* np = reinterpret_cast<const float4*>(S.bvh2 + node);
+            const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
+            const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+            float a0 = fmaf(bx.x, idx, -oodx), a1 = fmaf(bx.y, idx, -oodx);
+            float b0 = fmaf(bx.z, idy, -oody), b1 = fmaf(bx.w, idy, -oody);
+            float c0 = fmaf(bz.x, idz, -oodz), c1 = fmaf(bz.y, idz, -oodz);
+            const float near0 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), tmin_f));
+            const float far0 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), tmax_f));
+            a0 = fmaf(by.x, idx, -oodx); a1 = fmaf(by.y, idx, -oodx);
+            b0 = fmaf(by.z, idy, -oody); b1 = fmaf(by.w, idy, -oody);
+            c0 = fmaf(bz.z, idz, -oodz); c1 = fmaf(bz.w, idz, -oodz);
+            const float near1 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), tmin_f));
+            const float far1 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), tmax_f));
+            const bool h0 = near0 <= far0 * slack, h1 = near1 <= far1 * slack;
+            if (h0 && h1) {
+                const bool swap = near1 < near0;
+                const int second = swap ? ch.x : ch.y;
+                const float second_near = swap ? near0 : near1;
+                if (sp < RS_STACK) stack[sp++] = ((unsigned long long)__float_as_uint(second_near) << 32) | (unsigned long long)(uint32_t)second;
+                node = swap ? ch.y : ch.x;
+            } else if (h0) {
+                node = ch.x;
+            } else if (h1) {
+                node = ch.y;
+            } else {
+                RS_POP();
+            }
+        }
+        while (WIDE && node >= 0) {
             // one 128-byte QBVH node: seven 128-bit ld.global.nc
             const float4* np = reinterpret_cast<const float4*>(S.bvh + node);
             const float4 lox = __ldg(np), hix = __ldg(np + 1), loy = __ldg(np + 2), hiy = __ldg(np + 3), loz = __ldg(np + 4), hiz = __ldg(np + 5);
@@ -290,23 +331,26 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
             RS_CSWAP(key0, key1) RS_CSWAP(key2, key3) RS_CSWAP(key0, key2) RS_CSWAP(key1, key3) RS_CSWAP(key1, key2)
 #undef RS_CSWAP
 #define RS_CHILD(key) (((key) & 3u) == 0u ? ch.x : (((key) & 3u) == 1u ? ch.y : (((key) & 3u) == 2u ? ch.z : ch.w)))
+#define RS_PUSH(key) stack[sp++] = ((unsigned long long)(key) << 32) | (unsigned long long)(uint32_t)RS_CHILD(key)
             if (key0 == 0xffffffffu) {
-                node = stack[--sp];
+                RS_POP();
             } else {
                 // push the farther hits (farthest first) so that the nearest is popped first
-                if (key3 != 0xffffffffu && sp < RS_STACK) stack[sp++] = RS_CHILD(key3);
-                if (key2 != 0xffffffffu && sp < RS_STACK) stack[sp++] = RS_CHILD(key2);
-                if (key1 != 0xffffffffu && sp < RS_STACK) stack[sp++] = RS_CHILD(key1);
+                if (key3 != 0xffffffffu && sp < RS_STACK) RS_PUSH(key3);
+                if (key2 != 0xffffffffu && sp < RS_STACK) RS_PUSH(key2);
+                if (key1 != 0xffffffffu && sp < RS_STACK) RS_PUSH(key1);
                 node = RS_CHILD(key0);
             }
+#undef RS_PUSH
 #undef RS_CHILD
         }
         if (node == RS_BVH_SENTINEL) break;
         test_root<MODE>(S, ~node, ray, rng, best);
         // shrink the f32 limit (rounded up) so farther boxes are culled
         tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
-        node = stack[--sp];
+        RS_POP();
     }
+#undef RS_POP
 }
 
 __device__ __forceinline__ int root_material(const DScene& S, const Closest& best) {
@@ -329,7 +373,7 @@ __device__ __forceinline__ int resolve_mixed(const DScene& S, int m, const RngCt
     return m;
 }
 
-template <int MODE>
+template <int MODE, bool WIDE>
 __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                                                      const __grid_constant__ WaveState ws, const int bounce) {
     const uint32_t n = ws.ctr->n_rays[bounce];
@@ -355,7 +399,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
             load_ray_only(in, i, ray, rng.pixel, rng.sample);
             rng.depth = (uint32_t)bounce + 1;
             Closest best;
-            closest_hit<MODE>(S, ray, rng, best);
+            closest_hit<MODE, WIDE>(S, ray, rng, best);
             HitA h;
             h.t = best.t;
             h.root = best.root;
@@ -535,8 +579,11 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
         // miss / light never continue; Metal / DiffuseMetal may absorb and reserve afterwards.
         const bool always = cls == 1 + RS_MAT_LAMBERTIAN || cls == 1 + RS_MAT_DIELECTRIC || cls == 1 + RS_MAT_ISOTROPIC || cls == 1 + RS_MAT_BLINN_PHONG;
         const bool never = cls == 0 || cls == 1 + RS_MAT_DIFFUSE_LIGHT || last_bounce;
-        uint32_t pos = 0;
-        if (always && !never) pos = warp_append(out_count, live);
+        // issue now, consume (shfl) only when the record is stored
+        uint32_t pos = 0, early_base = 0;
+        const uint32_t early_mask = (always && !never) ? __ballot_sync(0xffffffffu, live) : 0u;
+        const uint32_t early_leader = early_mask ? (uint32_t)(__ffs(early_mask) - 1) : 0u;
+        if (early_mask && lane_id() == early_leader) early_base = atomicAdd(out_count, __popc(early_mask));
 
         bool survive = false;
         PathRec p;
@@ -685,12 +732,10 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
             }
 
             if (add.x != 0.f || add.y != 0.f || add.z != 0.f) {
-                // the path owns its slot; result-less atomics compile to RED (fire and forget), so
-                // nothing waits on the read-modify-write
-                float* c = reinterpret_cast<float*>(ws.contrib + p.slot);
-                atomicAdd(c + 0, p.T.x * add.x);
-                atomicAdd(c + 1, p.T.y * add.y);
-                atomicAdd(c + 2, p.T.z * add.z);
+                // No material of the reference both emits and scatters (DiffuseLight never scatters,
+                // material/light.rs; nothing else overrides `emitted`), so a path adds radiance exactly
+                // once — when it ends on a light or leaves the scene: a plain 128-bit store, no RMW.
+                ws.contrib[p.slot] = make_float4(p.T.x * add.x, p.T.y * add.y, p.T.z * add.z, 0.f);
             }
             if (has_dbg) {
                 if (dbg.kind) dbg.kind[p.pixel] = kind;
@@ -708,7 +753,8 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
                 p.T.x *= (float)w_r; p.T.y *= (float)w_g; p.T.z *= (float)w_b;
             }
         }
-        if (!always && !never) pos = warp_append(out_count, survive);
+        if (early_mask) pos = __shfl_sync(0xffffffffu, early_base, early_leader) + __popc(early_mask & ((1u << lane_id()) - 1u));
+        else if (!never) pos = warp_append(out_count, survive);
         if (survive) store_path(out, pos, p);
     }
 }
@@ -842,10 +888,15 @@ static int grid_for(int64_t n) {
 void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s) {
     raygen_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(fp, ws);
 }
-void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int grid, cudaStream_t s) {
-    if (mode == 0) extend_kernel<0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce);
-    else if (mode == 1) extend_kernel<1><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce);
-    else extend_kernel<2><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce);
+template <int MODE, bool WIDE>
+static const void* extend_fn() { return (const void*)extend_kernel<MODE, WIDE>; }
+static const void* extend_fn_for(int mode, int wide) {
+    if (wide) return mode == 0 ? extend_fn<0, true>() : (mode == 1 ? extend_fn<1, true>() : extend_fn<2, true>());
+    return mode == 0 ? extend_fn<0, false>() : (mode == 1 ? extend_fn<1, false>() : extend_fn<2, false>());
+}
+void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int grid, cudaStream_t s) {
+    void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce};
+    cudaLaunchKernel(extend_fn_for(mode, wide), dim3(grid), dim3(RS_BLOCK), args, 0, s);
 }
 void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int grid, const DebugOut* dbg, cudaStream_t s) {
     DebugOut d = {};
@@ -871,11 +922,9 @@ void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaS
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s) {
     quantize_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(px, rgb, n);
 }
-int extend_blocks_per_sm(int mode) {
+int extend_blocks_per_sm(int mode, int wide) {
     int n = 0;
-    if (mode == 0) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_kernel<0>, RS_BLOCK, 0);
-    else if (mode == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_kernel<1>, RS_BLOCK, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_kernel<2>, RS_BLOCK, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_fn_for(mode, wide), RS_BLOCK, 0);
     return n > 0 ? n : 1;
 }
 int shade_blocks_per_sm(int generic) {

@@ -86,7 +86,7 @@ struct DebugOut {  // all device pointers, indexed by pixel; any may be null
 
 // launchers (kernels.cu)
 void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s);
-void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int grid, cudaStream_t s);
+void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int grid, cudaStream_t s);
 void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int grid, const DebugOut* dbg, cudaStream_t s);
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s);
 void launch_accumulate(const FrameParams& fp, const WaveState& ws, float4* accum, cudaStream_t s);
@@ -94,7 +94,7 @@ void launch_finalize(const float4* accum, const unsigned char* mask, float4* out
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s);
 void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s);
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);
-int extend_blocks_per_sm(int mode);
+int extend_blocks_per_sm(int mode, int wide);
 int shade_blocks_per_sm(int generic);
 
 }  // namespace rsd

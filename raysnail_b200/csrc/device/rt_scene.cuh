@@ -45,7 +45,8 @@ enum RootKind : int { ROOT_SPHERE = 0, ROOT_TRIANGLE = 1, ROOT_GENERIC = 2 };
 struct DScene {
     const rs_node* nodes;
     const XformPre* xf;          // indexed by rs_node.first_xform (rewritten at upload)
-    const BvhNode4* bvh;
+    const BvhNode4* bvh;         // 4-wide QBVH (when selected)
+    const BvhNode* bvh2;         // binary tree (default)
     int bvh_root;                // >= 0 node, < 0 single leaf ref
     int n_roots;
     const int* root_node;        // node index or ~triangle

@@ -188,3 +188,27 @@ def test_passes_kernels_bit_exact(renderer):
     exp = np.empty((h, w, 3), np.uint8)
     ol.rso_quantize_rgb8(new.ctypes.data, exp.ctypes.data, w * h)
     assert np.array_equal(d_rgb.cpu().numpy(), exp)
+
+
+@pytest.mark.parametrize("name", ["rtow_final", "mesh", "csg", "cornell"])
+def test_qbvh_gives_the_same_hits_and_image_as_the_binary_bvh(renderer, name):
+    """RS_OPT_BVH_WIDTH = 4 (128-byte QBVH nodes) vs 2 (64-byte binary nodes): the closest hit is a
+    property of the scene, not of the tree, so ids/t must be identical and the image bit-equal."""
+    scene = load_scene(name)
+    oracle = OracleWorld(scene)
+    cam = scene.camera(W, H)
+    params = make_params(samples=9)
+    try:
+        renderer.set_bvh_width(4)
+        renderer.upload(scene)
+        g4 = renderer.debug_primary(cam, params, 4)
+        img4 = renderer.render(cam, params)
+    finally:
+        renderer.set_bvh_width(2)
+    renderer.upload(scene)
+    g2 = renderer.debug_primary(cam, params, 4)
+    img2 = renderer.render(cam, params)
+    o = oracle.debug_primary(cam, params, 4)
+    assert np.array_equal(g4["obj_id"], o["obj_id"]) and np.array_equal(g2["obj_id"], o["obj_id"])
+    assert np.array_equal(g4["t"], g2["t"])
+    assert np.array_equal(img4, img2)
