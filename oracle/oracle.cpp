@@ -174,6 +174,13 @@ struct Rng {
     }
 };
 
+// The lobe samplers of ReflectionPdf / BlinnPhongPdf (pdf.rs:124-140, 195-209) loop until the
+// sample lies above the surface.  When a ray hits the BACK of a shading normal (triangle normals
+// are not face-forwarded, triangle_mesh.rs:115-116) the reflected lobe can lie entirely below
+// it and the reference's `loop {}` never ends.  Oracle and GPU give up after this many
+// candidates and keep the last one.
+constexpr uint32_t REJECTION_CAP = 256;
+
 // vec3.rs:100-111
 inline Vec3 cosine_direction(double r1, double r2) {
     double q2 = std::sqrt(r2);
@@ -343,7 +350,7 @@ struct ReflectionPdf : PDF {  // pdf.rs:86-141
             rng.pair(P_BRDF, 0, k, r1, xi2);
             Vec3 direction = onb_reflected.local(cosine_direction_exponent(exponent, r1, xi2));
             if (dot(direction, onb_normal.axis[2]) > 0.0) return direction;
-            if (k > 4096) return direction;  // the reference would spin; unreachable in practice
+            if (k + 1 >= REJECTION_CAP) return direction;  // the reference spins on (see REJECTION_CAP)
         }
     }
 };
@@ -372,7 +379,7 @@ struct BlinnPhongPdf : PDF {  // pdf.rs:145-210
                 rng.pair(P_BRDF, 1, k, r1, xi2);
                 Vec3 direction = onb_reflected.local(cosine_direction_exponent(exponent, r1, xi2));
                 if (dot(direction, onb_normal.axis[2]) > 0.0) return direction;
-                if (k > 4096) return direction;
+                if (k + 1 >= REJECTION_CAP) return direction;
             }
         }
         return onb_normal.local(cosine_direction(u01(w[1]), u01(w[2])));

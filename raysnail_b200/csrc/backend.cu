@@ -479,7 +479,7 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
             ++launches;
             for (int b = 0; b < p->depth; ++b) {
                 tm.mark(1);
-                launch_extend(ctx->scene, fp, ctx->ws, b, ctx->extend_mode, ctx->bvh_width == 4, ctx->extend_grid, stream);
+                launch_extend(ctx->scene, fp, ctx->ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, stream);
                 tm.mark(2);
                 launch_shade(ctx->scene, fp, ctx->ws, b, ctx->shade_generic ? 1 : 0, ctx->shade_grid, nullptr, stream);
                 launches += 2;
@@ -895,7 +895,7 @@ static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     CK(cudaMemsetAsync(ctx->ws.ctr, 0, sizeof(WaveCounters), 0));
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), 0));
     launch_raygen(fp, ctx->ws, 0);
-    launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->bvh_width == 4, ctx->extend_grid, 0);
+    launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->bvh_width == 4, 0, ctx->extend_grid, 0);  // probes: misses stay visible to shade
     if (shade) launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic ? 1 : 0, ctx->shade_grid, &dbg, 0);
     else launch_probe_primary(ctx->scene, fp, ctx->ws, dbg, 0);
     CK(cudaGetLastError());

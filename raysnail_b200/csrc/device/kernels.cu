@@ -375,7 +375,8 @@ __device__ __forceinline__ int resolve_mixed(const DScene& S, int m, const RngCt
 
 template <int MODE, bool WIDE>
 __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
-                                                                                     const __grid_constant__ WaveState ws, const int bounce) {
+                                                                                     const __grid_constant__ WaveState ws, const int bounce,
+                                                                                     const int miss_in_extend) {
     const uint32_t n = ws.ctr->n_rays[bounce];
     const PathBuf& in = ws.buf[bounce & 1];
     uint32_t* head = &ws.ctr->extend_head[bounce];
@@ -411,12 +412,23 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                 h.matinfo = (uint32_t)leaf | ((uint32_t)top << 16);
                 cls = 1 + S.materials[leaf].type;
                 if (S.root_kind[best.root] == ROOT_GENERIC) ws.hit_end[i] = best.end_then;
+                ws.hit[i] = h;
+            } else if (miss_in_extend) {
+                // a miss ends the path with `world.background(ray)` (camera.rs:253-254): finish it
+                // here instead of sending it through a queue to the shade kernel
+                const float4 bg = background(S, ray.d);
+                float tr, tg;
+                unpack_f2(in.d[i].y, tr, tg);
+                const uint4 e = in.e[i];
+                ws.contrib[e.y] = make_float4(tr * bg.x, tg * bg.y, __uint_as_float(e.x) * bg.z, 0.f);
+                cls = -1;
+            } else {
+                ws.hit[i] = h;
             }
-            ws.hit[i] = h;
         }
         // material-coherent bucketing
-        const uint32_t active = __ballot_sync(0xffffffffu, live);
-        if (live) {
+        const uint32_t active = __ballot_sync(0xffffffffu, live && cls >= 0);
+        if (live && cls >= 0) {
             const uint32_t peers = __match_any_sync(active, cls);
             const uint32_t leader = __ffs(peers) - 1;
             uint32_t qbase = 0;
@@ -894,8 +906,9 @@ static const void* extend_fn_for(int mode, int wide) {
     if (wide) return mode == 0 ? extend_fn<0, true>() : (mode == 1 ? extend_fn<1, true>() : extend_fn<2, true>());
     return mode == 0 ? extend_fn<0, false>() : (mode == 1 ? extend_fn<1, false>() : extend_fn<2, false>());
 }
-void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int grid, cudaStream_t s) {
-    void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce};
+void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int miss_in_extend, int grid,
+                   cudaStream_t s) {
+    void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
     cudaLaunchKernel(extend_fn_for(mode, wide), dim3(grid), dim3(RS_BLOCK), args, 0, s);
 }
 void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int grid, const DebugOut* dbg, cudaStream_t s) {

@@ -86,7 +86,8 @@ struct DebugOut {  // all device pointers, indexed by pixel; any may be null
 
 // launchers (kernels.cu)
 void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s);
-void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int grid, cudaStream_t s);
+void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int miss_in_extend, int grid,
+                   cudaStream_t s);
 void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int grid, const DebugOut* dbg, cudaStream_t s);
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s);
 void launch_accumulate(const FrameParams& fp, const WaveState& ws, float4* accum, cudaStream_t s);
