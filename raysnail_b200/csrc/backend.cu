@@ -627,6 +627,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
         if (two && (n.child1 < 0 || n.child1 >= i)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "child1 must precede its parent");
         if (n.type == RS_NODE_MEDIUM && n.material < 0) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "medium needs its isotropic material");
         if (n.type == RS_NODE_RECT && (n.rect_axis < 0 || n.rect_axis > 2)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad rect axis");
+        // device copy only: 1/r for `(p - c) / r` = `(p - c) * (1.0 / r)` (sphere.rs:56-58, vec3.rs:486-500);
+        // the same IEEE quotient the device would compute per hit
+        if (n.type == RS_NODE_SPHERE) n.p[7] = 1.0 / n.p[3];
         if (n.type == RS_NODE_TRANSFORM) {
             if (n.first_xform < 0 || n.n_xform < 0 || n.first_xform + n.n_xform > s->n_xforms) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "transform stack out of range");
             // pre-multiply the stack (transform.rs:133-157): forward applies entry 0 first,
@@ -754,7 +757,19 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if ((rc = upload(ctx, ctx->d_tri_material, s->tri_material, (size_t)s->n_tris)) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_lights, s->lights, (size_t)s->n_lights)) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_materials, s->materials, (size_t)s->n_materials)) != RS_OK) return rc;
-    if ((rc = upload(ctx, ctx->d_textures, s->textures, (size_t)s->n_textures)) != RS_OK) return rc;
+    {
+        // device copy only: `reserved` = 1 when a lookup in this texture reads (u, v) — an image,
+        // or a checker that (transitively) nests one (checker.rs is generic over its children)
+        std::vector<rs_texture> tex(s->textures, s->textures + s->n_textures);
+        for (auto& t : tex) t.reserved = t.type == RS_TEX_IMAGE ? 1 : 0;
+        for (int pass = 0; pass < 16; ++pass) {
+            bool changed = false;
+            for (auto& t : tex)
+                if (t.type == RS_TEX_CHECKER && !t.reserved && (tex[t.odd].reserved || tex[t.even].reserved)) { t.reserved = 1; changed = true; }
+            if (!changed) break;
+        }
+        if ((rc = upload(ctx, ctx->d_textures, tex.data(), tex.size())) != RS_OK) return rc;
+    }
     if ((rc = upload(ctx, ctx->d_texels, s->texels, (size_t)s->n_texel_bytes)) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_perm, s->perlin_perm, (size_t)s->n_perlin_perm)) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_values, s->perlin_values, (size_t)s->n_perlin_values)) != RS_OK) return rc;

@@ -84,6 +84,22 @@ __device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
     return base + __popc(mask & ((1u << lane_id()) - 1u));
 }
 
+// Asynchronous global->shared staging (LDGSTS, 16 bytes per lane, L2 only).  The persistent
+// kernels know the NEXT batch of work items while they process the current one, so its path /
+// hit records are copied into shared memory in the background and the DRAM latency of the
+// queue reads is off the critical path (the kernels were long-scoreboard bound without it).
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+
+#define RS_WARPS (RS_BLOCK / 32)
+// staging slots per lane of shade: the 5 path elements + the hit record; double buffered
+#define RS_SHADE_STAGE 6
+#define RS_SHADE_SMEM (RS_WARPS * 2 * RS_SHADE_STAGE * 32 * 16)
+
 // =============================================================================================
 // raygen
 // =============================================================================================
@@ -476,6 +492,13 @@ __device__ __forceinline__ double phong_highlight(V3 dir_to_light, V3 ray_dir, V
     return specular * factor;
 }
 
+// The lobe samplers of ReflectionPdf / BlinnPhongPdf (pdf.rs:124-140, 195-209) loop until the
+// sample lies above the surface; when a ray hits the BACK of a shading normal (triangle normals
+// are not face-forwarded, triangle_mesh.rs:115-116) the lobe points below it and the reference
+// spins (forever if the lobe is entirely below).  Oracle and GPU give up after this many
+// candidates and keep the last one (oracle/oracle.cpp REJECTION_CAP).
+#define RS_REJECTION_CAP 256u
+
 struct PdfState {  // the `Box<dyn PDF>` of a ScatterRecord, flattened
     int kind;      // 0 Cosine, 1 Reflection, 2 BlinnPhong, 3 Sphere
     V3 n_w;        // onb_normal.axis[2]
@@ -488,18 +511,18 @@ __device__ __forceinline__ double pdf_value(const PdfState& P, V3 dir) {
     switch (P.kind) {
         case 0: {  // pdf.rs:36-43
             double c = dot(dir, P.n_w);
-            return c < 0.0 ? 0.0 : c / RS_PI;
+            return c < 0.0 ? 0.0 : c * RS_INV_PI;
         }
         case 1: {  // pdf.rs:114-122
-            double v = dot(dir, P.r_w) / RS_PI;
+            double v = dot(dir, P.r_w) * RS_INV_PI;
             return v < 0.0 ? 0.0 : v;
         }
         case 2: {  // pdf.rs:177-192
             double cosine = dot(dir, P.n_w);
-            V3 random_normal = unit((-P.r_in) + dir);
+            V3 random_normal = unit_fast((-P.r_in) + dir);
             double cosine_specular = fmax(dot(random_normal, P.n_w), 0.0);
             double normal_pdf = (P.exponent + 1.0) / (2.0 * RS_PI) * pow(cosine_specular, P.exponent);
-            return fmax(cosine / RS_PI, 0.0) * (1.0 - P.k_specular) + normal_pdf / (4.0 * dot(P.r_in * -1.0, random_normal)) * P.k_specular;
+            return fmax(cosine * RS_INV_PI, 0.0) * (1.0 - P.k_specular) + normal_pdf / (4.0 * dot(P.r_in * -1.0, random_normal)) * P.k_specular;
         }
         default: return 1.0 / (4.0 * RS_PI);  // pdf.rs:226-228
     }
@@ -509,13 +532,13 @@ __device__ __noinline__ V3 pdf_generate(const PdfState& P, V3 normal, V3 reflect
     switch (P.kind) {
         case 0: {  // pdf.rs:45-47
             uint4 w = rng_words(rng, P_BRDF, 0);
-            ONB onb = onb_build(normal);
+            ONB onb = onb_build_fast(normal);
             return onb_local(onb, cosine_direction(u01(w.x), u01(w.y)));
         }
         case 1: {  // pdf.rs:124-140
-            ONB onb = onb_build(reflected);
+            ONB onb = onb_build_fast(reflected);
             V3 dir = v3(0.0, 0.0, 0.0);
-            for (uint32_t k = 0; k < 4096; ++k) {
+            for (uint32_t k = 0; k < RS_REJECTION_CAP; ++k) {
                 double r1, xi2;
                 rng_pair(rng, P_BRDF, 0, k, r1, xi2);
                 dir = onb_local(onb, cosine_direction_exponent(P.exponent, r1, xi2));
@@ -526,9 +549,9 @@ __device__ __noinline__ V3 pdf_generate(const PdfState& P, V3 normal, V3 reflect
         case 2: {  // pdf.rs:195-209
             uint4 w = rng_words(rng, P_BRDF, 0);
             if (u01(w.x) < P.k_specular) {
-                ONB onb = onb_build(reflected);
+                ONB onb = onb_build_fast(reflected);
                 V3 dir = v3(0.0, 0.0, 0.0);
-                for (uint32_t k = 0; k < 4096; ++k) {
+                for (uint32_t k = 0; k < RS_REJECTION_CAP; ++k) {
                     double r1, xi2;
                     rng_pair(rng, P_BRDF, 1, k, r1, xi2);
                     dir = onb_local(onb, cosine_direction_exponent(P.exponent, r1, xi2));
@@ -536,16 +559,15 @@ __device__ __noinline__ V3 pdf_generate(const PdfState& P, V3 normal, V3 reflect
                 }
                 return dir;
             }
-            ONB onb = onb_build(normal);
+            ONB onb = onb_build_fast(normal);
             return onb_local(onb, cosine_direction(u01(w.y), u01(w.z)));
         }
         default: {  // vec3.rs:91-96
             uint4 w = rng_words(rng, P_BRDF, 0);
-            double a = u01(w.x) * (2.0 * RS_PI);
             double z = -1.0 + u01(w.y) * 2.0;
             double r = sqrt(1.0 - z * z);
             double s, c;
-            sincos(a, &s, &c);
+            sincospi(2.0 * u01(w.x), &s, &c);  // a = U(0, 2 pi)
             return v3(r * c, r * s, z);
         }
     }
@@ -559,32 +581,95 @@ template <bool GENERIC>
 __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS_TUNE_SHADE_LEAN) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                             const __grid_constant__ WaveState ws, const int bounce,
                                                             const __grid_constant__ DebugOut dbg, const int has_dbg) {
+    extern __shared__ __align__(16) uint4 s_stage[];
     const PathBuf& in = ws.buf[bounce & 1];
     const PathBuf& out = ws.buf[(bounce + 1) & 1];
     const uint32_t* class_count = ws.ctr->class_count[bounce];
     uint32_t* head = &ws.ctr->shade_head[bounce];
     uint32_t* out_count = &ws.ctr->n_rays[bounce + 1];
     const bool last_bounce = bounce + 1 >= fp.depth;
+    const uint32_t lane = lane_id();
+    uint4* const stage = s_stage + (size_t)(threadIdx.x >> 5) * (2 * RS_SHADE_STAGE * 32) + lane;
 
     // virtual index space: each class padded to a multiple of 32 so a warp never mixes classes
-    uint32_t cls_begin[RS_NUM_CLASSES + 1];
+    uint32_t cls_count[RS_NUM_CLASSES], cls_begin[RS_NUM_CLASSES + 1];
     cls_begin[0] = 0;
 #pragma unroll
-    for (int c = 0; c < RS_NUM_CLASSES; ++c) cls_begin[c + 1] = cls_begin[c] + ((class_count[c] + 31u) & ~31u);
+    for (int c = 0; c < RS_NUM_CLASSES; ++c) {
+        cls_count[c] = class_count[c];
+        cls_begin[c + 1] = cls_begin[c] + ((cls_count[c] + 31u) & ~31u);
+    }
     const uint32_t total = cls_begin[RS_NUM_CLASSES];
 
-    uint32_t next_base = 0;
-    if (lane_id() == 0) next_base = atomicAdd(head, 32u);
-    while (true) {
-        const uint32_t base = __shfl_sync(0xffffffffu, next_base, 0);
-        if (base >= total) break;
-        if (lane_id() == 0) next_base = atomicAdd(head, 32u);
-        int cls = 0;
+    // batch -> (class, this lane's queue entry); the table stays in registers (constant indices)
+    auto lookup = [&](uint32_t base, int& cls, bool& live, uint32_t& idx) {
+        cls = 0;
+        uint32_t cb = 0, cn = cls_count[0];
 #pragma unroll
         for (int c = 1; c < RS_NUM_CLASSES; ++c)
-            if (base >= cls_begin[c]) cls = c;
-        const uint32_t qi = base - cls_begin[cls] + lane_id();
-        const bool live = qi < class_count[cls];
+            if (base >= cls_begin[c]) { cls = c; cb = cls_begin[c]; cn = cls_count[c]; }
+        const uint32_t qi = base - cb + lane;
+        live = base < total && qi < cn;
+        idx = 0;
+        if (live) idx = ws.class_queue[(size_t)cls * ws.capacity + qi];
+    };
+    auto stage_item = [&](int buf, uint32_t i) {
+        uint4* s = stage + buf * (RS_SHADE_STAGE * 32);
+        cp_async16(s, in.a + i);
+        cp_async16(s + 32, in.b + i);
+        cp_async16(s + 64, in.c + i);
+        cp_async16(s + 96, in.d + i);
+        cp_async16(s + 128, in.e + i);
+        cp_async16(s + 160, ws.hit + i);
+    };
+
+    // Lean scenes (STAGED): three-deep software pipeline over the batches a warp fetches (one
+    // atomicAdd each):
+    //   batch k   : records already staged in shared memory -> shade
+    //   batch k+1 : queue entry loaded one iteration ago -> issue the cp.async of its records
+    //   batch k+2 : cursor value arrives now -> issue the load of its queue entry
+    // Generic scenes keep the plain loads: their kernel is register-bound (expression-tree
+    // interpreter) and the extra pipeline state costs more in spills than the latency it hides
+    // (measured on the Cornell box).
+    constexpr bool STAGED = !GENERIC;
+    uint32_t pend = 0, base0 = 0, base1 = 0;
+    int cls0 = 0, cls1 = 0;
+    bool live0 = false, live1 = false;
+    uint32_t idx0 = 0, idx1 = 0;
+    int buf = 0;
+    if constexpr (STAGED) {
+        if (lane == 0) {
+            base0 = atomicAdd(head, 32u);
+            base1 = atomicAdd(head, 32u);
+            pend = atomicAdd(head, 32u);
+        }
+        base0 = __shfl_sync(0xffffffffu, base0, 0);
+        base1 = __shfl_sync(0xffffffffu, base1, 0);
+        lookup(base0, cls0, live0, idx0);
+        if (live0) stage_item(0, idx0);
+        cp_async_commit();
+        lookup(base1, cls1, live1, idx1);
+    } else {
+        if (lane == 0) pend = atomicAdd(head, 32u);
+    }
+    while (true) {
+        int cls;
+        bool live;
+        uint32_t i;
+        uint32_t base2 = 0;
+        if constexpr (STAGED) {
+            if (base0 >= total) break;
+            base2 = __shfl_sync(0xffffffffu, pend, 0);
+            if (lane == 0) pend = atomicAdd(head, 32u);
+            cls = cls0;
+            live = live0;
+            i = idx0;
+        } else {
+            base0 = __shfl_sync(0xffffffffu, pend, 0);
+            if (base0 >= total) break;
+            if (lane == 0) pend = atomicAdd(head, 32u);
+            lookup(base0, cls, live, i);
+        }
 
         // Lambertian / Dielectric / Isotropic / BlinnPhong always scatter: their slot in the output
         // queue can be reserved before the shading math, so the atomic's latency is hidden;
@@ -595,14 +680,42 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
         uint32_t pos = 0, early_base = 0;
         const uint32_t early_mask = (always && !never) ? __ballot_sync(0xffffffffu, live) : 0u;
         const uint32_t early_leader = early_mask ? (uint32_t)(__ffs(early_mask) - 1) : 0u;
-        if (early_mask && lane_id() == early_leader) early_base = atomicAdd(out_count, __popc(early_mask));
+        if (early_mask && lane == early_leader) early_base = atomicAdd(out_count, __popc(early_mask));
+
+        const uint4* s = stage + buf * (RS_SHADE_STAGE * 32);
+        int cls2 = 0;
+        bool live2 = false;
+        uint32_t idx2 = 0;
+        if constexpr (STAGED) {
+            cp_async_wait_all();
+            if (live1) stage_item(buf ^ 1, idx1);
+            cp_async_commit();
+            lookup(base2, cls2, live2, idx2);
+        }
 
         bool survive = false;
         PathRec p;
         if (live) {
-            const uint32_t i = ws.class_queue[(size_t)cls * ws.capacity + qi];
-            load_path(in, i, p);
-            const HitA ha = ws.hit[i];
+            HitA ha;
+            if constexpr (STAGED) {
+                const double2 a = *reinterpret_cast<const double2*>(s), b = *reinterpret_cast<const double2*>(s + 32);
+                const double2 c = *reinterpret_cast<const double2*>(s + 64), d = *reinterpret_cast<const double2*>(s + 96);
+                const uint4 e = s[128], hh = s[160];
+                p.ray.o = v3(a.x, a.y, b.x);
+                p.ray.time = b.y;
+                p.ray.d = v3(c.x, c.y, d.x);
+                unpack_f2(d.y, p.T.x, p.T.y);
+                p.T.z = __uint_as_float(e.x);
+                p.slot = e.y;
+                p.pixel = e.z;
+                p.sample = e.w;
+                ha.t = __hiloint2double((int)hh.y, (int)hh.x);
+                ha.root = (int)hh.z;
+                ha.matinfo = hh.w;
+            } else {
+                load_path(in, i, p);
+                ha = ws.hit[i];
+            }
             RngCtx rng;
             rng.key = fp.key;
             rng.pixel = p.pixel;
@@ -709,15 +822,15 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
                     kind = 2;
                     w_r = (double)col.x; w_g = (double)col.y; w_b = (double)col.z;
                 } else if (scattered) {
-                    P.n_w = unit(h.normal);
+                    P.n_w = unit_fast(h.normal);
                     P.r_in = p.ray.d;
-                    P.r_w = (P.kind == 1 || P.kind == 2) ? unit(reflected) : v3(0, 0, 0);
+                    P.r_w = (P.kind == 1 || P.kind == 2) ? unit_fast(reflected) : v3(0, 0, 0);
                     double light_multi = 1.0, pdf_val;
                     uint4 w = rng_words(rng, P_SCATTER, 0);
                     if (u01(w.x) < 0.5) {  // camera.rs:198-213
                         kind = 3;
                         pdf_val = 0.3183098861837907;
-                        const int light_node = S.lights[w.y % (uint32_t)S.n_lights];  // list.rs:49-52
+                        const int light_node = S.lights[S.n_lights == 1 ? 0u : w.y % (uint32_t)S.n_lights];  // list.rs:49-52
                         V3 to_light;
                         if (GENERIC) {
                             to_light = TreeTop::random(S, light_node, h.point, rng);
@@ -725,7 +838,7 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
                             const rs_node& ln = S.nodes[light_node];
                             to_light = ln.type == RS_NODE_SPHERE ? sphere_random(ln, h.point, rng) : rect_random(ln, h.point, rng);
                         }
-                        V3 dir_to_light = unit(to_light);
+                        V3 dir_to_light = unit_fast(to_light);
                         if (smat.phong_factor > 0.0)
                             light_multi += phong_highlight(-dir_to_light, p.ray.d, h.normal, smat.phong_exponent, smat.phong_factor);
                         next_o = ray_at(p.ray, h.t1 - 0.0002);
@@ -737,8 +850,9 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
                         next_o = h.point;
                     }
                     if (pdf_val <= 0.0 || pdf_val != pdf_val) pdf_val = 1e-5;  // camera.rs:236-238
-                    const double scattering_pdf_val = pdf_value(P, next_d);
-                    const double mult = light_multi * (scattering_pdf_val / pdf_val);
+                    // BRDF branch: the two values are the same number, x / x == 1 exactly
+                    const double ratio = (kind == 4 && pdf_val > 0.0 && pdf_val < RS_F64_MAX) ? 1.0 : pdf_value(P, next_d) / pdf_val;
+                    const double mult = light_multi * ratio;
                     w_r = (double)col.x * mult; w_g = (double)col.y * mult; w_b = (double)col.z * mult;
                 }
             }
@@ -765,9 +879,14 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
                 p.T.x *= (float)w_r; p.T.y *= (float)w_g; p.T.z *= (float)w_b;
             }
         }
-        if (early_mask) pos = __shfl_sync(0xffffffffu, early_base, early_leader) + __popc(early_mask & ((1u << lane_id()) - 1u));
+        if (early_mask) pos = __shfl_sync(0xffffffffu, early_base, early_leader) + __popc(early_mask & ((1u << lane) - 1u));
         else if (!never) pos = warp_append(out_count, survive);
         if (survive) store_path(out, pos, p);
+        if constexpr (STAGED) {  // rotate the pipeline
+            base0 = base1; cls0 = cls1; live0 = live1; idx0 = idx1;
+            base1 = base2; cls1 = cls2; live1 = live2; idx1 = idx2;
+            buf ^= 1;
+        }
     }
 }
 
@@ -915,7 +1034,7 @@ void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, i
     DebugOut d = {};
     if (dbg) d = *dbg;
     if (generic) shade_kernel<true><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else shade_kernel<false><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else shade_kernel<false><<<grid, RS_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
 }
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s) {
     probe_primary_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(S, fp, ws, dbg);
@@ -942,8 +1061,9 @@ int extend_blocks_per_sm(int mode, int wide) {
 }
 int shade_blocks_per_sm(int generic) {
     int n = 0;
+    cudaFuncSetAttribute(shade_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, RS_SHADE_SMEM);
     if (generic) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<true>, RS_BLOCK, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<false>, RS_BLOCK, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<false>, RS_BLOCK, RS_SHADE_SMEM);
     return n > 0 ? n : 1;
 }
 

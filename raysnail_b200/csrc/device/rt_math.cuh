@@ -14,6 +14,7 @@ namespace rsd {
 
 #define RS_PI 3.14159265358979323846
 #define RS_F64_MAX 1.7976931348623157e308
+#define RS_INV_PI 0.31830988618379067154
 
 struct V3 {
     double x, y, z;
@@ -32,6 +33,10 @@ __device__ __forceinline__ V3 cross(V3 a, V3 b) { return v3(a.y * b.z - a.z * b.
 // vec3.rs:486-500: `v / s` is `v * (1/s)`
 __device__ __forceinline__ V3 vdiv(V3 a, double s) { return a * (1.0 / s); }
 __device__ __forceinline__ V3 unit(V3 a) { return vdiv(a, length(a)); }
+// Shade-side variants (scatter directions / weights are compared with the reference at 1e-5,
+// not bit for bit): one rsqrt instead of sqrt + reciprocal.  Never used where an object id or a
+// primary ray is decided (raygen, extend).
+__device__ __forceinline__ V3 unit_fast(V3 a) { return a * rsqrt(length_squared(a)); }
 __device__ __forceinline__ double comp(V3 a, int i) { return i == 0 ? a.x : (i == 1 ? a.y : a.z); }
 __device__ __forceinline__ void set_comp(V3& a, int i, double v) { if (i == 0) a.x = v; else if (i == 1) a.y = v; else a.z = v; }
 
@@ -52,6 +57,15 @@ __device__ __forceinline__ ONB onb_build(V3 n) {
     V3 uc = cross(v3(0.0, 1.0, 0.0), o.w);
     if (length_squared(uc) < 0.00000001) o.u = unit(cross(v3(1.0, 0.0, 0.0), o.w));
     else o.u = unit(uc);
+    o.v = cross(o.w, o.u);
+    return o;
+}
+__device__ __forceinline__ ONB onb_build_fast(V3 n) {  // shade only, see unit_fast
+    ONB o;
+    o.w = unit_fast(n);
+    V3 uc = cross(v3(0.0, 1.0, 0.0), o.w);
+    if (length_squared(uc) < 0.00000001) o.u = unit_fast(cross(v3(1.0, 0.0, 0.0), o.w));
+    else o.u = unit_fast(uc);
     o.v = cross(o.w, o.u);
     return o;
 }
@@ -97,18 +111,16 @@ __device__ __forceinline__ void rng_pair(const RngCtx& r, uint32_t purpose, uint
 // vec3.rs:100-111
 __device__ __forceinline__ V3 cosine_direction(double r1, double r2) {
     double q2 = sqrt(r2);
-    double phi = 2.0 * RS_PI * r1;
     double s, c;
-    sincos(phi, &s, &c);
+    sincospi(2.0 * r1, &s, &c);  // phi = 2 pi r1; sincospi reduces the argument exactly
     return v3(c * q2, s * q2, sqrt(1.0 - r2));
 }
 // vec3.rs:115-126
 __device__ __forceinline__ V3 cosine_direction_exponent(double exponent, double r1, double xi2) {
     double r2 = pow(xi2, 1.0 / (exponent + 1.0));
     double sin_theta = sqrt(1.0 - r2 * r2);
-    double phi = 2.0 * RS_PI * r1;
     double s, c;
-    sincos(phi, &s, &c);
+    sincospi(2.0 * r1, &s, &c);  // phi = 2 pi r1
     return v3(c * sin_theta, s * sin_theta, r2);
 }
 

@@ -150,7 +150,7 @@ __device__ __forceinline__ void sphere_uv(V3 center, V3 point, double& u, double
 __device__ __forceinline__ void sphere_record(const double* p, int material, const Ray& ray, double t1, double t2, bool want_uv, HitRec& h) {
     V3 c = v3(p[0], p[1], p[2]);
     h.point = ray_at(ray, t1);
-    V3 n = vdiv(h.point - c, p[3]);
+    V3 n = (h.point - c) * p[7];  // p[7] = 1.0 / r, filled in at upload (vec3.rs:486-500: v / s = v * (1/s))
     h.outside = dot(ray.d, n) < 0.0;
     h.normal = h.outside ? n : -n;
     h.material = material;
@@ -307,7 +307,7 @@ __device__ __forceinline__ void triangle_record(const DScene& S, int tri, const 
 // sphere.rs:149-164: quarter disk of radius 1 about the centre
 __device__ __forceinline__ V3 sphere_random(const rs_node& n, V3 origin, const RngCtx& rng) {
     V3 c = v3(n.p[0], n.p[1], n.p[2]);
-    ONB uvw = onb_build(c - origin);
+    ONB uvw = onb_build_fast(c - origin);
     for (uint32_t k = 0;; ++k) {
         double a, b;
         rng_pair(rng, P_LIGHT, 0, k, a, b);
@@ -527,9 +527,14 @@ static __device__ __noinline__ float4 texture_color(const DScene& S, int ti, dou
     for (int guard = 0; guard < 16; ++guard) {
         const rs_texture& t = S.textures[ti];
         if (t.type == RS_TEX_SOLID) return make_float4(t.color[0], t.color[1], t.color[2], t.color[3]);
-        if (t.type == RS_TEX_CHECKER) {  // checker.rs:22-29
-            double value = sin(t.scale * p.x) * sin(t.scale * p.y) * sin(t.scale * p.z);
-            ti = value < 0.0 ? t.odd : t.even;
+        if (t.type == RS_TEX_CHECKER) {  // checker.rs:22-29: sign of sin(s x) sin(s y) sin(s z)
+            // only the sign is used: sin(a) < 0 <=> floor(a / pi) is odd, and the product is
+            // negative iff an odd number of factors is; a factor of exactly 0 makes it `even`
+            const double ax = t.scale * p.x, ay = t.scale * p.y, az = t.scale * p.z;
+            const double inv_pi = 0.31830988618379067154;
+            const long long par = __double2ll_rd(ax * inv_pi) ^ __double2ll_rd(ay * inv_pi) ^ __double2ll_rd(az * inv_pi);
+            const bool negative = (par & 1) && ax != 0.0 && ay != 0.0 && az != 0.0;
+            ti = negative ? t.odd : t.even;
             continue;
         }
         if (t.type == RS_TEX_IMAGE) {  // image.rs:36-49
@@ -563,9 +568,9 @@ static __device__ __noinline__ float4 texture_color(const DScene& S, int ti, dou
 }
 
 __device__ __forceinline__ bool texture_needs_uv(const DScene& S, int ti) {
-    // only image lookups read (u, v); a checker may nest one
-    const rs_texture& t = S.textures[ti];
-    return t.type == RS_TEX_IMAGE || t.type == RS_TEX_CHECKER;
+    // only image lookups read (u, v); a checker may nest one: resolved at upload into the
+    // `reserved` word of the device copy
+    return S.textures[ti].reserved != 0;
 }
 
 // color.rs:50-58 + world background closures
