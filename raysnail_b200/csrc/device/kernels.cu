@@ -74,12 +74,26 @@ __device__ __forceinline__ void load_ray_only(const PathBuf& B, uint32_t i, Ray&
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
+// atomicAdd whose result is consumed LATER.  ptxas rewrites an atomic add on a warp-uniform
+// address into its own warp-aggregated form (elect + ATOMG + SHFL) — also for inline PTX and
+// even when a single lane executes it — and that SHFL waits for the atomic on the spot, which
+// exposes the full L2 round trip (the top stall of shade and extend in the first profiles).
+// `lane_zero` is a per-lane value that is always 0 at run time but that the compiler cannot
+// prove uniform, so the address looks divergent and the instruction stays as written: the
+// latency then overlaps with the work between the atomic and the first use of its result.
+__device__ __forceinline__ uint32_t atomic_add_async(uint32_t* p, uint32_t v, uint32_t lane_zero) {
+    uint32_t old;
+    asm volatile("atom.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p + lane_zero), "r"(v) : "memory");
+    return old;
+}
+#define RS_LANE_ZERO(ws) (lane_id() & ((ws).capacity >> 31))  // capacity < 2^31 always
+
 // warp-aggregated append: returns this lane's position; `counter` is bumped once per warp
-__device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
+__device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred, uint32_t lane_zero) {
     uint32_t mask = __ballot_sync(0xffffffffu, pred);
     if (mask == 0) return 0;
     uint32_t leader = __ffs(mask) - 1, base = 0;
-    if (lane_id() == leader) base = atomicAdd(counter, __popc(mask));
+    if (lane_id() == leader) base = atomic_add_async(counter, __popc(mask), lane_zero);
     base = __shfl_sync(0xffffffffu, base, leader);
     return base + __popc(mask & ((1u << lane_id()) - 1u));
 }
@@ -92,13 +106,19 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
 }
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
 #define RS_WARPS (RS_BLOCK / 32)
 // staging slots per lane of shade: the 5 path elements + the hit record; double buffered
 #define RS_SHADE_STAGE 6
-#define RS_SHADE_SMEM (RS_WARPS * 2 * RS_SHADE_STAGE * 32 * 16)
+// per warp: two record buffers + two 32-entry queue-index buffers
+#define RS_SHADE_WARP_SMEM (2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 4)
+#define RS_SHADE_SMEM (RS_WARPS * RS_SHADE_WARP_SMEM)
 
 // =============================================================================================
 // raygen
@@ -170,7 +190,7 @@ __global__ void __launch_bounds__(RS_BLOCK) raygen_kernel(const __grid_constant_
                 p.sample = rng.sample;
             }
         }
-        uint32_t pos = warp_append(&ws.ctr->n_rays[0], live);
+        uint32_t pos = warp_append(&ws.ctr->n_rays[0], live, RS_LANE_ZERO(ws));
         if (live) store_path(ws.buf[0], pos, p);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_samples, (unsigned long long)total);
@@ -393,21 +413,27 @@ template <int MODE, bool WIDE>
 __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                                                      const __grid_constant__ WaveState ws, const int bounce,
                                                                                      const int miss_in_extend) {
-    const uint32_t n = ws.ctr->n_rays[bounce];
+    // virtual index space: [0, nf32) = the front stack padded to a multiple of 32 (so that no warp
+    // mixes the two kinds of rays), [nf32, nf32 + nb) = the back stack, top first
+    const uint32_t nf = ws.ctr->n_rays[bounce], nb = ws.ctr->n_back[bounce];
+    const uint32_t nf32 = (nf + 31u) & ~31u;
+    const uint32_t n = nf32 + nb;
+    const uint32_t lane_zero = RS_LANE_ZERO(ws);
     const PathBuf& in = ws.buf[bounce & 1];
     uint32_t* head = &ws.ctr->extend_head[bounce];
     uint32_t* class_count = ws.ctr->class_count[bounce];
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_segments, (unsigned long long)n);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_segments, (unsigned long long)(nf + nb));
     // the cursor bump for the NEXT batch is issued before the current batch is processed, so the
     // atomic's round trip to L2 overlaps with the traversal instead of heading every batch
-    uint32_t next_base = 0;
-    if (lane_id() == 0) next_base = atomicAdd(head, 32u);
+    uint32_t pend = 0;
+    if (lane_id() == 0) pend = atomic_add_async(head, 32u, lane_zero);
     while (true) {
-        const uint32_t base = __shfl_sync(0xffffffffu, next_base, 0);
+        const uint32_t base = __shfl_sync(0xffffffffu, pend, 0);
         if (base >= n) break;
-        if (lane_id() == 0) next_base = atomicAdd(head, 32u);
-        const uint32_t i = base + lane_id();
-        const bool live = i < n;
+        if (lane_id() == 0) pend = atomic_add_async(head, 32u, lane_zero);
+        const uint32_t v = base + lane_id();
+        const bool live = v < nf32 ? v < nf : v < n;
+        const uint32_t i = v < nf32 ? v : ws.capacity - 1u - (v - nf32);
         int cls = -1;
         if (live) {
             Ray ray;
@@ -448,7 +474,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
             const uint32_t peers = __match_any_sync(active, cls);
             const uint32_t leader = __ffs(peers) - 1;
             uint32_t qbase = 0;
-            if (lane_id() == leader) qbase = atomicAdd(&class_count[cls], __popc(peers));
+            if (lane_id() == leader) qbase = atomic_add_async(&class_count[cls], __popc(peers), lane_zero);
             qbase = __shfl_sync(peers, qbase, leader);
             const uint32_t rank = __popc(peers & ((1u << lane_id()) - 1u));
             ws.class_queue[(size_t)cls * ws.capacity + qbase + rank] = i;
@@ -586,10 +612,14 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
     const PathBuf& out = ws.buf[(bounce + 1) & 1];
     const uint32_t* class_count = ws.ctr->class_count[bounce];
     uint32_t* head = &ws.ctr->shade_head[bounce];
-    uint32_t* out_count = &ws.ctr->n_rays[bounce + 1];
+    uint32_t* out_front = &ws.ctr->n_rays[bounce + 1];
+    uint32_t* out_back = &ws.ctr->n_back[bounce + 1];
     const bool last_bounce = bounce + 1 >= fp.depth;
     const uint32_t lane = lane_id();
-    uint4* const stage = s_stage + (size_t)(threadIdx.x >> 5) * (2 * RS_SHADE_STAGE * 32) + lane;
+    const uint32_t lane_zero = RS_LANE_ZERO(ws);
+    unsigned char* const warp_smem = reinterpret_cast<unsigned char*>(s_stage) + (size_t)(threadIdx.x >> 5) * RS_SHADE_WARP_SMEM;
+    uint4* const stage = reinterpret_cast<uint4*>(warp_smem) + lane;
+    uint32_t* const idxq = reinterpret_cast<uint32_t*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16) + lane;  // [2][32]
 
     // virtual index space: each class padded to a multiple of 32 so a warp never mixes classes
     uint32_t cls_count[RS_NUM_CLASSES], cls_begin[RS_NUM_CLASSES + 1];
@@ -601,8 +631,9 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
     }
     const uint32_t total = cls_begin[RS_NUM_CLASSES];
 
-    // batch -> (class, this lane's queue entry); the table stays in registers (constant indices)
-    auto lookup = [&](uint32_t base, int& cls, bool& live, uint32_t& idx) {
+    // batch -> (class, is this lane's entry real, its address in the class queue); the table stays
+    // in registers (constant indices)
+    auto classify = [&](uint32_t base, int& cls, bool& live, const uint32_t*& entry) {
         cls = 0;
         uint32_t cb = 0, cn = cls_count[0];
 #pragma unroll
@@ -610,8 +641,15 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
             if (base >= cls_begin[c]) { cls = c; cb = cls_begin[c]; cn = cls_count[c]; }
         const uint32_t qi = base - cb + lane;
         live = base < total && qi < cn;
-        idx = 0;
-        if (live) idx = ws.class_queue[(size_t)cls * ws.capacity + qi];
+        entry = ws.class_queue + ((size_t)cls * ws.capacity + qi);
+    };
+    // one atomicAdd per batch of 32, issued one batch ahead of its use
+    uint32_t pend = 0;
+    if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
+    auto next_batch = [&]() -> uint32_t {
+        const uint32_t b = __shfl_sync(0xffffffffu, pend, 0);
+        if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
+        return b;
     };
     auto stage_item = [&](int buf, uint32_t i) {
         uint4* s = stage + buf * (RS_SHADE_STAGE * 32);
@@ -624,76 +662,60 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
     };
 
     // Lean scenes (STAGED): three-deep software pipeline over the batches a warp fetches (one
-    // atomicAdd each):
-    //   batch k   : records already staged in shared memory -> shade
-    //   batch k+1 : queue entry loaded one iteration ago -> issue the cp.async of its records
-    //   batch k+2 : cursor value arrives now -> issue the load of its queue entry
+    // atomic each), entirely through cp.async so that no register is held across the latency:
+    //   batch k   : records staged in shared memory -> shade
+    //   batch k+1 : its queue entries arrived in shared memory -> issue the cp.async of its records
+    //   batch k+2 : its cursor value arrived -> issue the cp.async of its queue entries
     // Generic scenes keep the plain loads: their kernel is register-bound (expression-tree
     // interpreter) and the extra pipeline state costs more in spills than the latency it hides
     // (measured on the Cornell box).
     constexpr bool STAGED = !GENERIC;
-    uint32_t pend = 0, base0 = 0, base1 = 0;
+    uint32_t base0 = 0, base1 = 0;
     int cls0 = 0, cls1 = 0;
     bool live0 = false, live1 = false;
-    uint32_t idx0 = 0, idx1 = 0;
     int buf = 0;
     if constexpr (STAGED) {
-        if (lane == 0) {
-            base0 = atomicAdd(head, 32u);
-            base1 = atomicAdd(head, 32u);
-            pend = atomicAdd(head, 32u);
-        }
-        base0 = __shfl_sync(0xffffffffu, base0, 0);
-        base1 = __shfl_sync(0xffffffffu, base1, 0);
-        lookup(base0, cls0, live0, idx0);
-        if (live0) stage_item(0, idx0);
+        base0 = next_batch();
+        base1 = next_batch();
+        const uint32_t* entry;
+        classify(base0, cls0, live0, entry);
+        if (live0) stage_item(0, *entry);
+        classify(base1, cls1, live1, entry);
+        if (live1) cp_async4(idxq + 32, entry);
         cp_async_commit();
-        lookup(base1, cls1, live1, idx1);
-    } else {
-        if (lane == 0) pend = atomicAdd(head, 32u);
     }
     while (true) {
         int cls;
         bool live;
-        uint32_t i;
+        uint32_t i = 0;
         uint32_t base2 = 0;
         if constexpr (STAGED) {
             if (base0 >= total) break;
-            base2 = __shfl_sync(0xffffffffu, pend, 0);
-            if (lane == 0) pend = atomicAdd(head, 32u);
+            base2 = next_batch();
             cls = cls0;
             live = live0;
-            i = idx0;
         } else {
-            base0 = __shfl_sync(0xffffffffu, pend, 0);
+            base0 = next_batch();
             if (base0 >= total) break;
-            if (lane == 0) pend = atomicAdd(head, 32u);
-            lookup(base0, cls, live, i);
+            const uint32_t* entry;
+            classify(base0, cls, live, entry);
+            if (live) i = *entry;
         }
-
-        // Lambertian / Dielectric / Isotropic / BlinnPhong always scatter: their slot in the output
-        // queue can be reserved before the shading math, so the atomic's latency is hidden;
-        // miss / light never continue; Metal / DiffuseMetal may absorb and reserve afterwards.
-        const bool always = cls == 1 + RS_MAT_LAMBERTIAN || cls == 1 + RS_MAT_DIELECTRIC || cls == 1 + RS_MAT_ISOTROPIC || cls == 1 + RS_MAT_BLINN_PHONG;
-        const bool never = cls == 0 || cls == 1 + RS_MAT_DIFFUSE_LIGHT || last_bounce;
-        // issue now, consume (shfl) only when the record is stored
-        uint32_t pos = 0, early_base = 0;
-        const uint32_t early_mask = (always && !never) ? __ballot_sync(0xffffffffu, live) : 0u;
-        const uint32_t early_leader = early_mask ? (uint32_t)(__ffs(early_mask) - 1) : 0u;
-        if (early_mask && lane == early_leader) early_base = atomicAdd(out_count, __popc(early_mask));
+        const bool never = cls == 0 || cls == 1 + RS_MAT_DIFFUSE_LIGHT || last_bounce;  // miss / light never continue
 
         const uint4* s = stage + buf * (RS_SHADE_STAGE * 32);
         int cls2 = 0;
         bool live2 = false;
-        uint32_t idx2 = 0;
         if constexpr (STAGED) {
-            cp_async_wait_all();
-            if (live1) stage_item(buf ^ 1, idx1);
+            cp_async_wait_all();  // records of batch k (stage[buf]) and queue entries of k+1 (idxq[buf ^ 1])
+            if (live1) stage_item(buf ^ 1, idxq[(buf ^ 1) * 32]);
+            const uint32_t* entry;
+            classify(base2, cls2, live2, entry);
+            if (live2) cp_async4(idxq + buf * 32, entry);
             cp_async_commit();
-            lookup(base2, cls2, live2, idx2);
         }
 
-        bool survive = false;
+        bool survive = false, front = false;
         PathRec p;
         if (live) {
             HitA ha;
@@ -874,17 +896,27 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
             }
             if (kind >= 2 && !last_bounce) {
                 survive = true;
+                front = kind == 3;
                 p.ray.o = next_o;
                 p.ray.d = next_d;
                 p.T.x *= (float)w_r; p.T.y *= (float)w_g; p.T.z *= (float)w_b;
             }
         }
-        if (early_mask) pos = __shfl_sync(0xffffffffu, early_base, early_leader) + __popc(early_mask & ((1u << lane) - 1u));
-        else if (!never) pos = warp_append(out_count, survive);
-        if (survive) store_path(out, pos, p);
+        if (!never) {
+            // survivors: light-directed rays onto the front stack, the others onto the back stack
+            const uint32_t mf = __ballot_sync(0xffffffffu, survive && front), mb = __ballot_sync(0xffffffffu, survive && !front);
+            const uint32_t lf = mf ? (uint32_t)(__ffs(mf) - 1) : 0u, lb = mb ? (uint32_t)(__ffs(mb) - 1) : 0u;
+            uint32_t bf = 0, bb = 0;
+            if (mf && lane == lf) bf = atomic_add_async(out_front, __popc(mf), lane_zero);
+            if (mb && lane == lb) bb = atomic_add_async(out_back, __popc(mb), lane_zero);
+            bf = __shfl_sync(0xffffffffu, bf, lf);
+            bb = __shfl_sync(0xffffffffu, bb, lb);
+            const uint32_t lt = (1u << lane) - 1u;
+            if (survive) store_path(out, front ? bf + __popc(mf & lt) : ws.capacity - 1u - (bb + __popc(mb & lt)), p);
+        }
         if constexpr (STAGED) {  // rotate the pipeline
-            base0 = base1; cls0 = cls1; live0 = live1; idx0 = idx1;
-            base1 = base2; cls1 = cls2; live1 = live2; idx1 = idx2;
+            base0 = base1; cls0 = cls1; live0 = live1;
+            base1 = base2; cls1 = cls2; live1 = live2;
             buf ^= 1;
         }
     }

@@ -33,7 +33,13 @@ struct __align__(16) HitA {
 };
 
 struct WaveCounters {
-    uint32_t n_rays[RS_MAX_DEPTH + 1];            // live paths entering bounce b
+    // Live paths entering bounce b sit in two stacks of the path buffer: n_rays[b] records grow
+    // up from index 0 (camera rays; after a bounce: the rays sampled TOWARDS A LIGHT, camera.rs:198-213)
+    // and n_back[b] records grow down from index capacity-1 (BRDF-sampled and specular rays).
+    // Light-directed rays are mutually coherent and usually short; keeping them apart from the
+    // incoherent ones keeps the warps of extend homogeneous.
+    uint32_t n_rays[RS_MAX_DEPTH + 1];
+    uint32_t n_back[RS_MAX_DEPTH + 1];
     uint32_t class_count[RS_MAX_DEPTH][RS_NUM_CLASSES];
     uint32_t extend_head[RS_MAX_DEPTH];           // persistent-thread work cursors
     uint32_t shade_head[RS_MAX_DEPTH];
