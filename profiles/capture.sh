@@ -1,0 +1,12 @@
+#!/bin/bash
+# Round evidence on one B200: the bench line, the ncu launch list of the same command and one
+# `ncu --set full` capture of the two hot kernels (bounce 0 and bounce 1 of the second wave).
+# usage (on the GPU box): bash profiles/capture.sh r01b
+TAG=${1:-rXX}
+set -x
+python bench.py --steps 3 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err || exit 1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv \
+    python bench.py --steps 1 --warmup 1 --sqrt-spp 4 --no-cpu > gpurun_out/${TAG}_launches.log 2>&1
+ncu --set full --import-source on --clock-control none -k regex:"shade_kernel|extend_kernel" --launch-skip 16 --launch-count 4 \
+    -o gpurun_out/${TAG}_full python bench.py --steps 1 --warmup 1 --sqrt-spp 4 --no-cpu > gpurun_out/${TAG}_full.log 2>&1
+tail -1 gpurun_out/${TAG}_bench.json

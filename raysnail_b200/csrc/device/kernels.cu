@@ -113,7 +113,11 @@ __device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
-#define RS_WARPS (RS_BLOCK / 32)
+// threads per block of the lean shade kernel (the generic one uses RS_BLOCK); tunable
+#ifndef RS_TUNE_SHADE_BLOCK
+#define RS_TUNE_SHADE_BLOCK 256
+#endif
+#define RS_WARPS (RS_TUNE_SHADE_BLOCK / 32)
 // staging slots per lane of shade: the 5 path elements + the hit record; double buffered
 #define RS_SHADE_STAGE 6
 // per warp: two record buffers + two 32-entry queue-index buffers
@@ -258,7 +262,7 @@ __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); 
 // resident 256-thread blocks per SM the kernels are compiled for (register budget); tunable
 // at build time (make TUNE="-DRS_TUNE_EXTEND_LEAN=4 ...")
 #ifndef RS_TUNE_EXTEND_LEAN
-#define RS_TUNE_EXTEND_LEAN 3
+#define RS_TUNE_EXTEND_LEAN 4
 #endif
 #ifndef RS_TUNE_EXTEND_GENERIC
 #define RS_TUNE_EXTEND_GENERIC 2
@@ -604,7 +608,7 @@ __device__ __forceinline__ void dbg_store3(double* p, uint32_t i, V3 v) {
 }
 
 template <bool GENERIC>
-__global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS_TUNE_SHADE_LEAN) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+__global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS_TUNE_SHADE_LEAN) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                             const __grid_constant__ WaveState ws, const int bounce,
                                                             const __grid_constant__ DebugOut dbg, const int has_dbg) {
     extern __shared__ __align__(16) uint4 s_stage[];
@@ -622,6 +626,7 @@ __global__ void __launch_bounds__(RS_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS
     uint32_t* const idxq = reinterpret_cast<uint32_t*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16) + lane;  // [2][32]
 
     // virtual index space: each class padded to a multiple of 32 so a warp never mixes classes
+    // (the table stays in registers: a shared-memory copy measured 20% slower)
     uint32_t cls_count[RS_NUM_CLASSES], cls_begin[RS_NUM_CLASSES + 1];
     cls_begin[0] = 0;
 #pragma unroll
@@ -1066,7 +1071,7 @@ void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, i
     DebugOut d = {};
     if (dbg) d = *dbg;
     if (generic) shade_kernel<true><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else shade_kernel<false><<<grid, RS_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else shade_kernel<false><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
 }
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s) {
     probe_primary_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(S, fp, ws, dbg);
@@ -1095,7 +1100,7 @@ int shade_blocks_per_sm(int generic) {
     int n = 0;
     cudaFuncSetAttribute(shade_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, RS_SHADE_SMEM);
     if (generic) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<true>, RS_BLOCK, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<false>, RS_BLOCK, RS_SHADE_SMEM);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<false>, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM);
     return n > 0 ? n : 1;
 }
 
