@@ -99,11 +99,15 @@ def measured_peak_gbs():
 
 
 def ncu_traffic(kernel):
-    """per-launch dram bytes of the dominant kernel from the committed ncu capture, if any"""
+    """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of one launch of the dominant
+    kernel from the committed `ncu --set full` capture (profiles/traffic.json, written by
+    profiles/ncu_metrics.py): the bounce-0 launch of one full 8.29 M-path wave, i.e. the largest
+    launch — compare it with that launch's algorithmic bytes (roofline.traffic_launch), not with
+    the average over all bounces in algorithmic_bytes_per_launch."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get(kernel)
+            return float(json.load(open(p))[kernel + "_kernel"]["per_launch_bytes"][0])
         except Exception:
             return None
     return None
@@ -181,7 +185,7 @@ def run_gpu(args):
     import torch
     import torch.distributed as dist
     from raysnail_b200 import RS_FLAG_KERNEL_TIMING, Renderer, Scene, make_params
-    from raysnail_b200.distributed import reduce_accum, stratum_rows
+    from raysnail_b200.distributed import PeerImage, reduce_accum, stratum_rows
 
     world_size, rank, local_rank = env_int("WORLD_SIZE", 1), env_int("RANK", 0), env_int("LOCAL_RANK", 0)
     if not torch.cuda.is_available():
@@ -204,15 +208,28 @@ def run_gpu(args):
     r0, r1 = stratum_rows(rank, world_size, q)
     params = make_params(sqrt_spp=q, depth=depth, rows=(r0, r1), max_wave_paths=args.wave)
     params_t = make_params(sqrt_spp=q, depth=depth, rows=(r0, r1), max_wave_paths=args.wave, flags=RS_FLAG_KERNEL_TIMING)
-    accum = torch.zeros((height, width, 4), dtype=torch.float32, device=dev)
-    out = torch.empty_like(accum)
+    # N > 1: the per-rank accumulators are NVLink peer memory and the combine step is the fused
+    # reduce + finalize kernel (rs_finalize_peers); `--reduce nccl` times the library baseline
+    # (ncclReduce + rs_finalize on rank 0) instead
+    peer = PeerImage(renderer, width, height) if (world_size > 1 and args.reduce == "peer") else None
+    if peer is not None:
+        accum, out = peer.accum_t, peer.out_t
+    else:
+        accum = torch.zeros((height, width, 4), dtype=torch.float32, device=dev)
+        out = torch.empty_like(accum)
+
+    def combine(d_mask=None):
+        if peer is not None:
+            peer.reduce_finalize(q * q, True, stream, d_mask)
+            return
+        reduce_accum(accum, 0)
+        if rank == 0:
+            renderer.finalize(accum.data_ptr(), d_mask, out.data_ptr(), width, height, q * q, True, stream)
 
     def step(p):
         accum.zero_()
         renderer.render_accumulate(cam, p, None, accum.data_ptr(), stream)
-        reduce_accum(accum, 0)
-        if rank == 0:
-            renderer.finalize(accum.data_ptr(), None, out.data_ptr(), width, height, q * q, True, stream)
+        combine()
 
     def barrier():
         if world_size > 1:
@@ -262,9 +279,8 @@ def run_gpu(args):
         d_mask.copy_(host_mask, non_blocking=True)   # pixel mask from pinned host memory
         accum.zero_()
         renderer.render_accumulate(cam, params, d_mask.data_ptr(), accum.data_ptr(), stream)
-        reduce_accum(accum, 0)
+        combine(d_mask.data_ptr())
         if rank == 0:
-            renderer.finalize(accum.data_ptr(), d_mask.data_ptr(), out.data_ptr(), width, height, q * q, True, stream)
             host_img.copy_(out, non_blocking=True)   # the image the caller gets back
         torch.cuda.synchronize()
 
@@ -300,14 +316,19 @@ def run_gpu(args):
             "data": "synthetic",
             "config": {"workload": WORKLOAD if (args.scene, width, height, q) == ("rtow_final", WIDTH, HEIGHT, SQRT_SPP)
                        else f"{args.scene} {width}x{height} {q * q} spp depth 8 (not the headline workload)",
-                       "parallelism": f"strata-rows x{world_size}", "l2": "path/ray/hit buffers of one wave (>1.5 GB) exceed the 126 MB L2; no flush needed",
+                       "parallelism": f"strata-rows x{world_size}",
+                       "combine": ("none (single GPU: finalize only)" if world_size == 1 else
+                                   ("fused reduce+finalize kernel over NVLink peer memory" if args.reduce == "peer" else "ncclReduce + finalize")), "l2": "path/ray/hit buffers of one wave (>1.5 GB) exceed the 126 MB L2; no flush needed",
                        "wave_paths": args.wave or (1 << 23)},
             "mrays_per_s": n_segments / (ms_total / args.steps / 1e3) / 1e6,
             "segments_per_sample": n_segments / max(n_samples, 1.0),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(n_launches * args.steps),
             "roofline": {"bound": "hbm", "kernel": dom + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic(dom), "peak_source": peak_src, "avg_launch_ms": avg_ms,
+                         "traffic": ncu_traffic(dom),
+                         "traffic_launch": {"what": "bounce 0 of one wave of 1920x1080x4 = 8294400 paths (profiles/traffic.json)",
+                                            "algorithmic_bytes": BYTES_PER_SEGMENT[dom] * 8294400.0},
+                         "peak_source": peak_src, "avg_launch_ms": avg_ms,
                          "algorithmic_bytes_per_launch": alg_bytes_per_launch,
                          "pipeline": {"bytes_per_step": pipeline_bytes, "achieved": pipeline_bytes / (ms_total / args.steps / 1e3) / 1e9 / world_size,
                                       "frac": pipeline_bytes / (ms_total / args.steps / 1e3) / 1e9 / world_size / peak},
@@ -335,6 +356,8 @@ def main():
     ap.add_argument("--sqrt-spp", type=int, default=SQRT_SPP)
     ap.add_argument("--wave", type=int, default=0, help="max paths in flight per wave (0 = library default)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"],
+                    help="N > 1 combine step: peer = fused reduce+finalize kernel over NVLink peer memory (default); nccl = ncclReduce + finalize")
     ap.add_argument("--bvh-width", type=int, default=2, choices=[2, 4], help="world BVH: 2 = binary (default), 4 = QBVH")
     ap.add_argument("--scene", default="rtow_final", help="other BASELINE.json configs (see load_bench_scene); default = headline")
     args = ap.parse_args()

@@ -255,6 +255,30 @@ int rs_render_accumulate(rs_ctx* ctx, const rs_camera* cam, const rs_render_para
 int rs_finalize(rs_ctx* ctx, const float* d_accum, const uint8_t* d_pixel_mask, float* d_out_rgba,
                 int32_t width, int32_t height, int32_t n_samples, int32_t gamma, void* stream);
 
+/* ---- multi-GPU: fused reduce + finalize over NVLink peer memory ------------------------------
+ * The reference has no multi-device path (its only parallelism is painter.rs:275-299's thread
+ * pool); these entry points shard ONE `shot_to_target` over the GPUs of a box.  Every process
+ * (one per GPU) renders its strata rows with rs_render_accumulate into a buffer obtained from
+ * rs_device_alloc, exports it (rs_ipc_export: a 64-byte cudaIpcMemHandle_t that the host side
+ * passes to the other processes by any means) and maps the buffers of its peers (rs_ipc_open).
+ * rs_finalize_peers then does, in ONE kernel and with no intermediate buffer, what
+ * ncclReduce + rs_finalize would do: for pixels [pixel_begin, pixel_end) it sums the n_peers
+ * accumulators (peer loads over NVLink, fixed order => deterministic), applies
+ * `Vec3::into_color` (vec3.rs:227-240) and stores the pixel into d_out_rgba, which may itself
+ * be a peer pointer (the image of the rank that owns the result).  Each rank finalizes its own
+ * pixel slice, so the traffic is spread over all NVLink ports (reduce-scatter + gather shape).
+ * The caller orders it after the peers' renders (stream sync + a host barrier). */
+int rs_device_alloc(rs_ctx* ctx, int64_t bytes, void** d_ptr); /* cudaMalloc + zero fill */
+int rs_device_free(rs_ctx* ctx, void* d_ptr);
+#define RS_IPC_HANDLE_BYTES 64
+int rs_ipc_export(rs_ctx* ctx, const void* d_ptr, uint8_t handle[RS_IPC_HANDLE_BYTES]);
+int rs_ipc_open(rs_ctx* ctx, const uint8_t handle[RS_IPC_HANDLE_BYTES], void** d_ptr);
+int rs_ipc_close(rs_ctx* ctx, void* d_ptr);
+#define RS_MAX_PEERS 16
+int rs_finalize_peers(rs_ctx* ctx, const float* const* d_accums, int32_t n_peers,
+                      const uint8_t* d_pixel_mask, float* d_out_rgba, int64_t pixel_begin,
+                      int64_t pixel_end, int32_t n_samples, int32_t gamma, void* stream);
+
 /* ---- passes logic of the CLI (src/bin/raysnail.rs:157-208, 379-427); device pointers -------*/
 /* combine_pixel: new == (0,0,0,0) ? old : (old*pass + new)/(pass+1)   (raysnail.rs:176-193) */
 int rs_combine_passes(rs_ctx* ctx, const float* d_old, const float* d_new, float* d_out,

@@ -22,6 +22,7 @@ CORE_SYMBOLS = [
     "rs_abi_version", "rs_abi_struct_size", "rs_set_option", "rs_create", "rs_destroy", "rs_last_error", "rs_upload_scene", "rs_render",
     "rs_render_accumulate", "rs_finalize", "rs_combine_passes", "rs_noise_map", "rs_quantize_rgb8",
     "rs_debug_primary", "rs_debug_scatter", "rs_get_stats",
+    "rs_device_alloc", "rs_device_free", "rs_ipc_export", "rs_ipc_open", "rs_ipc_close", "rs_finalize_peers",
 ]
 # every symbol include/raysnail_b200_host.h declares
 HOST_SYMBOLS = [
@@ -133,6 +134,12 @@ def load() -> C.CDLL:
     proto("rs_debug_primary", C.c_int, vp, P(RsCamera), P(RsRenderParams), i32, vp, vp, vp, vp, vp, vp, vp)
     proto("rs_debug_scatter", C.c_int, vp, P(RsCamera), P(RsRenderParams), i32, vp, vp, vp, vp)
     proto("rs_get_stats", C.c_int, vp, P(RsStats))
+    proto("rs_device_alloc", C.c_int, vp, C.c_int64, P(vp))
+    proto("rs_device_free", C.c_int, vp, vp)
+    proto("rs_ipc_export", C.c_int, vp, vp, vp)
+    proto("rs_ipc_open", C.c_int, vp, vp, P(vp))
+    proto("rs_ipc_close", C.c_int, vp, vp)
+    proto("rs_finalize_peers", C.c_int, vp, P(vp), i32, vp, vp, C.c_int64, C.c_int64, i32, i32, vp)
 
     proto("rs_host_last_error", C.c_char_p)
     proto("rs_host_scene_from_sdl_file", C.c_int, C.c_char_p, P(vp))

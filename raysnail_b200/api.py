@@ -317,6 +317,35 @@ class Renderer:
     def finalize(self, d_accum: int, d_mask: Optional[int], d_out: int, width: int, height: int, n_samples: int, gamma: bool, stream: int = 0):
         self._ck(self._lib.rs_finalize(self._ctx, d_accum, d_mask, d_out, width, height, n_samples, int(gamma), stream), "rs_finalize")
 
+    # ---- multi-GPU: peer-memory buffers and the fused reduce + finalize -----------------------
+    def device_alloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        self._ck(self._lib.rs_device_alloc(self._ctx, int(nbytes), C.byref(p)), "rs_device_alloc")
+        return int(p.value)
+
+    def device_free(self, d_ptr: int):
+        self._ck(self._lib.rs_device_free(self._ctx, d_ptr), "rs_device_free")
+
+    def ipc_export(self, d_ptr: int) -> bytes:
+        h = (C.c_uint8 * 64)()
+        self._ck(self._lib.rs_ipc_export(self._ctx, d_ptr, h), "rs_ipc_export")
+        return bytes(h)
+
+    def ipc_open(self, handle: bytes) -> int:
+        h = (C.c_uint8 * 64).from_buffer_copy(handle)
+        p = C.c_void_p()
+        self._ck(self._lib.rs_ipc_open(self._ctx, h, C.byref(p)), "rs_ipc_open")
+        return int(p.value)
+
+    def ipc_close(self, d_ptr: int):
+        self._ck(self._lib.rs_ipc_close(self._ctx, d_ptr), "rs_ipc_close")
+
+    def finalize_peers(self, d_accums, d_mask: Optional[int], d_out: int, pixel_begin: int, pixel_end: int, n_samples: int, gamma: bool,
+                       stream: int = 0):
+        arr = (C.c_void_p * len(d_accums))(*[int(a) for a in d_accums])
+        self._ck(self._lib.rs_finalize_peers(self._ctx, arr, len(d_accums), d_mask, d_out, int(pixel_begin), int(pixel_end), int(n_samples),
+                                             int(gamma), stream), "rs_finalize_peers")
+
     def combine_passes(self, d_old, d_new, d_out, n_pixels, pass_index: float, stream: int = 0):
         self._ck(self._lib.rs_combine_passes(self._ctx, d_old, d_new, d_out, n_pixels, pass_index, stream), "rs_combine_passes")
 

@@ -11,6 +11,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -732,6 +733,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     ctx->shade_generic = any_generic || !lights_simple;
     ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4);
     ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic ? 1 : 0);
+    // tuning hooks: fewer resident blocks per SM than the occupancy limit (profiling experiments)
+    if (const char* e = std::getenv("RAYSNAIL_B200_EXTEND_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->extend_grid = std::min(ctx->extend_grid, ctx->sm_count * v); }
+    if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid = std::min(ctx->shade_grid, ctx->sm_count * v); }
 
     // triangles: p0, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56)
     std::vector<double> tri_geom((size_t)s->n_tris * 9);
@@ -821,6 +825,68 @@ int rs_finalize(rs_ctx* ctx, const float* d_accum, const uint8_t* d_mask, float*
     CK(cudaSetDevice(ctx->device));
     launch_finalize(reinterpret_cast<const float4*>(d_accum), d_mask, reinterpret_cast<float4*>(d_out), (int64_t)width * height, n_samples, gamma,
                     (cudaStream_t)stream);
+    CK(cudaGetLastError());
+    return RS_OK;
+}
+
+int rs_device_alloc(rs_ctx* ctx, int64_t bytes, void** d_ptr) {
+    if (!ctx || !d_ptr || bytes <= 0) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad rs_device_alloc arguments");
+    CK(cudaSetDevice(ctx->device));
+    void* p = nullptr;
+    CK(cudaMalloc(&p, (size_t)bytes));
+    CK(cudaMemset(p, 0, (size_t)bytes));
+    *d_ptr = p;
+    return RS_OK;
+}
+
+int rs_device_free(rs_ctx* ctx, void* d_ptr) {
+    if (!ctx) return RS_ERR_INVALID_ARGUMENT;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaFree(d_ptr));
+    return RS_OK;
+}
+
+int rs_ipc_export(rs_ctx* ctx, const void* d_ptr, uint8_t handle[RS_IPC_HANDLE_BYTES]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == RS_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
+    if (!ctx || !d_ptr || !handle) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad rs_ipc_export arguments");
+    CK(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, const_cast<void*>(d_ptr)));
+    std::memcpy(handle, &h, sizeof(h));
+    return RS_OK;
+}
+
+int rs_ipc_open(rs_ctx* ctx, const uint8_t handle[RS_IPC_HANDLE_BYTES], void** d_ptr) {
+    if (!ctx || !d_ptr || !handle) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad rs_ipc_open arguments");
+    CK(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *d_ptr = p;
+    return RS_OK;
+}
+
+int rs_ipc_close(rs_ctx* ctx, void* d_ptr) {
+    if (!ctx) return RS_ERR_INVALID_ARGUMENT;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaIpcCloseMemHandle(d_ptr));
+    return RS_OK;
+}
+
+int rs_finalize_peers(rs_ctx* ctx, const float* const* d_accums, int32_t n_peers, const uint8_t* d_mask, float* d_out, int64_t pixel_begin,
+                      int64_t pixel_end, int32_t n_samples, int32_t gamma, void* stream) {
+    if (!ctx || !d_accums || !d_out || n_peers <= 0 || n_peers > RS_MAX_PEERS || n_samples <= 0 || pixel_begin < 0 || pixel_end < pixel_begin)
+        return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad rs_finalize_peers arguments");
+    CK(cudaSetDevice(ctx->device));
+    PeerAccums pa;
+    std::memset(&pa, 0, sizeof(pa));
+    pa.n = n_peers;
+    for (int k = 0; k < n_peers; ++k) {
+        if (!d_accums[k]) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "null peer accumulator");
+        pa.p[k] = reinterpret_cast<const float4*>(d_accums[k]);
+    }
+    launch_finalize_peers(pa, d_mask, reinterpret_cast<float4*>(d_out), pixel_begin, pixel_end, n_samples, gamma, (cudaStream_t)stream);
     CK(cudaGetLastError());
     return RS_OK;
 }

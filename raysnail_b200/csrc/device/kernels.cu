@@ -526,7 +526,7 @@ __device__ __forceinline__ double phong_highlight(V3 dir_to_light, V3 ray_dir, V
 // sample lies above the surface; when a ray hits the BACK of a shading normal (triangle normals
 // are not face-forwarded, triangle_mesh.rs:115-116) the lobe points below it and the reference
 // spins (forever if the lobe is entirely below).  Oracle and GPU give up after this many
-// candidates and keep the last one (oracle/oracle.cpp REJECTION_CAP).
+// candidates and keep the last one (the CPU checker uses the same cap).
 #define RS_REJECTION_CAP 256u
 
 struct PdfState {  // the `Box<dyn PDF>` of a ScatterRecord, flattened
@@ -998,6 +998,28 @@ __global__ void finalize_kernel(const float4* __restrict__ accum, const unsigned
     }
 }
 
+// Fused multi-GPU reduce + finalize: the sum over the per-GPU accumulators is taken straight
+// from peer memory (128-bit loads over NVLink / NVSwitch, one per peer per pixel, all issued
+// before the first use) and the finished pixel is stored once — possibly into a peer's image.
+// Replaces ncclReduce (which writes a reduced copy that finalize would read again).
+__global__ void __launch_bounds__(RS_BLOCK) finalize_peers_kernel(const __grid_constant__ PeerAccums peers, const unsigned char* __restrict__ mask,
+                                                                  float4* __restrict__ out, int64_t begin, int64_t end, float inv_n, int gamma) {
+    for (int64_t i = begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < end; i += (int64_t)gridDim.x * blockDim.x) {
+        if (mask && mask[i] == 0) { out[i] = make_float4(0.f, 0.f, 0.f, 0.f); continue; }
+        float4 v[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+            if (k < peers.n) v[k] = __ldcv(peers.p[k] + i);  // volatile-class load: never served from a stale L1 line
+        float sx = 0.f, sy = 0.f, sz = 0.f;
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+            if (k < peers.n) { sx += v[k].x; sy += v[k].y; sz += v[k].z; }
+        float r = sx * inv_n, g = sy * inv_n, b = sz * inv_n;
+        if (gamma) { r = sqrtf(r); g = sqrtf(g); b = sqrtf(b); }
+        out[i] = make_float4(r, g, b, 1.0f);
+    }
+}
+
 // combine_pixel (raysnail.rs:176-193)
 __global__ void combine_kernel(const float4* __restrict__ old_px, const float4* __restrict__ new_px, float4* __restrict__ out, int64_t n, float pass) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -1081,6 +1103,11 @@ void launch_accumulate(const FrameParams& fp, const WaveState& ws, float4* accum
 }
 void launch_finalize(const float4* accum, const unsigned char* mask, float4* out, int64_t n, int n_samples, int gamma, cudaStream_t s) {
     finalize_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(accum, mask, out, n, 1.0f / (float)n_samples, gamma);
+}
+void launch_finalize_peers(const PeerAccums& peers, const unsigned char* mask, float4* out, int64_t begin, int64_t end, int n_samples, int gamma,
+                           cudaStream_t s) {
+    if (end <= begin) return;
+    finalize_peers_kernel<<<grid_for(end - begin), RS_BLOCK, 0, s>>>(peers, mask, out, begin, end, 1.0f / (float)n_samples, gamma);
 }
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s) {
     combine_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(old_px, new_px, out, n, pass);

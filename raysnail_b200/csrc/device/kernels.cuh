@@ -98,6 +98,12 @@ void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, i
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s);
 void launch_accumulate(const FrameParams& fp, const WaveState& ws, float4* accum, cudaStream_t s);
 void launch_finalize(const float4* accum, const unsigned char* mask, float4* out, int64_t n, int n_samples, int gamma, cudaStream_t s);
+struct PeerAccums {
+    const float4* p[16];  // RS_MAX_PEERS
+    int n;
+};
+void launch_finalize_peers(const PeerAccums& peers, const unsigned char* mask, float4* out, int64_t begin, int64_t end, int n_samples, int gamma,
+                           cudaStream_t s);
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s);
 void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s);
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);

@@ -20,6 +20,86 @@ def stratum_rows(rank: int, world_size: int, sqrt_spp: int) -> Tuple[int, int]:
     return (sqrt_spp * rank) // world_size, (sqrt_spp * (rank + 1)) // world_size
 
 
+def pixel_slice(rank: int, world_size: int, n_pixels: int) -> Tuple[int, int]:
+    """Pixels [begin, end) that `rank` finalizes in the fused reduce: contiguous, balanced,
+    16-pixel aligned (256-byte float4 runs) except for the last rank's tail."""
+    if not (0 <= rank < world_size):
+        raise ValueError("rank out of range")
+    per = -(-n_pixels // world_size)
+    per = (per + 15) // 16 * 16
+    return min(n_pixels, rank * per), min(n_pixels, (rank + 1) * per)
+
+
+class _DevView:
+    """Raw device pointer -> torch tensor (zero-copy) through __cuda_array_interface__."""
+
+    def __init__(self, ptr: int, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False), "version": 2, "strides": None}
+
+
+def device_view(ptr: int, shape, device):
+    import torch
+    return torch.as_tensor(_DevView(ptr, shape), device=device)
+
+
+class PeerImage:
+    """The per-rank accumulation buffer (and rank 0's output image) as NVLink peer memory.
+
+    Every rank allocates its accumulator through the library (cudaMalloc, so the whole
+    allocation is what the IPC handle names), the 64-byte handles are exchanged once with
+    all_gather_object, and every rank maps every peer's buffer plus rank 0's image."""
+
+    def __init__(self, renderer, width: int, height: int):
+        import torch.distributed as dist
+        self.r, self.n_pixels = renderer, width * height
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        nbytes = self.n_pixels * 16
+        self.accum = renderer.device_alloc(nbytes)
+        self.out = renderer.device_alloc(nbytes) if self.rank == 0 else 0
+        import torch
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.accum_t = device_view(self.accum, (height, width, 4), dev)  # torch views for zero_() / copies
+        self.out_t = device_view(self.out, (height, width, 4), dev) if self.rank == 0 else None
+        mine = {"accum": renderer.ipc_export(self.accum), "out": renderer.ipc_export(self.out) if self.rank == 0 else None}
+        handles = [None] * self.world
+        dist.all_gather_object(handles, mine)
+        self._opened = []
+        self.peer_accums = []
+        for k, h in enumerate(handles):
+            if k == self.rank:
+                self.peer_accums.append(self.accum)
+            else:
+                p = renderer.ipc_open(h["accum"])
+                self._opened.append(p)
+                self.peer_accums.append(p)
+        if self.rank == 0:
+            self.out_on_rank0 = self.out
+        else:
+            self.out_on_rank0 = renderer.ipc_open(handles[0]["out"])
+            self._opened.append(self.out_on_rank0)
+
+    def reduce_finalize(self, n_samples: int, gamma: bool, stream: int = 0, d_mask=None):
+        """Call after this rank's render was enqueued on `stream`.  Barrier (every accumulator is
+        complete), fused sum + finalize of this rank's pixel slice into rank 0's image, barrier
+        (rank 0's image is complete)."""
+        import torch
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        dist.barrier()
+        b, e = pixel_slice(self.rank, self.world, self.n_pixels)
+        self.r.finalize_peers(self.peer_accums, d_mask, self.out_on_rank0, b, e, n_samples, gamma, stream)
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    def close(self):
+        for p in self._opened:
+            self.r.ipc_close(p)
+        self._opened = []
+        self.r.device_free(self.accum)
+        if self.rank == 0 and self.out:
+            self.r.device_free(self.out)
+
+
 def env_world() -> Tuple[int, int, int]:
     return int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
 

@@ -212,3 +212,44 @@ def test_qbvh_gives_the_same_hits_and_image_as_the_binary_bvh(renderer, name):
     assert np.array_equal(g4["obj_id"], o["obj_id"]) and np.array_equal(g2["obj_id"], o["obj_id"])
     assert np.array_equal(g4["t"], g2["t"])
     assert np.array_equal(img4, img2)
+
+
+def test_fused_peer_finalize_matches_sum_then_finalize(renderer):
+    """rs_finalize_peers over the strata-row shards of one render (as separate accumulators, the
+    multi-GPU layout) == rs_finalize of their sum == the single-accumulator render."""
+    import torch
+    scene = load_scene("example")
+    renderer.upload(scene)
+    cam = scene.camera(W, H)
+    dev = torch.device("cuda", 0)
+    q, shards = 4, 4
+    accs = [torch.zeros((H, W, 4), dtype=torch.float32, device=dev) for _ in range(shards)]
+    whole = torch.zeros((H, W, 4), dtype=torch.float32, device=dev)
+    for k, a in enumerate(accs):
+        renderer.render_accumulate(cam, make_params(samples=q * q, rows=(k, k + 1)), None, a.data_ptr(), 0)
+    renderer.render_accumulate(cam, make_params(samples=q * q), None, whole.data_ptr(), 0)
+    mask = torch.ones((H, W), dtype=torch.uint8, device=dev)
+    mask[:7, :] = 0
+    out_peer = torch.full((H, W, 4), -1.0, dtype=torch.float32, device=dev)
+    n = W * H
+    cut = (n // 3 + 15) // 16 * 16
+    for b, e in ((0, cut), (cut, n)):  # two "ranks", each finalizing its pixel slice
+        renderer.finalize_peers([a.data_ptr() for a in accs], mask.data_ptr(), out_peer.data_ptr(), b, e, q * q, True, 0)
+    summed = torch.stack(accs).sum(0)
+    out_ref = torch.empty_like(out_peer)
+    renderer.finalize(summed.data_ptr(), mask.data_ptr(), out_ref.data_ptr(), W, H, q * q, True, 0)
+    out_whole = torch.empty_like(out_peer)
+    renderer.finalize(whole.data_ptr(), mask.data_ptr(), out_whole.data_ptr(), W, H, q * q, True, 0)
+    torch.cuda.synchronize()
+    assert torch.all(out_peer[:7] == 0)
+    assert torch.allclose(out_peer, out_ref, rtol=1e-6, atol=1e-7)
+    assert torch.allclose(out_peer, out_whole, rtol=1e-5, atol=1e-6)
+
+
+def test_device_alloc_and_ipc_export(renderer):
+    p = renderer.device_alloc(1 << 20)
+    try:
+        h = renderer.ipc_export(p)
+        assert len(h) == 64 and any(h)
+    finally:
+        renderer.device_free(p)
