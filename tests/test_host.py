@@ -285,3 +285,14 @@ def test_gloo_two_rank_sharded_render_equals_single_rank():
                           "--master-port", "29533", script], capture_output=True, text=True, env=env, timeout=600)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert "SHARDED_OK" in out.stdout
+
+
+def test_pixel_slices_of_the_fused_reduce_cover_the_image_once():
+    from raysnail_b200.distributed import pixel_slice
+    for n_pixels in (1, 15, 16, 17, 1920 * 1080, 3840 * 2160, 800 * 500):
+        for world in (1, 2, 3, 4, 8):
+            cuts = [pixel_slice(r, world, n_pixels) for r in range(world)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == n_pixels
+            for (b0, e0), (b1, e1) in zip(cuts, cuts[1:]):
+                assert e0 == b1 and b0 <= e0
+            assert all(b % 16 == 0 for b, _ in cuts if b < n_pixels)
