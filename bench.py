@@ -200,6 +200,7 @@ def run_gpu(args):
     scene = load_bench_scene(args.scene)
     renderer = Renderer(local_rank)
     renderer.set_bvh_width(args.bvh_width)
+    renderer.set_wave_streams(args.wave_streams)
     renderer.upload(scene)
     cam = scene.camera(width, height)
     stream = torch.cuda.current_stream().cuda_stream
@@ -359,6 +360,7 @@ def main():
     ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"],
                     help="N > 1 combine step: peer = fused reduce+finalize kernel over NVLink peer memory (default); nccl = ncclReduce + finalize")
     ap.add_argument("--bvh-width", type=int, default=2, choices=[2, 4], help="world BVH: 2 = binary (default), 4 = QBVH")
+    ap.add_argument("--wave-streams", type=int, default=2, choices=[1, 2, 3, 4], help="streams consecutive waves rotate over")
     ap.add_argument("--scene", default="rtow_final", help="other BASELINE.json configs (see load_bench_scene); default = headline")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -233,6 +233,10 @@ const char* rs_last_error(const rs_ctx* ctx);
  * 64-byte nodes, 4 = QBVH of 128-byte nodes (both give identical hits; see DESIGN.md for the
  * measured trade-off).  */
 #define RS_OPT_BVH_WIDTH 1
+/* RS_OPT_WAVE_STREAMS: n in 1..4 (default 2) = consecutive waves rotate over the caller's stream and
+ * n-1 internal ones, so the tail of each persistent kernel overlaps with another wave's work (the image
+ * is bit-identical: accumulation stays in wave order); 1 = every kernel on the caller's stream. */
+#define RS_OPT_WAVE_STREAMS 2
 int rs_set_option(rs_ctx* ctx, int option, int value);
 
 /* ---- scene: replaces `World::new` (world.rs:40-53) + `BVH::new` (bvh.rs:47-112) -----------*/

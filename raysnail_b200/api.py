@@ -292,6 +292,10 @@ class Renderer:
         if self._scene is not None:
             self.upload(self._scene)
 
+    def set_wave_streams(self, n: int):
+        """RS_OPT_WAVE_STREAMS: 2 = consecutive waves overlap on two streams (default), 1 = one stream."""
+        self._ck(self._lib.rs_set_option(self._ctx, 2, int(n)), "rs_set_option")
+
     def upload(self, scene: Scene):
         self._ck(self._lib.rs_upload_scene(self._ctx, scene.desc), "rs_upload_scene")
         self._scene = scene  # keep the host buffers alive

@@ -78,10 +78,21 @@ struct rs_ctx {
     double scene_omax = 0.0, padded_omax = -1.0;
     int n_lights = 0;
 
-    // wave state
-    DevBuf d_pa[2], d_pb[2], d_pc[2], d_pd[2], d_pe[2], d_hit, d_hit_end, d_cq, d_contrib, d_ctr, d_stats;
+    // wave state.  Two complete sets: consecutive waves run on two streams so that the tail of
+    // every persistent kernel of one wave (SMs going idle as its last batches finish) is filled by
+    // blocks of the other wave's kernel (RS_OPT_WAVE_STREAMS; `ws` is set 0 and the one the probes use)
+    struct WaveSet {
+        DevBuf d_pa[2], d_pb[2], d_pc[2], d_pd[2], d_pe[2], d_hit, d_hit_end, d_cq, d_contrib, d_ctr;
+        uint32_t capacity = 0;
+    };
+    static constexpr int kMaxSets = 4;
+    WaveSet wset[kMaxSets];
+    DevBuf d_stats;
     uint32_t capacity = 0;
-    WaveState ws{};
+    WaveState ws{}, ws_aux[kMaxSets - 1] = {};
+    int wave_streams = 2;
+    cudaStream_t aux_stream[kMaxSets - 1] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join[kMaxSets - 1] = {}, ev_acc[kMaxSets] = {};
     int extend_grid = 148, shade_grid = 148;
 
     // scratch for rs_render / probes
@@ -365,34 +376,45 @@ void mat3x4_mul(const long double* a, const double* b16, long double* out) {  //
         }
 }
 
-int ensure_wave(rs_ctx* ctx, uint32_t cap) {
-    if (cap <= ctx->capacity) return RS_OK;
-    for (int b = 0; b < 2; ++b) {
-        CK(ctx->d_pa[b].ensure((size_t)cap * sizeof(double2)));
-        CK(ctx->d_pb[b].ensure((size_t)cap * sizeof(double2)));
-        CK(ctx->d_pc[b].ensure((size_t)cap * sizeof(double2)));
-        CK(ctx->d_pd[b].ensure((size_t)cap * sizeof(double2)));
-        CK(ctx->d_pe[b].ensure((size_t)cap * sizeof(uint4)));
-        ctx->ws.buf[b].a = ctx->d_pa[b].as<double2>();
-        ctx->ws.buf[b].b = ctx->d_pb[b].as<double2>();
-        ctx->ws.buf[b].c = ctx->d_pc[b].as<double2>();
-        ctx->ws.buf[b].d = ctx->d_pd[b].as<double2>();
-        ctx->ws.buf[b].e = ctx->d_pe[b].as<uint4>();
-    }
-    CK(ctx->d_hit.ensure((size_t)cap * sizeof(HitA)));
-    CK(ctx->d_hit_end.ensure((size_t)cap * sizeof(double)));
-    CK(ctx->d_cq.ensure((size_t)cap * RS_NUM_CLASSES * sizeof(uint32_t)));
-    CK(ctx->d_contrib.ensure((size_t)cap * sizeof(float4)));
-    CK(ctx->d_ctr.ensure(sizeof(WaveCounters)));
+int ensure_wave_set(rs_ctx* ctx, int k, uint32_t cap) {
+    rs_ctx::WaveSet& w = ctx->wset[k];
+    WaveState& ws = k == 0 ? ctx->ws : ctx->ws_aux[k - 1];
     CK(ctx->d_stats.ensure(sizeof(DeviceStats)));
-    ctx->ws.hit = ctx->d_hit.as<HitA>();
-    ctx->ws.hit_end = ctx->d_hit_end.as<double>();
-    ctx->ws.class_queue = ctx->d_cq.as<uint32_t>();
-    ctx->ws.contrib = ctx->d_contrib.as<float4>();
-    ctx->ws.ctr = ctx->d_ctr.as<WaveCounters>();
-    ctx->ws.stats = ctx->d_stats.as<DeviceStats>();
-    ctx->ws.capacity = cap;
-    ctx->capacity = cap;
+    ws.stats = ctx->d_stats.as<DeviceStats>();  // shared by both sets (atomic counters)
+    if (cap <= w.capacity) return RS_OK;
+    for (int b = 0; b < 2; ++b) {
+        CK(w.d_pa[b].ensure((size_t)cap * sizeof(double2)));
+        CK(w.d_pb[b].ensure((size_t)cap * sizeof(double2)));
+        CK(w.d_pc[b].ensure((size_t)cap * sizeof(double2)));
+        CK(w.d_pd[b].ensure((size_t)cap * sizeof(double2)));
+        CK(w.d_pe[b].ensure((size_t)cap * sizeof(uint4)));
+        ws.buf[b].a = w.d_pa[b].as<double2>();
+        ws.buf[b].b = w.d_pb[b].as<double2>();
+        ws.buf[b].c = w.d_pc[b].as<double2>();
+        ws.buf[b].d = w.d_pd[b].as<double2>();
+        ws.buf[b].e = w.d_pe[b].as<uint4>();
+    }
+    CK(w.d_hit.ensure((size_t)cap * sizeof(HitA)));
+    CK(w.d_hit_end.ensure((size_t)cap * sizeof(double)));
+    CK(w.d_cq.ensure((size_t)cap * RS_NUM_CLASSES * sizeof(uint32_t)));
+    CK(w.d_contrib.ensure((size_t)cap * sizeof(float4)));
+    CK(w.d_ctr.ensure(sizeof(WaveCounters)));
+    ws.hit = w.d_hit.as<HitA>();
+    ws.hit_end = w.d_hit_end.as<double>();
+    ws.class_queue = w.d_cq.as<uint32_t>();
+    ws.contrib = w.d_contrib.as<float4>();
+    ws.ctr = w.d_ctr.as<WaveCounters>();
+    ws.capacity = cap;
+    w.capacity = cap;
+    return RS_OK;
+}
+
+int ensure_wave(rs_ctx* ctx, uint32_t cap, int n_sets = 1) {
+    for (int k = 0; k < n_sets; ++k) {
+        int rc = ensure_wave_set(ctx, k, cap);
+        if (rc != RS_OK) return rc;
+    }
+    ctx->capacity = ctx->wset[0].capacity;
     return RS_OK;
 }
 
@@ -459,36 +481,63 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
     cap = std::max(cap, 1024u);
     const uint32_t P = std::min(np, cap);
     const uint32_t K = std::max(1u, std::min(s_total, cap / P));
-    int rc = ensure_wave(ctx, P * K);
+    const uint32_t n_waves = ((np + P - 1) / P) * ((s_total + K - 1) / K);
+    // kernel timing needs the kernels back to back on one stream
+    const int n_sets = timing ? 1 : (int)std::min<uint32_t>((uint32_t)ctx->wave_streams, n_waves);
+    int rc = ensure_wave(ctx, P * K, n_sets);
     if (rc != RS_OK) return rc;
     rc = prepare_camera(ctx, cam);
     if (rc != RS_OK) return rc;
     FrameParams fp = make_frame(cam, p);
     fp.mask = d_mask;
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), stream));
+    if (n_sets > 1) {
+        if (!ctx->ev_fork) {
+            CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+            for (int k = 0; k < rs_ctx::kMaxSets; ++k) CK(cudaEventCreateWithFlags(&ctx->ev_acc[k], cudaEventDisableTiming));
+            for (int k = 0; k < rs_ctx::kMaxSets - 1; ++k) {
+                CK(cudaStreamCreateWithFlags(&ctx->aux_stream[k], cudaStreamNonBlocking));
+                CK(cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming));
+            }
+        }
+        // fork: everything already queued on the caller's stream (e.g. the clear of d_accum) comes first
+        CK(cudaEventRecord(ctx->ev_fork, stream));
+        for (int k = 1; k < n_sets; ++k) CK(cudaStreamWaitEvent(ctx->aux_stream[k - 1], ctx->ev_fork, 0));
+    }
     Timing tm{ctx, stream, timing};
     uint64_t launches = 0;
+    uint32_t wave = 0;
     for (uint32_t pixel0 = 0; pixel0 < np; pixel0 += P) {
         fp.pixel0 = pixel0;
         fp.n_pixels = std::min(P, np - pixel0);
-        for (uint32_t sample0 = 0; sample0 < s_total; sample0 += K) {
+        for (uint32_t sample0 = 0; sample0 < s_total; sample0 += K, ++wave) {
             fp.sample0 = sample0;
             fp.n_samples = std::min(K, s_total - sample0);
-            CK(cudaMemsetAsync(ctx->ws.ctr, 0, sizeof(WaveCounters), stream));
+            const int set = (int)(wave % (uint32_t)n_sets);
+            const WaveState& ws = set ? ctx->ws_aux[set - 1] : ctx->ws;
+            cudaStream_t st = set ? ctx->aux_stream[set - 1] : stream;
+            CK(cudaMemsetAsync(ws.ctr, 0, sizeof(WaveCounters), st));
             tm.mark(0);
-            launch_raygen(fp, ctx->ws, stream);
+            launch_raygen(fp, ws, st);
             ++launches;
             for (int b = 0; b < p->depth; ++b) {
                 tm.mark(1);
-                launch_extend(ctx->scene, fp, ctx->ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, stream);
+                launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
                 tm.mark(2);
-                launch_shade(ctx->scene, fp, ctx->ws, b, ctx->shade_generic ? 1 : 0, ctx->shade_grid, nullptr, stream);
+                launch_shade(ctx->scene, fp, ws, b, ctx->shade_generic ? 1 : 0, ctx->shade_grid, nullptr, st);
                 launches += 2;
             }
             tm.mark(3);
-            launch_accumulate(fp, ctx->ws, d_accum, stream);
+            // the accumulators are read-modify-written without atomics: one accumulate at a time, in wave order
+            if (n_sets > 1 && wave > 0) CK(cudaStreamWaitEvent(st, ctx->ev_acc[(set + n_sets - 1) % n_sets], 0));
+            launch_accumulate(fp, ws, d_accum, st);
+            if (n_sets > 1) CK(cudaEventRecord(ctx->ev_acc[set], st));
             ++launches;
         }
+    }
+    for (int k = 1; k < n_sets; ++k) {  // join: the caller's stream continues after all streams are done
+        CK(cudaEventRecord(ctx->ev_join[k - 1], ctx->aux_stream[k - 1]));
+        CK(cudaStreamWaitEvent(stream, ctx->ev_join[k - 1], 0));
     }
     tm.mark(4);
     CK(cudaGetLastError());
@@ -573,6 +622,12 @@ void rs_destroy(rs_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
+    if (ctx->ev_fork) {
+        cudaEventDestroy(ctx->ev_fork);
+        for (cudaEvent_t e : ctx->ev_acc) if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : ctx->ev_join) if (e) cudaEventDestroy(e);
+        for (cudaStream_t q : ctx->aux_stream) if (q) cudaStreamDestroy(q);
+    }
     delete ctx;
 }
 
@@ -583,6 +638,10 @@ int rs_set_option(rs_ctx* ctx, int option, int value) {
     if (option == RS_OPT_BVH_WIDTH && (value == 2 || value == 4)) {
         if (ctx->bvh_width != value) ctx->has_scene = false;  // the tree must be rebuilt by the next upload
         ctx->bvh_width = value;
+        return RS_OK;
+    }
+    if (option == RS_OPT_WAVE_STREAMS && value >= 1 && value <= rs_ctx::kMaxSets) {
+        ctx->wave_streams = value;
         return RS_OK;
     }
     return fail(ctx, RS_ERR_INVALID_ARGUMENT, "unknown option or value");

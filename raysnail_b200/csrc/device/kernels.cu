@@ -270,6 +270,18 @@ __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); 
 #ifndef RS_TUNE_SHADE_LEAN
 #define RS_TUNE_SHADE_LEAN 2
 #endif
+// work distribution of the persistent kernels: 0 = one atomicAdd on a global cursor per batch of 32
+// (issued a batch ahead), 1 = static round robin (batch = warp index + k * warps in the grid)
+#ifndef RS_TUNE_EXTEND_STATIC
+#define RS_TUNE_EXTEND_STATIC 0
+#endif
+#ifndef RS_TUNE_SHADE_STATIC
+#define RS_TUNE_SHADE_STATIC 0
+#endif
+// shade: classes whose paths always continue reserve their output slots before the shading math
+#ifndef RS_TUNE_SHADE_EARLY
+#define RS_TUNE_SHADE_EARLY 0
+#endif
 #ifndef RS_TUNE_SHADE_GENERIC
 #define RS_TUNE_SHADE_GENERIC 2
 #endif
@@ -429,12 +441,24 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_segments, (unsigned long long)(nf + nb));
     // the cursor bump for the NEXT batch is issued before the current batch is processed, so the
     // atomic's round trip to L2 overlaps with the traversal instead of heading every batch
+#if RS_TUNE_EXTEND_STATIC
+    (void)head;
+    uint32_t next_base = (blockIdx.x * (RS_BLOCK / 32) + (threadIdx.x >> 5)) * 32u;
+    const uint32_t base_stride = gridDim.x * (RS_BLOCK / 32) * 32u;
+#else
     uint32_t pend = 0;
     if (lane_id() == 0) pend = atomic_add_async(head, 32u, lane_zero);
+#endif
     while (true) {
+#if RS_TUNE_EXTEND_STATIC
+        const uint32_t base = next_base;
+        if (base >= n) break;
+        next_base += base_stride;
+#else
         const uint32_t base = __shfl_sync(0xffffffffu, pend, 0);
         if (base >= n) break;
         if (lane_id() == 0) pend = atomic_add_async(head, 32u, lane_zero);
+#endif
         const uint32_t v = base + lane_id();
         const bool live = v < nf32 ? v < nf : v < n;
         const uint32_t i = v < nf32 ? v : ws.capacity - 1u - (v - nf32);
@@ -649,6 +673,18 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
         entry = ws.class_queue + ((size_t)cls * ws.capacity + qi);
     };
     // one atomicAdd per batch of 32, issued one batch ahead of its use
+#if RS_TUNE_SHADE_STATIC
+    // every batch of one class costs about the same, so a static round robin balances as well as
+    // a global cursor and needs no atomic (the cursor was the top stall of this kernel)
+    (void)head;
+    uint32_t next_base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32u;
+    const uint32_t base_stride = gridDim.x * (blockDim.x >> 5) * 32u;
+    auto next_batch = [&]() -> uint32_t {
+        const uint32_t b = next_base;
+        next_base = b < total ? b + base_stride : b;  // saturates: no wrap-around past `total`
+        return b;
+    };
+#else
     uint32_t pend = 0;
     if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
     auto next_batch = [&]() -> uint32_t {
@@ -656,6 +692,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
         if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
         return b;
     };
+#endif
     auto stage_item = [&](int buf, uint32_t i) {
         uint4* s = stage + buf * (RS_SHADE_STAGE * 32);
         cp_async16(s, in.a + i);
@@ -722,8 +759,13 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
 
         bool survive = false, front = false;
         PathRec p;
+        HitA ha;
+        RngCtx rng;
+        rng.key = fp.key;
+        rng.pixel = 0;
+        rng.sample = 0;
+        rng.depth = (uint32_t)bounce + 1;
         if (live) {
-            HitA ha;
             if constexpr (STAGED) {
                 const double2 a = *reinterpret_cast<const double2*>(s), b = *reinterpret_cast<const double2*>(s + 32);
                 const double2 c = *reinterpret_cast<const double2*>(s + 64), d = *reinterpret_cast<const double2*>(s + 96);
@@ -743,12 +785,29 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                 load_path(in, i, p);
                 ha = ws.hit[i];
             }
-            RngCtx rng;
-            rng.key = fp.key;
             rng.pixel = p.pixel;
             rng.sample = p.sample;
-            rng.depth = (uint32_t)bounce + 1;
-
+        }
+        // Paths of these classes always continue (their `scatter` never returns None), and whether
+        // the next ray is light-directed is decided by the first word of the P_SCATTER draw alone
+        // (camera.rs:198): their output slots are reserved BEFORE the shading math, so the two
+        // atomics' round trips to L2 overlap with it instead of ending every batch.
+        const bool early = RS_TUNE_SHADE_EARLY && !never &&
+                           (cls == 1 + RS_MAT_LAMBERTIAN || cls == 1 + RS_MAT_DIELECTRIC || cls == 1 + RS_MAT_ISOTROPIC || cls == 1 + RS_MAT_BLINN_PHONG);
+        uint4 w_sc = make_uint4(0u, 0u, 0u, 0u);
+        uint32_t e_mf = 0, e_mb = 0, e_bf = 0, e_bb = 0;
+        if (early) {
+            bool e_front = false;
+            if (live) {
+                w_sc = rng_words(rng, P_SCATTER, 0);
+                e_front = cls != 1 + RS_MAT_DIELECTRIC && u01(w_sc.x) < 0.5;
+            }
+            e_mf = __ballot_sync(0xffffffffu, live && e_front);
+            e_mb = __ballot_sync(0xffffffffu, live && !e_front);
+            if (e_mf && lane == (uint32_t)(__ffs(e_mf) - 1)) e_bf = atomic_add_async(out_front, __popc(e_mf), lane_zero);
+            if (e_mb && lane == (uint32_t)(__ffs(e_mb) - 1)) e_bb = atomic_add_async(out_back, __popc(e_mb), lane_zero);
+        }
+        if (live) {
             float3 add = make_float3(0.f, 0.f, 0.f);  // radiance added at this vertex (before T)
             int kind = 0;
             V3 next_o = v3(0, 0, 0), next_d = v3(0, 0, 0);
@@ -817,7 +876,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                                 double x = 1.0 - cos_theta;
                                 reflect_prob = fma(1.0 - r0, x * x * x * x * x, r0);
                             }
-                            uint4 w = rng_words(rng, P_SCATTER, 0);
+                            const uint4 w = early ? w_sc : rng_words(rng, P_SCATTER, 0);
                             if (!(u01(w.w) < reflect_prob)) {
                                 V3 r_parallel = refractive * (p.ray.d + cos_theta * h.normal);
                                 V3 r_perp = (-sqrt(1.0 - length_squared(r_parallel))) * h.normal;
@@ -853,7 +912,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                     P.r_in = p.ray.d;
                     P.r_w = (P.kind == 1 || P.kind == 2) ? unit_fast(reflected) : v3(0, 0, 0);
                     double light_multi = 1.0, pdf_val;
-                    uint4 w = rng_words(rng, P_SCATTER, 0);
+                    const uint4 w = early ? w_sc : rng_words(rng, P_SCATTER, 0);
                     if (u01(w.x) < 0.5) {  // camera.rs:198-213
                         kind = 3;
                         pdf_val = 0.3183098861837907;
@@ -909,11 +968,16 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
         }
         if (!never) {
             // survivors: light-directed rays onto the front stack, the others onto the back stack
-            const uint32_t mf = __ballot_sync(0xffffffffu, survive && front), mb = __ballot_sync(0xffffffffu, survive && !front);
+            uint32_t mf = e_mf, mb = e_mb, bf = e_bf, bb = e_bb;
+            if (!early) {
+                mf = __ballot_sync(0xffffffffu, survive && front);
+                mb = __ballot_sync(0xffffffffu, survive && !front);
+            }
             const uint32_t lf = mf ? (uint32_t)(__ffs(mf) - 1) : 0u, lb = mb ? (uint32_t)(__ffs(mb) - 1) : 0u;
-            uint32_t bf = 0, bb = 0;
-            if (mf && lane == lf) bf = atomic_add_async(out_front, __popc(mf), lane_zero);
-            if (mb && lane == lb) bb = atomic_add_async(out_back, __popc(mb), lane_zero);
+            if (!early) {
+                if (mf && lane == lf) bf = atomic_add_async(out_front, __popc(mf), lane_zero);
+                if (mb && lane == lb) bb = atomic_add_async(out_back, __popc(mb), lane_zero);
+            }
             bf = __shfl_sync(0xffffffffu, bf, lf);
             bb = __shfl_sync(0xffffffffu, bb, lb);
             const uint32_t lt = (1u << lane) - 1u;
