@@ -396,12 +396,12 @@ int ensure_wave_set(rs_ctx* ctx, int k, uint32_t cap) {
     }
     CK(w.d_hit.ensure((size_t)cap * sizeof(HitA)));
     CK(w.d_hit_end.ensure((size_t)cap * sizeof(double)));
-    CK(w.d_cq.ensure((size_t)cap * RS_NUM_CLASSES * sizeof(uint32_t)));
+    CK(w.d_cq.ensure((size_t)cap * RS_NUM_CLASSES * sizeof(uint2)));
     CK(w.d_contrib.ensure((size_t)cap * sizeof(float4)));
     CK(w.d_ctr.ensure(sizeof(WaveCounters)));
     ws.hit = w.d_hit.as<HitA>();
     ws.hit_end = w.d_hit_end.as<double>();
-    ws.class_queue = w.d_cq.as<uint32_t>();
+    ws.class_queue = w.d_cq.as<uint2>();
     ws.contrib = w.d_contrib.as<float4>();
     ws.ctr = w.d_ctr.as<WaveCounters>();
     ws.capacity = cap;

@@ -106,9 +106,9 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
 }
-__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
@@ -120,8 +120,9 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 #define RS_WARPS (RS_TUNE_SHADE_BLOCK / 32)
 // staging slots per lane of shade: the 5 path elements + the hit record; double buffered
 #define RS_SHADE_STAGE 6
-// per warp: two record buffers + two 32-entry queue-index buffers
-#define RS_SHADE_WARP_SMEM (2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 4)
+// per warp: two record buffers + two 32-entry queue-entry buffers (uint2) + two 32-entry buffers
+// of reserved output slots
+#define RS_SHADE_WARP_SMEM (2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 8 + 2 * 32 * 4)
 #define RS_SHADE_SMEM (RS_WARPS * RS_SHADE_WARP_SMEM)
 
 // =============================================================================================
@@ -259,6 +260,9 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
 __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); }
 
 #define RS_BVH_SENTINEL ((int)0x80000000)
+// material classes (1 + rs_material_type) whose `scatter` always returns Some
+#define RS_ALWAYS_CONTINUES(cls) \
+    ((cls) == 1 + RS_MAT_LAMBERTIAN || (cls) == 1 + RS_MAT_DIELECTRIC || (cls) == 1 + RS_MAT_ISOTROPIC || (cls) == 1 + RS_MAT_BLINN_PHONG)
 // resident 256-thread blocks per SM the kernels are compiled for (register budget); tunable
 // at build time (make TUNE="-DRS_TUNE_EXTEND_LEAN=4 ...")
 #ifndef RS_TUNE_EXTEND_LEAN
@@ -278,10 +282,15 @@ __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); 
 #ifndef RS_TUNE_SHADE_STATIC
 #define RS_TUNE_SHADE_STATIC 0
 #endif
-// shade: classes whose paths always continue reserve their output slots before the shading math
-#ifndef RS_TUNE_SHADE_EARLY
-#define RS_TUNE_SHADE_EARLY 0
+// extend reserves the output slots of always-continuing classes for shade (lean kernels)
+#ifndef RS_TUNE_RESERVE
+#define RS_TUNE_RESERVE 1
 #endif
+// shade: batches of 32 hits a warp takes per atomicAdd on the work cursor
+#ifndef RS_TUNE_SHADE_CHUNK
+#define RS_TUNE_SHADE_CHUNK 2
+#endif
+
 #ifndef RS_TUNE_SHADE_GENERIC
 #define RS_TUNE_SHADE_GENERIC 2
 #endif
@@ -438,6 +447,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
     const PathBuf& in = ws.buf[bounce & 1];
     uint32_t* head = &ws.ctr->extend_head[bounce];
     uint32_t* class_count = ws.ctr->class_count[bounce];
+    const bool last_bounce = bounce + 1 >= fp.depth;
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_segments, (unsigned long long)(nf + nb));
     // the cursor bump for the NEXT batch is issued before the current batch is processed, so the
     // atomic's round trip to L2 overlaps with the traversal instead of heading every batch
@@ -463,12 +473,19 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
         const bool live = v < nf32 ? v < nf : v < n;
         const uint32_t i = v < nf32 ? v : ws.capacity - 1u - (v - nf32);
         int cls = -1;
+        uint2* queue_slot = nullptr;
+        RngCtx rng_of_lane;
+        rng_of_lane.key = fp.key;
+        rng_of_lane.pixel = 0;
+        rng_of_lane.sample = 0;
+        rng_of_lane.depth = (uint32_t)bounce + 1;
         if (live) {
             Ray ray;
             RngCtx rng;
             rng.key = fp.key;
             load_ray_only(in, i, ray, rng.pixel, rng.sample);
             rng.depth = (uint32_t)bounce + 1;
+            if constexpr (RS_TUNE_RESERVE && MODE < 2) rng_of_lane = rng;
             Closest best;
             closest_hit<MODE, WIDE>(S, ray, rng, best);
             HitA h;
@@ -498,6 +515,27 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
         }
         // material-coherent bucketing
         const uint32_t active = __ballot_sync(0xffffffffu, live && cls >= 0);
+        // Paths of the classes in RS_ALWAYS_CONTINUES always go on after shading (their `scatter`
+        // never returns None), and whether the next ray is the light-directed one is decided by the
+        // first word of the P_SCATTER draw alone (camera.rs:198).  Their slot in the next bounce's
+        // path buffer is therefore reserved HERE and handed to shade with the queue entry: shade
+        // (4 warps per scheduler, latency-bound) runs these classes without any atomic or ballot,
+        // while this kernel has the warps to hide the two extra round trips to L2.
+        constexpr bool RESERVE = RS_TUNE_RESERVE && MODE < 2;  // lean kernels only: the generic one is register-bound and its shade does not gain
+        bool reserve = false, res_front = false;
+        uint32_t mf = 0, mb = 0, bf = 0, bb = 0, lf = 0, lb = 0;
+        if constexpr (RESERVE) {
+            if (live && cls >= 0 && !last_bounce && RS_ALWAYS_CONTINUES(cls)) {
+                reserve = true;
+                res_front = cls != 1 + RS_MAT_DIELECTRIC && u01(rng_words(rng_of_lane, P_SCATTER, 0).x) < 0.5;
+            }
+            mf = __ballot_sync(0xffffffffu, reserve && res_front);
+            mb = __ballot_sync(0xffffffffu, reserve && !res_front);
+            lf = mf ? (uint32_t)(__ffs(mf) - 1) : 0u;
+            lb = mb ? (uint32_t)(__ffs(mb) - 1) : 0u;
+            if (mf && lane_id() == lf) bf = atomic_add_async(&ws.ctr->n_rays[bounce + 1], __popc(mf), lane_zero);
+            if (mb && lane_id() == lb) bb = atomic_add_async(&ws.ctr->n_back[bounce + 1], __popc(mb), lane_zero);
+        }
         if (live && cls >= 0) {
             const uint32_t peers = __match_any_sync(active, cls);
             const uint32_t leader = __ffs(peers) - 1;
@@ -505,7 +543,18 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
             if (lane_id() == leader) qbase = atomic_add_async(&class_count[cls], __popc(peers), lane_zero);
             qbase = __shfl_sync(peers, qbase, leader);
             const uint32_t rank = __popc(peers & ((1u << lane_id()) - 1u));
-            ws.class_queue[(size_t)cls * ws.capacity + qbase + rank] = i;
+            uint2* const slot = ws.class_queue + ((size_t)cls * ws.capacity + qbase + rank);
+            if constexpr (!RESERVE) *slot = make_uint2(i, 0xffffffffu);
+            else queue_slot = slot;
+        }
+        if constexpr (RESERVE) {
+            bf = __shfl_sync(0xffffffffu, bf, lf);
+            bb = __shfl_sync(0xffffffffu, bb, lb);
+            if (live && cls >= 0) {
+                const uint32_t lt = (1u << lane_id()) - 1u;
+                const uint32_t out_pos = !reserve ? 0xffffffffu : (res_front ? bf + __popc(mf & lt) : ws.capacity - 1u - (bb + __popc(mb & lt)));
+                *queue_slot = make_uint2(i, out_pos);
+            }
         }
     }
 }
@@ -647,7 +696,8 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
     const uint32_t lane_zero = RS_LANE_ZERO(ws);
     unsigned char* const warp_smem = reinterpret_cast<unsigned char*>(s_stage) + (size_t)(threadIdx.x >> 5) * RS_SHADE_WARP_SMEM;
     uint4* const stage = reinterpret_cast<uint4*>(warp_smem) + lane;
-    uint32_t* const idxq = reinterpret_cast<uint32_t*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16) + lane;  // [2][32]
+    uint2* const idxq = reinterpret_cast<uint2*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16) + lane;                   // [2][32]
+    uint32_t* const outq = reinterpret_cast<uint32_t*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 8) + lane;  // [2][32]
 
     // virtual index space: each class padded to a multiple of 32 so a warp never mixes classes
     // (the table stays in registers: a shared-memory copy measured 20% slower)
@@ -662,7 +712,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
 
     // batch -> (class, is this lane's entry real, its address in the class queue); the table stays
     // in registers (constant indices)
-    auto classify = [&](uint32_t base, int& cls, bool& live, const uint32_t*& entry) {
+    auto classify = [&](uint32_t base, int& cls, bool& live, const uint2*& entry) {
         cls = 0;
         uint32_t cb = 0, cn = cls_count[0];
 #pragma unroll
@@ -674,8 +724,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
     };
     // one atomicAdd per batch of 32, issued one batch ahead of its use
 #if RS_TUNE_SHADE_STATIC
-    // every batch of one class costs about the same, so a static round robin balances as well as
-    // a global cursor and needs no atomic (the cursor was the top stall of this kernel)
+    // static round robin (measured slower than the cursor: kept for experiments)
     (void)head;
     uint32_t next_base = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32u;
     const uint32_t base_stride = gridDim.x * (blockDim.x >> 5) * 32u;
@@ -685,15 +734,36 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
         return b;
     };
 #else
-    uint32_t pend = 0;
-    if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
+    // Lean kernel: one atomicAdd on the cursor per RS_TUNE_SHADE_CHUNK batches.  At 128 registers ptxas spills
+    // a cursor value that is fetched a batch ahead, and the spill store waits for the atomic on the
+    // spot (the top stall of this kernel in the profiles) — so the round trip is paid where the
+    // value is needed, but only once per chunk.
+    // The generic kernel keeps the cursor value fetched a batch ahead (it has no staging pipeline
+    // to feed, and measured faster that way).
+    constexpr uint32_t CHUNK = GENERIC ? 1u : (uint32_t)RS_TUNE_SHADE_CHUNK;
+    uint32_t chunk_base = 0, chunk_left = 0, pend = 0;
+    if (CHUNK == 1 && lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
     auto next_batch = [&]() -> uint32_t {
-        const uint32_t b = __shfl_sync(0xffffffffu, pend, 0);
-        if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
+        if constexpr (CHUNK == 1) {
+            const uint32_t b = __shfl_sync(0xffffffffu, pend, 0);
+            if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
+            return b;
+        }
+        if (chunk_left == 0) {
+            uint32_t v = 0;
+            if (lane == 0) v = atomic_add_async(head, 32u * CHUNK, lane_zero);
+            chunk_base = __shfl_sync(0xffffffffu, v, 0);
+            chunk_left = CHUNK;
+        }
+        const uint32_t b = chunk_base;
+        chunk_base += 32u;
+        --chunk_left;
         return b;
     };
 #endif
-    auto stage_item = [&](int buf, uint32_t i) {
+    auto stage_item = [&](int buf, uint2 entry) {  // entry = (path index, output slot reserved by extend)
+        const uint32_t i = entry.x;
+        outq[buf * 32] = entry.y;
         uint4* s = stage + buf * (RS_SHADE_STAGE * 32);
         cp_async16(s, in.a + i);
         cp_async16(s + 32, in.b + i);
@@ -719,17 +789,17 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
     if constexpr (STAGED) {
         base0 = next_batch();
         base1 = next_batch();
-        const uint32_t* entry;
+        const uint2* entry;
         classify(base0, cls0, live0, entry);
         if (live0) stage_item(0, *entry);
         classify(base1, cls1, live1, entry);
-        if (live1) cp_async4(idxq + 32, entry);
+        if (live1) cp_async8(idxq + 32, entry);
         cp_async_commit();
     }
     while (true) {
         int cls;
         bool live;
-        uint32_t i = 0;
+        uint32_t i = 0, out_pos = 0xffffffffu;
         uint32_t base2 = 0;
         if constexpr (STAGED) {
             if (base0 >= total) break;
@@ -739,9 +809,13 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
         } else {
             base0 = next_batch();
             if (base0 >= total) break;
-            const uint32_t* entry;
+            const uint2* entry;
             classify(base0, cls, live, entry);
-            if (live) i = *entry;
+            if (live) {
+                const uint2 e = *entry;
+                i = e.x;
+                out_pos = e.y;
+            }
         }
         const bool never = cls == 0 || cls == 1 + RS_MAT_DIFFUSE_LIGHT || last_bounce;  // miss / light never continue
 
@@ -751,9 +825,9 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
         if constexpr (STAGED) {
             cp_async_wait_all();  // records of batch k (stage[buf]) and queue entries of k+1 (idxq[buf ^ 1])
             if (live1) stage_item(buf ^ 1, idxq[(buf ^ 1) * 32]);
-            const uint32_t* entry;
+            const uint2* entry;
             classify(base2, cls2, live2, entry);
-            if (live2) cp_async4(idxq + buf * 32, entry);
+            if (live2) cp_async8(idxq + buf * 32, entry);
             cp_async_commit();
         }
 
@@ -787,25 +861,6 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
             }
             rng.pixel = p.pixel;
             rng.sample = p.sample;
-        }
-        // Paths of these classes always continue (their `scatter` never returns None), and whether
-        // the next ray is light-directed is decided by the first word of the P_SCATTER draw alone
-        // (camera.rs:198): their output slots are reserved BEFORE the shading math, so the two
-        // atomics' round trips to L2 overlap with it instead of ending every batch.
-        const bool early = RS_TUNE_SHADE_EARLY && !never &&
-                           (cls == 1 + RS_MAT_LAMBERTIAN || cls == 1 + RS_MAT_DIELECTRIC || cls == 1 + RS_MAT_ISOTROPIC || cls == 1 + RS_MAT_BLINN_PHONG);
-        uint4 w_sc = make_uint4(0u, 0u, 0u, 0u);
-        uint32_t e_mf = 0, e_mb = 0, e_bf = 0, e_bb = 0;
-        if (early) {
-            bool e_front = false;
-            if (live) {
-                w_sc = rng_words(rng, P_SCATTER, 0);
-                e_front = cls != 1 + RS_MAT_DIELECTRIC && u01(w_sc.x) < 0.5;
-            }
-            e_mf = __ballot_sync(0xffffffffu, live && e_front);
-            e_mb = __ballot_sync(0xffffffffu, live && !e_front);
-            if (e_mf && lane == (uint32_t)(__ffs(e_mf) - 1)) e_bf = atomic_add_async(out_front, __popc(e_mf), lane_zero);
-            if (e_mb && lane == (uint32_t)(__ffs(e_mb) - 1)) e_bb = atomic_add_async(out_back, __popc(e_mb), lane_zero);
         }
         if (live) {
             float3 add = make_float3(0.f, 0.f, 0.f);  // radiance added at this vertex (before T)
@@ -876,7 +931,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                                 double x = 1.0 - cos_theta;
                                 reflect_prob = fma(1.0 - r0, x * x * x * x * x, r0);
                             }
-                            const uint4 w = early ? w_sc : rng_words(rng, P_SCATTER, 0);
+                            const uint4 w = rng_words(rng, P_SCATTER, 0);
                             if (!(u01(w.w) < reflect_prob)) {
                                 V3 r_parallel = refractive * (p.ray.d + cos_theta * h.normal);
                                 V3 r_perp = (-sqrt(1.0 - length_squared(r_parallel))) * h.normal;
@@ -912,7 +967,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                     P.r_in = p.ray.d;
                     P.r_w = (P.kind == 1 || P.kind == 2) ? unit_fast(reflected) : v3(0, 0, 0);
                     double light_multi = 1.0, pdf_val;
-                    const uint4 w = early ? w_sc : rng_words(rng, P_SCATTER, 0);
+                    const uint4 w = rng_words(rng, P_SCATTER, 0);
                     if (u01(w.x) < 0.5) {  // camera.rs:198-213
                         kind = 3;
                         pdf_val = 0.3183098861837907;
@@ -967,21 +1022,23 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
             }
         }
         if (!never) {
-            // survivors: light-directed rays onto the front stack, the others onto the back stack
-            uint32_t mf = e_mf, mb = e_mb, bf = e_bf, bb = e_bb;
-            if (!early) {
-                mf = __ballot_sync(0xffffffffu, survive && front);
-                mb = __ballot_sync(0xffffffffu, survive && !front);
-            }
-            const uint32_t lf = mf ? (uint32_t)(__ffs(mf) - 1) : 0u, lb = mb ? (uint32_t)(__ffs(mb) - 1) : 0u;
-            if (!early) {
+            if constexpr (STAGED) out_pos = outq[buf * 32];
+            if (__any_sync(0xffffffffu, live && out_pos != 0xffffffffu)) {
+                // the slots were reserved by extend (see there; the same for every hit of the class):
+                // no atomic, no ballot
+                if (survive) store_path(out, out_pos, p);
+            } else {
+                // survivors: light-directed rays onto the front stack, the others onto the back stack
+                const uint32_t mf = __ballot_sync(0xffffffffu, survive && front), mb = __ballot_sync(0xffffffffu, survive && !front);
+                const uint32_t lf = mf ? (uint32_t)(__ffs(mf) - 1) : 0u, lb = mb ? (uint32_t)(__ffs(mb) - 1) : 0u;
+                uint32_t bf = 0, bb = 0;
                 if (mf && lane == lf) bf = atomic_add_async(out_front, __popc(mf), lane_zero);
                 if (mb && lane == lb) bb = atomic_add_async(out_back, __popc(mb), lane_zero);
+                bf = __shfl_sync(0xffffffffu, bf, lf);
+                bb = __shfl_sync(0xffffffffu, bb, lb);
+                const uint32_t lt = (1u << lane) - 1u;
+                if (survive) store_path(out, front ? bf + __popc(mf & lt) : ws.capacity - 1u - (bb + __popc(mb & lt)), p);
             }
-            bf = __shfl_sync(0xffffffffu, bf, lf);
-            bb = __shfl_sync(0xffffffffu, bb, lb);
-            const uint32_t lt = (1u << lane) - 1u;
-            if (survive) store_path(out, front ? bf + __popc(mf & lt) : ws.capacity - 1u - (bb + __popc(mb & lt)), p);
         }
         if constexpr (STAGED) {  // rotate the pipeline
             base0 = base1; cls0 = cls1; live0 = live1;

@@ -54,7 +54,7 @@ struct WaveState {
     PathBuf buf[2];
     HitA* hit;
     double* hit_end;
-    uint32_t* class_queue;  // RS_NUM_CLASSES * capacity
+    uint2* class_queue;     // RS_NUM_CLASSES * capacity entries of (path index, output slot reserved by extend or ~0)
     float4* contrib;        // per slot: radiance of the finished path
     WaveCounters* ctr;
     DeviceStats* stats;
