@@ -152,7 +152,36 @@ int build_bvh(std::vector<BuildPrim>& prims, size_t lo, size_t hi, int depth, st
     size_t mid = lo + (hi - lo) / 2;
     int axis = 0;
     bool split_done = false;
-    if (depth < 24) {
+    // small ranges: exact sweep SAH (every split position on every axis, objects sorted by centroid)
+    static const int sweep_max = [] { const char* e = std::getenv("RAYSNAIL_B200_SAH_SWEEP"); return e ? std::atoi(e) : 4096; }();
+    if (depth < 48 && prims.size() <= (size_t)sweep_max) {  // whole scene small: build time stays negligible
+        const size_t n = hi - lo;
+        double best_cost = DBL_MAX;
+        int best_axis = -1;
+        size_t best_k = 0;
+        std::vector<double> rarea(n);
+        for (int a = 0; a < 3; ++a) {
+            std::stable_sort(prims.begin() + lo, prims.begin() + hi, [&](const BuildPrim& x, const BuildPrim& y) { return x.c[a] < y.c[a]; });
+            double rl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, rh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+            for (size_t k = n; k-- > 1;) {
+                for (int d = 0; d < 3; ++d) { rl[d] = std::min(rl[d], prims[lo + k].lo[d]); rh[d] = std::max(rh[d], prims[lo + k].hi[d]); }
+                rarea[k] = half_area(rl, rh);
+            }
+            double ll[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, lh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+            for (size_t k = 1; k < n; ++k) {
+                for (int d = 0; d < 3; ++d) { ll[d] = std::min(ll[d], prims[lo + k - 1].lo[d]); lh[d] = std::max(lh[d], prims[lo + k - 1].hi[d]); }
+                const double cost = half_area(ll, lh) * (double)k + rarea[k] * (double)(n - k);
+                if (cost < best_cost) { best_cost = cost; best_axis = a; best_k = k; }
+            }
+        }
+        if (best_axis >= 0) {
+            axis = best_axis;
+            if (axis != 2) std::stable_sort(prims.begin() + lo, prims.begin() + hi, [&](const BuildPrim& x, const BuildPrim& y) { return x.c[axis] < y.c[axis]; });
+            mid = lo + best_k;
+            split_done = true;
+        }
+    }
+    if (!split_done && depth < 24) {
         double cb[6];
         for (int a = 0; a < 3; ++a) { cb[a] = DBL_MAX; cb[3 + a] = -DBL_MAX; }
         for (size_t i = lo; i < hi; ++i)
