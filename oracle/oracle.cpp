@@ -1343,9 +1343,9 @@ rso_world* rso_world_create(const rs_scene_desc* desc, int use_desc_bbox) {
 void rso_world_free(rso_world* w) { delete w; }
 
 // The oracle's own `Hittable::bbox` of every world object (6 doubles each).
-int rso_root_bbox(const rso_world* w, double* out) {
+int rso_root_bbox(const rso_world* w, double time_start, double time_end, double* out) {
     for (size_t i = 0; i < w->scene.roots.size(); ++i) {
-        AABB b = w->scene.roots[i]->bbox(Range{0.0, 0.0});
+        AABB b = w->scene.roots[i]->bbox(Range{time_start, time_end});
         double* o = out + 6 * i;
         o[0] = b.min.x; o[1] = b.min.y; o[2] = b.min.z; o[3] = b.max.x; o[4] = b.max.y; o[5] = b.max.z;
     }

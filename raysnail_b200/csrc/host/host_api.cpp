@@ -82,6 +82,7 @@ int rs_host_scene_builtin(const char* name, uint64_t seed, int32_t iparam, rs_ho
         else if (n == "cornell") s->world = recipes::cornell_box_world(true, true, false, s->camera);
         else if (n == "cornell_smoke") s->world = recipes::cornell_box_world(true, true, true, s->camera);
         else if (n == "cornell_plain") s->world = recipes::cornell_box_world(true, false, false, s->camera);
+        else if (n == "all_feature") s->world = recipes::all_feature_world(seed, s->camera);
         else if (n == "mesh") s->world = recipes::mesh_test_world(iparam > 2 ? iparam : 64, false, s->camera);
         else if (n == "mesh_blinn") s->world = recipes::mesh_test_world(iparam > 2 ? iparam : 64, true, s->camera);
         else { g_host_error = "unknown builtin scene: " + n; return (int)RS_ERR_INVALID_ARGUMENT; }

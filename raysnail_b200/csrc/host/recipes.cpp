@@ -5,6 +5,8 @@
 //   mesh test                        : examples/preview_sdl2.rs:452-525 (procedural mesh: the
 //                                      reference's objects/dragon.obj is not in its repository)
 #include <cmath>
+#include <cstdlib>
+#include <string>
 
 #include "scene.hpp"
 #include "seed_random.hpp"
@@ -205,6 +207,89 @@ std::unique_ptr<World> mesh_test_world(int grid_n, bool blinn_phong, CameraBuild
     world.add(Sphere(Point3(0.0, -1000.0, 0.0), 1000.0, std::make_shared<Metal>(solid(0.08f, 0.1f, 0.06f))));
     return std::make_unique<World>(world, lights, Color(0.68f, 0.80f, 0.95f, 1.0f), Color(0.2f, 0.4f, 0.7f, 1.0f),
                                    TimeRange{0.0, 0.0});
+}
+
+// examples/common/scene.rs:336-468 (`all_feature_scene`, the book-2 final scene).  The nested
+// `BVH::new(boxes1)` object (scene.rs:361) is an accelerator, not geometry: `BVH::hit` returns the
+// closest hit of its members, so its 400 boxes are added to the world list directly (the world
+// BVH takes its place).  `boxes2` is built but never added by the reference (scene.rs:437-458);
+// its 3000 draws are still consumed so that the RNG stream stays aligned.  No binary of the
+// reference renders this scene: lights = the ceiling rect, black background (book convention).
+// The earth texture is `examples/earth-map.png` relative to the working directory like in the
+// reference, else $RAYSNAIL_ASSETS/earth-map.png, else a procedural 1920x960 stand-in.
+std::unique_ptr<World> all_feature_world(uint64_t seed, CameraBuilder& cam_out) {
+    const TimeRange time_limit{0.0, 1.0};
+    const int boxes_per_side = 20;
+    SeedRandom rng(seed);
+    HittableList objects;
+    auto ground = std::make_shared<Lambertian>(solid(0.48f, 0.83f, 0.53f));
+    for (int i = 0; i < boxes_per_side; ++i)
+        for (int j = 0; j < boxes_per_side; ++j) {
+            const double w = 100.0;
+            const double x0 = -1000.0 + (double)i * w, z0 = -1000.0 + (double)j * w, y0 = 0.0;
+            const double x1 = x0 + w, y1 = rng.range(1.0, 100.0), z1 = z0 + w;
+            objects.add(Box(Point3(x0, y0, z0), Point3(x1, y1, z1), ground));
+        }
+    auto light = std::make_shared<DiffuseLight>(solid(1.f, 1.f, 1.f));
+    light->multiplier(7.0);
+    HittablePtr light_rect = std::make_shared<AARect>(AARect::new_xz(AARectMetrics(554.0, 123.0, 423.0, 147.0, 412.0), light));
+    objects.add_ref(light_rect);
+
+    Sphere moving(Point3(400.0, 400.0, 200.0), 50.0, std::make_shared<Lambertian>(solid(0.7f, 0.3f, 0.1f)));
+    moving.with_speed(Vec3(30.0, 0.0, 0.0));
+    objects.add(std::move(moving));
+
+    auto glass = [] {
+        auto d = std::make_shared<Dielectric>(Color(1.f, 1.f, 1.f, 1.f), 1.5);
+        d->reflect_curve_glass();
+        return d;
+    };
+    objects.add(Sphere(Point3(260.0, 150.0, 45.0), 50.0, glass()));
+    objects.add(Sphere(Point3(0.0, 150.0, 145.0), 50.0, std::make_shared<Metal>(solid(0.8f, 0.8f, 0.9f))));
+    objects.add(Sphere(Point3(360.0, 170.0, 145.0), 70.0, glass()));
+    objects.add_ref(std::make_shared<ConstantMedium>(
+        std::make_shared<Sphere>(Point3(360.0, 170.0, 145.0), 70.0, std::make_shared<Lambertian>(solid(1.f, 1.f, 1.f))),
+        Color(0.2f, 0.4f, 0.9f, 1.f), 0.2));
+    objects.add_ref(std::make_shared<ConstantMedium>(std::make_shared<Sphere>(Point3(0.0, 0.0, 0.0), 5000.0, glass()),
+                                                     Color(1.f, 1.f, 1.f, 1.f), 0.0001));
+
+    std::shared_ptr<Image> earth;
+    for (std::string path : {std::string("examples/earth-map.png"),
+                             std::string(std::getenv("RAYSNAIL_ASSETS") ? std::getenv("RAYSNAIL_ASSETS") : ".") + "/earth-map.png"}) {
+        try { earth = Image::open(path); break; } catch (...) {}
+    }
+    if (!earth) {  // procedural stand-in: oceans, two "continents", polar caps
+        const int W = 1920, H = 960;
+        std::vector<uint8_t> px((size_t)W * H * 4);
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x) {
+                const double u = (double)x / W, v = (double)y / H;
+                const double land = std::sin(6.2831853 * 2.0 * u + 3.0 * std::sin(9.0 * v)) * std::cos(3.14159265 * (v - 0.5) * 1.7);
+                uint8_t r = 20, g = 60, b = 140;
+                if (land > 0.35) { r = 60; g = 130; b = 50; }
+                if (v < 0.07 || v > 0.93) { r = 235; g = 240; b = 245; }
+                uint8_t* q = &px[4 * ((size_t)y * W + x)];
+                q[0] = r; q[1] = g; q[2] = b; q[3] = 255;
+            }
+        earth = std::make_shared<Image>(W, H, std::move(px));
+    }
+    objects.add(Sphere(Point3(400.0, 200.0, 400.0), 100.0, std::make_shared<Lambertian>(earth)));
+
+    auto tex = std::make_shared<Perlin>(256, true, seed ^ 0x9E3779B97F4A7C15ull);
+    tex->scale(0.1).smooth(SmoothType::HermitianCubic);
+    objects.add(Sphere(Point3(220.0, 280.0, 300.0), 80.0, std::make_shared<Lambertian>(tex)));
+
+    for (int k = 0; k < 1000; ++k) {  // boxes2: drawn, then dropped (scene.rs:437-458)
+        (void)rng.range(0.0, 165.0);
+        (void)rng.range(0.0, 165.0);
+        (void)rng.range(0.0, 165.0);
+    }
+
+    cam_out = CameraBuilder();
+    cam_out.look_from(Point3(478.0, 278.0, -600.0)).look_at(Point3(278.0, 278.0, 0.0)).fov(40.0).shutter_speed(1.0);
+    HittableList lights;
+    lights.add_ref(light_rect);
+    return std::make_unique<World>(objects, lights, Color(0.f, 0.f, 0.f, 1.f), Color(0.f, 0.f, 0.f, 1.f), time_limit);
 }
 
 }  // namespace recipes

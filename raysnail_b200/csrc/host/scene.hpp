@@ -472,6 +472,7 @@ std::unique_ptr<World> rtow_final_world(uint64_t seed, CameraBuilder& cam_out);
 std::unique_ptr<World> cornell_box_world(bool carton, bool carton_rotation, bool smoke, CameraBuilder& cam_out);
 // scene shape of examples/preview_sdl2.rs:452-525 with a procedural mesh instead of dragon.obj
 std::unique_ptr<World> mesh_test_world(int grid_n, bool blinn_phong, CameraBuilder& cam_out);
+std::unique_ptr<World> all_feature_world(uint64_t seed, CameraBuilder& cam_out);  // scene.rs:336-468
 }  // namespace recipes
 
 }  // namespace raysnail

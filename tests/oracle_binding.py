@@ -29,7 +29,7 @@ def load():
     lib.rso_world_create.argtypes = [P(RsSceneDesc), C.c_int]
     lib.rso_world_free.restype = None
     lib.rso_world_free.argtypes = [vp]
-    lib.rso_root_bbox.argtypes = [vp, vp]
+    lib.rso_root_bbox.argtypes = [vp, C.c_double, C.c_double, vp]
     lib.rso_philox4x32_10.argtypes = [vp, vp, vp]
     lib.rso_render.argtypes = [vp, P(RsCamera), P(RsRenderParams), vp, vp, C.c_int, P(RsStats)]
     lib.rso_debug_primary.argtypes = [vp, P(RsCamera), P(RsRenderParams), i32, vp, vp, vp, vp, vp, vp, vp]
@@ -58,9 +58,10 @@ class OracleWorld:
         except Exception:
             pass
 
-    def root_bbox(self):
+    def root_bbox(self, time_range=(0.0, 0.0)):
+        """`Hittable::bbox(time_limit)` of every world object (the range only matters for moving spheres)."""
         out = np.zeros((self.n_roots, 6))
-        self._lib.rso_root_bbox(self._w, out.ctypes.data)
+        self._lib.rso_root_bbox(self._w, float(time_range[0]), float(time_range[1]), out.ctypes.data)
         return out
 
     def render(self, cam, params, mask=None, threads=0):

@@ -85,6 +85,7 @@ def _luminance(img):
     ("csg", (64, 40), 1024),
     ("cornell", (48, 48), 1024),
     ("mesh_blinn", (64, 64), 256),
+    ("all_feature", (48, 48), 1024),
 ])
 def test_converged_image_parity(renderer, name, size, samples):
     """Same Philox streams on both sides, so the images agree far better than the Monte-Carlo

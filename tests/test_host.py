@@ -133,7 +133,8 @@ def test_host_bbox_rules_match_the_oracle(name):
     """Two independent restatements of every Hittable::bbox (host C++ layer vs oracle)."""
     s = load_scene(name)
     host = s.root_bbox()
-    oracle = OracleWorld(s, use_desc_bbox=False).root_bbox()
+    # the recipes' `time_limit`: 0..1 for all_feature_scene (scene.rs:337), 0..0 elsewhere
+    oracle = OracleWorld(s, use_desc_bbox=False).root_bbox((0.0, 1.0) if name == "all_feature" else (0.0, 0.0))
     assert host.shape == oracle.shape and np.array_equal(host, oracle)
 
 
@@ -193,6 +194,29 @@ def test_rtow_final_scene_recipe():
     assert all(n.p[3] == 0.2 and 0.2 <= n.p[1] <= 1.1 for n in small)
     kinds = np.bincount([d.materials[n.material].type for n in small], minlength=4)
     assert kinds[0] > 300 and kinds[3] > 5 and kinds[1] + kinds[2] > 30
+
+
+def test_all_feature_scene_recipe():
+    """examples/common/scene.rs:336-468: 400 ground boxes (the nested BVH flattened), the ceiling light,
+    a moving sphere, glass / metal spheres, two constant media, an image and a Perlin texture."""
+    s = Scene.builtin("all_feature", 7)
+    d = s.desc.contents
+    assert d.n_roots == 409 and d.n_lights == 1
+    boxes = [d.nodes[d.roots[i]] for i in range(400)]
+    assert all(b.type == 1 for b in boxes)                                   # RS_NODE_BOX
+    assert tuple(boxes[0].p[:3]) == (-1000.0, 0.0, -1000.0) and boxes[0].p[3] == -900.0 and boxes[0].p[5] == -900.0
+    assert all(1.0 <= b.p[4] < 100.0 for b in boxes)                         # y1 = rng.range(1..100)
+    light = d.nodes[d.roots[400]]
+    assert light.type == 2 and d.materials[light.material].type == 4 and d.materials[light.material].a == 7.0
+    moving = d.nodes[d.roots[401]]
+    assert tuple(moving.p[:7]) == (400.0, 400.0, 200.0, 50.0, 30.0, 0.0, 0.0)
+    assert [d.nodes[d.roots[i]].type for i in (405, 406)] == [7, 7]          # RS_NODE_MEDIUM
+    assert d.nodes[d.roots[406]].p[0] == 0.0001 or 0.0001 in tuple(d.nodes[d.roots[406]].p[:8])
+    tex_types = sorted(d.textures[i].type for i in range(d.n_textures))
+    assert 2 in tex_types and 3 in tex_types                                 # image + Perlin
+    assert d.n_texel_bytes == 1920 * 960 * 4 and d.n_perlin_perm == 3 * 256
+    cam = s.camera(64, 64)
+    assert cam.shutter_speed == 1.0
 
 
 def test_chacha12_block_known_answer_and_stdrng_stream():
