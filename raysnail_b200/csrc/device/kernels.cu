@@ -537,13 +537,14 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
             if (mb && lane_id() == lb) bb = atomic_add_async(&ws.ctr->n_back[bounce + 1], __popc(mb), lane_zero);
         }
         if (live && cls >= 0) {
-            const uint32_t peers = __match_any_sync(active, cls);
+            const int key = (RESERVE && res_front) ? RS_FRONT_CLASS(cls) : cls;  // (class, branch) bucket
+            const uint32_t peers = __match_any_sync(active, key);
             const uint32_t leader = __ffs(peers) - 1;
             uint32_t qbase = 0;
-            if (lane_id() == leader) qbase = atomic_add_async(&class_count[cls], __popc(peers), lane_zero);
+            if (lane_id() == leader) qbase = atomic_add_async(&class_count[key * RS_COUNTER_STRIDE], __popc(peers), lane_zero);
             qbase = __shfl_sync(peers, qbase, leader);
             const uint32_t rank = __popc(peers & ((1u << lane_id()) - 1u));
-            uint2* const slot = ws.class_queue + ((size_t)cls * ws.capacity + qbase + rank);
+            uint2* const slot = ws.class_queue + ((size_t)key * ws.capacity + qbase + rank);
             if constexpr (!RESERVE) *slot = make_uint2(i, 0xffffffffu);
             else queue_slot = slot;
         }
@@ -699,30 +700,31 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
     uint2* const idxq = reinterpret_cast<uint2*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16) + lane;                   // [2][32]
     uint32_t* const outq = reinterpret_cast<uint32_t*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 8) + lane;  // [2][32]
 
-    // virtual index space: each class padded to a multiple of 32 so a warp never mixes classes
-    // (the table stays in registers: a shared-memory copy measured 20% slower)
-    uint32_t cls_count[RS_NUM_CLASSES], cls_begin[RS_NUM_CLASSES + 1];
-    cls_begin[0] = 0;
+    // virtual index space: each class padded to a multiple of 32 so a warp never mixes classes.
+    // The table is spread over the lanes of the warp (lane c holds class c: two registers instead
+    // of 2 * RS_NUM_CLASSES): padded begins by a warp scan, lane RS_NUM_CLASSES holds the total.
+    uint32_t my_count = lane < RS_NUM_CLASSES ? class_count[lane * RS_COUNTER_STRIDE] : 0u;
+    uint32_t my_begin = (my_count + 31u) & ~31u;
 #pragma unroll
-    for (int c = 0; c < RS_NUM_CLASSES; ++c) {
-        cls_count[c] = class_count[c];
-        cls_begin[c + 1] = cls_begin[c] + ((cls_count[c] + 31u) & ~31u);
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, my_begin, d);
+        if ((int)lane >= d) my_begin += v;
     }
-    const uint32_t total = cls_begin[RS_NUM_CLASSES];
+    my_begin = __shfl_up_sync(0xffffffffu, my_begin, 1);  // inclusive -> exclusive
+    if (lane == 0) my_begin = 0;
+    const uint32_t total = __shfl_sync(0xffffffffu, my_begin, RS_NUM_CLASSES);
 
-    // batch -> (class, is this lane's entry real, its address in the class queue); the table stays
-    // in registers (constant indices)
+    // batch -> (class, is this lane's entry real, its address in the class queue)
     auto classify = [&](uint32_t base, int& cls, bool& live, const uint2*& entry) {
-        cls = 0;
-        uint32_t cb = 0, cn = cls_count[0];
-#pragma unroll
-        for (int c = 1; c < RS_NUM_CLASSES; ++c)
-            if (base >= cls_begin[c]) { cls = c; cb = cls_begin[c]; cn = cls_count[c]; }
+        // highest class whose padded range starts at or before `base` (empty classes share their
+        // begin with the next one, so the highest index is the non-empty one)
+        const uint32_t m = __ballot_sync(0xffffffffu, lane < RS_NUM_CLASSES && my_begin <= base);
+        cls = 31 - __clz((int)(m | 1u));
+        const uint32_t cb = __shfl_sync(0xffffffffu, my_begin, cls), cn = __shfl_sync(0xffffffffu, my_count, cls);
         const uint32_t qi = base - cb + lane;
         live = base < total && qi < cn;
         entry = ws.class_queue + ((size_t)cls * ws.capacity + qi);
     };
-    // one atomicAdd per batch of 32, issued one batch ahead of its use
 #if RS_TUNE_SHADE_STATIC
     // static round robin (measured slower than the cursor: kept for experiments)
     (void)head;
@@ -817,6 +819,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                 out_pos = e.y;
             }
         }
+        cls = RS_BASE_CLASS(cls);  // the (class, branch) bucket -> the material class
         const bool never = cls == 0 || cls == 1 + RS_MAT_DIFFUSE_LIGHT || last_bounce;  // miss / light never continue
 
         const uint4* s = stage + buf * (RS_SHADE_STAGE * 32);

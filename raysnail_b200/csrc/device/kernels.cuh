@@ -10,7 +10,14 @@ namespace rsd {
 
 #define RS_MAX_DEPTH 64   // TakePhotoSettings::depth upper bound supported by the counter block
 #define RS_TRAVERSAL_STACK 96  // per-thread QBVH traversal stack entries (3 pushes per level at most)
-#define RS_NUM_CLASSES 8  // 0 = miss, 1 + rs_material_type for the resolved (non-mixed) material
+// Shade work classes: 0 = miss, 1 + rs_material_type for the resolved (non-mixed) material, and —
+// lean kernels, where extend already knows the light/BRDF branch draw — 8, 9, 10 = the hits of
+// Lambertian / Isotropic / BlinnPhong whose next ray is the light-directed one (camera.rs:198-213),
+// so that a warp of shade runs ONE of the two branches instead of both with half its lanes
+#define RS_NUM_CLASSES 11
+#define RS_COUNTER_STRIDE 32  // uint32 slots between two class counters (128 B)
+#define RS_FRONT_CLASS(cls) ((cls) == 1 + RS_MAT_LAMBERTIAN ? 8 : ((cls) == 1 + RS_MAT_ISOTROPIC ? 9 : ((cls) == 1 + RS_MAT_BLINN_PHONG ? 10 : (cls))))
+#define RS_BASE_CLASS(k) ((k) < 8 ? (k) : ((k) == 8 ? 1 + RS_MAT_LAMBERTIAN : ((k) == 9 ? 1 + RS_MAT_ISOTROPIC : 1 + RS_MAT_BLINN_PHONG)))
 
 // One path record is five 16-byte SoA elements (80 B), so every load/store is a full
 // 128-bit transaction and linear queues coalesce perfectly:
@@ -40,7 +47,9 @@ struct WaveCounters {
     // incoherent ones keeps the warps of extend homogeneous.
     uint32_t n_rays[RS_MAX_DEPTH + 1];
     uint32_t n_back[RS_MAX_DEPTH + 1];
-    uint32_t class_count[RS_MAX_DEPTH][RS_NUM_CLASSES];
+    // every hot counter on its own 128-byte line: atomics on one line serialise in L2, and in bounce 0
+    // all warps of extend bump the same two or three buckets
+    uint32_t class_count[RS_MAX_DEPTH][RS_NUM_CLASSES * RS_COUNTER_STRIDE];
     uint32_t extend_head[RS_MAX_DEPTH];           // persistent-thread work cursors
     uint32_t shade_head[RS_MAX_DEPTH];
 };
