@@ -75,6 +75,7 @@ struct rs_ctx {
     int bvh_width = 2;       // RS_OPT_BVH_WIDTH: 2 = binary 64-byte nodes (default), 4 = QBVH 128-byte nodes
     int extend_mode = 2;     // 0 static spheres only, 1 + triangles, 2 everything
     bool shade_generic = true;
+    bool uses_time = false;  // some sphere moves: rays carry their shutter time
     double scene_omax = 0.0, padded_omax = -1.0;
     int n_lights = 0;
 
@@ -82,7 +83,7 @@ struct rs_ctx {
     // every persistent kernel of one wave (SMs going idle as its last batches finish) is filled by
     // blocks of the other wave's kernel (RS_OPT_WAVE_STREAMS; `ws` is set 0 and the one the probes use)
     struct WaveSet {
-        DevBuf d_pa[2], d_pb[2], d_pc[2], d_pd[2], d_pe[2], d_hit, d_hit_end, d_cq, d_contrib, d_ctr;
+        DevBuf d_rec[2], d_time[2], d_hit, d_hit_end, d_cq, d_contrib, d_ctr;
         uint32_t capacity = 0;
     };
     static constexpr int kMaxSets = 4;
@@ -410,18 +411,13 @@ int ensure_wave_set(rs_ctx* ctx, int k, uint32_t cap) {
     WaveState& ws = k == 0 ? ctx->ws : ctx->ws_aux[k - 1];
     CK(ctx->d_stats.ensure(sizeof(DeviceStats)));
     ws.stats = ctx->d_stats.as<DeviceStats>();  // shared by both sets (atomic counters)
+    ws.uses_time = ctx->uses_time ? 1 : 0;
     if (cap <= w.capacity) return RS_OK;
     for (int b = 0; b < 2; ++b) {
-        CK(w.d_pa[b].ensure((size_t)cap * sizeof(double2)));
-        CK(w.d_pb[b].ensure((size_t)cap * sizeof(double2)));
-        CK(w.d_pc[b].ensure((size_t)cap * sizeof(double2)));
-        CK(w.d_pd[b].ensure((size_t)cap * sizeof(double2)));
-        CK(w.d_pe[b].ensure((size_t)cap * sizeof(uint4)));
-        ws.buf[b].a = w.d_pa[b].as<double2>();
-        ws.buf[b].b = w.d_pb[b].as<double2>();
-        ws.buf[b].c = w.d_pc[b].as<double2>();
-        ws.buf[b].d = w.d_pd[b].as<double2>();
-        ws.buf[b].e = w.d_pe[b].as<uint4>();
+        CK(w.d_rec[b].ensure((size_t)cap * 4 * sizeof(uint4)));
+        CK(w.d_time[b].ensure((size_t)cap * sizeof(double)));
+        ws.buf[b].rec = w.d_rec[b].as<uint4>();
+        ws.buf[b].time = w.d_time[b].as<double>();
     }
     CK(w.d_hit.ensure((size_t)cap * sizeof(HitA)));
     CK(w.d_hit_end.ensure((size_t)cap * sizeof(double)));
@@ -813,6 +809,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
         any_generic |= root_kind[p.root] == ROOT_GENERIC;
     }
     ctx->extend_mode = any_generic ? 2 : (any_tri ? 1 : 0);
+    ctx->uses_time = false;
+    for (const rs_node& n : nodes)
+        if (n.type == RS_NODE_SPHERE && (n.p[4] != 0.0 || n.p[5] != 0.0 || n.p[6] != 0.0)) ctx->uses_time = true;
     bool lights_simple = true;  // lights the lean shade kernel samples inline: plain spheres and rects
     for (int i = 0; i < s->n_lights; ++i) {
         const rs_node& n = nodes[s->lights[i]];

@@ -29,47 +29,54 @@ namespace rsd {
 // conversions of the ray; the absolute part (origin rounding) is folded into the padded boxes.
 #define RS_SLAB_EPS 9.5367431640625e-07f  // 2^-20
 
-__device__ __forceinline__ double pack_f2(float a, float b) {
-    return __hiloint2double(__float_as_int(b), __float_as_int(a));
-}
-__device__ __forceinline__ void unpack_f2(double d, float& a, float& b) {
-    a = __int_as_float(__double2loint(d));
-    b = __int_as_float(__double2hiint(d));
-}
-
 struct PathRec {
     Ray ray;
     float3 T;
     uint32_t slot, pixel, sample;
 };
 
-__device__ __forceinline__ void store_path(const PathBuf& B, uint32_t i, const PathRec& p) {
-    B.a[i] = make_double2(p.ray.o.x, p.ray.o.y);
-    B.b[i] = make_double2(p.ray.o.z, p.ray.time);
-    B.c[i] = make_double2(p.ray.d.x, p.ray.d.y);
-    B.d[i] = make_double2(p.ray.d.z, pack_f2(p.T.x, p.T.y));
-    B.e[i] = make_uint4(__float_as_uint(p.T.z), p.slot, p.pixel, p.sample);
+// slot -> (pixel, absolute sample index): the inverse of raygen's numbering
+__device__ __forceinline__ void decode_slot(const FrameParams& fp, uint32_t slot, uint32_t& pixel, uint32_t& sample) {
+    const uint32_t k_local = slot / fp.n_pixels, p_local = slot - k_local * fp.n_pixels;
+    pixel = fp.pixel0 + p_local;
+    const uint32_t j = fp.sample0 + k_local, q = (uint32_t)fp.sqrt_spp;
+    const uint32_t row = j / q;
+    sample = ((uint32_t)fp.stratum_row_begin + row) * q + (j - row * q);
 }
-__device__ __forceinline__ void load_path(const PathBuf& B, uint32_t i, PathRec& p) {
-    double2 a = B.a[i], b = B.b[i], c = B.c[i], d = B.d[i];
-    uint4 e = B.e[i];
-    p.ray.o = v3(a.x, a.y, b.x);
-    p.ray.time = b.y;
-    p.ray.d = v3(c.x, c.y, d.x);
-    unpack_f2(d.y, p.T.x, p.T.y);
-    p.T.z = __uint_as_float(e.x);
-    p.slot = e.y;
-    p.pixel = e.z;
-    p.sample = e.w;
+__device__ __forceinline__ void unpack_path(const FrameParams& fp, uint4 q0, uint4 q1, uint4 q2, uint4 q3, PathRec& p) {
+    p.ray.o = v3(__hiloint2double((int)q0.y, (int)q0.x), __hiloint2double((int)q0.w, (int)q0.z), __hiloint2double((int)q1.y, (int)q1.x));
+    p.ray.d = v3(__hiloint2double((int)q1.w, (int)q1.z), __hiloint2double((int)q2.y, (int)q2.x), __hiloint2double((int)q2.w, (int)q2.z));
+    p.ray.time = 0.0;
+    p.T = make_float3(__uint_as_float(q3.x), __uint_as_float(q3.y), __uint_as_float(q3.z));
+    p.slot = q3.w;
+    decode_slot(fp, p.slot, p.pixel, p.sample);
 }
-__device__ __forceinline__ void load_ray_only(const PathBuf& B, uint32_t i, Ray& r, uint32_t& pixel, uint32_t& sample) {
-    double2 a = B.a[i], b = B.b[i], c = B.c[i], d = B.d[i];
-    uint4 e = B.e[i];
-    r.o = v3(a.x, a.y, b.x);
-    r.time = b.y;
-    r.d = v3(c.x, c.y, d.x);
-    pixel = e.z;
-    sample = e.w;
+__device__ __forceinline__ uint4 pack_d2(double a, double b) {
+    return make_uint4((uint32_t)__double2loint(a), (uint32_t)__double2hiint(a), (uint32_t)__double2loint(b), (uint32_t)__double2hiint(b));
+}
+__device__ __forceinline__ void store_path(const WaveState& ws, const PathBuf& B, uint32_t i, const PathRec& p) {
+    uint4* r = B.rec + 4 * (size_t)i;
+    r[0] = pack_d2(p.ray.o.x, p.ray.o.y);
+    r[1] = pack_d2(p.ray.o.z, p.ray.d.x);
+    r[2] = pack_d2(p.ray.d.y, p.ray.d.z);
+    r[3] = make_uint4(__float_as_uint(p.T.x), __float_as_uint(p.T.y), __float_as_uint(p.T.z), p.slot);
+    if (ws.uses_time) B.time[i] = p.ray.time;
+}
+__device__ __forceinline__ void load_path(const FrameParams& fp, const WaveState& ws, const PathBuf& B, uint32_t i, PathRec& p) {
+    const uint4* r = B.rec + 4 * (size_t)i;
+    const uint4 q0 = r[0], q1 = r[1], q2 = r[2], q3 = r[3];
+    unpack_path(fp, q0, q1, q2, q3, p);
+    if (ws.uses_time) p.ray.time = B.time[i];
+}
+__device__ __forceinline__ void load_ray_only(const FrameParams& fp, const WaveState& ws, const PathBuf& B, uint32_t i, Ray& r, uint32_t& pixel,
+                                              uint32_t& sample) {
+    const uint4* rec = B.rec + 4 * (size_t)i;
+    const uint4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
+    const uint32_t slot = rec[3].w;
+    r.o = v3(__hiloint2double((int)q0.y, (int)q0.x), __hiloint2double((int)q0.w, (int)q0.z), __hiloint2double((int)q1.y, (int)q1.x));
+    r.d = v3(__hiloint2double((int)q1.w, (int)q1.z), __hiloint2double((int)q2.y, (int)q2.x), __hiloint2double((int)q2.w, (int)q2.z));
+    r.time = ws.uses_time ? B.time[i] : 0.0;
+    decode_slot(fp, slot, pixel, sample);
 }
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
@@ -118,8 +125,8 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 #define RS_TUNE_SHADE_BLOCK 256
 #endif
 #define RS_WARPS (RS_TUNE_SHADE_BLOCK / 32)
-// staging slots per lane of shade: the 5 path elements + the hit record; double buffered
-#define RS_SHADE_STAGE 6
+// staging slots per lane of shade: the 4 path elements + the hit record; double buffered
+#define RS_SHADE_STAGE 5
 // per warp: two record buffers + two 32-entry queue-entry buffers (uint2) + two 32-entry buffers
 // of reserved output slots
 #define RS_SHADE_WARP_SMEM (2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 8 + 2 * 32 * 4)
@@ -196,7 +203,7 @@ __global__ void __launch_bounds__(RS_BLOCK) raygen_kernel(const __grid_constant_
             }
         }
         uint32_t pos = warp_append(&ws.ctr->n_rays[0], live, RS_LANE_ZERO(ws));
-        if (live) store_path(ws.buf[0], pos, p);
+        if (live) store_path(ws, ws.buf[0], pos, p);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_samples, (unsigned long long)total);
 }
@@ -483,7 +490,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
             Ray ray;
             RngCtx rng;
             rng.key = fp.key;
-            load_ray_only(in, i, ray, rng.pixel, rng.sample);
+            load_ray_only(fp, ws, in, i, ray, rng.pixel, rng.sample);
             rng.depth = (uint32_t)bounce + 1;
             if constexpr (RS_TUNE_RESERVE && MODE < 2) rng_of_lane = rng;
             Closest best;
@@ -504,10 +511,8 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                 // a miss ends the path with `world.background(ray)` (camera.rs:253-254): finish it
                 // here instead of sending it through a queue to the shade kernel
                 const float4 bg = background(S, ray.d);
-                float tr, tg;
-                unpack_f2(in.d[i].y, tr, tg);
-                const uint4 e = in.e[i];
-                ws.contrib[e.y] = make_float4(tr * bg.x, tg * bg.y, __uint_as_float(e.x) * bg.z, 0.f);
+                const uint4 q3 = in.rec[4 * (size_t)i + 3];  // (T, slot)
+                ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * bg.x, __uint_as_float(q3.y) * bg.y, __uint_as_float(q3.z) * bg.z, 0.f);
                 cls = -1;
             } else {
                 ws.hit[i] = h;
@@ -767,12 +772,12 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
         const uint32_t i = entry.x;
         outq[buf * 32] = entry.y;
         uint4* s = stage + buf * (RS_SHADE_STAGE * 32);
-        cp_async16(s, in.a + i);
-        cp_async16(s + 32, in.b + i);
-        cp_async16(s + 64, in.c + i);
-        cp_async16(s + 96, in.d + i);
-        cp_async16(s + 128, in.e + i);
-        cp_async16(s + 160, ws.hit + i);
+        const uint4* r = in.rec + 4 * (size_t)i;
+        cp_async16(s, r);
+        cp_async16(s + 32, r + 1);
+        cp_async16(s + 64, r + 2);
+        cp_async16(s + 96, r + 3);
+        cp_async16(s + 128, ws.hit + i);
     };
 
     // Lean scenes (STAGED): three-deep software pipeline over the batches a warp fetches (one
@@ -844,22 +849,13 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
         rng.depth = (uint32_t)bounce + 1;
         if (live) {
             if constexpr (STAGED) {
-                const double2 a = *reinterpret_cast<const double2*>(s), b = *reinterpret_cast<const double2*>(s + 32);
-                const double2 c = *reinterpret_cast<const double2*>(s + 64), d = *reinterpret_cast<const double2*>(s + 96);
-                const uint4 e = s[128], hh = s[160];
-                p.ray.o = v3(a.x, a.y, b.x);
-                p.ray.time = b.y;
-                p.ray.d = v3(c.x, c.y, d.x);
-                unpack_f2(d.y, p.T.x, p.T.y);
-                p.T.z = __uint_as_float(e.x);
-                p.slot = e.y;
-                p.pixel = e.z;
-                p.sample = e.w;
+                const uint4 hh = s[128];
+                unpack_path(fp, s[0], s[32], s[64], s[96], p);
                 ha.t = __hiloint2double((int)hh.y, (int)hh.x);
                 ha.root = (int)hh.z;
                 ha.matinfo = hh.w;
             } else {
-                load_path(in, i, p);
+                load_path(fp, ws, in, i, p);
                 ha = ws.hit[i];
             }
             rng.pixel = p.pixel;
@@ -1029,7 +1025,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
             if (__any_sync(0xffffffffu, live && out_pos != 0xffffffffu)) {
                 // the slots were reserved by extend (see there; the same for every hit of the class):
                 // no atomic, no ballot
-                if (survive) store_path(out, out_pos, p);
+                if (survive) store_path(ws, out, out_pos, p);
             } else {
                 // survivors: light-directed rays onto the front stack, the others onto the back stack
                 const uint32_t mf = __ballot_sync(0xffffffffu, survive && front), mb = __ballot_sync(0xffffffffu, survive && !front);
@@ -1040,7 +1036,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                 bf = __shfl_sync(0xffffffffu, bf, lf);
                 bb = __shfl_sync(0xffffffffu, bb, lb);
                 const uint32_t lt = (1u << lane) - 1u;
-                if (survive) store_path(out, front ? bf + __popc(mf & lt) : ws.capacity - 1u - (bb + __popc(mb & lt)), p);
+                if (survive) store_path(ws, out, front ? bf + __popc(mf & lt) : ws.capacity - 1u - (bb + __popc(mb & lt)), p);
             }
         }
         if constexpr (STAGED) {  // rotate the pipeline
@@ -1059,7 +1055,7 @@ __global__ void __launch_bounds__(RS_BLOCK) probe_primary_kernel(const __grid_co
     const uint32_t n = ws.ctr->n_rays[0];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         PathRec p;
-        load_path(ws.buf[0], i, p);
+        load_path(fp, ws, ws.buf[0], i, p);
         const HitA ha = ws.hit[i];
         const uint32_t px = p.pixel;
         if (dbg.ray_od6) {

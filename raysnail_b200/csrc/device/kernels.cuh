@@ -19,16 +19,15 @@ namespace rsd {
 #define RS_FRONT_CLASS(cls) ((cls) == 1 + RS_MAT_LAMBERTIAN ? 8 : ((cls) == 1 + RS_MAT_ISOTROPIC ? 9 : ((cls) == 1 + RS_MAT_BLINN_PHONG ? 10 : (cls))))
 #define RS_BASE_CLASS(k) ((k) < 8 ? (k) : ((k) == 8 ? 1 + RS_MAT_LAMBERTIAN : ((k) == 9 ? 1 + RS_MAT_ISOTROPIC : 1 + RS_MAT_BLINN_PHONG)))
 
-// One path record is five 16-byte SoA elements (80 B), so every load/store is a full
-// 128-bit transaction and linear queues coalesce perfectly:
-//   a = (o.x, o.y)  b = (o.z, time)  c = (d.x, d.y)  d = (d.z, bits(T.r, T.g))
-//   e = (bits T.b, slot, pixel, sample)
+// One path record is 64 contiguous, 64-byte aligned bytes (four 128-bit elements), so a record
+// that is GATHERED through a queue index (shade) costs exactly two 32-byte DRAM sectors, and a
+// linear sweep (extend) stays fully coalesced:
+//   q0 = (o.x, o.y)  q1 = (o.z, d.x)  q2 = (d.y, d.z)  q3 = (bits T.r, T.g, T.b, slot)
+// `slot` = sample-major index of the path in its wave; pixel and sample index are derived from it.
+// The ray's shutter time lives in a separate array that only scenes with moving spheres touch.
 struct PathBuf {
-    double2* a;
-    double2* b;
-    double2* c;
-    double2* d;
-    uint4* e;
+    uint4* rec;    // 4 * capacity
+    double* time;  // capacity (used when WaveState::uses_time)
 };
 
 // closest-hit record written by extend, read by shade (16 B) + the limit the object was
@@ -68,6 +67,7 @@ struct WaveState {
     WaveCounters* ctr;
     DeviceStats* stats;
     uint32_t capacity;
+    int uses_time;  // the scene holds moving spheres: rays carry their shutter time (sphere.rs:50-53)
 };
 
 struct FrameParams {
