@@ -65,6 +65,7 @@ struct rs_ctx {
 
     // scene (device)
     DevBuf d_nodes, d_xf, d_bvh, d_root_node, d_root_kind, d_root_sphere, d_root_bbox, d_root_gate;
+    DevBuf d_mat_hot, d_root_inv_r, d_root_material, d_light_nodes;
     DevBuf d_tri_geom, d_tri_normals, d_tri_material, d_lights, d_materials, d_textures, d_texels, d_perm, d_values;
     DScene scene{};
     // scene (host side, kept to re-pad the f32 boxes when the camera moves far away)
@@ -849,6 +850,59 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if ((rc = upload(ctx, ctx->d_lights, s->lights, (size_t)s->n_lights)) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_materials, s->materials, (size_t)s->n_materials)) != RS_OK) return rc;
     {
+        // flattened per-root / per-material / per-light tables (see MatHot in rt_scene.cuh)
+        std::vector<double> root_inv_r(s->n_roots, 0.0);
+        std::vector<int> root_material(s->n_roots, -1);
+        bool all_spheres = s->n_roots > 0;
+        for (int i = 0; i < s->n_roots; ++i) {
+            const int r = s->roots[i];
+            if (root_kind[i] == ROOT_SPHERE) { root_inv_r[i] = nodes[r].p[7]; root_material[i] = nodes[r].material; }
+            else if (root_kind[i] == ROOT_TRIANGLE) root_material[i] = s->tri_material[~r];
+            all_spheres &= root_kind[i] == ROOT_SPHERE;
+        }
+        std::vector<MatHot> hot(s->n_materials);
+        for (int i = 0; i < s->n_materials; ++i) {
+            const rs_material& m = s->materials[i];
+            MatHot& h = hot[i];
+            std::memset(&h, 0, sizeof(h));
+            h.a = m.a; h.b = m.b; h.phong_factor = m.phong_factor; h.phong_exponent = m.phong_exponent; h.texture = m.texture;
+            int mode = 2, needs_uv = 0;
+            if (m.type == RS_MAT_DIELECTRIC || m.type == RS_MAT_ISOTROPIC || m.type == RS_MAT_MIXED) {
+                mode = 0;  // constant colour (dielectric.rs:76, isotropic.rs:30); Mixed is resolved before shading
+                h.c0 = make_float4(m.color[0], m.color[1], m.color[2], m.color[3]);
+            } else if (m.texture >= 0) {
+                const rs_texture& t = s->textures[m.texture];
+                if (t.type == RS_TEX_SOLID) {
+                    mode = 0;
+                    h.c0 = make_float4(t.color[0], t.color[1], t.color[2], t.color[3]);
+                } else if (t.type == RS_TEX_CHECKER && s->textures[t.odd].type == RS_TEX_SOLID && s->textures[t.even].type == RS_TEX_SOLID) {
+                    mode = 1;
+                    const rs_texture &e = s->textures[t.even], &o = s->textures[t.odd];
+                    h.c0 = make_float4(e.color[0], e.color[1], e.color[2], e.color[3]);
+                    h.c1 = make_float4(o.color[0], o.color[1], o.color[2], o.color[3]);
+                    h.scale = t.scale;
+                }
+            }
+            if (mode == 2 && m.texture >= 0) {
+                // does a lookup read (u, v)?  an image, or a checker that (transitively) nests one
+                std::vector<int> todo{m.texture};
+                for (size_t k = 0; k < todo.size() && k < 64; ++k) {
+                    const rs_texture& t = s->textures[todo[k]];
+                    if (t.type == RS_TEX_IMAGE) needs_uv = 1;
+                    if (t.type == RS_TEX_CHECKER) { todo.push_back(t.odd); todo.push_back(t.even); }
+                }
+            }
+            h.type_flags = m.type | (mode << 8) | ((m.has_curve ? 1 : 0) << 16) | (needs_uv << 17);
+        }
+        std::vector<rs_node> light_nodes(s->n_lights);
+        for (int i = 0; i < s->n_lights; ++i) light_nodes[i] = nodes[s->lights[i]];
+        if ((rc = upload(ctx, ctx->d_root_inv_r, root_inv_r.data(), root_inv_r.size())) != RS_OK) return rc;
+        if ((rc = upload(ctx, ctx->d_root_material, root_material.data(), root_material.size())) != RS_OK) return rc;
+        if ((rc = upload(ctx, ctx->d_mat_hot, hot.data(), hot.size())) != RS_OK) return rc;
+        if ((rc = upload(ctx, ctx->d_light_nodes, light_nodes.data(), light_nodes.size())) != RS_OK) return rc;
+        ctx->scene.all_spheres = all_spheres ? 1 : 0;
+    }
+    {
         // device copy only: `reserved` = 1 when a lookup in this texture reads (u, v) — an image,
         // or a checker that (transitively) nests one (checker.rs is generic over its children)
         std::vector<rs_texture> tex(s->textures, s->textures + s->n_textures);
@@ -881,6 +935,10 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     S.lights = ctx->d_lights.as<int>();
     S.n_lights = s->n_lights;
     S.materials = ctx->d_materials.as<rs_material>();
+    S.mat_hot = ctx->d_mat_hot.as<MatHot>();
+    S.root_inv_r = ctx->d_root_inv_r.as<double>();
+    S.root_material = ctx->d_root_material.as<int>();
+    S.light_nodes = ctx->d_light_nodes.as<rs_node>();
     S.textures = ctx->d_textures.as<rs_texture>();
     S.texels = ctx->d_texels.as<unsigned char>();
     S.perlin_perm = ctx->d_perm.as<int>();

@@ -240,6 +240,7 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
         if (sphere_nearest(v3(c01.x, c01.y, c23.x), c23.y * c23.y, ray, RS_TMIN, next_up(best.t), t1) && (t1 < best.t || root < best.root)) {
             best.t = t1;
             best.root = root;
+            if (MODE >= 2) best.material = -2;  // look it up in root_material
         }
     } else if (MODE >= 1 && kind == ROOT_TRIANGLE) {
         const int tri = ~__ldg(&S.root_node[root]);
@@ -247,6 +248,7 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
         if (triangle_test(S.tri_geom + 9 * (size_t)tri, ray, RS_TMIN, best.t, t, beta, gamma) && (t < best.t || root < best.root)) {
             best.t = t;
             best.root = root;
+            if (MODE >= 2) best.material = -2;
         }
     } else if (MODE >= 2) {
         if (__ldg(&S.root_gate[root])) {
@@ -300,6 +302,10 @@ __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); 
 
 #ifndef RS_TUNE_SHADE_GENERIC
 #define RS_TUNE_SHADE_GENERIC 2
+#endif
+// shade (lean): percent of the batches dealt statically before the cursor takes over (0 = cursor only)
+#ifndef RS_TUNE_SHADE_HYBRID
+#define RS_TUNE_SHADE_HYBRID 0
 #endif
 #define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) == 2 ? RS_TUNE_EXTEND_GENERIC : RS_TUNE_EXTEND_LEAN)
 
@@ -421,19 +427,17 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
 #undef RS_POP
 }
 
+template <int MODE>
 __device__ __forceinline__ int root_material(const DScene& S, const Closest& best) {
-    const int kind = S.root_kind[best.root];
-    int m;
-    if (kind == ROOT_SPHERE) m = S.nodes[S.root_node[best.root]].material;
-    else if (kind == ROOT_TRIANGLE) m = S.tri_material[~S.root_node[best.root]];
-    else m = best.material;
+    int m = best.material;  // generic objects: the material their expression tree resolved
+    if (MODE < 2 || m == -2) m = __ldg(&S.root_material[best.root]);
     return m < 0 ? S.default_material : m;
 }
 
 // MixedMaterial::scatter (mixed_material.rs:43-51) resolved ahead of shading, so that the
 // class buckets hold concrete materials.  Level 0 uses word 2 of the P_SCATTER call.
 __device__ __forceinline__ int resolve_mixed(const DScene& S, int m, const RngCtx& rng) {
-    for (uint32_t level = 0; level < 8 && S.materials[m].type == RS_MAT_MIXED; ++level) {
+    for (uint32_t level = 0; level < 8 && RS_MATHOT_TYPE(S.mat_hot[m]) == RS_MAT_MIXED; ++level) {
         const rs_material& mm = S.materials[m];
         uint32_t word = level == 0 ? rng_words(rng, P_SCATTER, 0).z : rng_words(rng, P_MIXED, level).x;
         m = ((double)word < 4294967295.0 * mm.a) ? mm.mat1 : mm.mat2;
@@ -501,12 +505,27 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
             h.matinfo = 0;
             cls = 0;
             if (best.root >= 0) {
-                int top = root_material(S, best);
+                int top = root_material<MODE>(S, best);
                 int leaf = resolve_mixed(S, top, rng);
                 h.matinfo = (uint32_t)leaf | ((uint32_t)top << 16);
-                cls = 1 + S.materials[leaf].type;
-                if (S.root_kind[best.root] == ROOT_GENERIC) ws.hit_end[i] = best.end_then;
-                ws.hit[i] = h;
+                const MatHot& mh = S.mat_hot[leaf];
+                const int tf = mh.type_flags;
+                cls = 1 + (tf & 0xff);
+                if (miss_in_extend && (tf & 0x3ff) == RS_MAT_DIFFUSE_LIGHT) {
+                    // a DiffuseLight never scatters (light.rs:33-35): the path ends here with
+                    // T * colour * multiplier.  With a solid colour (tex_mode 0) nothing about the
+                    // hit point is needed, so it is finished on the spot like a miss — no hit
+                    // record, no queue entry, no gather of the path record in shade.
+                    const float4 c = mh.c0;
+                    const double mul = mh.a;
+                    const uint4 q3 = in.rec[4 * (size_t)i + 3];  // (T, slot)
+                    ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * (float)((double)c.x * mul), __uint_as_float(q3.y) * (float)((double)c.y * mul),
+                                                   __uint_as_float(q3.z) * (float)((double)c.z * mul), 0.f);
+                    cls = -1;
+                } else {
+                    if (MODE >= 2 && S.root_kind[best.root] == ROOT_GENERIC) ws.hit_end[i] = best.end_then;
+                    ws.hit[i] = h;
+                }
             } else if (miss_in_extend) {
                 // a miss ends the path with `world.background(ray)` (camera.rs:253-254): finish it
                 // here instead of sending it through a queue to the shade kernel
@@ -573,12 +592,18 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
 template <bool GENERIC>
 __device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, const RngCtx& rng, const HitA& ha, double end_then,
                                             bool want_uv, HitRec& h) {
-    const int kind = S.root_kind[ha.root];
-    const int rn = S.root_node[ha.root];
+    // static spheres: centre and 1/r straight from the per-root tables (one level of loads
+    // instead of root -> node index -> node)
+    const int kind = (!GENERIC && S.all_spheres) ? (int)ROOT_SPHERE : __ldg(&S.root_kind[ha.root]);
     if (kind == ROOT_SPHERE) {
-        const rs_node& n = S.nodes[rn];
-        sphere_record(n.p, n.material, ray, ha.t, ha.t, want_uv, h);
-    } else if (kind == ROOT_TRIANGLE) {
+        const double2* sp = reinterpret_cast<const double2*>(S.root_sphere + ha.root);
+        const double2 c01 = __ldg(sp), c23 = __ldg(sp + 1);
+        const double pr[8] = {c01.x, c01.y, c23.x, c23.y, 0.0, 0.0, 0.0, __ldg(&S.root_inv_r[ha.root])};
+        sphere_record(pr, -1, ray, ha.t, ha.t, want_uv, h);
+        return;
+    }
+    const int rn = S.root_node[ha.root];
+    if (kind == ROOT_TRIANGLE) {
         double t, beta, gamma;
         const double inf = __longlong_as_double(0x7ff0000000000000LL);
         triangle_test(S.tri_geom + 9 * (size_t)(~rn), ray, -inf, inf, t, beta, gamma);
@@ -748,6 +773,15 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
     // The generic kernel keeps the cursor value fetched a batch ahead (it has no staging pipeline
     // to feed, and measured faster that way).
     constexpr uint32_t CHUNK = GENERIC ? 1u : (uint32_t)RS_TUNE_SHADE_CHUNK;
+    // Hybrid distribution (lean kernel): the first RS_TUNE_SHADE_HYBRID percent of the batches are
+    // dealt round robin (batch = warp + k * warps in the grid: no atomic, no round trip to L2 on the
+    // critical path of this latency-bound kernel), the rest through the cursor so that the tail
+    // still balances.
+    constexpr uint32_t HYBRID = GENERIC ? 0u : (uint32_t)RS_TUNE_SHADE_HYBRID;
+    const uint32_t n_warps_grid = gridDim.x * (blockDim.x >> 5);
+    uint32_t static_left = HYBRID ? (uint32_t)(((unsigned long long)(total >> 5) * HYBRID / 100u) / n_warps_grid) : 0u;
+    const uint32_t dynamic_begin = static_left * n_warps_grid * 32u;
+    uint32_t static_next = ((threadIdx.x >> 5) * gridDim.x + blockIdx.x) * 32u;
     uint32_t chunk_base = 0, chunk_left = 0, pend = 0;
     if (CHUNK == 1 && lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
     auto next_batch = [&]() -> uint32_t {
@@ -756,9 +790,17 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
             if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
             return b;
         }
+        if constexpr (HYBRID != 0) {
+            if (static_left) {
+                const uint32_t b = static_next;
+                static_next += n_warps_grid * 32u;
+                --static_left;
+                return b;
+            }
+        }
         if (chunk_left == 0) {
             uint32_t v = 0;
-            if (lane == 0) v = atomic_add_async(head, 32u * CHUNK, lane_zero);
+            if (lane == 0) v = atomic_add_async(head, 32u * CHUNK, lane_zero) + dynamic_begin;
             chunk_base = __shfl_sync(0xffffffffu, v, 0);
             chunk_left = CHUNK;
         }
@@ -872,23 +914,23 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                 float4 bg = background(S, p.ray.d);
                 add = make_float3(bg.x, bg.y, bg.z);
             } else {
-                const rs_material& mat = S.materials[ha.matinfo & 0xffffu];
-                const rs_material& smat = S.materials[ha.matinfo >> 16];
-                const bool want_uv = mat.texture >= 0 && texture_needs_uv(S, mat.texture);
+                const MatHot& mat = S.mat_hot[ha.matinfo & 0xffffu];
+                const MatHot& smat = S.mat_hot[ha.matinfo >> 16];
+                const int mat_type = RS_MATHOT_TYPE(mat);
+                const bool want_uv = RS_MATHOT_NEEDS_UV(mat);
                 HitRec h;
-                const double end_then = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_end[i] : 0.0;
+                double end_then = 0.0;
+                if constexpr (GENERIC) end_then = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_end[i] : 0.0;
                 rebuild_hit<GENERIC>(S, p.ray, rng, ha, end_then, want_uv, h);
 
-                float4 col = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (mat.type == RS_MAT_DIELECTRIC || mat.type == RS_MAT_ISOTROPIC) col = make_float4(mat.color[0], mat.color[1], mat.color[2], mat.color[3]);
-                else col = texture_color(S, mat.texture, h.u, h.v, h.point);
+                const float4 col = material_color(S, mat, h.u, h.v, h.point);
 
                 kind = 1;
                 bool scattered = false, specular = false;
                 PdfState P;
                 P.kind = 0;
                 V3 reflected = v3(0, 0, 0);
-                switch (mat.type) {
+                switch (mat_type) {
                     case RS_MAT_DIFFUSE_LIGHT: {  // light.rs:33-35: emitted = colour * multiplier, no scatter
                         add = make_float3((float)((double)col.x * mat.a), (float)((double)col.y * mat.a), (float)((double)col.z * mat.a));
                         break;
@@ -903,7 +945,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                         reflected = p.ray.d - (2.0 * dot(p.ray.d, h.normal)) * h.normal;
                         if (dot(reflected, h.normal) > 0.0) {
                             scattered = true;
-                            if (mat.type == RS_MAT_METAL) {
+                            if (mat_type == RS_MAT_METAL) {
                                 specular = true;
                                 next_o = h.point;
                                 next_d = reflected;
@@ -924,7 +966,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                         bool refracted = false;
                         if (!(refractive * sin_theta > 1.0)) {
                             double reflect_prob = 0.0;
-                            if (mat.has_curve) {  // Glass::reflect_prob (dielectric.rs:20-24)
+                            if (RS_MATHOT_HAS_CURVE(mat)) {  // Glass::reflect_prob (dielectric.rs:20-24)
                                 double r0 = (1.0 - refractive) / (1.0 + refractive);
                                 r0 = r0 * r0;
                                 double x = 1.0 - cos_theta;
@@ -970,12 +1012,12 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                     if (u01(w.x) < 0.5) {  // camera.rs:198-213
                         kind = 3;
                         pdf_val = 0.3183098861837907;
-                        const int light_node = S.lights[S.n_lights == 1 ? 0u : w.y % (uint32_t)S.n_lights];  // list.rs:49-52
+                        const uint32_t light_k = S.n_lights == 1 ? 0u : w.y % (uint32_t)S.n_lights;  // list.rs:49-52
                         V3 to_light;
                         if (GENERIC) {
-                            to_light = TreeTop::random(S, light_node, h.point, rng);
+                            to_light = TreeTop::random(S, S.lights[light_k], h.point, rng);
                         } else {
-                            const rs_node& ln = S.nodes[light_node];
+                            const rs_node& ln = S.light_nodes[light_k];
                             to_light = ln.type == RS_NODE_SPHERE ? sphere_random(ln, h.point, rng) : rect_random(ln, h.point, rng);
                         }
                         V3 dir_to_light = unit_fast(to_light);

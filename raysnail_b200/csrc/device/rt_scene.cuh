@@ -42,6 +42,27 @@ struct __align__(16) XformPre {
 
 enum RootKind : int { ROOT_SPHERE = 0, ROOT_TRIANGLE = 1, ROOT_GENERIC = 2 };
 
+// Everything shade reads of a (resolved) material in ONE record, so that the dependent chain
+// material -> texture -> nested texture (three round trips to L1/L2 in a latency-bound kernel) is a
+// single level for the common cases.  Built at upload from rs_material + rs_texture:
+//   tex_mode 0: the colour is c0 (a solid texture; the constant colour of Dielectric / Isotropic)
+//   tex_mode 1: a checker of two solid textures: c0 = `even`, c1 = `odd`, `scale`
+//   tex_mode 2: anything else: texture_color(texture)
+#define RS_MATHOT_TYPE(m) ((m).type_flags & 0xff)
+#define RS_MATHOT_TEX_MODE(m) (((m).type_flags >> 8) & 3)
+#define RS_MATHOT_HAS_CURVE(m) (((m).type_flags >> 16) & 1)
+#define RS_MATHOT_NEEDS_UV(m) (((m).type_flags >> 17) & 1)
+struct __align__(16) MatHot {
+    float4 c0, c1;
+    double a, b;           // rs_material.a / .b
+    double phong_factor;   // CommonMaterialSettings
+    double scale;          // checker scale
+    int type_flags;        // type | tex_mode << 8 | has_curve << 16 | needs_uv << 17
+    int texture;
+    int phong_exponent;
+    int pad;
+};
+
 struct DScene {
     const rs_node* nodes;
     const XformPre* xf;          // indexed by rs_node.first_xform (rewritten at upload)
@@ -52,6 +73,11 @@ struct DScene {
     const int* root_node;        // node index or ~triangle
     const int* root_kind;        // RootKind
     const double4* root_sphere;  // ROOT_SPHERE: (cx, cy, cz, r)
+    const double* root_inv_r;    // ROOT_SPHERE: 1.0 / r (the IEEE quotient, computed on the host)
+    const int* root_material;    // ROOT_SPHERE / ROOT_TRIANGLE: the object's material (-1 = None)
+    const MatHot* mat_hot;       // one per material
+    int all_spheres;             // every root is a ROOT_SPHERE
+    const rs_node* light_nodes;  // copy of nodes[lights[k]]: the lean shade kernel samples plain sphere / rect lights
     const double* root_bbox;     // 6 per root (reference bbox, for the gate)
     const unsigned char* root_gate;
     const double* tri_geom;      // 9 per triangle: p0.xyz, (a,b,c) = p0-p1, (d,e,f) = p0-p2
@@ -565,6 +591,20 @@ static __device__ __noinline__ float4 texture_color(const DScene& S, int ti, dou
         return make_float4(1.0f * ff, 1.0f * ff, 1.0f * ff, 1.0f);
     }
     return make_float4(0.f, 0.f, 0.f, 1.f);
+}
+
+// Texture::color of a material through its flattened record
+__device__ __forceinline__ float4 material_color(const DScene& S, const MatHot& m, double u, double v, V3 p) {
+    const int mode = RS_MATHOT_TEX_MODE(m);
+    if (mode == 0) return m.c0;
+    if (mode == 1) {  // checker.rs:22-29, see texture_color
+        const double ax = m.scale * p.x, ay = m.scale * p.y, az = m.scale * p.z;
+        const double inv_pi = 0.31830988618379067154;
+        const long long par = __double2ll_rd(ax * inv_pi) ^ __double2ll_rd(ay * inv_pi) ^ __double2ll_rd(az * inv_pi);
+        const bool negative = (par & 1) && ax != 0.0 && ay != 0.0 && az != 0.0;
+        return negative ? m.c1 : m.c0;
+    }
+    return texture_color(S, m.texture, u, v, p);
 }
 
 __device__ __forceinline__ bool texture_needs_uv(const DScene& S, int ti) {
