@@ -304,7 +304,12 @@ def run_gpu(args):
         # dominant kernel by CUDA-event time on rank 0's stream
         shares = {"extend": kt.ms_extend, "shade": kt.ms_shade, "raygen": kt.ms_raygen, "accumulate": kt.ms_accumulate}
         dom = max(("extend", "shade"), key=lambda k: shares[k])
-        waves = max(1, int(kt.n_launches) // (2 * depth + 2))  # per wave: raygen + depth x (extend, shade) + accumulate
+        # waves of one render (the partition of render_into, csrc/backend.cu): P pixels x K samples each
+        cap = max(args.wave or (1 << 23), 1024)
+        s_total = (r1 - r0) * q
+        P = min(width * height, cap)
+        K = max(1, min(s_total, cap // P))
+        waves = max(1, -(-(width * height) // P) * -(-s_total // K))
         n_dom_launches = float(waves * depth)
         seg_rank0 = float(kt.n_segments)
         alg_bytes_per_launch = BYTES_PER_SEGMENT[dom] * seg_rank0 / n_dom_launches

@@ -95,7 +95,7 @@ struct rs_ctx {
     int wave_streams = 2;
     cudaStream_t aux_stream[kMaxSets - 1] = {};
     cudaEvent_t ev_fork = nullptr, ev_join[kMaxSets - 1] = {}, ev_acc[kMaxSets] = {};
-    int extend_grid = 148, shade_grid = 148;
+    int extend_grid = 148, shade_grid = 148, shade_grid_lambert = 148;
 
     // scratch for rs_render / probes
     DevBuf d_accum, d_out, d_mask, d_dbg[11];
@@ -550,7 +550,13 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
                 tm.mark(1);
                 launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
                 tm.mark(2);
-                launch_shade(ctx->scene, fp, ws, b, ctx->shade_generic ? 1 : 0, ctx->shade_grid, nullptr, st);
+                if (ctx->shade_generic) {
+                    launch_shade(ctx->scene, fp, ws, b, 1, 0, ctx->shade_grid, nullptr, st);
+                } else {  // lean scenes: the Lambertian hits, then the other classes (see shade_kernel)
+                    launch_shade(ctx->scene, fp, ws, b, 0, 1, ctx->shade_grid_lambert, nullptr, st);
+                    launch_shade(ctx->scene, fp, ws, b, 0, 2, ctx->shade_grid, nullptr, st);
+                    ++launches;
+                }
                 launches += 2;
             }
             tm.mark(3);
@@ -639,7 +645,7 @@ int rs_create(rs_ctx** out, int device) {
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
     ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(2, 0);
-    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(1);
+    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(1, 0);
     *out = ctx;
     return RS_OK;
 }
@@ -820,10 +826,12 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     }
     ctx->shade_generic = any_generic || !lights_simple;
     ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4);
-    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic ? 1 : 0);
+    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic ? 1 : 0, ctx->shade_generic ? 0 : 2);
+    ctx->shade_grid_lambert = ctx->sm_count * shade_blocks_per_sm(0, 1);
     // tuning hooks: fewer resident blocks per SM than the occupancy limit (profiling experiments)
     if (const char* e = std::getenv("RAYSNAIL_B200_EXTEND_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->extend_grid = std::min(ctx->extend_grid, ctx->sm_count * v); }
     if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid = std::min(ctx->shade_grid, ctx->sm_count * v); }
+    if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_LAMBERT_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid_lambert = std::min(ctx->shade_grid_lambert, ctx->sm_count * v); }
 
     // triangles: p0, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56)
     std::vector<double> tri_geom((size_t)s->n_tris * 9);
@@ -1122,7 +1130,11 @@ static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), 0));
     launch_raygen(fp, ctx->ws, 0);
     launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->bvh_width == 4, 0, ctx->extend_grid, 0);  // probes: misses stay visible to shade
-    if (shade) launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic ? 1 : 0, ctx->shade_grid, &dbg, 0);
+    if (shade && ctx->shade_generic) launch_shade(ctx->scene, fp, ctx->ws, 0, 1, 0, ctx->shade_grid, &dbg, 0);
+    if (shade && !ctx->shade_generic) {
+        launch_shade(ctx->scene, fp, ctx->ws, 0, 0, 1, ctx->shade_grid_lambert, &dbg, 0);
+        launch_shade(ctx->scene, fp, ctx->ws, 0, 0, 2, ctx->shade_grid, &dbg, 0);
+    }
     else launch_probe_primary(ctx->scene, fp, ctx->ws, dbg, 0);
     CK(cudaGetLastError());
     for (int i = 0; i < 11; ++i)

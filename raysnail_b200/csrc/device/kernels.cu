@@ -304,6 +304,10 @@ __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); 
 #define RS_TUNE_SHADE_GENERIC 2
 #endif
 // shade (lean): percent of the batches dealt statically before the cursor takes over (0 = cursor only)
+// resident blocks per SM of the Lambertian-only shade kernel
+#ifndef RS_TUNE_SHADE_LAMBERT
+#define RS_TUNE_SHADE_LAMBERT 2
+#endif
 #ifndef RS_TUNE_SHADE_HYBRID
 #define RS_TUNE_SHADE_HYBRID 0
 #endif
@@ -711,15 +715,22 @@ __device__ __forceinline__ void dbg_store3(double* p, uint32_t i, V3 v) {
     if (p) { p[3 * (size_t)i] = v.x; p[3 * (size_t)i + 1] = v.y; p[3 * (size_t)i + 2] = v.z; }
 }
 
-template <bool GENERIC>
-__global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : RS_TUNE_SHADE_LEAN) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+// SET selects the work classes a launch takes: 0 = all of them, 1 = the hits of Lambertian
+// surfaces only (most hits of most scenes: a kernel that holds nothing but that one material
+// fits its 128 registers without a single spill, which the all-material kernel does not; measured:
+// shade -8 %; capping it at 96 / 85 / 64 registers for a third, fourth or fifth resident block
+// spills again and is slower than two blocks), 2 = everything else.  Lean scenes launch 1 then 2,
+// generic scenes 0.
+#define RS_SHADE_IN_SET(SET, c) ((SET) == 0 || (((c) == 1 + RS_MAT_LAMBERTIAN || (c) == RS_FRONT_CLASS(1 + RS_MAT_LAMBERTIAN)) == ((SET) == 1)))
+template <bool GENERIC, int SET>
+__global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : (SET == 1 ? RS_TUNE_SHADE_LAMBERT : RS_TUNE_SHADE_LEAN)) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                             const __grid_constant__ WaveState ws, const int bounce,
                                                             const __grid_constant__ DebugOut dbg, const int has_dbg) {
     extern __shared__ __align__(16) uint4 s_stage[];
     const PathBuf& in = ws.buf[bounce & 1];
     const PathBuf& out = ws.buf[(bounce + 1) & 1];
     const uint32_t* class_count = ws.ctr->class_count[bounce];
-    uint32_t* head = &ws.ctr->shade_head[bounce];
+    uint32_t* head = SET == 2 ? &ws.ctr->shade_head2[bounce] : &ws.ctr->shade_head[bounce];
     uint32_t* out_front = &ws.ctr->n_rays[bounce + 1];
     uint32_t* out_back = &ws.ctr->n_back[bounce + 1];
     const bool last_bounce = bounce + 1 >= fp.depth;
@@ -733,7 +744,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
     // virtual index space: each class padded to a multiple of 32 so a warp never mixes classes.
     // The table is spread over the lanes of the warp (lane c holds class c: two registers instead
     // of 2 * RS_NUM_CLASSES): padded begins by a warp scan, lane RS_NUM_CLASSES holds the total.
-    uint32_t my_count = lane < RS_NUM_CLASSES ? class_count[lane * RS_COUNTER_STRIDE] : 0u;
+    uint32_t my_count = (lane < RS_NUM_CLASSES && RS_SHADE_IN_SET(SET, lane)) ? class_count[lane * RS_COUNTER_STRIDE] : 0u;
     uint32_t my_begin = (my_count + 31u) & ~31u;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -916,7 +927,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
             } else {
                 const MatHot& mat = S.mat_hot[ha.matinfo & 0xffffu];
                 const MatHot& smat = S.mat_hot[ha.matinfo >> 16];
-                const int mat_type = RS_MATHOT_TYPE(mat);
+                const int mat_type = SET == 1 ? (int)RS_MAT_LAMBERTIAN : RS_MATHOT_TYPE(mat);
                 const bool want_uv = RS_MATHOT_NEEDS_UV(mat);
                 HitRec h;
                 double end_then = 0.0;
@@ -1027,7 +1038,13 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                         next_d = dir_to_light;
                     } else {  // camera.rs:214-218
                         kind = 4;
-                        next_d = pdf_generate(P, h.normal, reflected, rng);
+                        if constexpr (SET == 1) {  // CosinePdf::generate (pdf.rs:45-47), inlined: the only PDF of this kernel
+                            const uint4 wb = rng_words(rng, P_BRDF, 0);
+                            const ONB onb = onb_build_fast(h.normal);
+                            next_d = onb_local(onb, cosine_direction(u01(wb.x), u01(wb.y)));
+                        } else {
+                            next_d = pdf_generate(P, h.normal, reflected, rng);
+                        }
                         pdf_val = pdf_value(P, next_d);
                         next_o = h.point;
                     }
@@ -1251,11 +1268,13 @@ void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, 
     void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
     cudaLaunchKernel(extend_fn_for(mode, wide), dim3(grid), dim3(RS_BLOCK), args, 0, s);
 }
-void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int grid, const DebugOut* dbg, cudaStream_t s) {
+void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int set, int grid, const DebugOut* dbg, cudaStream_t s) {
     DebugOut d = {};
     if (dbg) d = *dbg;
-    if (generic) shade_kernel<true><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else shade_kernel<false><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    if (generic) shade_kernel<true, 0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else if (set == 1) shade_kernel<false, 1><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else if (set == 2) shade_kernel<false, 2><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else shade_kernel<false, 0><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
 }
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s) {
     probe_primary_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(S, fp, ws, dbg);
@@ -1285,11 +1304,15 @@ int extend_blocks_per_sm(int mode, int wide) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_fn_for(mode, wide), RS_BLOCK, 0);
     return n > 0 ? n : 1;
 }
-int shade_blocks_per_sm(int generic) {
+int shade_blocks_per_sm(int generic, int set) {
     int n = 0;
-    cudaFuncSetAttribute(shade_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, RS_SHADE_SMEM);
-    if (generic) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<true>, RS_BLOCK, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<false>, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM);
+    if (generic) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<true, 0>, RS_BLOCK, 0);
+    } else {
+        const void* fn = set == 1 ? (const void*)shade_kernel<false, 1> : (set == 2 ? (const void*)shade_kernel<false, 2> : (const void*)shade_kernel<false, 0>);
+        cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, RS_SHADE_SMEM);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM);
+    }
     return n > 0 ? n : 1;
 }
 

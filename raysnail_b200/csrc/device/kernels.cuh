@@ -51,6 +51,7 @@ struct WaveCounters {
     uint32_t class_count[RS_MAX_DEPTH][RS_NUM_CLASSES * RS_COUNTER_STRIDE];
     uint32_t extend_head[RS_MAX_DEPTH];           // persistent-thread work cursors
     uint32_t shade_head[RS_MAX_DEPTH];
+    uint32_t shade_head2[RS_MAX_DEPTH];          // second class set of a bounce (see shade_kernel)
 };
 
 struct DeviceStats {
@@ -103,7 +104,7 @@ struct DebugOut {  // all device pointers, indexed by pixel; any may be null
 void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s);
 void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int miss_in_extend, int grid,
                    cudaStream_t s);
-void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int grid, const DebugOut* dbg, cudaStream_t s);
+void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int set, int grid, const DebugOut* dbg, cudaStream_t s);
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s);
 void launch_accumulate(const FrameParams& fp, const WaveState& ws, float4* accum, cudaStream_t s);
 void launch_finalize(const float4* accum, const unsigned char* mask, float4* out, int64_t n, int n_samples, int gamma, cudaStream_t s);
@@ -117,6 +118,6 @@ void launch_combine(const float4* old_px, const float4* new_px, float4* out, int
 void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s);
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);
 int extend_blocks_per_sm(int mode, int wide);
-int shade_blocks_per_sm(int generic);
+int shade_blocks_per_sm(int generic, int set);
 
 }  // namespace rsd
