@@ -464,6 +464,7 @@ FrameParams make_frame(const rs_camera* cam, const rs_render_params* p) {
     std::memset(&fp, 0, sizeof(fp));
     fp.cam = *cam;
     fp.sqrt_spp = p->sqrt_spp;
+    fp.magic_q = div_magic((uint32_t)p->sqrt_spp);
     fp.depth = p->depth;
     fp.stratum_row_begin = p->stratum_row_begin;
     fp.flags = p->flags;
@@ -536,6 +537,7 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
     for (uint32_t pixel0 = 0; pixel0 < np; pixel0 += P) {
         fp.pixel0 = pixel0;
         fp.n_pixels = std::min(P, np - pixel0);
+        fp.magic_pixels = div_magic(fp.n_pixels);
         for (uint32_t sample0 = 0; sample0 < s_total; sample0 += K, ++wave) {
             fp.sample0 = sample0;
             fp.n_samples = std::min(K, s_total - sample0);
@@ -1109,6 +1111,7 @@ static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     fp.mask = nullptr;
     fp.pixel0 = 0;
     fp.n_pixels = np;
+    fp.magic_pixels = div_magic(fp.n_pixels);
     // local sample index such that s_j * sqrt_spp + s_i == sample_index
     fp.stratum_row_begin = 0;
     fp.sample0 = (uint32_t)sample_index;

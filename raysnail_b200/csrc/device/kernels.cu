@@ -37,11 +37,14 @@ struct PathRec {
 
 // slot -> (pixel, absolute sample index): the inverse of raygen's numbering
 __device__ __forceinline__ void decode_slot(const FrameParams& fp, uint32_t slot, uint32_t& pixel, uint32_t& sample) {
-    const uint32_t k_local = slot / fp.n_pixels, p_local = slot - k_local * fp.n_pixels;
+    // x / d = umulhi(x, floor(2^32 / d)) or one more (FrameParams::magic_*)
+    uint32_t k_local = __umulhi(slot, fp.magic_pixels), p_local = slot - k_local * fp.n_pixels;
+    if (p_local >= fp.n_pixels) { ++k_local; p_local -= fp.n_pixels; }
     pixel = fp.pixel0 + p_local;
     const uint32_t j = fp.sample0 + k_local, q = (uint32_t)fp.sqrt_spp;
-    const uint32_t row = j / q;
-    sample = ((uint32_t)fp.stratum_row_begin + row) * q + (j - row * q);
+    uint32_t row = __umulhi(j, fp.magic_q), col = j - row * q;
+    if (col >= q) { ++row; col -= q; }
+    sample = ((uint32_t)fp.stratum_row_begin + row) * q + col;
 }
 __device__ __forceinline__ void unpack_path(const FrameParams& fp, uint4 q0, uint4 q1, uint4 q2, uint4 q3, PathRec& p) {
     p.ray.o = v3(__hiloint2double((int)q0.y, (int)q0.x), __hiloint2double((int)q0.w, (int)q0.z), __hiloint2double((int)q1.y, (int)q1.x));
@@ -181,21 +184,21 @@ __global__ void __launch_bounds__(RS_BLOCK) raygen_kernel(const __grid_constant_
         bool live = i < total;
         PathRec p;
         if (live) {
-            uint32_t p_local = i % fp.n_pixels, k_local = i / fp.n_pixels;
-            uint32_t pixel = fp.pixel0 + p_local;
+            uint32_t pixel, sample;
+            decode_slot(fp, i, pixel, sample);
             ws.contrib[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (fp.mask && fp.mask[pixel] == 0) {
                 live = false;
             } else {
                 int row = (int)(pixel / (uint32_t)fp.cam.width), col = (int)(pixel % (uint32_t)fp.cam.width);
-                uint32_t j = fp.sample0 + k_local;
-                int s_j = fp.stratum_row_begin + (int)(j / (uint32_t)fp.sqrt_spp), s_i = (int)(j % (uint32_t)fp.sqrt_spp);
+                uint32_t s_j = __umulhi(sample, fp.magic_q), s_i = sample - s_j * (uint32_t)fp.sqrt_spp;
+                if (s_i >= (uint32_t)fp.sqrt_spp) { ++s_j; s_i -= (uint32_t)fp.sqrt_spp; }
                 RngCtx rng;
                 rng.key = fp.key;
                 rng.pixel = pixel;
-                rng.sample = (uint32_t)(s_j * fp.sqrt_spp + s_i);
+                rng.sample = sample;
                 rng.depth = 0;
-                p.ray = camera_ray(fp, row, col, s_i, s_j, rng);
+                p.ray = camera_ray(fp, row, col, (int)s_i, (int)s_j, rng);
                 p.T = make_float3(1.f, 1.f, 1.f);
                 p.slot = i;
                 p.pixel = pixel;

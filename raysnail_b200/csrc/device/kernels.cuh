@@ -83,6 +83,9 @@ struct FrameParams {
     uint32_t n_pixels;   // P
     uint32_t sample0;    // first local sample index (0 .. S)
     uint32_t n_samples;  // K
+    // floor(2^32 / d) for d = n_pixels and d = sqrt_spp: slot -> (pixel, sample) without integer
+    // divisions (decode_slot; two divisions per ray in extend and per hit in shade otherwise)
+    uint32_t magic_pixels, magic_q;
     const unsigned char* mask;
 };
 
@@ -99,6 +102,8 @@ struct DebugOut {  // all device pointers, indexed by pixel; any may be null
     double* weight3;
     double* emitted3;
 };
+
+inline uint32_t div_magic(uint32_t d) { return d <= 1u ? 0xffffffffu : (uint32_t)(0x100000000ull / d); }
 
 // launchers (kernels.cu)
 void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s);
