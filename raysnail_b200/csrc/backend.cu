@@ -771,7 +771,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
                 root_kind[i] = ROOT_SPHERE;
                 for (int k = 0; k < 4; ++k) root_sphere[4 * (size_t)i + k] = n.p[k];
             } else {
-                root_kind[i] = ROOT_GENERIC;
+                // rect / box, bare or under one TfFacade: inline distance tests in extend
+                const rs_node& inner = n.type == RS_NODE_TRANSFORM ? nodes[n.child0] : n;
+                root_kind[i] = (inner.type == RS_NODE_BOX || inner.type == RS_NODE_RECT) ? ROOT_FLAT : ROOT_GENERIC;
                 // spheres / boxes / rects always lie inside their reference bbox; everything
                 // else is clipped by it the way the reference's BVH leaf clips it
                 root_gate[i] = !(n.type == RS_NODE_SPHERE || n.type == RS_NODE_BOX || n.type == RS_NODE_RECT);
@@ -815,7 +817,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     bool any_tri = false, any_generic = false;
     for (const BuildPrim& p : prims) {
         any_tri |= root_kind[p.root] == ROOT_TRIANGLE;
-        any_generic |= root_kind[p.root] == ROOT_GENERIC;
+        any_generic |= root_kind[p.root] >= ROOT_GENERIC;
     }
     ctx->extend_mode = any_generic ? 2 : (any_tri ? 1 : 0);
     ctx->uses_time = false;
@@ -868,6 +870,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
             const int r = s->roots[i];
             if (root_kind[i] == ROOT_SPHERE) { root_inv_r[i] = nodes[r].p[7]; root_material[i] = nodes[r].material; }
             else if (root_kind[i] == ROOT_TRIANGLE) root_material[i] = s->tri_material[~r];
+            else if (root_kind[i] == ROOT_FLAT) root_material[i] = (nodes[r].type == RS_NODE_TRANSFORM ? nodes[nodes[r].child0] : nodes[r]).material;
             all_spheres &= root_kind[i] == ROOT_SPHERE;
         }
         std::vector<MatHot> hot(s->n_materials);

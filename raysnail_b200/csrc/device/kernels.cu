@@ -205,10 +205,16 @@ __global__ void __launch_bounds__(RS_BLOCK) raygen_kernel(const __grid_constant_
                 p.sample = rng.sample;
             }
         }
-        uint32_t pos = warp_append(&ws.ctr->n_rays[0], live, RS_LANE_ZERO(ws));
+        // without a pixel mask every path is live and path i simply goes to record i: no compaction,
+        // no atomic (its round trip to L2 was the top stall of this kernel)
+        uint32_t pos = i;
+        if (fp.mask) pos = warp_append(&ws.ctr->n_rays[0], live, RS_LANE_ZERO(ws));
         if (live) store_path(ws, ws.buf[0], pos, p);
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_samples, (unsigned long long)total);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(&ws.stats->n_samples, (unsigned long long)total);
+        if (!fp.mask) ws.ctr->n_rays[0] = total;
+    }
 }
 
 // =============================================================================================
@@ -252,6 +258,25 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
             best.t = t;
             best.root = root;
             if (MODE >= 2) best.material = -2;
+        }
+    } else if (MODE >= 2 && kind == ROOT_FLAT) {
+        const rs_node* n = S.nodes + __ldg(&S.root_node[root]);
+        Ray r = ray;
+        if (n->type == RS_NODE_TRANSFORM) {  // tf_facade.rs:41-56: the ray goes to object space, t is kept
+            const XformPre& x = S.xf[n->first_xform];
+            r.o = xf_apply(x.inv, ray.o, 1.0);
+            r.d = xf_apply(x.inv, ray.d, 0.0);
+            n = S.nodes + n->child0;
+        }
+        const double hi = next_up(best.t);
+        double t;
+        const bool hit = n->type == RS_NODE_BOX ? box_t(n->p, r, RS_TMIN, hi, t)
+                                                : rect_t(n->rect_axis, n->p[0], n->p[1], n->p[2], n->p[3], n->p[4], r, RS_TMIN, hi, t);
+        if (hit && (t < best.t || root < best.root)) {
+            best.end_then = hi;
+            best.t = t;
+            best.root = root;
+            best.material = -2;
         }
     } else if (MODE >= 2) {
         if (__ldg(&S.root_gate[root])) {
@@ -530,7 +555,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                                                    __uint_as_float(q3.z) * (float)((double)c.z * mul), 0.f);
                     cls = -1;
                 } else {
-                    if (MODE >= 2 && S.root_kind[best.root] == ROOT_GENERIC) ws.hit_end[i] = best.end_then;
+                    if (MODE >= 2 && S.root_kind[best.root] >= ROOT_GENERIC) ws.hit_end[i] = best.end_then;
                     ws.hit[i] = h;
                 }
             } else if (miss_in_extend) {
@@ -934,7 +959,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                 const bool want_uv = RS_MATHOT_NEEDS_UV(mat);
                 HitRec h;
                 double end_then = 0.0;
-                if constexpr (GENERIC) end_then = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_end[i] : 0.0;
+                if constexpr (GENERIC) end_then = S.root_kind[ha.root] >= ROOT_GENERIC ? ws.hit_end[i] : 0.0;
                 rebuild_hit<GENERIC>(S, p.ray, rng, ha, end_then, want_uv, h);
 
                 const float4 col = material_color(S, mat, h.u, h.v, h.point);
@@ -1136,7 +1161,7 @@ __global__ void __launch_bounds__(RS_BLOCK) probe_primary_kernel(const __grid_co
         RngCtx rng;
         rng.key = fp.key; rng.pixel = p.pixel; rng.sample = p.sample; rng.depth = 1;
         HitRec h;
-        const double end_then = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_end[i] : 0.0;
+        const double end_then = S.root_kind[ha.root] >= ROOT_GENERIC ? ws.hit_end[i] : 0.0;
         rebuild_hit<true>(S, p.ray, rng, ha, end_then, true, h);
         if (dbg.t) dbg.t[px] = h.t1;
         dbg_store3(dbg.normal3, px, h.normal);

@@ -40,7 +40,9 @@ struct __align__(16) XformPre {
     double inv[12];
 };
 
-enum RootKind : int { ROOT_SPHERE = 0, ROOT_TRIANGLE = 1, ROOT_GENERIC = 2 };
+// ROOT_FLAT: a rect, a box, or a TfFacade around one of them: extend finds their distance with inline code
+// (rect_t / box_t) instead of walking the expression tree; shade rebuilds the record like a generic root
+enum RootKind : int { ROOT_SPHERE = 0, ROOT_TRIANGLE = 1, ROOT_GENERIC = 2, ROOT_FLAT = 3 };
 
 // Everything shade reads of a (resolved) material in ONE record, so that the dependent chain
 // material -> texture -> nested texture (three round trips to L1/L2 in a latency-bound kernel) is a
@@ -202,18 +204,51 @@ __device__ __forceinline__ void rect_axes(int kind, int& a, int& b, int& c) {
     else { a = 1; b = 2; c = 0; }
 }
 
+// rect.rs:102-120, the distance only (what the closest-hit search of extend needs)
+__device__ __forceinline__ bool rect_t(int kind, double k, double a0, double a1, double b0, double b1, const Ray& ray, double lo, double hi, double& t1) {
+    int ax0, ax1, ax2;
+    rect_axes(kind, ax0, ax1, ax2);
+    double dk = comp(ray.d, ax2);
+    t1 = (k - comp(ray.o, ax2)) / dk;
+    if (!in_range(t1, lo, hi)) return false;
+    double a = fma(t1, comp(ray.d, ax0), comp(ray.o, ax0));
+    if (a < a0 || a > a1) return false;
+    double b = fma(t1, comp(ray.d, ax1), comp(ray.o, ax1));
+    if (b < b0 || b > b1) return false;
+    return true;
+}
+
+// box.rs:125-150, the distance only: the nearer of the first two faces hit (order back, front, left,
+// right, down, up; see hit_box)
+__device__ __forceinline__ bool box_t(const double* p, const Ray& ray, double lo, double hi, double& t) {
+    const double mnx = p[0], mny = p[1], mnz = p[2], mxx = p[3], mxy = p[4], mxz = p[5];
+    double first = 0.0, second = 0.0, cur;
+    int count = 0;
+#define RS_BOX_FACE_T(kind, k, a0, a1, b0, b1)                                  \
+    if (count < 2 && rect_t(kind, k, a0, a1, b0, b1, ray, lo, hi, cur)) {       \
+        if (count == 0) first = cur; else second = cur;                         \
+        ++count;                                                                \
+    }
+    RS_BOX_FACE_T(RS_RECT_XY, mnz, mnx, mxx, mny, mxy)
+    RS_BOX_FACE_T(RS_RECT_XY, mxz, mnx, mxx, mny, mxy)
+    RS_BOX_FACE_T(RS_RECT_YZ, mnx, mny, mxy, mnz, mxz)
+    RS_BOX_FACE_T(RS_RECT_YZ, mxx, mny, mxy, mnz, mxz)
+    RS_BOX_FACE_T(RS_RECT_XZ, mny, mnx, mxx, mnz, mxz)
+    RS_BOX_FACE_T(RS_RECT_XZ, mxy, mnx, mxx, mnz, mxz)
+#undef RS_BOX_FACE_T
+    if (count == 0) return false;
+    t = (count == 1 || first < second) ? first : second;
+    return true;
+}
+
 // rect.rs:102-120 + HitRecord::new
 __device__ __forceinline__ bool hit_rect(int kind, double k, double a0, double a1, double b0, double b1, int material,
                                          const Ray& ray, double lo, double hi, HitRec& h) {
     int ax0, ax1, ax2;
     rect_axes(kind, ax0, ax1, ax2);
     double dk = comp(ray.d, ax2);
-    double t1 = (k - comp(ray.o, ax2)) / dk;
-    if (!in_range(t1, lo, hi)) return false;
-    double a = fma(t1, comp(ray.d, ax0), comp(ray.o, ax0));
-    if (a < a0 || a > a1) return false;
-    double b = fma(t1, comp(ray.d, ax1), comp(ray.o, ax1));
-    if (b < b0 || b > b1) return false;
+    double t1;
+    if (!rect_t(kind, k, a0, a1, b0, b1, ray, lo, hi, t1)) return false;
     h.point = ray_at(ray, t1);
     h.outside = dk < 0.0;  // dot(d, +axis) < 0
     V3 n = v3(0.0, 0.0, 0.0);
