@@ -74,8 +74,8 @@ struct rs_ctx {
     std::vector<int> root_kind_host;
     int bvh_root = 0;
     int bvh_width = 2;       // RS_OPT_BVH_WIDTH: 2 = binary 64-byte nodes (default), 4 = QBVH 128-byte nodes
-    int extend_mode = 2;     // 0 static spheres only, 1 + triangles, 2 everything
-    bool shade_generic = true;
+    int extend_mode = 3;     // 0 static spheres only, 1 + triangles, 2 + flat roots (rect / box), 3 everything
+    int shade_generic = 2;  // shade tier: 0 = lean, 1 = + flat roots (no expression trees), 2 = everything
     bool uses_time = false;  // some sphere moves: rays carry their shutter time
     double scene_omax = 0.0, padded_omax = -1.0;
     int n_lights = 0;
@@ -553,7 +553,7 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
                 launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
                 tm.mark(2);
                 if (ctx->shade_generic) {
-                    launch_shade(ctx->scene, fp, ws, b, 1, 0, ctx->shade_grid, nullptr, st);
+                    launch_shade(ctx->scene, fp, ws, b, ctx->shade_generic, 0, ctx->shade_grid, nullptr, st);
                 } else {  // lean scenes: the Lambertian hits, then the other classes (see shade_kernel)
                     launch_shade(ctx->scene, fp, ws, b, 0, 1, ctx->shade_grid_lambert, nullptr, st);
                     launch_shade(ctx->scene, fp, ws, b, 0, 2, ctx->shade_grid, nullptr, st);
@@ -646,8 +646,8 @@ int rs_create(rs_ctx** out, int device) {
     rs_ctx* ctx = new rs_ctx();
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
-    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(2, 0);
-    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(1, 0);
+    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(3, 0);
+    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(2, 0);
     *out = ctx;
     return RS_OK;
 }
@@ -814,12 +814,13 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     // (binary tree: depth <= 24 SAH levels + log2(n) median levels, one push per level: fits)
     ctx->scene_omax = omax;
     // which kernel specialisations this scene needs
-    bool any_tri = false, any_generic = false;
+    bool any_tri = false, any_flat = false, any_tree = false;
     for (const BuildPrim& p : prims) {
         any_tri |= root_kind[p.root] == ROOT_TRIANGLE;
-        any_generic |= root_kind[p.root] >= ROOT_GENERIC;
+        any_flat |= root_kind[p.root] == ROOT_FLAT;
+        any_tree |= root_kind[p.root] == ROOT_GENERIC;
     }
-    ctx->extend_mode = any_generic ? 2 : (any_tri ? 1 : 0);
+    ctx->extend_mode = any_tree ? 3 : (any_flat ? 2 : (any_tri ? 1 : 0));
     ctx->uses_time = false;
     for (const rs_node& n : nodes)
         if (n.type == RS_NODE_SPHERE && (n.p[4] != 0.0 || n.p[5] != 0.0 || n.p[6] != 0.0)) ctx->uses_time = true;
@@ -828,9 +829,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
         const rs_node& n = nodes[s->lights[i]];
         lights_simple &= (n.type == RS_NODE_SPHERE || n.type == RS_NODE_RECT);
     }
-    ctx->shade_generic = any_generic || !lights_simple;
+    ctx->shade_generic = (any_tree || !lights_simple) ? 2 : (any_flat ? 1 : 0);
     ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4);
-    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic ? 1 : 0, ctx->shade_generic ? 0 : 2);
+    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, ctx->shade_generic ? 0 : 2);
     ctx->shade_grid_lambert = ctx->sm_count * shade_blocks_per_sm(0, 1);
     // tuning hooks: fewer resident blocks per SM than the occupancy limit (profiling experiments)
     if (const char* e = std::getenv("RAYSNAIL_B200_EXTEND_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->extend_grid = std::min(ctx->extend_grid, ctx->sm_count * v); }
@@ -1136,7 +1137,7 @@ static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), 0));
     launch_raygen(fp, ctx->ws, 0);
     launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->bvh_width == 4, 0, ctx->extend_grid, 0);  // probes: misses stay visible to shade
-    if (shade && ctx->shade_generic) launch_shade(ctx->scene, fp, ctx->ws, 0, 1, 0, ctx->shade_grid, &dbg, 0);
+    if (shade && ctx->shade_generic) launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic, 0, ctx->shade_grid, &dbg, 0);
     if (shade && !ctx->shade_generic) {
         launch_shade(ctx->scene, fp, ctx->ws, 0, 0, 1, ctx->shade_grid_lambert, &dbg, 0);
         launch_shade(ctx->scene, fp, ctx->ws, 0, 0, 2, ctx->shade_grid, &dbg, 0);

@@ -236,7 +236,8 @@ __device__ __forceinline__ double next_up(double x) {
 // exact tie the object its randomly-built tree visits first wins; the canonical rule here (and
 // in the oracle) is order-independent: the limit admits t == best.t and the lower id wins.
 // MODE selects what a leaf may hold, so that scenes made of plain spheres (and triangles) get a
-// lean kernel without the expression-tree code: 0 = static spheres, 1 = + triangles, 2 = all.
+// lean kernel without the expression-tree code: 0 = static spheres, 1 = + triangles, 2 = + rects and
+// boxes, bare or under one TfFacade (ROOT_FLAT: still no expression-tree code), 3 = everything.
 // `ref` is the decoded leaf reference (root << 2 | kind).
 template <int MODE>
 __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& ray, const RngCtx& rng, Closest& best) {
@@ -278,7 +279,7 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
             best.root = root;
             best.material = -2;
         }
-    } else if (MODE >= 2) {
+    } else if (MODE >= 3) {
         if (__ldg(&S.root_gate[root])) {
             const double inf = __longlong_as_double(0x7ff0000000000000LL);
             if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
@@ -339,7 +340,10 @@ __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); 
 #ifndef RS_TUNE_SHADE_HYBRID
 #define RS_TUNE_SHADE_HYBRID 0
 #endif
-#define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) == 2 ? RS_TUNE_EXTEND_GENERIC : RS_TUNE_EXTEND_LEAN)
+#ifndef RS_TUNE_EXTEND_FLAT
+#define RS_TUNE_EXTEND_FLAT 3
+#endif
+#define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) == 3 ? RS_TUNE_EXTEND_GENERIC : ((MODE) == 2 ? RS_TUNE_EXTEND_FLAT : RS_TUNE_EXTEND_LEAN))
 
 // while-while traversal: every lane first walks inner nodes until it holds a leaf (or is done),
 // the warp reconverges, then the lanes holding leaves run the (expensive, f64) object test
@@ -621,7 +625,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
 // =============================================================================================
 // GENERIC = false: the scene holds only static spheres and triangles and its lights are plain
 // spheres/rects, so no expression-tree code is compiled into the kernel.
-template <bool GENERIC>
+template <bool GENERIC, bool TREES>
 __device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, const RngCtx& rng, const HitA& ha, double end_then,
                                             bool want_uv, HitRec& h) {
     // static spheres: centre and 1/r straight from the per-root tables (one level of loads
@@ -642,7 +646,24 @@ __device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, con
         triangle_record(S, ~rn, ray, ha.t, beta, gamma, h);
     } else if (GENERIC) {
         // same limit as in extend => bit-identical record
-        if (!TreeTop::hit(S, rn, ray, RS_TMIN, end_then, rng, h)) {
+        bool ok;
+        if (!TREES || kind == ROOT_FLAT) {  // rect / box, bare or under one TfFacade (tf_facade.rs:41-56)
+            const rs_node* n = S.nodes + rn;
+            const XformPre* x = nullptr;
+            Ray r = ray;
+            if (n->type == RS_NODE_TRANSFORM) {
+                x = S.xf + n->first_xform;
+                r.o = xf_apply(x->inv, ray.o, 1.0);
+                r.d = xf_apply(x->inv, ray.d, 0.0);
+                n = S.nodes + n->child0;
+            }
+            ok = n->type == RS_NODE_BOX ? hit_box(*n, r, RS_TMIN, end_then, h)
+                                        : hit_rect(n->rect_axis, n->p[0], n->p[1], n->p[2], n->p[3], n->p[4], n->material, r, RS_TMIN, end_then, h);
+            if (ok && x) h.point = xf_apply(x->fwd, h.point, 1.0);
+        } else {
+            ok = TreeTop::hit(S, rn, ray, RS_TMIN, end_then, rng, h);
+        }
+        if (!ok) {
             h.point = ray_at(ray, ha.t);
             h.normal = v3(0.0, 1.0, 0.0);
             h.t1 = ha.t; h.t2 = ha.t; h.u = 0.0; h.v = 0.0; h.material = -1; h.outside = true;
@@ -750,10 +771,13 @@ __device__ __forceinline__ void dbg_store3(double* p, uint32_t i, V3 v) {
 // spills again and is slower than two blocks), 2 = everything else.  Lean scenes launch 1 then 2,
 // generic scenes 0.
 #define RS_SHADE_IN_SET(SET, c) ((SET) == 0 || (((c) == 1 + RS_MAT_LAMBERTIAN || (c) == RS_FRONT_CLASS(1 + RS_MAT_LAMBERTIAN)) == ((SET) == 1)))
-template <bool GENERIC, int SET>
-__global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENERIC ? RS_TUNE_SHADE_GENERIC : (SET == 1 ? RS_TUNE_SHADE_LAMBERT : RS_TUNE_SHADE_LEAN)) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+// TIER: 0 = lean scenes (spheres, triangles; staged pipeline), 1 = + ROOT_FLAT objects, lights are plain
+// spheres / rects (no expression-tree code), 2 = everything
+template <int TIER, int SET>
+__global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? RS_TUNE_SHADE_GENERIC : (SET == 1 ? RS_TUNE_SHADE_LAMBERT : RS_TUNE_SHADE_LEAN)) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                             const __grid_constant__ WaveState ws, const int bounce,
                                                             const __grid_constant__ DebugOut dbg, const int has_dbg) {
+    constexpr bool GENERIC = TIER >= 1, TREES = TIER >= 2;
     extern __shared__ __align__(16) uint4 s_stage[];
     const PathBuf& in = ws.buf[bounce & 1];
     const PathBuf& out = ws.buf[(bounce + 1) & 1];
@@ -960,7 +984,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                 HitRec h;
                 double end_then = 0.0;
                 if constexpr (GENERIC) end_then = S.root_kind[ha.root] >= ROOT_GENERIC ? ws.hit_end[i] : 0.0;
-                rebuild_hit<GENERIC>(S, p.ray, rng, ha, end_then, want_uv, h);
+                rebuild_hit<GENERIC, TREES>(S, p.ray, rng, ha, end_then, want_uv, h);
 
                 const float4 col = material_color(S, mat, h.u, h.v, h.point);
 
@@ -1053,7 +1077,7 @@ __global__ void __launch_bounds__(GENERIC ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, GENE
                         pdf_val = 0.3183098861837907;
                         const uint32_t light_k = S.n_lights == 1 ? 0u : w.y % (uint32_t)S.n_lights;  // list.rs:49-52
                         V3 to_light;
-                        if (GENERIC) {
+                        if (TREES) {
                             to_light = TreeTop::random(S, S.lights[light_k], h.point, rng);
                         } else {
                             const rs_node& ln = S.light_nodes[light_k];
@@ -1162,7 +1186,7 @@ __global__ void __launch_bounds__(RS_BLOCK) probe_primary_kernel(const __grid_co
         rng.key = fp.key; rng.pixel = p.pixel; rng.sample = p.sample; rng.depth = 1;
         HitRec h;
         const double end_then = S.root_kind[ha.root] >= ROOT_GENERIC ? ws.hit_end[i] : 0.0;
-        rebuild_hit<true>(S, p.ray, rng, ha, end_then, true, h);
+        rebuild_hit<true, true>(S, p.ray, rng, ha, end_then, true, h);
         if (dbg.t) dbg.t[px] = h.t1;
         dbg_store3(dbg.normal3, px, h.normal);
         dbg_store3(dbg.point3, px, h.point);
@@ -1288,8 +1312,8 @@ void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s) {
 template <int MODE, bool WIDE>
 static const void* extend_fn() { return (const void*)extend_kernel<MODE, WIDE>; }
 static const void* extend_fn_for(int mode, int wide) {
-    if (wide) return mode == 0 ? extend_fn<0, true>() : (mode == 1 ? extend_fn<1, true>() : extend_fn<2, true>());
-    return mode == 0 ? extend_fn<0, false>() : (mode == 1 ? extend_fn<1, false>() : extend_fn<2, false>());
+    if (wide) return mode == 0 ? extend_fn<0, true>() : (mode == 1 ? extend_fn<1, true>() : (mode == 2 ? extend_fn<2, true>() : extend_fn<3, true>()));
+    return mode == 0 ? extend_fn<0, false>() : (mode == 1 ? extend_fn<1, false>() : (mode == 2 ? extend_fn<2, false>() : extend_fn<3, false>()));
 }
 void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int miss_in_extend, int grid,
                    cudaStream_t s) {
@@ -1299,10 +1323,11 @@ void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, 
 void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int set, int grid, const DebugOut* dbg, cudaStream_t s) {
     DebugOut d = {};
     if (dbg) d = *dbg;
-    if (generic) shade_kernel<true, 0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else if (set == 1) shade_kernel<false, 1><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else if (set == 2) shade_kernel<false, 2><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else shade_kernel<false, 0><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    if (generic == 2) shade_kernel<2, 0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else if (generic == 1) shade_kernel<1, 0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else if (set == 1) shade_kernel<0, 1><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else if (set == 2) shade_kernel<0, 2><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else shade_kernel<0, 0><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
 }
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s) {
     probe_primary_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(S, fp, ws, dbg);
@@ -1335,9 +1360,10 @@ int extend_blocks_per_sm(int mode, int wide) {
 int shade_blocks_per_sm(int generic, int set) {
     int n = 0;
     if (generic) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<true, 0>, RS_BLOCK, 0);
+        if (generic == 2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<2, 0>, RS_BLOCK, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<1, 0>, RS_BLOCK, 0);
     } else {
-        const void* fn = set == 1 ? (const void*)shade_kernel<false, 1> : (set == 2 ? (const void*)shade_kernel<false, 2> : (const void*)shade_kernel<false, 0>);
+        const void* fn = set == 1 ? (const void*)shade_kernel<0, 1> : (set == 2 ? (const void*)shade_kernel<0, 2> : (const void*)shade_kernel<0, 0>);
         cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, RS_SHADE_SMEM);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM);
     }
