@@ -552,11 +552,11 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
                 tm.mark(1);
                 launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
                 tm.mark(2);
-                if (ctx->shade_generic) {
-                    launch_shade(ctx->scene, fp, ws, b, ctx->shade_generic, 0, ctx->shade_grid, nullptr, st);
-                } else {  // lean scenes: the Lambertian hits, then the other classes (see shade_kernel)
-                    launch_shade(ctx->scene, fp, ws, b, 0, 1, ctx->shade_grid_lambert, nullptr, st);
-                    launch_shade(ctx->scene, fp, ws, b, 0, 2, ctx->shade_grid, nullptr, st);
+                if (ctx->shade_generic == 2) {
+                    launch_shade(ctx->scene, fp, ws, b, 2, 0, ctx->shade_grid, nullptr, st);
+                } else {  // lean / flat scenes: the Lambertian hits, then the other classes (see shade_kernel)
+                    launch_shade(ctx->scene, fp, ws, b, ctx->shade_generic, 1, ctx->shade_grid_lambert, nullptr, st);
+                    launch_shade(ctx->scene, fp, ws, b, ctx->shade_generic, 2, ctx->shade_grid, nullptr, st);
                     ++launches;
                 }
                 launches += 2;
@@ -831,8 +831,8 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     }
     ctx->shade_generic = (any_tree || !lights_simple) ? 2 : (any_flat ? 1 : 0);
     ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4);
-    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, ctx->shade_generic ? 0 : 2);
-    ctx->shade_grid_lambert = ctx->sm_count * shade_blocks_per_sm(0, 1);
+    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, ctx->shade_generic == 2 ? 0 : 2);
+    ctx->shade_grid_lambert = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic == 2 ? 0 : ctx->shade_generic, 1);
     // tuning hooks: fewer resident blocks per SM than the occupancy limit (profiling experiments)
     if (const char* e = std::getenv("RAYSNAIL_B200_EXTEND_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->extend_grid = std::min(ctx->extend_grid, ctx->sm_count * v); }
     if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid = std::min(ctx->shade_grid, ctx->sm_count * v); }
@@ -1137,10 +1137,10 @@ static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), 0));
     launch_raygen(fp, ctx->ws, 0);
     launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->bvh_width == 4, 0, ctx->extend_grid, 0);  // probes: misses stay visible to shade
-    if (shade && ctx->shade_generic) launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic, 0, ctx->shade_grid, &dbg, 0);
-    if (shade && !ctx->shade_generic) {
-        launch_shade(ctx->scene, fp, ctx->ws, 0, 0, 1, ctx->shade_grid_lambert, &dbg, 0);
-        launch_shade(ctx->scene, fp, ctx->ws, 0, 0, 2, ctx->shade_grid, &dbg, 0);
+    if (shade && ctx->shade_generic == 2) launch_shade(ctx->scene, fp, ctx->ws, 0, 2, 0, ctx->shade_grid, &dbg, 0);
+    if (shade && ctx->shade_generic != 2) {
+        launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic, 1, ctx->shade_grid_lambert, &dbg, 0);
+        launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic, 2, ctx->shade_grid, &dbg, 0);
     }
     else launch_probe_primary(ctx->scene, fp, ctx->ws, dbg, 0);
     CK(cudaGetLastError());

@@ -1324,6 +1324,8 @@ void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, i
     DebugOut d = {};
     if (dbg) d = *dbg;
     if (generic == 2) shade_kernel<2, 0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else if (generic == 1 && set == 1) shade_kernel<1, 1><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    else if (generic == 1 && set == 2) shade_kernel<1, 2><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
     else if (generic == 1) shade_kernel<1, 0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
     else if (set == 1) shade_kernel<0, 1><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
     else if (set == 2) shade_kernel<0, 2><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
@@ -1361,6 +1363,8 @@ int shade_blocks_per_sm(int generic, int set) {
     int n = 0;
     if (generic) {
         if (generic == 2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<2, 0>, RS_BLOCK, 0);
+        else if (set == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<1, 1>, RS_BLOCK, 0);
+        else if (set == 2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<1, 2>, RS_BLOCK, 0);
         else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<1, 0>, RS_BLOCK, 0);
     } else {
         const void* fn = set == 1 ? (const void*)shade_kernel<0, 1> : (set == 2 ? (const void*)shade_kernel<0, 2> : (const void*)shade_kernel<0, 0>);

@@ -241,16 +241,12 @@ __device__ __forceinline__ bool box_t(const double* p, const Ray& ray, double lo
     return true;
 }
 
-// rect.rs:102-120 + HitRecord::new
-__device__ __forceinline__ bool hit_rect(int kind, double k, double a0, double a1, double b0, double b1, int material,
-                                         const Ray& ray, double lo, double hi, HitRec& h) {
+// HitRecord::new for a rect hit at distance t1 (rect.rs:102-120, hit.rs:32-53)
+__device__ __forceinline__ void rect_record(int kind, double a0, double a1, double b0, double b1, int material, const Ray& ray, double t1, HitRec& h) {
     int ax0, ax1, ax2;
     rect_axes(kind, ax0, ax1, ax2);
-    double dk = comp(ray.d, ax2);
-    double t1;
-    if (!rect_t(kind, k, a0, a1, b0, b1, ray, lo, hi, t1)) return false;
     h.point = ray_at(ray, t1);
-    h.outside = dk < 0.0;  // dot(d, +axis) < 0
+    h.outside = comp(ray.d, ax2) < 0.0;  // dot(d, +axis) < 0
     V3 n = v3(0.0, 0.0, 0.0);
     set_comp(n, ax2, h.outside ? 1.0 : -1.0);
     h.normal = n;
@@ -259,33 +255,47 @@ __device__ __forceinline__ bool hit_rect(int kind, double k, double a0, double a
     h.t2 = RS_F64_MAX;
     h.u = (comp(h.point, ax0) - a0) / (a1 - a0);
     h.v = (comp(h.point, ax1) - b0) / (b1 - b0);
+}
+
+__device__ __forceinline__ bool hit_rect(int kind, double k, double a0, double a1, double b0, double b1, int material,
+                                         const Ray& ray, double lo, double hi, HitRec& h) {
+    double t1;
+    if (!rect_t(kind, k, a0, a1, b0, b1, ray, lo, hi, t1)) return false;
+    rect_record(kind, a0, a1, b0, b1, material, ray, t1, h);
     return true;
 }
 
-// box.rs:125-150: six faces in the order back, front, left, right, down, up
+// box.rs:125-150: six faces in the order back, front, left, right, down, up; the first two that
+// are hit count.  One record is built, for the face that is returned.
 static __device__ __noinline__ bool hit_box(const rs_node& n, const Ray& ray, double lo, double hi, HitRec& h) {
     const double mnx = n.p[0], mny = n.p[1], mnz = n.p[2], mxx = n.p[3], mxy = n.p[4], mxz = n.p[5];
-    HitRec first, second;
-    int count = 0;
-    HitRec cur;
-#define RS_BOX_FACE(kind, k, a0, a1, b0, b1)                                   \
-    if (count < 2 && hit_rect(kind, k, a0, a1, b0, b1, n.material, ray, lo, hi, cur)) { \
-        if (count == 0) first = cur; else second = cur;                          \
-        ++count;                                                                 \
+    double t_first = 0.0, t_second = 0.0, cur;
+    int f_first = 0, f_second = 0, count = 0;
+#define RS_BOX_FACE(face, kind, k, a0, a1, b0, b1)                              \
+    if (count < 2 && rect_t(kind, k, a0, a1, b0, b1, ray, lo, hi, cur)) {       \
+        if (count == 0) { t_first = cur; f_first = face; }                      \
+        else { t_second = cur; f_second = face; }                               \
+        ++count;                                                                \
     }
-    RS_BOX_FACE(RS_RECT_XY, mnz, mnx, mxx, mny, mxy)
-    RS_BOX_FACE(RS_RECT_XY, mxz, mnx, mxx, mny, mxy)
-    RS_BOX_FACE(RS_RECT_YZ, mnx, mny, mxy, mnz, mxz)
-    RS_BOX_FACE(RS_RECT_YZ, mxx, mny, mxy, mnz, mxz)
-    RS_BOX_FACE(RS_RECT_XZ, mny, mnx, mxx, mnz, mxz)
-    RS_BOX_FACE(RS_RECT_XZ, mxy, mnx, mxx, mnz, mxz)
+    RS_BOX_FACE(0, RS_RECT_XY, mnz, mnx, mxx, mny, mxy)
+    RS_BOX_FACE(1, RS_RECT_XY, mxz, mnx, mxx, mny, mxy)
+    RS_BOX_FACE(2, RS_RECT_YZ, mnx, mny, mxy, mnz, mxz)
+    RS_BOX_FACE(3, RS_RECT_YZ, mxx, mny, mxy, mnz, mxz)
+    RS_BOX_FACE(4, RS_RECT_XZ, mny, mnx, mxx, mnz, mxz)
+    RS_BOX_FACE(5, RS_RECT_XZ, mxy, mnx, mxx, mnz, mxz)
 #undef RS_BOX_FACE
     if (count == 0) return false;
-    if (count == 1) { h = first; return true; }
-    // two hits: HitRecord::with_normal -> outside = true, t2 = the other face
-    if (first.t1 < second.t1) { h = first; h.t2 = second.t1; }
-    else { h = second; h.t2 = first.t1; }
-    h.outside = true;
+    // two hits: the nearer one with HitRecord::with_normal -> outside = true, t2 = the other face
+    const bool take_first = count == 1 || t_first < t_second;
+    const int face = take_first ? f_first : f_second;
+    const double t1 = take_first ? t_first : t_second;
+    if (face < 2) rect_record(RS_RECT_XY, mnx, mxx, mny, mxy, n.material, ray, t1, h);
+    else if (face < 4) rect_record(RS_RECT_YZ, mny, mxy, mnz, mxz, n.material, ray, t1, h);
+    else rect_record(RS_RECT_XZ, mnx, mxx, mnz, mxz, n.material, ray, t1, h);
+    if (count == 2) {
+        h.t2 = take_first ? t_second : t_first;
+        h.outside = true;
+    }
     return true;
 }
 
