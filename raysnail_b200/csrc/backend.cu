@@ -95,7 +95,8 @@ struct rs_ctx {
     int wave_streams = 2;
     cudaStream_t aux_stream[kMaxSets - 1] = {};
     cudaEvent_t ev_fork = nullptr, ev_join[kMaxSets - 1] = {}, ev_acc[kMaxSets] = {};
-    int extend_grid = 148, shade_grid = 148, shade_grid_lambert = 148;
+    int extend_grid = 148, shade_grid = 148, shade_grid_lambert = 148, extend_dyn_grid = 148;
+    int dyn_from = -1;  // first bounce that uses the dynamic-fetch extend kernel (lean scenes, binary BVH); -1 = never
 
     // scratch for rs_render / probes
     DevBuf d_accum, d_out, d_mask, d_dbg[11];
@@ -550,7 +551,10 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
             ++launches;
             for (int b = 0; b < p->depth; ++b) {
                 tm.mark(1);
-                launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
+                if (ctx->dyn_from >= 0 && b >= ctx->dyn_from && ctx->extend_mode < 2 && ctx->bvh_width == 2)
+                    launch_extend_dyn(ctx->scene, fp, ws, b, ctx->extend_mode, 1, ctx->extend_dyn_grid, st);
+                else
+                    launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
                 tm.mark(2);
                 if (ctx->shade_generic == 2) {
                     launch_shade(ctx->scene, fp, ws, b, 2, 0, ctx->shade_grid, nullptr, st);
@@ -833,6 +837,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4);
     ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, ctx->shade_generic == 2 ? 0 : 2);
     ctx->shade_grid_lambert = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic == 2 ? 0 : ctx->shade_generic, 1);
+    ctx->extend_dyn_grid = ctx->sm_count * extend_dyn_blocks_per_sm(ctx->extend_mode < 2 ? ctx->extend_mode : 0);
+    ctx->dyn_from = -1;
+    if (const char* e = std::getenv("RAYSNAIL_B200_DYN_FROM")) ctx->dyn_from = std::atoi(e);
     // tuning hooks: fewer resident blocks per SM than the occupancy limit (profiling experiments)
     if (const char* e = std::getenv("RAYSNAIL_B200_EXTEND_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->extend_grid = std::min(ctx->extend_grid, ctx->sm_count * v); }
     if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid = std::min(ctx->shade_grid, ctx->sm_count * v); }

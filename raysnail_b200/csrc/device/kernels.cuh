@@ -122,6 +122,8 @@ void launch_finalize_peers(const PeerAccums& peers, const unsigned char* mask, f
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s);
 void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s);
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);
+void launch_extend_dyn(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int miss_in_extend, int grid, cudaStream_t s);
+int extend_dyn_blocks_per_sm(int mode);
 int extend_blocks_per_sm(int mode, int wide);
 int shade_blocks_per_sm(int generic, int set);
 
