@@ -276,6 +276,12 @@ def run_gpu(args):
     d2h = height * width * 16 if rank == 0 else 0
 
     def e2e_step():
+        if world_size == 1:
+            # the reference-facing call itself: rs_upload_scene (host scene buffers -> HBM, BVH build) +
+            # rs_render with a HOST pixel mask and a HOST output image (the C ABI's shot_to_target)
+            renderer.upload(scene)
+            renderer.render_to_ptr(cam, params, host_mask.data_ptr(), host_img.data_ptr())
+            return
         renderer.upload(scene)                       # host scene buffers -> HBM (incl. BVH build)
         d_mask.copy_(host_mask, non_blocking=True)   # pixel mask from pinned host memory
         accum.zero_()
