@@ -297,6 +297,22 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
 
 __device__ __forceinline__ float up(float x) { return x * (1.0f + RS_SLAB_EPS); }
 
+// Packed f32x2 FMA (sm_100: one FFMA2 issue slot for two fused multiply-adds, each rounded like
+// fmaf): the slab test of a node is 12 FMAs = 6 FFMA2.  extend is issue-bound.
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long ra, rb, rc, rd;
+    float2 d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
+#ifndef RS_TUNE_FFMA2
+#define RS_TUNE_FFMA2 1
+#endif
+
 #define RS_BVH_SENTINEL ((int)0x80000000)
 // material classes (1 + rs_material_type) whose `scatter` always returns Some
 #define RS_ALWAYS_CONTINUES(cls) \
@@ -390,6 +406,16 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
             const float4* np = reinterpret_cast<const float4*>(S.bvh2 + node);
             const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
             const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+#if RS_TUNE_FFMA2
+            const float2 ix2 = make_float2(idx, idx), iy2 = make_float2(idy, idy), iz2 = make_float2(idz, idz);
+            const float2 ox2 = make_float2(-oodx, -oodx), oy2 = make_float2(-oody, -oody), oz2 = make_float2(-oodz, -oodz);
+            float2 ta = ffma2(make_float2(bx.x, bx.y), ix2, ox2), tb = ffma2(make_float2(bx.z, bx.w), iy2, oy2), tc = ffma2(make_float2(bz.x, bz.y), iz2, oz2);
+            const float near0 = fmaxf(fmaxf(fminf(ta.x, ta.y), fminf(tb.x, tb.y)), fmaxf(fminf(tc.x, tc.y), tmin_f));
+            const float far0 = fminf(fminf(fmaxf(ta.x, ta.y), fmaxf(tb.x, tb.y)), fminf(fmaxf(tc.x, tc.y), tmax_f));
+            ta = ffma2(make_float2(by.x, by.y), ix2, ox2); tb = ffma2(make_float2(by.z, by.w), iy2, oy2); tc = ffma2(make_float2(bz.z, bz.w), iz2, oz2);
+            const float near1 = fmaxf(fmaxf(fminf(ta.x, ta.y), fminf(tb.x, tb.y)), fmaxf(fminf(tc.x, tc.y), tmin_f));
+            const float far1 = fminf(fminf(fmaxf(ta.x, ta.y), fmaxf(tb.x, tb.y)), fminf(fmaxf(tc.x, tc.y), tmax_f));
+#else
             float a0 = fmaf(bx.x, idx, -oodx), a1 = fmaf(bx.y, idx, -oodx);
             float b0 = fmaf(bx.z, idy, -oody), b1 = fmaf(bx.w, idy, -oody);
             float c0 = fmaf(bz.x, idz, -oodz), c1 = fmaf(bz.y, idz, -oodz);
@@ -400,6 +426,7 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
             c0 = fmaf(bz.z, idz, -oodz); c1 = fmaf(bz.w, idz, -oodz);
             const float near1 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), tmin_f));
             const float far1 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), tmax_f));
+#endif
             const bool h0 = near0 <= far0 * slack, h1 = near1 <= far1 * slack;
             if (h0 && h1) {
                 const bool swap = near1 < near0;
