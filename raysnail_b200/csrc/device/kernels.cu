@@ -286,7 +286,7 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
         }
         HitRec h;
         const double hi = next_up(best.t);
-        if (TreeTop::hit(S, __ldg(&S.root_node[root]), ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || root < best.root)) {
+        if (TreeTop::hit<false>(S, __ldg(&S.root_node[root]), ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || root < best.root)) {
             best.end_then = hi;
             best.t = h.t1;
             best.root = root;

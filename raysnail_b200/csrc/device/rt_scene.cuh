@@ -189,12 +189,25 @@ __device__ __forceinline__ void sphere_record(const double* p, int material, con
     if (want_uv) sphere_uv(c, h.point, h.u, h.v);
 }
 
+// FULL = false (all `hit` routines below): only what the closest-hit search and the CSG rules
+// consult is filled in — t1, t2, point, material — not the normal, uv and `outside` (a sphere's
+// uv alone is an atan2 and an asin per candidate hit).  extend searches with FULL = false; shade
+// rebuilds the record of the winner with FULL = true from the same distances.
+__device__ __forceinline__ void lean_record(const Ray& ray, double t1, double t2, int material, HitRec& h) {
+    h.point = ray_at(ray, t1);
+    h.t1 = t1;
+    h.t2 = t2;
+    h.material = material;
+}
+
+template <bool FULL>
 __device__ __forceinline__ bool hit_sphere_node(const rs_node& n, const Ray& ray, double lo, double hi, HitRec& h) {
     V3 c = v3(n.p[0], n.p[1], n.p[2]);
     if (n.p[4] != 0.0 || n.p[5] != 0.0 || n.p[6] != 0.0) c = c + v3(n.p[4], n.p[5], n.p[6]) * ray.time;  // center_at
     double t1, t2;
     if (!sphere_roots(c, n.p[3] * n.p[3], ray, lo, hi, t1, t2)) return false;
-    sphere_record(n.p, n.material, ray, t1, t2, true, h);
+    if (FULL) sphere_record(n.p, n.material, ray, t1, t2, true, h);
+    else lean_record(ray, t1, t2, n.material, h);
     return true;
 }
 
@@ -257,16 +270,19 @@ __device__ __forceinline__ void rect_record(int kind, double a0, double a1, doub
     h.v = (comp(h.point, ax1) - b0) / (b1 - b0);
 }
 
+template <bool FULL = true>
 __device__ __forceinline__ bool hit_rect(int kind, double k, double a0, double a1, double b0, double b1, int material,
                                          const Ray& ray, double lo, double hi, HitRec& h) {
     double t1;
     if (!rect_t(kind, k, a0, a1, b0, b1, ray, lo, hi, t1)) return false;
-    rect_record(kind, a0, a1, b0, b1, material, ray, t1, h);
+    if (FULL) rect_record(kind, a0, a1, b0, b1, material, ray, t1, h);
+    else lean_record(ray, t1, RS_F64_MAX, material, h);
     return true;
 }
 
 // box.rs:125-150: six faces in the order back, front, left, right, down, up; the first two that
 // are hit count.  One record is built, for the face that is returned.
+template <bool FULL = true>
 static __device__ __noinline__ bool hit_box(const rs_node& n, const Ray& ray, double lo, double hi, HitRec& h) {
     const double mnx = n.p[0], mny = n.p[1], mnz = n.p[2], mxx = n.p[3], mxy = n.p[4], mxz = n.p[5];
     double t_first = 0.0, t_second = 0.0, cur;
@@ -289,6 +305,10 @@ static __device__ __noinline__ bool hit_box(const rs_node& n, const Ray& ray, do
     const bool take_first = count == 1 || t_first < t_second;
     const int face = take_first ? f_first : f_second;
     const double t1 = take_first ? t_first : t_second;
+    if (!FULL) {
+        lean_record(ray, t1, count == 2 ? (take_first ? t_second : t_first) : RS_F64_MAX, n.material, h);
+        return true;
+    }
     if (face < 2) rect_record(RS_RECT_XY, mnx, mxx, mny, mxy, n.material, ray, t1, h);
     else if (face < 4) rect_record(RS_RECT_YZ, mny, mxy, mnz, mxz, n.material, ray, t1, h);
     else rect_record(RS_RECT_XZ, mnx, mxx, mnz, mxz, n.material, ray, t1, h);
@@ -311,6 +331,7 @@ __device__ __forceinline__ V3 quadric_normal(const double* q, V3 p) {
 }
 
 // quadric.rs:112-182
+template <bool FULL = true>
 static __device__ __noinline__ bool hit_quadric(const rs_node& n, const Ray& ray, double lo, double hi, HitRec& h) {
     const double qa = n.p[0], qb = n.p[1], qc = n.p[2], qd = n.p[3], qe = n.p[4], qf = n.p[5], qg = n.p[6], qh = n.p[7], qi = n.p[8], qj = n.p[9];
     const double xo = ray.o.x, yo = ray.o.y, zo = ray.o.z, xd = ray.d.x, yd = ray.d.y, zd = ray.d.z;
@@ -332,6 +353,10 @@ static __device__ __noinline__ bool hit_quadric(const rs_node& n, const Ray& ray
         if (in_range(ta, lo, hi)) { t1 = ta; t2 = tb; }
         else if (in_range(tb, lo, hi)) { t1 = tb; t2 = RS_F64_MAX; }
         else return false;
+    }
+    if (!FULL) {
+        lean_record(ray, t1, t2, n.material, h);
+        return true;
     }
     h.point = ray_at(ray, t1);
     V3 nn = quadric_normal(n.p, h.point);
@@ -425,18 +450,19 @@ struct Tree {
     }
 
     // `Hittable::hit`
+    template <bool FULL = true>
     static __device__ __noinline__ bool hit(const DScene& S, int ni, const Ray& ray, double lo, double hi, const RngCtx& rng, HitRec& h) {
         const rs_node& n = S.nodes[ni];
         switch (n.type) {
-            case RS_NODE_SPHERE: return hit_sphere_node(n, ray, lo, hi, h);
-            case RS_NODE_BOX: return hit_box(n, ray, lo, hi, h);
-            case RS_NODE_RECT: return hit_rect(n.rect_axis, n.p[0], n.p[1], n.p[2], n.p[3], n.p[4], n.material, ray, lo, hi, h);
-            case RS_NODE_QUADRIC: return hit_quadric(n, ray, lo, hi, h);
+            case RS_NODE_SPHERE: return hit_sphere_node<FULL>(n, ray, lo, hi, h);
+            case RS_NODE_BOX: return hit_box<FULL>(n, ray, lo, hi, h);
+            case RS_NODE_RECT: return hit_rect<FULL>(n.rect_axis, n.p[0], n.p[1], n.p[2], n.p[3], n.p[4], n.material, ray, lo, hi, h);
+            case RS_NODE_QUADRIC: return hit_quadric<FULL>(n, ray, lo, hi, h);
             case RS_NODE_DIFFERENCE: {  // difference.rs:57-107
                 HitRec hp, hm;
-                bool has_p = Tree<D - 1>::hit(S, n.child0, ray, lo, hi, rng, hp);
+                bool has_p = Tree<D - 1>::template hit<FULL>(S, n.child0, ray, lo, hi, rng, hp);
                 if (!has_p) return false;
-                bool has_m = Tree<D - 1>::hit(S, n.child1, ray, lo, hi, rng, hm);
+                bool has_m = Tree<D - 1>::template hit<FULL>(S, n.child1, ray, lo, hi, rng, hm);
                 if (!has_m) { h = hp; return true; }
                 if (hp.t1 < hm.t1) {
                     if (!Tree<D - 1>::contains(S, n.child1, hp.point)) {
@@ -457,10 +483,10 @@ struct Tree {
                     // minus.normal(p) / minus.material(): only primitives implement them
                     V3 nn = v3(0.0, 0.0, 0.0);
                     int mm = -1;
-                    if (m.type == RS_NODE_SPHERE) { nn = vdiv(p - v3(m.p[0], m.p[1], m.p[2]), m.p[3]); mm = m.material; }
+                    if (m.type == RS_NODE_SPHERE) { if (FULL) nn = vdiv(p - v3(m.p[0], m.p[1], m.p[2]), m.p[3]); mm = m.material; }
                     else if (m.type == RS_NODE_BOX) { nn = v3(0.0, 1.0, 0.0); mm = m.material; }
                     else if (m.type == RS_NODE_RECT) { int a, b, c; rect_axes(m.rect_axis, a, b, c); set_comp(nn, c, 1.0); mm = m.material; }
-                    else if (m.type == RS_NODE_QUADRIC) { nn = quadric_normal(m.p, p); mm = m.material; }
+                    else if (m.type == RS_NODE_QUADRIC) { if (FULL) nn = quadric_normal(m.p, p); mm = m.material; }
                     h.point = p;
                     h.normal = -nn;
                     h.material = mm >= 0 ? mm : n.material;
@@ -473,8 +499,8 @@ struct Tree {
             }
             case RS_NODE_INTERSECTION: {  // intersection.rs:58-96
                 HitRec h1, h2;
-                if (!Tree<D - 1>::hit(S, n.child0, ray, lo, hi, rng, h1)) return false;
-                if (!Tree<D - 1>::hit(S, n.child1, ray, lo, hi, rng, h2)) return false;
+                if (!Tree<D - 1>::template hit<FULL>(S, n.child0, ray, lo, hi, rng, h1)) return false;
+                if (!Tree<D - 1>::template hit<FULL>(S, n.child1, ray, lo, hi, rng, h2)) return false;
                 bool first_is_1 = h1.t1 < h2.t1;
                 const HitRec& near = first_is_1 ? h1 : h2;
                 const HitRec& far = first_is_1 ? h2 : h1;
@@ -491,15 +517,15 @@ struct Tree {
                 r.o = xf_apply(x.inv, ray.o, 1.0);
                 r.d = xf_apply(x.inv, ray.d, 0.0);
                 r.time = ray.time;
-                if (!Tree<D - 1>::hit(S, n.child0, r, lo, hi, rng, h)) return false;
+                if (!Tree<D - 1>::template hit<FULL>(S, n.child0, r, lo, hi, rng, h)) return false;
                 h.point = xf_apply(x.fwd, h.point, 1.0);
                 return true;
             }
             case RS_NODE_MEDIUM: {  // constant.rs:42-80
                 HitRec r1, r2;
                 const double inf = __longlong_as_double(0x7ff0000000000000LL);
-                if (!Tree<D - 1>::hit(S, n.child0, ray, -inf, inf, rng, r1)) return false;
-                if (!Tree<D - 1>::hit(S, n.child0, ray, r1.t1 + 0.0001, inf, rng, r2)) return false;
+                if (!Tree<D - 1>::template hit<FULL>(S, n.child0, ray, -inf, inf, rng, r1)) return false;
+                if (!Tree<D - 1>::template hit<FULL>(S, n.child0, ray, r1.t1 + 0.0001, inf, rng, r2)) return false;
                 if (r1.t1 < lo) r1.t1 = lo;
                 if (r2.t1 > hi) r2.t1 = hi;
                 if (r1.t1 >= r2.t1) return false;
@@ -539,6 +565,7 @@ struct Tree {
 template <>
 struct Tree<0> {
     static __device__ __forceinline__ bool contains(const DScene&, int, V3) { return false; }
+    template <bool FULL = true>
     static __device__ __forceinline__ bool hit(const DScene&, int, const Ray&, double, double, const RngCtx&, HitRec&) { return false; }
     static __device__ __forceinline__ V3 random(const DScene&, int, V3, const RngCtx&) { return v3(1.0, 0.0, 0.0); }
 };
