@@ -96,6 +96,8 @@ struct rs_ctx {
     cudaStream_t aux_stream[kMaxSets - 1] = {};
     cudaEvent_t ev_fork = nullptr, ev_join[kMaxSets - 1] = {}, ev_acc[kMaxSets] = {};
     int extend_grid = 148, shade_grid = 148, shade_grid_lambert = 148, extend_dyn_grid = 148;
+    int extend_first_grid = 148;
+    int fuse_raygen = 1;  // bounce 0 of a render without pixel mask generates its camera rays inside extend
     int dyn_from = -1;  // first bounce that uses the dynamic-fetch extend kernel (lean scenes, binary BVH); -1 = never
 
     // scratch for rs_render / probes
@@ -546,12 +548,17 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
             const WaveState& ws = set ? ctx->ws_aux[set - 1] : ctx->ws;
             cudaStream_t st = set ? ctx->aux_stream[set - 1] : stream;
             CK(cudaMemsetAsync(ws.ctr, 0, sizeof(WaveCounters), st));
+            const bool fused_first = ctx->fuse_raygen && !fp.mask && ctx->bvh_width == 2 && p->depth > 0;
             tm.mark(0);
-            launch_raygen(fp, ws, st);
-            ++launches;
+            if (!fused_first) {
+                launch_raygen(fp, ws, st);
+                ++launches;
+            }
             for (int b = 0; b < p->depth; ++b) {
                 tm.mark(1);
-                if (ctx->dyn_from >= 0 && b >= ctx->dyn_from && ctx->extend_mode < 2 && ctx->bvh_width == 2)
+                if (b == 0 && fused_first)
+                    launch_extend_first(ctx->scene, fp, ws, ctx->extend_mode, ctx->extend_first_grid, st);
+                else if (ctx->dyn_from >= 0 && b >= ctx->dyn_from && ctx->extend_mode < 2 && ctx->bvh_width == 2)
                     launch_extend_dyn(ctx->scene, fp, ws, b, ctx->extend_mode, 1, ctx->extend_dyn_grid, st);
                 else
                     launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
@@ -840,6 +847,8 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     ctx->extend_dyn_grid = ctx->sm_count * extend_dyn_blocks_per_sm(ctx->extend_mode < 2 ? ctx->extend_mode : 0);
     ctx->dyn_from = -1;
     if (const char* e = std::getenv("RAYSNAIL_B200_DYN_FROM")) ctx->dyn_from = std::atoi(e);
+    ctx->extend_first_grid = ctx->sm_count * extend_first_blocks_per_sm(ctx->extend_mode);
+    if (const char* e = std::getenv("RAYSNAIL_B200_FUSE_RAYGEN")) ctx->fuse_raygen = std::atoi(e);
     // tuning hooks: fewer resident blocks per SM than the occupancy limit (profiling experiments)
     if (const char* e = std::getenv("RAYSNAIL_B200_EXTEND_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->extend_grid = std::min(ctx->extend_grid, ctx->sm_count * v); }
     if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid = std::min(ctx->shade_grid, ctx->sm_count * v); }

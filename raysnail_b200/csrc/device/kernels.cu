@@ -508,13 +508,17 @@ __device__ __forceinline__ int resolve_mixed(const DScene& S, int m, const RngCt
     return m;
 }
 
-template <int MODE, bool WIDE>
+// FIRST = true (bounce 0, no pixel mask): the kernel GENERATES the camera ray of path i itself
+// (raygen fused in: Camera::ray + the strata loop of painter.rs:154-187) instead of reading a
+// record raygen wrote — one kernel, one 64-byte record read per path less, and a path that ends on
+// its first segment (sky, light) never gets a record at all.
+template <int MODE, bool WIDE, bool FIRST>
 __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                                                      const __grid_constant__ WaveState ws, const int bounce,
                                                                                      const int miss_in_extend) {
     // virtual index space: [0, nf32) = the front stack padded to a multiple of 32 (so that no warp
     // mixes the two kinds of rays), [nf32, nf32 + nb) = the back stack, top first
-    const uint32_t nf = ws.ctr->n_rays[bounce], nb = ws.ctr->n_back[bounce];
+    const uint32_t nf = FIRST ? fp.n_pixels * fp.n_samples : ws.ctr->n_rays[bounce], nb = FIRST ? 0u : ws.ctr->n_back[bounce];
     const uint32_t nf32 = (nf + 31u) & ~31u;
     const uint32_t n = nf32 + nb;
     const uint32_t lane_zero = RS_LANE_ZERO(ws);
@@ -522,7 +526,10 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
     uint32_t* head = &ws.ctr->extend_head[bounce];
     uint32_t* class_count = ws.ctr->class_count[bounce];
     const bool last_bounce = bounce + 1 >= fp.depth;
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_segments, (unsigned long long)(nf + nb));
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(&ws.stats->n_segments, (unsigned long long)(nf + nb));
+        if (FIRST) atomicAdd(&ws.stats->n_samples, (unsigned long long)nf);
+    }
     // the cursor bump for the NEXT batch is issued before the current batch is processed, so the
     // atomic's round trip to L2 overlaps with the traversal instead of heading every batch
 #if RS_TUNE_EXTEND_STATIC
@@ -557,7 +564,16 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
             Ray ray;
             RngCtx rng;
             rng.key = fp.key;
-            load_ray_only(fp, ws, in, i, ray, rng.pixel, rng.sample);
+            if constexpr (FIRST) {
+                decode_slot(fp, i, rng.pixel, rng.sample);
+                const uint32_t width = (uint32_t)fp.cam.width, row = rng.pixel / width, col = rng.pixel - row * width;
+                uint32_t s_j = __umulhi(rng.sample, fp.magic_q), s_i = rng.sample - s_j * (uint32_t)fp.sqrt_spp;
+                if (s_i >= (uint32_t)fp.sqrt_spp) { ++s_j; s_i -= (uint32_t)fp.sqrt_spp; }
+                rng.depth = 0;
+                ray = camera_ray(fp, (int)row, (int)col, (int)s_i, (int)s_j, rng);
+            } else {
+                load_ray_only(fp, ws, in, i, ray, rng.pixel, rng.sample);
+            }
             rng.depth = (uint32_t)bounce + 1;
             if constexpr (RS_TUNE_RESERVE && MODE < 2) rng_of_lane = rng;
             Closest best;
@@ -581,7 +597,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                     // record, no queue entry, no gather of the path record in shade.
                     const float4 c = mh.c0;
                     const double mul = mh.a;
-                    const uint4 q3 = in.rec[4 * (size_t)i + 3];  // (T, slot)
+                    const uint4 q3 = FIRST ? make_uint4(0x3f800000u, 0x3f800000u, 0x3f800000u, i) : in.rec[4 * (size_t)i + 3];  // (T, slot)
                     ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * (float)((double)c.x * mul), __uint_as_float(q3.y) * (float)((double)c.y * mul),
                                                    __uint_as_float(q3.z) * (float)((double)c.z * mul), 0.f);
                     cls = -1;
@@ -593,11 +609,21 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                 // a miss ends the path with `world.background(ray)` (camera.rs:253-254): finish it
                 // here instead of sending it through a queue to the shade kernel
                 const float4 bg = background(S, ray.d);
-                const uint4 q3 = in.rec[4 * (size_t)i + 3];  // (T, slot)
+                const uint4 q3 = FIRST ? make_uint4(0x3f800000u, 0x3f800000u, 0x3f800000u, i) : in.rec[4 * (size_t)i + 3];  // (T, slot)
                 ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * bg.x, __uint_as_float(q3.y) * bg.y, __uint_as_float(q3.z) * bg.z, 0.f);
                 cls = -1;
             } else {
                 ws.hit[i] = h;
+            }
+            if constexpr (FIRST) {
+                if (cls >= 0) {  // the path goes on to shade: now it needs its record (and a zeroed contribution)
+                    PathRec p;
+                    p.ray = ray;
+                    p.T = make_float3(1.f, 1.f, 1.f);
+                    p.slot = i;
+                    store_path(ws, in, i, p);
+                    ws.contrib[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
             }
         }
         // material-coherent bucketing
@@ -1557,7 +1583,21 @@ void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s) {
     raygen_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(fp, ws);
 }
 template <int MODE, bool WIDE>
-static const void* extend_fn() { return (const void*)extend_kernel<MODE, WIDE>; }
+static const void* extend_fn() { return (const void*)extend_kernel<MODE, WIDE, false>; }
+static const void* extend_first_fn_for(int mode) {
+    return mode == 0 ? (const void*)extend_kernel<0, false, true> : (mode == 1 ? (const void*)extend_kernel<1, false, true>
+                     : (mode == 2 ? (const void*)extend_kernel<2, false, true> : (const void*)extend_kernel<3, false, true>));
+}
+void launch_extend_first(const DScene& S, const FrameParams& fp, const WaveState& ws, int mode, int grid, cudaStream_t s) {
+    int bounce = 0, miss_in_extend = 1;
+    void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
+    cudaLaunchKernel(extend_first_fn_for(mode), dim3(grid), dim3(RS_BLOCK), args, 0, s);
+}
+int extend_first_blocks_per_sm(int mode) {
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_first_fn_for(mode), RS_BLOCK, 0);
+    return n > 0 ? n : 1;
+}
 static const void* extend_fn_for(int mode, int wide) {
     if (wide) return mode == 0 ? extend_fn<0, true>() : (mode == 1 ? extend_fn<1, true>() : (mode == 2 ? extend_fn<2, true>() : extend_fn<3, true>()));
     return mode == 0 ? extend_fn<0, false>() : (mode == 1 ? extend_fn<1, false>() : (mode == 2 ? extend_fn<2, false>() : extend_fn<3, false>()));

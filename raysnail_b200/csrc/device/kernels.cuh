@@ -124,6 +124,8 @@ void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaS
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);
 void launch_extend_dyn(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int miss_in_extend, int grid, cudaStream_t s);
 int extend_dyn_blocks_per_sm(int mode);
+void launch_extend_first(const DScene& S, const FrameParams& fp, const WaveState& ws, int mode, int grid, cudaStream_t s);
+int extend_first_blocks_per_sm(int mode);
 int extend_blocks_per_sm(int mode, int wide);
 int shade_blocks_per_sm(int generic, int set);
 
