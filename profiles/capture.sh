@@ -7,10 +7,8 @@ set -x
 python bench.py --steps 3 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv \
     python bench.py --steps 1 --warmup 1 --sqrt-spp 4 --no-cpu > gpurun_out/${TAG}_launches.log 2>&1
-# one wave = 8 bounces x (extend, shade<Lambertian>, shade<rest>) = 24 matching launches: skip the first wave,
-# capture bounce 0 and bounce 1 of the second one; plus one raygen launch
+# one wave = 8 bounces x (extend, shade<Lambertian>, shade<rest>) = 24 matching launches (bounce 0 = the extend
+# that generates the camera rays itself): skip the first wave, capture bounce 0 and bounce 1 of the second one
 ncu --set full --import-source on --clock-control none -k regex:"shade_kernel|extend_kernel" --launch-skip 24 --launch-count 6 \
     -o gpurun_out/${TAG}_full python bench.py --steps 1 --warmup 1 --sqrt-spp 4 --no-cpu > gpurun_out/${TAG}_full.log 2>&1
-ncu --set full --import-source on --clock-control none -k regex:"raygen_kernel" --launch-skip 1 --launch-count 1 \
-    -o gpurun_out/${TAG}_raygen python bench.py --steps 1 --warmup 1 --sqrt-spp 4 --no-cpu > gpurun_out/${TAG}_raygen.log 2>&1
 tail -1 gpurun_out/${TAG}_bench.json
