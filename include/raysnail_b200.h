@@ -53,8 +53,10 @@ typedef enum rs_node_type {
     RS_NODE_DIFFERENCE = 4,   /* src/hittable/csg/difference.rs    child0 = plus, child1 = minus    */
     RS_NODE_INTERSECTION = 5, /* src/hittable/csg/intersection.rs  child0 = o1,   child1 = o2       */
     RS_NODE_TRANSFORM = 6,    /* src/hittable/transform/tf_facade.rs child0; xforms[first..first+n) */
-    RS_NODE_MEDIUM = 7        /* src/hittable/medium/constant.rs   child0 = boundary; p[0]=density;
+    RS_NODE_MEDIUM = 7,       /* src/hittable/medium/constant.rs   child0 = boundary; p[0]=density;
                                  material = the Isotropic material                                  */
+    RS_NODE_RAYMARCHER = 8    /* src/hittable/geometry/raymarching.rs  the power-8 Mandelbulb about the
+                                 origin; p[0] = iterations (RayMarcher::new: 100)                  */
 } rs_node_type;
 
 /* rect_axis: which AARect constructor built it (src/hittable/geometry/rect.rs:56-78) */

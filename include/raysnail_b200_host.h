@@ -67,6 +67,7 @@ int rs_host_obj_sphere(rs_host_scene* s, const double center[3], double radius, 
 int rs_host_obj_box(rs_host_scene* s, const double p0[3], const double p1[3], int mat);
 int rs_host_obj_rect(rs_host_scene* s, int32_t rect_axis, double k, double a0, double a1, double b0, double b1, int mat);
 int rs_host_obj_quadric(rs_host_scene* s, const double q[10], int mat);
+int rs_host_obj_raymarcher(rs_host_scene* s, int mat); /* RayMarcher::new (raymarching.rs:35-40) */
 int rs_host_obj_difference(rs_host_scene* s, int plus, int minus, int mat);
 int rs_host_obj_intersection(rs_host_scene* s, int o1, int o2, int mat);
 /* ops[i]: 0 translate(v) 1 rotate_x(v[0] rad) 2 rotate_y 3 rotate_z 4 scale(v); args = n*3 doubles */

@@ -766,6 +766,118 @@ struct QuadricObj : Hittable {  // geometry/quadric.rs
     Vec3 random(const Vec3& origin, const Rng&) const override { return -origin; }                       // :202-205
 };
 
+// geometry/raymarching.rs: the power-8 Mandelbulb about the origin.
+namespace marcher {
+// :202-241.  Note `dr` is computed from the ALREADY-raised r (`r = r.powf(power)` comes first).
+inline void iterate(const Vec3& p, int iterations, double& r, double& dr, bool& inside) {
+    double x = 0.0, y = 0.0, z = 0.0;
+    const double power = 8.0;
+    r = 0.0; dr = 0.0;
+    for (int i = 0; i < iterations; ++i) {
+        r = std::sqrt(x * x + y * y + z * z);
+        double theta = std::atan2(std::sqrt(x * x + y * y), z);
+        double phi = std::atan2(y, x);
+        r = std::pow(r, power);
+        theta *= power;
+        phi *= power;
+        dr = std::pow(r, power - 1.0) * power * dr + 1.0;
+        x = r * std::sin(theta) * std::cos(phi);
+        y = r * std::sin(theta) * std::sin(phi);
+        z = r * std::cos(theta);
+        x += p.x; y += p.y; z += p.z;
+        if (x * x + y * y + z * z > 8.0) { inside = false; return; }
+    }
+    inside = true;
+}
+inline bool is_inside(const Vec3& p, int iterations) {  // :187-190
+    double r, dr; bool in;
+    iterate(p, iterations, r, dr, in);
+    return in;
+}
+inline double distance_est(const Vec3& p, int iterations) {  // :193-197 (NaN when r == 0: ln(0) * 0)
+    double r, dr; bool in;
+    iterate(p, iterations, r, dr, in);
+    return 0.5 * std::log(r) * r / dr;
+}
+}  // namespace marcher
+
+struct RayMarcherObj : Hittable {
+    int iterations = 100;
+    Vec3 normal(const Vec3& pos, bool& ok) const override {  // :83-96 (always 100 iterations)
+        ok = true;
+        const double d = 0.01;
+        Vec3 xd(d, 0.0, 0.0), yd(0.0, d, 0.0), zd(0.0, 0.0, d);
+        return unit(Vec3(marcher::distance_est(pos + xd, 100) - marcher::distance_est(pos - xd, 100),
+                         marcher::distance_est(pos + yd, 100) - marcher::distance_est(pos - yd, 100),
+                         marcher::distance_est(pos + zd, 100) - marcher::distance_est(pos - zd, 100)));
+    }
+    void uv(const Vec3& point, double& u, double& v) const override {  // :102-111
+        Vec3 p = unit(point - Vec3(0.0, 0.0, 0.0));
+        double phi = std::atan2(-p.z, p.x);
+        double theta = std::asin(p.y);
+        u = phi / 2.0 / PI + 0.5;
+        v = theta / PI + 0.5;
+    }
+    // :43-57 (the recursion unrolled: `depth` halvings, is_inside always with 100 iterations)
+    static Vec3 binary_search_surface(Vec3 outside, Vec3 inside, int depth) {
+        for (; depth > 0; --depth) {
+            Vec3 mid = (outside + inside) * 0.5;
+            if (marcher::is_inside(mid, 100)) inside = mid; else outside = mid;
+        }
+        return outside;
+    }
+    bool search_surface(const Vec3& p, const Vec3& direction, Vec3& found) const {  // :59-76
+        Vec3 df = direction * 0.05;
+        Vec3 v = p;
+        for (int i = 0; i < 200; ++i) {
+            if (marcher::is_inside(v, iterations)) { found = binary_search_surface(v - df, v, 8); return true; }
+            v = v + df;
+        }
+        return false;
+    }
+    // :113-165.  The reference only checks `length > limit.start`; `limit.end` is ignored there, so with
+    // its randomly built BVH a farther marcher hit can replace a closer hit of a sibling
+    // (bvh.rs:184-191).  Canonical rule here (oracle and GPU): a hit at or beyond limit.end is no hit.
+    bool hit(const Ray& ray, const Range& limit, const Rng&, HitRecord& out) const override {
+        double len = length(ray.direction);
+        Vec3 direction = ray.direction * (1.0 / len);
+        Vec3 current = ray.origin;
+        int steps = 0;
+        double best = 1000000.0, est = 0.0;
+        while (steps < 1000 && est < best + 1.0) {
+            ++steps;
+            est = marcher::distance_est(current, iterations);
+            if (est != est) est = 0.1;
+            if (est < 1.3) {
+                Vec3 p;
+                if (search_surface(current, direction, p)) {
+                    double dist = length(p - ray.origin);
+                    if (dist > limit.start) {
+                        double t1 = dist / len;
+                        if (!(t1 < limit.end)) return false;
+                        out = new_hit_record(ray, *this, t1, t1);
+                        return true;
+                    }
+                }
+                return false;
+            }
+            if (est < best) best = est;
+            current = current + direction * est * 0.05;
+        }
+        return false;
+    }
+    bool contains(const Vec3& p) const override { return marcher::is_inside(p, iterations); }  // :167-170
+    AABB bbox(const Range&) const override { return {Vec3(-1.3, -1.3, -1.3), Vec3(1.3, 1.3, 1.3)}; }  // :172-181
+    Vec3 random(const Vec3&, const Rng& rng) const override {  // :188-190 -> vec3.rs:91-96
+        uint32_t w[4];
+        rng.words(P_LIGHT, 0, w);
+        double a = 0.0 + u01(w[0]) * (2.0 * PI - 0.0);
+        double z = -1.0 + u01(w[1]) * (1.0 - -1.0);
+        double r = std::sqrt(1.0 - z * z);
+        return {r * std::cos(a), r * std::sin(a), z};
+    }
+};
+
 struct TriangleObj : Hittable {  // geometry/triangle_mesh.rs:17-149
     Vec3 p0, n0, n1, n2;
     double a, b, c, d, e, f;
@@ -1124,6 +1236,7 @@ bool Scene::build(const rs_scene_desc& d, bool use_desc_bbox) {
                 auto p = std::make_unique<MediumObj>(); p->boundary = child(n.child0); if (!p->boundary) return false;
                 p->density = n.p[0]; p->neg_inv_density = -1.0 / n.p[0]; out = std::move(p); break;
             }
+            case RS_NODE_RAYMARCHER: { auto p = std::make_unique<RayMarcherObj>(); p->iterations = (int)n.p[0]; out = std::move(p); break; }
             default: return false;
         }
         out->mat = mat(n.material);

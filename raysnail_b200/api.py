@@ -134,6 +134,9 @@ class Scene:
         kind = {"xy": 0, "xz": 1, "yz": 2}[axis]
         return self._ck(self._lib.rs_host_obj_rect(self._h, kind, k, a[0], a[1], b[0], b[1], mat), "obj_rect")
 
+    def raymarcher(self, mat=-1):
+        return self._ck(self._lib.rs_host_obj_raymarcher(self._h, mat), "obj_raymarcher")
+
     def quadric(self, q, mat=-1):
         return self._ck(self._lib.rs_host_obj_quadric(self._h, (C.c_double * 10)(*[float(x) for x in q]), mat), "obj_quadric")
 

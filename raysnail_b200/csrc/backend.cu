@@ -725,7 +725,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     std::vector<XformPre> xf;
     for (int i = 0; i < s->n_nodes; ++i) {
         rs_node& n = nodes[i];
-        if (n.type < RS_NODE_SPHERE || n.type > RS_NODE_MEDIUM) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad node type");
+        if (n.type < RS_NODE_SPHERE || n.type > RS_NODE_RAYMARCHER) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad node type");
         if (n.material >= s->n_materials) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "node material out of range");
         bool two = n.type == RS_NODE_DIFFERENCE || n.type == RS_NODE_INTERSECTION, one = n.type == RS_NODE_TRANSFORM || n.type == RS_NODE_MEDIUM;
         if ((two || one) && (n.child0 < 0 || n.child0 >= i)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "child0 must precede its parent");

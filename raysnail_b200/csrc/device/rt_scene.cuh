@@ -419,6 +419,109 @@ __device__ __forceinline__ V3 rect_random(const rs_node& n, V3 origin, const Rng
 }
 
 // ---------------------------------------------------------------------------------------------
+// raymarching.rs: the power-8 Mandelbulb about the origin (RayMarcher)
+// ---------------------------------------------------------------------------------------------
+// raymarching.rs:202-241.  `dr` is computed from the ALREADY-raised r, as in the reference.  The sums of
+// squares are kept un-contracted (the reference has no mul_add here).
+static __device__ __noinline__ bool marcher_iterate(V3 p, int iterations, double& r_out, double& dr_out) {
+    double x = 0.0, y = 0.0, z = 0.0, r = 0.0, dr = 0.0;
+    bool inside = true;
+    for (int i = 0; i < iterations; ++i) {
+        const double xx_yy = __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y));
+        r = sqrt(__dadd_rn(xx_yy, __dmul_rn(z, z)));
+        double theta = atan2(sqrt(xx_yy), z);
+        double phi = atan2(y, x);
+        r = pow(r, 8.0);
+        theta *= 8.0;
+        phi *= 8.0;
+        dr = __dadd_rn(__dmul_rn(__dmul_rn(pow(r, 7.0), 8.0), dr), 1.0);
+        double st, ct, sp, cp;
+        sincos(theta, &st, &ct);
+        sincos(phi, &sp, &cp);
+        x = __dadd_rn(__dmul_rn(__dmul_rn(r, st), cp), p.x);
+        y = __dadd_rn(__dmul_rn(__dmul_rn(r, st), sp), p.y);
+        z = __dadd_rn(__dmul_rn(r, ct), p.z);
+        if (__dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z)) > 8.0) { inside = false; break; }
+    }
+    r_out = r;
+    dr_out = dr;
+    return inside;
+}
+__device__ __forceinline__ bool marcher_inside(V3 p, int iterations) {  // :187-190
+    double r, dr;
+    return marcher_iterate(p, iterations, r, dr);
+}
+__device__ __forceinline__ double marcher_distance(V3 p, int iterations) {  // :193-197 (NaN when r == 0)
+    double r, dr;
+    marcher_iterate(p, iterations, r, dr);
+    return __dmul_rn(__dmul_rn(0.5, log(r)), r) / dr;
+}
+// :83-96 (always 100 iterations)
+__device__ __forceinline__ V3 marcher_normal(V3 pos) {
+    const double d = 0.01;
+    V3 xd = v3(d, 0.0, 0.0), yd = v3(0.0, d, 0.0), zd = v3(0.0, 0.0, d);
+    return unit(v3(marcher_distance(pos + xd, 100) - marcher_distance(pos - xd, 100),
+                   marcher_distance(pos + yd, 100) - marcher_distance(pos - yd, 100),
+                   marcher_distance(pos + zd, 100) - marcher_distance(pos - zd, 100)));
+}
+// :113-165 (+ search_surface :59-76, binary_search_surface :43-57).  `hi`: see the oracle — the
+// reference ignores limit.end; the canonical rule drops a hit at or beyond it.
+template <bool FULL = true>
+static __device__ __noinline__ bool hit_marcher(const rs_node& n, const Ray& ray, double lo, double hi, HitRec& h) {
+    const int iterations = (int)n.p[0];
+    const double len = length(ray.d);
+    const V3 direction = ray.d * (1.0 / len);
+    V3 current = ray.o;
+    int steps = 0;
+    double best = 1000000.0, est = 0.0;
+    while (steps < 1000 && est < best + 1.0) {
+        ++steps;
+        est = marcher_distance(current, iterations);
+        if (est != est) est = 0.1;
+        if (est < 1.3) {
+            const V3 df = direction * 0.05;
+            V3 v = current;
+            bool found = false;
+            for (int i = 0; i < 200; ++i) {
+                if (marcher_inside(v, iterations)) { found = true; break; }
+                v = v + df;
+            }
+            if (!found) return false;
+            V3 outside = v - df, inside = v;
+            for (int depth = 8; depth > 0; --depth) {
+                V3 mid = (outside + inside) * 0.5;
+                if (marcher_inside(mid, 100)) inside = mid; else outside = mid;
+            }
+            const double dist = length(outside - ray.o);
+            if (!(dist > lo)) return false;
+            const double t1 = dist / len;
+            if (!(t1 < hi)) return false;
+            if (!FULL) { lean_record(ray, t1, t1, n.material, h); return true; }
+            h.point = ray_at(ray, t1);
+            V3 nn = marcher_normal(h.point);
+            h.outside = dot(ray.d, nn) < 0.0;
+            h.normal = h.outside ? nn : -nn;
+            h.material = n.material;
+            h.t1 = t1;
+            h.t2 = t1;
+            sphere_uv(v3(0.0, 0.0, 0.0), h.point, h.u, h.v);  // :102-111
+            return true;
+        }
+        if (est < best) best = est;
+        current = current + direction * est * 0.05;
+    }
+    return false;
+}
+// vec3.rs:91-96 (`RayMarcher::random`, raymarching.rs:188-190)
+__device__ __forceinline__ V3 marcher_random(const RngCtx& rng) {
+    uint4 w = rng_words(rng, P_LIGHT, 0);
+    double a = 0.0 + u01(w.x) * (2.0 * RS_PI - 0.0);
+    double z = -1.0 + u01(w.y) * (1.0 - -1.0);
+    double r = sqrt(1.0 - z * z);
+    return v3(r * cos(a), r * sin(a), z);
+}
+
+// ---------------------------------------------------------------------------------------------
 // Expression trees
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ V3 xf_apply(const double* m, V3 p, double w) {
@@ -445,6 +548,7 @@ struct Tree {
             case RS_NODE_DIFFERENCE: return Tree<D - 1>::contains(S, n.child0, p) && !Tree<D - 1>::contains(S, n.child1, p);
             case RS_NODE_INTERSECTION: return Tree<D - 1>::contains(S, n.child0, p) && Tree<D - 1>::contains(S, n.child1, p);
             case RS_NODE_TRANSFORM: return Tree<D - 1>::contains(S, n.child0, xf_apply(S.xf[n.first_xform].inv, p, 1.0));
+            case RS_NODE_RAYMARCHER: return marcher_inside(p, (int)n.p[0]);  // raymarching.rs:167-170
             default: return false;  // rect, medium
         }
     }
@@ -458,6 +562,7 @@ struct Tree {
             case RS_NODE_BOX: return hit_box<FULL>(n, ray, lo, hi, h);
             case RS_NODE_RECT: return hit_rect<FULL>(n.rect_axis, n.p[0], n.p[1], n.p[2], n.p[3], n.p[4], n.material, ray, lo, hi, h);
             case RS_NODE_QUADRIC: return hit_quadric<FULL>(n, ray, lo, hi, h);
+            case RS_NODE_RAYMARCHER: return hit_marcher<FULL>(n, ray, lo, hi, h);
             case RS_NODE_DIFFERENCE: {  // difference.rs:57-107
                 HitRec hp, hm;
                 bool has_p = Tree<D - 1>::template hit<FULL>(S, n.child0, ray, lo, hi, rng, hp);
@@ -487,6 +592,7 @@ struct Tree {
                     else if (m.type == RS_NODE_BOX) { nn = v3(0.0, 1.0, 0.0); mm = m.material; }
                     else if (m.type == RS_NODE_RECT) { int a, b, c; rect_axes(m.rect_axis, a, b, c); set_comp(nn, c, 1.0); mm = m.material; }
                     else if (m.type == RS_NODE_QUADRIC) { if (FULL) nn = quadric_normal(m.p, p); mm = m.material; }
+                    else if (m.type == RS_NODE_RAYMARCHER) { if (FULL) nn = marcher_normal(p); mm = m.material; }
                     h.point = p;
                     h.normal = -nn;
                     h.material = mm >= 0 ? mm : n.material;
@@ -554,6 +660,7 @@ struct Tree {
             case RS_NODE_SPHERE: return sphere_random(n, origin, rng);
             case RS_NODE_RECT: return rect_random(n, origin, rng);
             case RS_NODE_QUADRIC: return -origin;  // quadric.rs:202-205
+            case RS_NODE_RAYMARCHER: return marcher_random(rng);
             case RS_NODE_DIFFERENCE:
             case RS_NODE_INTERSECTION: return Tree<D - 1>::random(S, n.child0, origin, rng);
             case RS_NODE_TRANSFORM: return Tree<D - 1>::random(S, n.child0, xf_apply(S.xf[n.first_xform].inv, origin, 1.0), rng);

@@ -83,6 +83,7 @@ int rs_host_scene_builtin(const char* name, uint64_t seed, int32_t iparam, rs_ho
         else if (n == "cornell_smoke") s->world = recipes::cornell_box_world(true, true, true, s->camera);
         else if (n == "cornell_plain") s->world = recipes::cornell_box_world(true, false, false, s->camera);
         else if (n == "all_feature") s->world = recipes::all_feature_world(seed, s->camera);
+        else if (n == "raymarching") s->world = recipes::raymarching_test_world(s->camera);
         else if (n == "mesh") s->world = recipes::mesh_test_world(iparam > 2 ? iparam : 64, false, s->camera);
         else if (n == "mesh_blinn") s->world = recipes::mesh_test_world(iparam > 2 ? iparam : 64, true, s->camera);
         else { g_host_error = "unknown builtin scene: " + n; return (int)RS_ERR_INVALID_ARGUMENT; }
@@ -244,6 +245,9 @@ int rs_host_obj_quadric(rs_host_scene* s, const double q[10], int mat) {
     return guarded([&] {
         return add_obj(s, std::make_shared<Quadric>(q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7], q[8], q[9], mat_of(s, mat)));
     });
+}
+int rs_host_obj_raymarcher(rs_host_scene* s, int mat) {
+    return guarded([&] { return add_obj(s, std::make_shared<RayMarcher>(mat_of(s, mat))); });
 }
 int rs_host_obj_difference(rs_host_scene* s, int plus, int minus, int mat) {
     return guarded([&] { return add_obj(s, std::make_shared<Difference>(obj_of(s, plus), obj_of(s, minus), mat_of(s, mat))); });

@@ -209,6 +209,27 @@ std::unique_ptr<World> mesh_test_world(int grid_n, bool blinn_phong, CameraBuild
                                    TimeRange{0.0, 0.0});
 }
 
+// examples/preview_sdl2.rs:338-407 (`render_raymarching_test`): light sphere, the Mandelbulb with a
+// Lambertian that carries Phong settings (4.0, 2), r=1000 DiffuseMetal(800) checker ground.
+std::unique_ptr<World> raymarching_test_world(CameraBuilder& cam_out) {
+    cam_out = CameraBuilder();
+    cam_out.look_from(Point3(13.0, -1.7, 3.0) * 0.7).look_at(Point3(0.0, -0.4, 0.0)).fov(20.0).aperture(0.01).focus(10.0);
+    HittableList world, lights;
+    auto lm = std::make_shared<DiffuseLight>(solid(1.0f, 0.9f, 0.8f));
+    lm->multiplier(1.5);
+    auto rs = std::make_shared<Sphere>(Vec3(300.0, 400.0, 100.0), 12.0, lm);
+    lights.add_ref(rs);
+    world.add_ref(rs);
+    auto m = std::make_shared<Lambertian>(solid(0.5f, 0.5f, 0.5f));
+    m->settings.phong_factor = 4.0;
+    m->settings.phong_exponent = 2;
+    world.add(RayMarcher(m));
+    auto ground = std::make_shared<Checker>(solid(0.26f, 0.3f, 0.16f), solid(0.1f, 0.1f, 0.1f), 10.0);
+    world.add(Sphere(Point3(0.0, -1002.0, 0.0), 1000.0, std::make_shared<DiffuseMetal>(800.0, ground)));
+    return std::make_unique<World>(world, lights, Color(0.68f, 0.80f, 0.95f, 1.0f), Color(0.2f, 0.4f, 0.7f, 1.0f),
+                                   TimeRange{0.0, 0.0});
+}
+
 // examples/common/scene.rs:336-468 (`all_feature_scene`, the book-2 final scene).  The nested
 // `BVH::new(boxes1)` object (scene.rs:361) is an accelerator, not geometry: `BVH::hit` returns the
 // closest hit of its members, so its 400 boxes are added to the world list directly (the world

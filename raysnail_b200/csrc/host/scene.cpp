@@ -389,6 +389,17 @@ int Quadric::flatten(FlatScene& fs) const {
     });
 }
 
+// raymarching.rs:172-181
+AABB RayMarcher::bbox(const TimeRange&) const { return AABB(Vec3(-1.3, -1.3, -1.3), Vec3(1.3, 1.3, 1.3)); }
+int RayMarcher::flatten(FlatScene& fs) const {
+    return cached(fs.node_cache, this, [&] {
+        rs_node n = blank_node(RS_NODE_RAYMARCHER);
+        n.material = fs.material_index(material);
+        n.p[0] = (double)iterations;
+        return push_node(fs, n);
+    });
+}
+
 // difference.rs:114-116
 AABB Difference::bbox(const TimeRange& tr) const { return plus->bbox(tr); }
 int Difference::flatten(FlatScene& fs) const {

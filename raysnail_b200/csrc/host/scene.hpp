@@ -287,6 +287,15 @@ struct Quadric : Hittable {
     int flatten(FlatScene& fs) const override;
 };
 
+// geometry/raymarching.rs: the power-8 Mandelbulb about the origin (RayMarcher::new: 100 iterations)
+struct RayMarcher : Hittable {
+    MaterialPtr material;
+    int iterations = 100;
+    explicit RayMarcher(MaterialPtr m) : material(std::move(m)) {}
+    AABB bbox(const TimeRange& tr) const override;
+    int flatten(FlatScene& fs) const override;
+};
+
 struct Difference : Hittable {
     HittablePtr plus, minus;
     MaterialPtr material;
@@ -473,6 +482,8 @@ std::unique_ptr<World> cornell_box_world(bool carton, bool carton_rotation, bool
 // scene shape of examples/preview_sdl2.rs:452-525 with a procedural mesh instead of dragon.obj
 std::unique_ptr<World> mesh_test_world(int grid_n, bool blinn_phong, CameraBuilder& cam_out);
 std::unique_ptr<World> all_feature_world(uint64_t seed, CameraBuilder& cam_out);  // scene.rs:336-468
+// examples/preview_sdl2.rs:338-407 — `render_raymarching_test` (Mandelbulb over a checker ground)
+std::unique_ptr<World> raymarching_test_world(CameraBuilder& cam_out);
 }  // namespace recipes
 
 }  // namespace raysnail

@@ -43,7 +43,19 @@ def oracle_vectors():
     np.savez_compressed(os.path.join(HERE, "oracle_vectors.npz"), **out)
 
 
+def raymarching_vectors():
+    import numpy as np
+    from conftest import load_scene
+    from oracle_binding import OracleWorld
+    from raysnail_b200 import make_params, RS_FLAG_PIXEL_CENTRE
+    s = load_scene("raymarching")
+    o = OracleWorld(s).debug_primary(s.camera(48, 30), make_params(samples=4, flags=RS_FLAG_PIXEL_CENTRE), 0)
+    np.savez_compressed(os.path.join(HERE, "raymarching_vectors.npz"), id=o["obj_id"].astype(np.int32), t=o["t"], n=o["normal"])
+
+
 if __name__ == "__main__":
     copy_sdl()
-    oracle_vectors()
+    if "--only-raymarching" not in sys.argv:
+        oracle_vectors()
+    raymarching_vectors()
     print("fixtures written")

@@ -320,3 +320,23 @@ def test_pixel_slices_of_the_fused_reduce_cover_the_image_once():
             for (b0, e0), (b1, e1) in zip(cuts, cuts[1:]):
                 assert e0 == b1 and b0 <= e0
             assert all(b % 16 == 0 for b, _ in cuts if b < n_pixels)
+
+
+def test_raymarching_recipe_contents():
+    """`render_raymarching_test` (examples/preview_sdl2.rs:338-407): light sphere, RayMarcher with a
+    Lambertian carrying Phong settings (4.0, 2), r = 1000 DiffuseMetal(800) checker ground; the bulb's
+    bbox is the fixed +-1.3 cube (raymarching.rs:172-181)."""
+    s = load_scene("raymarching")
+    d = s.desc.contents
+    assert (d.n_roots, d.n_lights) == (3, 1)
+    types = [d.nodes[d.roots[i]].type for i in range(3)]
+    assert types == [0, 8, 0]                                   # sphere, RS_NODE_RAYMARCHER, sphere
+    bulb = d.nodes[d.roots[1]]
+    assert bulb.p[0] == 100.0
+    m = d.materials[bulb.material]
+    assert m.type == 0 and m.phong_factor == 4.0 and m.phong_exponent == 2
+    assert [d.root_bbox[6 + k] for k in range(6)] == [-1.3, -1.3, -1.3, 1.3, 1.3, 1.3]
+    g = d.materials[d.nodes[d.roots[2]].material]
+    assert g.type == 2 and g.a == 800.0
+    cam = s.camera(800, 500)
+    assert abs(cam.origin[0] - 9.1) < 1e-12 and abs(cam.origin[1] + 1.19) < 1e-12

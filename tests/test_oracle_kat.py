@@ -300,3 +300,60 @@ def test_oracle_image_is_deterministic_and_thread_count_invariant():
     mask[3:9, 5:20] = 1
     m, _ = w.render(cam, p, mask=mask)
     assert (m[mask == 0] == 0).all() and np.array_equal(m[mask == 1], a[mask == 1])
+
+
+# ---------------------------------------------------------------------------------------------
+# RayMarcher (src/hittable/geometry/raymarching.rs): the power-8 Mandelbulb
+# ---------------------------------------------------------------------------------------------
+def test_raymarcher_along_the_z_axis():
+    """On the z axis the bulb's iteration is the 1-D map z -> |z|^8 + c (theta = 0 or pi, 8*pi wraps).
+    For c > 0 it stays bounded iff z^8 + c = z has a root: c <= c* = 7/8 * 8^(-1/7) = 0.650146.  A ray
+    from (0,0,5) straight down the axis starts outside the bailout sphere (|p|^2 > 8: the distance
+    estimate is ln(0)*0 = NaN -> 0.1 -> search_surface, raymarching.rs:127-134), walks in 0.05 steps
+    and bisects 8 times: t = 5 - c_num with c_num in (c*, c* + a few 1e-3] (100 iterations let orbits
+    just above the tangent bifurcation survive) and t a multiple of 0.05/256."""
+    s, white = simple_scene()
+    s.add(s.raymarcher(white))
+    h = centre_probe(s, (0, 0, 5), (0, 0, 0))
+    c_star = 7.0 / 8.0 * 8.0 ** (-1.0 / 7.0)
+    assert h["obj_id"] == 1 and h["front"] == 1
+    assert 5 - c_star - 6e-3 < h["t"] < 5 - c_star + 0.05 / 256
+    assert abs(h["t"] / (0.05 / 256) - round(h["t"] / (0.05 / 256))) < 1e-6
+    # 8-fold symmetry about z: the gradient of the distance estimate on the axis points along z (up to the chaos of near-boundary orbits)
+    assert h["normal"][2] > 0.99
+    # from farther than 200 * 0.05 = 10 units the search gives up: no hit (raymarching.rs:64)
+    s2, white2 = simple_scene()
+    s2.add(s2.raymarcher(white2))
+    assert centre_probe(s2, (0, 0, 12), (0, 0, 0))["obj_id"] == -1
+
+
+def test_raymarcher_contains_through_difference():
+    """`contains` = is_inside (raymarching.rs:167-170).  Box(-2..2) minus the bulb, ray down the z axis:
+    the plus hit (box face z = 2, t = 3) is outside the bulb -> it is the hit (difference.rs:64-72).
+    Box(-0.3..0.3) minus the bulb: its face z = 0.3 < c* lies inside the bulb and so does its far
+    face -> no hit from the box; with the bulb as `plus` and the box as `minus` the surface hit stays."""
+    s, white = simple_scene()
+    s.add(s.difference(s.box((-2, -2, -2), (2, 2, 2), white), s.raymarcher(white), white))
+    h = centre_probe(s, (0, 0, 5), (0, 0, 0))
+    assert h["obj_id"] == 1 and abs(h["t"] - 3.0) < 1e-12
+    s, white = simple_scene()
+    s.add(s.difference(s.raymarcher(white), s.box((-0.3, -0.3, -0.3), (0.3, 0.3, 0.3), white), white))
+    h = centre_probe(s, (0, 0, 5), (0, 0, 0))
+    c_star = 7.0 / 8.0 * 8.0 ** (-1.0 / 7.0)
+    assert h["obj_id"] == 1 and abs(h["t"] - (5 - c_star)) < 6e-3
+
+
+def test_raymarching_scene_golden_vectors():
+    """Oracle vectors of the `render_raymarching_test` recipe (examples/preview_sdl2.rs:338-407),
+    made by tests/golden/make_fixtures.py.  Hit distances sit on the 0.05/256 search grid, so a libm
+    that rounds one pow/atan2/sincos differently can move single rays by a grid step: ids must be
+    equal, t equal on >= 99.5 % of the rays and within one march step (0.05) elsewhere."""
+    g = np.load(os.path.join(HERE, "golden", "raymarching_vectors.npz"))
+    s = load_scene("raymarching")
+    w = OracleWorld(s)
+    o = w.debug_primary(s.camera(48, 30), make_params(samples=4, flags=RS_FLAG_PIXEL_CENTRE), 0)
+    assert (o["obj_id"] == 1).sum() > 150
+    assert np.mean(o["obj_id"] == g["id"]) >= 0.995
+    both = (o["obj_id"] == g["id"]) & (g["id"] >= 0)
+    close = np.abs(o["t"][both] - g["t"][both]) <= 1e-9 * np.abs(g["t"][both])
+    assert close.mean() >= 0.995 and np.abs(o["t"][both] - g["t"][both]).max() <= 0.05
