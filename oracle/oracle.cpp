@@ -767,9 +767,65 @@ struct QuadricObj : Hittable {  // geometry/quadric.rs
 };
 
 // geometry/raymarching.rs: the power-8 Mandelbulb about the origin.
+//
+// Two evaluations of the SAME map (raymarching.rs:202-241):
+//   * mode 1, "libm": the literal restatement — sqrt / atan2 / powf / sin / cos / ln through the
+//     platform libm, exactly as the Rust source calls them;
+//   * mode 0, "canonical" (default; what the GPU computes bit for bit): the same triplex power
+//     written with IEEE-exact operations only — cos/sin of theta and phi as coordinate ratios,
+//     the 8-fold angles by three complex squarings, r^8 and r^56 by repeated multiplication, ln by
+//     a fixed atanh series.
+// Why: the surface is found by testing orbit boundedness on a 0.05/256 grid along the ray, and
+// the orbits near the surface are chaotic (a last-bit difference grows ~8x per iteration), so two
+// libms that round ONE call differently move ~1 % of the hit distances by whole grid steps
+// (measured: glibc vs CUDA libm, 40 of 3881 rays).  The Rust reference has the same spread between
+// platforms (f64::powf/atan2/sin/cos/ln are the platform's libm).  The canonical form differs from
+// the literal one by the same few ulp per call and is reproducible everywhere;
+// tests/test_oracle_kat.py::test_raymarcher_canonical_vs_libm pins it to the literal form.
 namespace marcher {
-// :202-241.  Note `dr` is computed from the ALREADY-raised r (`r = r.powf(power)` comes first).
-inline void iterate(const Vec3& p, int iterations, double& r, double& dr, bool& inside) {
+int g_mode = 0;
+
+// ln(x) by IEEE-exact steps only: x = m * 2^e, m in [sqrt(1/2), sqrt(2)), s = (m-1)/(m+1),
+// ln m = 2 atanh(s) = s * (2 + s^2 * (2/3 + s^2 * (2/5 + ...))) up to s^23 (|s| <= 0.1716).
+inline double det_log(double x) {
+    if (x != x || x < 0.0) return std::numeric_limits<double>::quiet_NaN();
+    if (x == 0.0) return -std::numeric_limits<double>::infinity();
+    if (x == std::numeric_limits<double>::infinity()) return x;
+    uint64_t bits;
+    std::memcpy(&bits, &x, 8);
+    int e = 0;
+    if ((bits >> 52) == 0) {  // subnormal: scale by 2^54 (exact)
+        x *= 18014398509481984.0;
+        std::memcpy(&bits, &x, 8);
+        e = -54;
+    }
+    e += (int)(bits >> 52) - 1023;
+    bits = (bits & 0x000FFFFFFFFFFFFFull) | 0x3FF0000000000000ull;
+    double m;
+    std::memcpy(&m, &bits, 8);  // [1, 2)
+    if (m > 1.4142135623730951) { m = m * 0.5; e += 1; }
+    double s = (m - 1.0) / (m + 1.0);
+    double s2 = s * s;
+    double p = 2.0 / 23.0;
+    p = std::fma(p, s2, 2.0 / 21.0);
+    p = std::fma(p, s2, 2.0 / 19.0);
+    p = std::fma(p, s2, 2.0 / 17.0);
+    p = std::fma(p, s2, 2.0 / 15.0);
+    p = std::fma(p, s2, 2.0 / 13.0);
+    p = std::fma(p, s2, 2.0 / 11.0);
+    p = std::fma(p, s2, 2.0 / 9.0);
+    p = std::fma(p, s2, 2.0 / 7.0);
+    p = std::fma(p, s2, 2.0 / 5.0);
+    p = std::fma(p, s2, 2.0 / 3.0);
+    p = std::fma(p, s2, 2.0);
+    double lm = s * p;
+    const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
+    double de = (double)e;
+    return std::fma(de, LN2_HI, std::fma(de, LN2_LO, lm));
+}
+
+// :202-241, literal.  Note `dr` is computed from the ALREADY-raised r (`r = r.powf(power)` comes first).
+inline void iterate_libm(const Vec3& p, int iterations, double& r, double& dr, bool& inside) {
     double x = 0.0, y = 0.0, z = 0.0;
     const double power = 8.0;
     r = 0.0; dr = 0.0;
@@ -789,6 +845,35 @@ inline void iterate(const Vec3& p, int iterations, double& r, double& dr, bool& 
     }
     inside = true;
 }
+// the same map, canonical form (see above)
+inline void iterate(const Vec3& p, int iterations, double& r, double& dr, bool& inside) {
+    if (g_mode == 1) { iterate_libm(p, iterations, r, dr, inside); return; }
+    double x = 0.0, y = 0.0, z = 0.0;
+    r = 0.0; dr = 0.0;
+    for (int i = 0; i < iterations; ++i) {
+        double rho2 = x * x + y * y;
+        double r2 = rho2 + z * z;
+        double rr = std::sqrt(r2), rho = std::sqrt(rho2);
+        double ct = 1.0, st = 0.0, cp = 1.0, sp = 0.0;  // atan2(0, +0) = 0
+        if (rr != 0.0) { ct = z / rr; st = rho / rr; }
+        if (rho != 0.0) { cp = x / rho; sp = y / rho; }
+        for (int k = 0; k < 3; ++k) {  // angle doubling: theta, phi -> 8 theta, 8 phi
+            double c2 = ct * ct - st * st, s2 = (2.0 * ct) * st;
+            ct = c2; st = s2;
+            double d2 = cp * cp - sp * sp, t2 = (2.0 * cp) * sp;
+            cp = d2; sp = t2;
+        }
+        double r4 = r2 * r2;
+        r = r4 * r4;  // |v|^8
+        double r16 = r * r, r32 = r16 * r16, r56 = (r32 * r16) * r;
+        dr = r56 * 8.0 * dr + 1.0;
+        x = r * st * cp + p.x;
+        y = r * st * sp + p.y;
+        z = r * ct + p.z;
+        if (x * x + y * y + z * z > 8.0) { inside = false; return; }
+    }
+    inside = true;
+}
 inline bool is_inside(const Vec3& p, int iterations) {  // :187-190
     double r, dr; bool in;
     iterate(p, iterations, r, dr, in);
@@ -797,7 +882,7 @@ inline bool is_inside(const Vec3& p, int iterations) {  // :187-190
 inline double distance_est(const Vec3& p, int iterations) {  // :193-197 (NaN when r == 0: ln(0) * 0)
     double r, dr; bool in;
     iterate(p, iterations, r, dr, in);
-    return 0.5 * std::log(r) * r / dr;
+    return 0.5 * (g_mode == 1 ? std::log(r) : det_log(r)) * r / dr;
 }
 }  // namespace marcher
 
@@ -1464,6 +1549,9 @@ int rso_root_bbox(const rso_world* w, double time_start, double time_end, double
     }
     return 0;
 }
+
+// 0 = canonical Mandelbulb arithmetic (default), 1 = literal libm restatement (see namespace marcher)
+int rso_set_marcher_mode(int mode) { marcher::g_mode = mode == 1 ? 1 : 0; return 0; }
 
 int rso_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
     philox4x32_10(ctr, key, out);

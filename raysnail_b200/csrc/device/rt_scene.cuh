@@ -421,23 +421,71 @@ __device__ __forceinline__ V3 rect_random(const rs_node& n, V3 origin, const Rng
 // ---------------------------------------------------------------------------------------------
 // raymarching.rs: the power-8 Mandelbulb about the origin (RayMarcher)
 // ---------------------------------------------------------------------------------------------
-// raymarching.rs:202-241.  `dr` is computed from the ALREADY-raised r, as in the reference.  The sums of
-// squares are kept un-contracted (the reference has no mul_add here).
+// ln(x) by IEEE-exact steps only (every operation individually rounded, fma where written), so
+// that the host-side checker's copy of this routine returns the same bits: x = m * 2^e,
+// m in [sqrt(1/2), sqrt(2)), s = (m-1)/(m+1), ln m = 2 atanh(s) as a fixed series up to s^23.
+__device__ __forceinline__ double marcher_log(double x) {
+    if (x != x || x < 0.0) return __longlong_as_double(0x7ff8000000000000LL);
+    if (x == 0.0) return __longlong_as_double(0xfff0000000000000LL);
+    if (x == __longlong_as_double(0x7ff0000000000000LL)) return x;
+    long long bits = __double_as_longlong(x);
+    int e = 0;
+    if ((bits >> 52) == 0) {  // subnormal: scale by 2^54 (exact)
+        x = __dmul_rn(x, 18014398509481984.0);
+        bits = __double_as_longlong(x);
+        e = -54;
+    }
+    e += (int)(bits >> 52) - 1023;
+    double m = __longlong_as_double((bits & 0x000FFFFFFFFFFFFFLL) | 0x3FF0000000000000LL);  // [1, 2)
+    if (m > 1.4142135623730951) { m = __dmul_rn(m, 0.5); e += 1; }
+    const double s = __ddiv_rn(__dadd_rn(m, -1.0), __dadd_rn(m, 1.0));
+    const double s2 = __dmul_rn(s, s);
+    double p = 2.0 / 23.0;
+    p = __fma_rn(p, s2, 2.0 / 21.0);
+    p = __fma_rn(p, s2, 2.0 / 19.0);
+    p = __fma_rn(p, s2, 2.0 / 17.0);
+    p = __fma_rn(p, s2, 2.0 / 15.0);
+    p = __fma_rn(p, s2, 2.0 / 13.0);
+    p = __fma_rn(p, s2, 2.0 / 11.0);
+    p = __fma_rn(p, s2, 2.0 / 9.0);
+    p = __fma_rn(p, s2, 2.0 / 7.0);
+    p = __fma_rn(p, s2, 2.0 / 5.0);
+    p = __fma_rn(p, s2, 2.0 / 3.0);
+    p = __fma_rn(p, s2, 2.0);
+    const double lm = __dmul_rn(s, p);
+    const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
+    const double de = (double)e;
+    return __fma_rn(de, LN2_HI, __fma_rn(de, LN2_LO, lm));
+}
+
+// raymarching.rs:202-241 in canonical form: the reference evaluates the triplex power through the
+// platform libm (sqrt, atan2, powf, sin, cos); orbits near the surface are chaotic, so two libms move
+// ~1 % of the hit distances by whole search-grid steps.  Here — and bit for bit in the CPU checker —
+// the same map is written with IEEE-exact operations only: cos/sin of theta and phi as coordinate
+// ratios, 8-fold angles by three complex squarings, r^8 and r^56 by repeated multiplication.  No
+// FMA contraction (the reference has no mul_add here).  `dr` is computed from the ALREADY-raised
+// r, as in the reference.
 static __device__ __noinline__ bool marcher_iterate(V3 p, int iterations, double& r_out, double& dr_out) {
     double x = 0.0, y = 0.0, z = 0.0, r = 0.0, dr = 0.0;
     bool inside = true;
     for (int i = 0; i < iterations; ++i) {
-        const double xx_yy = __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y));
-        r = sqrt(__dadd_rn(xx_yy, __dmul_rn(z, z)));
-        double theta = atan2(sqrt(xx_yy), z);
-        double phi = atan2(y, x);
-        r = pow(r, 8.0);
-        theta *= 8.0;
-        phi *= 8.0;
-        dr = __dadd_rn(__dmul_rn(__dmul_rn(pow(r, 7.0), 8.0), dr), 1.0);
-        double st, ct, sp, cp;
-        sincos(theta, &st, &ct);
-        sincos(phi, &sp, &cp);
+        const double rho2 = __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y));
+        const double r2 = __dadd_rn(rho2, __dmul_rn(z, z));
+        const double rr = __dsqrt_rn(r2), rho = __dsqrt_rn(rho2);
+        double ct = 1.0, st = 0.0, cp = 1.0, sp = 0.0;  // atan2(0, +0) = 0
+        if (rr != 0.0) { ct = __ddiv_rn(z, rr); st = __ddiv_rn(rho, rr); }
+        if (rho != 0.0) { cp = __ddiv_rn(x, rho); sp = __ddiv_rn(y, rho); }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {  // angle doubling: theta, phi -> 8 theta, 8 phi
+            const double c2 = __dadd_rn(__dmul_rn(ct, ct), -__dmul_rn(st, st)), s2 = __dmul_rn(__dmul_rn(2.0, ct), st);
+            ct = c2; st = s2;
+            const double d2 = __dadd_rn(__dmul_rn(cp, cp), -__dmul_rn(sp, sp)), t2 = __dmul_rn(__dmul_rn(2.0, cp), sp);
+            cp = d2; sp = t2;
+        }
+        const double r4 = __dmul_rn(r2, r2);
+        r = __dmul_rn(r4, r4);  // |v|^8
+        const double r16 = __dmul_rn(r, r), r32 = __dmul_rn(r16, r16), r56 = __dmul_rn(__dmul_rn(r32, r16), r);
+        dr = __dadd_rn(__dmul_rn(__dmul_rn(r56, 8.0), dr), 1.0);
         x = __dadd_rn(__dmul_rn(__dmul_rn(r, st), cp), p.x);
         y = __dadd_rn(__dmul_rn(__dmul_rn(r, st), sp), p.y);
         z = __dadd_rn(__dmul_rn(r, ct), p.z);
@@ -454,7 +502,7 @@ __device__ __forceinline__ bool marcher_inside(V3 p, int iterations) {  // :187-
 __device__ __forceinline__ double marcher_distance(V3 p, int iterations) {  // :193-197 (NaN when r == 0)
     double r, dr;
     marcher_iterate(p, iterations, r, dr);
-    return __dmul_rn(__dmul_rn(0.5, log(r)), r) / dr;
+    return __ddiv_rn(__dmul_rn(__dmul_rn(0.5, marcher_log(r)), r), dr);
 }
 // :83-96 (always 100 iterations)
 __device__ __forceinline__ V3 marcher_normal(V3 pos) {
@@ -508,7 +556,9 @@ static __device__ __noinline__ bool hit_marcher(const rs_node& n, const Ray& ray
             return true;
         }
         if (est < best) best = est;
-        current = current + direction * est * 0.05;
+        const double k = 0.05;  // (direction * est) * 0.05, each step rounded (no contraction into the add)
+        current = v3(__dadd_rn(current.x, __dmul_rn(__dmul_rn(direction.x, est), k)), __dadd_rn(current.y, __dmul_rn(__dmul_rn(direction.y, est), k)),
+                     __dadd_rn(current.z, __dmul_rn(__dmul_rn(direction.z, est), k)));
     }
     return false;
 }

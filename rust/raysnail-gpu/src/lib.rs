@@ -14,7 +14,8 @@ pub struct Error {
     pub message: String,
 }
 
-/// A `Hittable` the backend cannot express (e.g. `RayMarcher`): the caller falls back to
+/// A `Hittable` the backend cannot express (a user-defined implementor outside the reference's
+/// own set — every shipped one, `RayMarcher` included, has a node type): the caller falls back to
 /// `shot_to_target`.
 #[derive(Debug)]
 pub struct Unsupported(pub &'static str);

@@ -45,4 +45,4 @@ def load_scene(name):
     return Scene.builtin(name, 7, 0)
 
 
-ALL_SCENES = ["example", "quadric", "csg", "declares", "transforms", "rtow_final", "cornell", "cornell_smoke", "mesh", "mesh_blinn", "all_feature"]
+ALL_SCENES = ["example", "quadric", "csg", "declares", "transforms", "rtow_final", "cornell", "cornell_smoke", "mesh", "mesh_blinn", "all_feature", "raymarching"]

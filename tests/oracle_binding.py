@@ -31,6 +31,7 @@ def load():
     lib.rso_world_free.argtypes = [vp]
     lib.rso_root_bbox.argtypes = [vp, C.c_double, C.c_double, vp]
     lib.rso_philox4x32_10.argtypes = [vp, vp, vp]
+    lib.rso_set_marcher_mode.argtypes = [C.c_int]
     lib.rso_render.argtypes = [vp, P(RsCamera), P(RsRenderParams), vp, vp, C.c_int, P(RsStats)]
     lib.rso_debug_primary.argtypes = [vp, P(RsCamera), P(RsRenderParams), i32, vp, vp, vp, vp, vp, vp, vp]
     lib.rso_debug_scatter.argtypes = [vp, P(RsCamera), P(RsRenderParams), i32, vp, vp, vp, vp]
@@ -102,3 +103,8 @@ def philox(ctr, key):
     out = np.zeros(4, dtype=np.uint32)
     lib.rso_philox4x32_10(c.ctypes.data, k.ctypes.data, out.ctypes.data)
     return out
+
+
+def set_marcher_mode(mode):
+    """0 = canonical (IEEE-exact) Mandelbulb arithmetic, 1 = literal libm restatement (oracle.cpp, namespace marcher)"""
+    load().rso_set_marcher_mode(int(mode))
