@@ -164,12 +164,17 @@ __device__ __forceinline__ Ray camera_ray(const FrameParams& fp, int row, int co
     V3 rd = (aperture / 2.0) * p;
     V3 hu = v3(c.horizontal_unit[0], c.horizontal_unit[1], c.horizontal_unit[2]);
     V3 vu = v3(c.vertical_unit[0], c.vertical_unit[1], c.vertical_unit[2]);
-    V3 offset = hu * rd.x + vu * rd.y;
+    // every product and sum rounded on its own (no FMA contraction): the ray must be the oracle's bit
+    // for bit, because objects found by orbit tests (RayMarcher) amplify a last-bit difference
+    V3 offset = v3(__dadd_rn(__dmul_rn(hu.x, rd.x), __dmul_rn(vu.x, rd.y)), __dadd_rn(__dmul_rn(hu.y, rd.x), __dmul_rn(vu.y, rd.y)),
+                   __dadd_rn(__dmul_rn(hu.z, rd.x), __dmul_rn(vu.z, rd.y)));
     Ray r;
     r.o = v3(c.origin[0], c.origin[1], c.origin[2]) + offset;
     V3 hf = v3(c.horizontal_full[0], c.horizontal_full[1], c.horizontal_full[2]);
     V3 vf = v3(c.vertical_full[0], c.vertical_full[1], c.vertical_full[2]);
-    V3 dir = v3(c.lb[0], c.lb[1], c.lb[2]) + u * hf + v * vf - r.o;
+    V3 dir = v3(__dadd_rn(__dadd_rn(__dadd_rn(c.lb[0], __dmul_rn(u, hf.x)), __dmul_rn(v, vf.x)), -r.o.x),
+                __dadd_rn(__dadd_rn(__dadd_rn(c.lb[1], __dmul_rn(u, hf.y)), __dmul_rn(v, vf.y)), -r.o.y),
+                __dadd_rn(__dadd_rn(__dadd_rn(c.lb[2], __dmul_rn(u, hf.z)), __dmul_rn(v, vf.z)), -r.o.z));
     r.d = unit(dir);
     r.time = c.shutter_speed * jt;
     return r;

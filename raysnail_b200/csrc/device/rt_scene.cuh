@@ -507,42 +507,50 @@ __device__ __forceinline__ double marcher_distance(V3 p, int iterations) {  // :
 // :83-96 (always 100 iterations)
 __device__ __forceinline__ V3 marcher_normal(V3 pos) {
     const double d = 0.01;
-    V3 xd = v3(d, 0.0, 0.0), yd = v3(0.0, d, 0.0), zd = v3(0.0, 0.0, d);
-    return unit(v3(marcher_distance(pos + xd, 100) - marcher_distance(pos - xd, 100),
-                   marcher_distance(pos + yd, 100) - marcher_distance(pos - yd, 100),
-                   marcher_distance(pos + zd, 100) - marcher_distance(pos - zd, 100)));
+    const double gx = __dadd_rn(marcher_distance(v3(__dadd_rn(pos.x, d), pos.y, pos.z), 100), -marcher_distance(v3(__dadd_rn(pos.x, -d), pos.y, pos.z), 100));
+    const double gy = __dadd_rn(marcher_distance(v3(pos.x, __dadd_rn(pos.y, d), pos.z), 100), -marcher_distance(v3(pos.x, __dadd_rn(pos.y, -d), pos.z), 100));
+    const double gz = __dadd_rn(marcher_distance(v3(pos.x, pos.y, __dadd_rn(pos.z, d)), 100), -marcher_distance(v3(pos.x, pos.y, __dadd_rn(pos.z, -d)), 100));
+    const V3 g = v3(gx, gy, gz);
+    return v3(__dmul_rn(g.x, __drcp_rn(length(g))), __dmul_rn(g.y, __drcp_rn(length(g))), __dmul_rn(g.z, __drcp_rn(length(g))));
 }
-// :113-165 (+ search_surface :59-76, binary_search_surface :43-57).  `hi`: see the oracle — the
-// reference ignores limit.end; the canonical rule drops a hit at or beyond it.
+// Vector steps with every operation rounded on its own.  Plain `a * b + c` compiles to PTX mul.f64 /
+// add.f64 WITHOUT a rounding modifier, which ptxas is free to fuse into an FMA (and does, e.g.
+// `v + direction * 0.05`); the orbit tests amplify that last-bit difference into another hit point.
+__device__ __forceinline__ V3 add_rn(V3 a, V3 b) { return v3(__dadd_rn(a.x, b.x), __dadd_rn(a.y, b.y), __dadd_rn(a.z, b.z)); }
+__device__ __forceinline__ V3 sub_rn(V3 a, V3 b) { return v3(__dadd_rn(a.x, -b.x), __dadd_rn(a.y, -b.y), __dadd_rn(a.z, -b.z)); }
+__device__ __forceinline__ V3 mul_rn(V3 a, double s) { return v3(__dmul_rn(a.x, s), __dmul_rn(a.y, s), __dmul_rn(a.z, s)); }
+
+// :113-165 (+ search_surface :59-76, binary_search_surface :43-57).  `hi`: the reference ignores
+// limit.end here; the canonical rule (shared with the CPU checker) drops a hit at or beyond it.
 template <bool FULL = true>
 static __device__ __noinline__ bool hit_marcher(const rs_node& n, const Ray& ray, double lo, double hi, HitRec& h) {
     const int iterations = (int)n.p[0];
     const double len = length(ray.d);
-    const V3 direction = ray.d * (1.0 / len);
+    const V3 direction = mul_rn(ray.d, __drcp_rn(len));
     V3 current = ray.o;
     int steps = 0;
     double best = 1000000.0, est = 0.0;
-    while (steps < 1000 && est < best + 1.0) {
+    while (steps < 1000 && est < __dadd_rn(best, 1.0)) {
         ++steps;
         est = marcher_distance(current, iterations);
         if (est != est) est = 0.1;
         if (est < 1.3) {
-            const V3 df = direction * 0.05;
+            const V3 df = mul_rn(direction, 0.05);
             V3 v = current;
             bool found = false;
             for (int i = 0; i < 200; ++i) {
                 if (marcher_inside(v, iterations)) { found = true; break; }
-                v = v + df;
+                v = add_rn(v, df);
             }
             if (!found) return false;
-            V3 outside = v - df, inside = v;
+            V3 outside = sub_rn(v, df), inside = v;
             for (int depth = 8; depth > 0; --depth) {
-                V3 mid = (outside + inside) * 0.5;
+                V3 mid = mul_rn(add_rn(outside, inside), 0.5);
                 if (marcher_inside(mid, 100)) inside = mid; else outside = mid;
             }
-            const double dist = length(outside - ray.o);
+            const double dist = length(sub_rn(outside, ray.o));
             if (!(dist > lo)) return false;
-            const double t1 = dist / len;
+            const double t1 = __ddiv_rn(dist, len);
             if (!(t1 < hi)) return false;
             if (!FULL) { lean_record(ray, t1, t1, n.material, h); return true; }
             h.point = ray_at(ray, t1);
@@ -556,9 +564,7 @@ static __device__ __noinline__ bool hit_marcher(const rs_node& n, const Ray& ray
             return true;
         }
         if (est < best) best = est;
-        const double k = 0.05;  // (direction * est) * 0.05, each step rounded (no contraction into the add)
-        current = v3(__dadd_rn(current.x, __dmul_rn(__dmul_rn(direction.x, est), k)), __dadd_rn(current.y, __dmul_rn(__dmul_rn(direction.y, est), k)),
-                     __dadd_rn(current.z, __dmul_rn(__dmul_rn(direction.z, est), k)));
+        current = add_rn(current, mul_rn(mul_rn(direction, est), 0.05));  // (direction * est) * 0.05
     }
     return false;
 }
