@@ -938,6 +938,18 @@ __device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, con
             ok = n->type == RS_NODE_BOX ? hit_box(*n, r, RS_TMIN, end_then, h)
                                         : hit_rect(n->rect_axis, n->p[0], n->p[1], n->p[2], n->p[3], n->p[4], n->material, r, RS_TMIN, end_then, h);
             if (ok && x) h.point = xf_apply(x->fwd, h.point, 1.0);
+        } else if (S.nodes[rn].type == RS_NODE_RAYMARCHER) {
+            // a bare RayMarcher root: the record follows from the distance extend found (the same
+            // t1 the full search would return), without marching the ray a second time
+            h.point = ray_at(ray, ha.t);
+            V3 nn = marcher_normal(h.point);
+            h.outside = dot(ray.d, nn) < 0.0;
+            h.normal = h.outside ? nn : -nn;
+            h.material = S.nodes[rn].material;
+            h.t1 = ha.t; h.t2 = ha.t;
+            h.u = 0.0; h.v = 0.0;
+            if (want_uv) sphere_uv(v3(0.0, 0.0, 0.0), h.point, h.u, h.v);
+            ok = true;
         } else {
             ok = TreeTop::hit(S, rn, ray, RS_TMIN, end_then, rng, h);
         }
