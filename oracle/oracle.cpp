@@ -1553,6 +1553,20 @@ int rso_root_bbox(const rso_world* w, double time_start, double time_end, double
 // 0 = canonical Mandelbulb arithmetic (default), 1 = literal libm restatement (see namespace marcher)
 int rso_set_marcher_mode(int mode) { marcher::g_mode = mode == 1 ? 1 : 0; return 0; }
 
+// test hooks: the canonical orbit routine and logarithm on arrays of n points / values
+int rso_marcher_iterate(const double* xyz, int64_t n, int iterations, double* r_out, double* dr_out, int32_t* inside_out) {
+    for (int64_t i = 0; i < n; ++i) {
+        bool in;
+        marcher::iterate(Vec3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]), iterations, r_out[i], dr_out[i], in);
+        inside_out[i] = in ? 1 : 0;
+    }
+    return 0;
+}
+int rso_marcher_log(const double* x, int64_t n, double* out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = marcher::det_log(x[i]);
+    return 0;
+}
+
 int rso_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
     philox4x32_10(ctr, key, out);
     return 0;

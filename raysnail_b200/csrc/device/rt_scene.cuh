@@ -421,6 +421,7 @@ __device__ __forceinline__ V3 rect_random(const rs_node& n, V3 origin, const Rng
 // ---------------------------------------------------------------------------------------------
 // raymarching.rs: the power-8 Mandelbulb about the origin (RayMarcher)
 // ---------------------------------------------------------------------------------------------
+// [marcher-core-begin] (tests/test_marcher_source.py compiles this block for the host)
 // ln(x) by IEEE-exact steps only (every operation individually rounded, fma where written), so
 // that the host-side checker's copy of this routine returns the same bits: x = m * 2^e,
 // m in [sqrt(1/2), sqrt(2)), s = (m-1)/(m+1), ln m = 2 atanh(s) as a fixed series up to s^23.
@@ -495,6 +496,7 @@ static __device__ __noinline__ bool marcher_iterate(V3 p, int iterations, double
     dr_out = dr;
     return inside;
 }
+// [marcher-core-end]
 __device__ __forceinline__ bool marcher_inside(V3 p, int iterations) {  // :187-190
     double r, dr;
     return marcher_iterate(p, iterations, r, dr);
