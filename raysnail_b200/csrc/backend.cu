@@ -765,6 +765,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
 
     // ---- root tables + BVH ------------------------------------------------------------------
     std::vector<int> root_kind(s->n_roots);
+    bool any_quadric_root = false;
     std::vector<double> root_sphere((size_t)s->n_roots * 4, 0.0);
     std::vector<unsigned char> root_gate(s->n_roots, 0);
     std::vector<BuildPrim> prims;
@@ -784,7 +785,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
             } else {
                 // rect / box, bare or under one TfFacade: inline distance tests in extend
                 const rs_node& inner = n.type == RS_NODE_TRANSFORM ? nodes[n.child0] : n;
-                root_kind[i] = (inner.type == RS_NODE_BOX || inner.type == RS_NODE_RECT) ? ROOT_FLAT : ROOT_GENERIC;
+                // (a quadric root takes the same inline route, but only the generic-tier kernels hold its code)
+                root_kind[i] = (inner.type == RS_NODE_BOX || inner.type == RS_NODE_RECT || inner.type == RS_NODE_QUADRIC) ? ROOT_FLAT : ROOT_GENERIC;
+                any_quadric_root |= inner.type == RS_NODE_QUADRIC;
                 // spheres / boxes / rects always lie inside their reference bbox; everything
                 // else is clipped by it the way the reference's BVH leaf clips it
                 root_gate[i] = !(n.type == RS_NODE_SPHERE || n.type == RS_NODE_BOX || n.type == RS_NODE_RECT);
@@ -825,7 +828,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     // (binary tree: depth <= 24 SAH levels + log2(n) median levels, one push per level: fits)
     ctx->scene_omax = omax;
     // which kernel specialisations this scene needs
-    bool any_tri = false, any_flat = false, any_tree = false;
+    bool any_tri = false, any_flat = false, any_tree = any_quadric_root;
     for (const BuildPrim& p : prims) {
         any_tri |= root_kind[p.root] == ROOT_TRIANGLE;
         any_flat |= root_kind[p.root] == ROOT_FLAT;

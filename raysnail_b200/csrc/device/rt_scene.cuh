@@ -40,7 +40,7 @@ struct __align__(16) XformPre {
     double inv[12];
 };
 
-// ROOT_FLAT: a rect, a box, or a TfFacade around one of them: extend finds their distance with inline code
+// ROOT_FLAT: a rect, a box, a quadric (generic tier only), or a TfFacade around one of them: extend finds their distance with inline code
 // (rect_t / box_t) instead of walking the expression tree; shade rebuilds the record like a generic root
 enum RootKind : int { ROOT_SPHERE = 0, ROOT_TRIANGLE = 1, ROOT_GENERIC = 2, ROOT_FLAT = 3 };
 
@@ -328,6 +328,29 @@ __device__ __forceinline__ V3 quadric_normal(const double* q, V3 p) {
     double len = length(r);
     if (len == 0.0) return v3(1.0, 0.0, 0.0);
     return vdiv(r, len);
+}
+
+// quadric.rs:112-165, the roots only (what the closest-hit search of extend needs for a quadric that is a
+// world object itself, bare or under one TfFacade)
+__device__ __forceinline__ bool quadric_t(const double* q, const Ray& ray, double lo, double hi, double& t1) {
+    const double qa = q[0], qb = q[1], qc = q[2], qd = q[3], qe = q[4], qf = q[5], qg = q[6], qh = q[7], qi = q[8], qj = q[9];
+    const double xo = ray.o.x, yo = ray.o.y, zo = ray.o.z, xd = ray.d.x, yd = ray.d.y, zd = ray.d.z;
+    double a = xd * (qa * xd + qb * yd + qc * zd) + yd * (qe * yd + qf * zd) + zd * qh * zd;
+    double b = xd * (qa * xo + 0.5 * (qb * yo + qc * zo + qd)) + yd * (qe * yo + 0.5 * (qb * xo + qf * zo + qg)) +
+               zd * (qh * zo + 0.5 * (qc * xo + qf * yo + qi));
+    double c = xo * (qa * xo + qb * yo + qc * zo + qd) + yo * (qe * yo + qf * zo + qg) + zo * (qh * zo + qi) + qj;
+    if (a == 0.0) {
+        if (b == 0.0) return false;
+        t1 = -0.5 * c / b;
+        return in_range(t1, lo, hi);
+    }
+    double d = b * b - a * c;
+    if (d <= 0.0) return false;
+    double dr = sqrt(d);
+    t1 = (-b - dr) / a;
+    if (in_range(t1, lo, hi)) return true;
+    t1 = (-b + dr) / a;
+    return in_range(t1, lo, hi);
 }
 
 // quadric.rs:112-182
