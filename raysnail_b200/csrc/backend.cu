@@ -828,7 +828,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     // (binary tree: depth <= 24 SAH levels + log2(n) median levels, one push per level: fits)
     ctx->scene_omax = omax;
     // which kernel specialisations this scene needs
-    bool any_tri = false, any_flat = false, any_tree = any_quadric_root;
+    bool any_tri = false, any_flat = false, any_tree = RS_TUNE_QUADRIC_FLAT ? false : any_quadric_root;
     for (const BuildPrim& p : prims) {
         any_tri |= root_kind[p.root] == ROOT_TRIANGLE;
         any_flat |= root_kind[p.root] == ROOT_FLAT;

@@ -277,7 +277,7 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
         const double hi = next_up(best.t);
         double t;
         bool hit;
-        if (MODE >= 3 && n->type == RS_NODE_QUADRIC) {
+        if (MODE >= RS_QUADRIC_MODE && n->type == RS_NODE_QUADRIC) {
             // quadric.rs:191-196: the surface is unbounded, the reference clips it with its +-100 bbox
             const double inf = __longlong_as_double(0x7ff0000000000000LL);
             if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
@@ -943,7 +943,7 @@ __device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, con
                 r.d = xf_apply(x->inv, ray.d, 0.0);
                 n = S.nodes + n->child0;
             }
-            if (TREES && n->type == RS_NODE_QUADRIC) ok = hit_quadric<true>(*n, r, RS_TMIN, end_then, h);
+            if ((TREES || RS_TUNE_QUADRIC_FLAT) && n->type == RS_NODE_QUADRIC) ok = hit_quadric<true>(*n, r, RS_TMIN, end_then, h);
             else ok = n->type == RS_NODE_BOX ? hit_box(*n, r, RS_TMIN, end_then, h)
                                              : hit_rect(n->rect_axis, n->p[0], n->p[1], n->p[2], n->p[3], n->p[4], n->material, r, RS_TMIN, end_then, h);
             if (ok && x) h.point = xf_apply(x->fwd, h.point, 1.0);

@@ -42,6 +42,12 @@ struct __align__(16) XformPre {
 
 // ROOT_FLAT: a rect, a box, a quadric (generic tier only), or a TfFacade around one of them: extend finds their distance with inline code
 // (rect_t / box_t) instead of walking the expression tree; shade rebuilds the record like a generic root
+// RS_TUNE_QUADRIC_FLAT = 1: the flat-tier kernels (MODE 2 / TIER 1) hold the quadric code too, so a scene of
+// spheres, rects, boxes and quadrics needs no generic-tier kernel; 0: quadric roots force the generic tier
+#ifndef RS_TUNE_QUADRIC_FLAT
+#define RS_TUNE_QUADRIC_FLAT 0
+#endif
+#define RS_QUADRIC_MODE (RS_TUNE_QUADRIC_FLAT ? 2 : 3)
 enum RootKind : int { ROOT_SPHERE = 0, ROOT_TRIANGLE = 1, ROOT_GENERIC = 2, ROOT_FLAT = 3 };
 
 // Everything shade reads of a (resolved) material in ONE record, so that the dependent chain
