@@ -123,6 +123,9 @@ __device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
+#ifndef RS_TUNE_FIRST_LATE_FETCH
+#define RS_TUNE_FIRST_LATE_FETCH 1
+#endif
 // threads per block of the lean shade kernel (the generic one uses RS_BLOCK); tunable
 #ifndef RS_TUNE_SHADE_BLOCK
 #define RS_TUNE_SHADE_BLOCK 256
@@ -561,7 +564,10 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
 #else
         const uint32_t base = __shfl_sync(0xffffffffu, pend, 0);
         if (base >= n) break;
-        if (lane_id() == 0) pend = atomic_add_async(head, 32u, lane_zero);
+        // RS_TUNE_FIRST_LATE_FETCH: the bounce-0 kernels (camera ray generation fused in) spill `pend` at 64
+        // registers, so lane 0 waits for the atomic at the spill store; issuing it after the
+        // traversal instead keeps it in a register and overlaps it with the epilogue only
+        if (!(RS_TUNE_FIRST_LATE_FETCH && FIRST) && lane_id() == 0) pend = atomic_add_async(head, 32u, lane_zero);
 #endif
         const uint32_t v = base + lane_id();
         const bool live = v < nf32 ? v < nf : v < n;
@@ -639,6 +645,9 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                 }
             }
         }
+#if !RS_TUNE_EXTEND_STATIC
+        if (RS_TUNE_FIRST_LATE_FETCH && FIRST && lane_id() == 0) pend = atomic_add_async(head, 32u, lane_zero);
+#endif
         // material-coherent bucketing
         const uint32_t active = __ballot_sync(0xffffffffu, live && cls >= 0);
         // Paths of the classes in RS_ALWAYS_CONTINUES always go on after shading (their `scatter`
