@@ -298,3 +298,53 @@ def test_full_size_frames_on_sampled_pixels(renderer, name, size, sqrt_spp):
     assert np.median(diff) <= 1e-5 * scale
     assert (diff.max(axis=1) > 1e-3 * scale).mean() <= 0.002
     assert float(diff.mean()) <= 1e-3 * scale
+
+
+def _quadric_roots_scene():
+    """Quadrics as world objects themselves — bare and under one TfFacade — which extend tests with
+    its inline root routine (quadric_t) instead of the expression-tree walk; the shipped .sdl
+    scenes only hold quadrics inside Intersections."""
+    from raysnail_b200 import Scene
+    s = Scene()
+    red = s.lambertian(s.solid(0.8, 0.2, 0.2))
+    green = s.metal(s.solid(0.3, 0.8, 0.3))
+    blue = s.lambertian(s.checker(s.solid(0.1, 0.1, 0.9), s.solid(0.9, 0.9, 0.9), 4.0))
+    light = s.sphere((30, 60, 40), 12.0, s.diffuse_light(s.solid(1, 1, 1), 2.0))
+    s.add(light)
+    s.add_light(light)
+    s.add(s.quadric((1, 0, 0, 0, 1, 0, 0, 1, 0, -1), red))                                   # unit sphere as a quadric
+    s.add(s.transform(s.quadric((1, 0, 0, 0, 0, 0, 0, 1, 0, -0.25), green),                 # cylinder r = 0.5 about y ...
+                      [("rotate_z", 0.7), ("translate", (2.0, 0.0, -0.5))]))                # ... tilted and moved
+    s.add(s.transform(s.quadric((1, 0, 0, 0, 0, 0, -1, 1, 0, 0), blue),                     # paraboloid y = x^2 + z^2
+                      [("scale", (0.6, 0.6, 0.6)), ("translate", (-2.2, -1.0, 0.0))]))
+    s.add(s.quadric((0, 0, 0, 0, 0, 0, 1, 0, 0, 1.5), s.lambertian(s.solid(0.5, 0.5, 0.5))))  # a == 0: the plane y = -1.5
+    s.set_background((0.3, 0.4, 0.5), (0.7, 0.89, 1.0))
+    s.set_camera((0.5, 2.5, 9.0), (0.0, 0.0, 0.0), (0, 1, 0), fov=40.0, aperture=0.02, focus=9.0)
+    return s
+
+
+def test_quadric_roots_parity(renderer):
+    scene = _quadric_roots_scene()
+    renderer.upload(scene)
+    oracle = OracleWorld(scene)
+    cam = scene.camera(W, H)
+    for flags in (RS_FLAG_PIXEL_CENTRE, 0):
+        params = make_params(samples=9, flags=flags)
+        g = renderer.debug_primary(cam, params, 4)
+        o = oracle.debug_primary(cam, params, 4)
+        assert np.array_equal(g["obj_id"], o["obj_id"])
+        assert set(np.unique(o["obj_id"]).tolist()) >= {1, 2, 3, 4}
+        hit = o["obj_id"] >= 0
+        assert _rel_err(g["t"][hit], o["t"][hit]).max() < REL
+        assert np.abs(g["normal"][hit] - o["normal"][hit]).max() < REL
+        assert np.array_equal(g["front"][hit], o["front"][hit]) and np.array_equal(g["material"][hit], o["material"][hit])
+    sg = renderer.debug_scatter(cam, make_params(samples=9), 2)
+    so = oracle.debug_scatter(cam, make_params(samples=9), 2)
+    assert np.array_equal(sg["kind"], so["kind"])
+    sc = so["kind"] >= 2
+    assert np.abs(sg["next"][sc] - so["next"][sc]).max() < REL * max(1.0, np.abs(so["next"][sc]).max())
+    params = make_params(samples=256)
+    gi = renderer.render(scene.camera(64, 40), params)
+    oi, _ = oracle.render(scene.camera(64, 40), params)
+    rmse = float(np.sqrt(np.mean((gi[..., :3] - oi[..., :3]) ** 2))) / float(np.sqrt(np.mean(oi[..., :3] ** 2)))
+    assert rmse < 0.01 and abs(_luminance(gi).mean() - _luminance(oi).mean()) <= 0.005 * _luminance(oi).mean()
