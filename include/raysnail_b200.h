@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RS_ABI_VERSION 1
+#define RS_ABI_VERSION 2
 
 typedef enum rs_status {
     RS_OK = 0,
@@ -208,6 +208,11 @@ typedef struct rs_render_params {
 
 #define RS_FLAG_PIXEL_CENTRE 1u  /* probes only: no jitter, no lens, time 0 (u,v at stratum centre) */
 #define RS_FLAG_KERNEL_TIMING 2u /* record CUDA events around every kernel; fills rs_stats.ms_* (syncs the stream) */
+/* Opt-in integrator: the MixturePdf(HittablePdf(world.lights), srec.pdf) sampling that the reference keeps
+ * commented out in ray_color (src/camera.rs:188-192, 222-225; types in src/prelude/pdf.rs:237-307).  The
+ * scattered ray starts at the hit point, its direction is MixturePdf::generate, and the sample is weighted
+ * by srec.pdf.value / MixturePdf::value.  Default (flag clear) = the live 50/50 branch of camera.rs:194-247. */
+#define RS_FLAG_MIS 4u
 
 typedef struct rs_stats {
     uint64_t n_samples;        /* camera paths started */
@@ -295,6 +300,44 @@ int rs_noise_map(rs_ctx* ctx, const float* d_pixels, float* d_noise, int32_t wid
 /* PNG quantisation (raysnail.rs:437-441): (clamp(c,0,1)*255.5) as u8; out = W*H*3 bytes. */
 int rs_quantize_rgb8(rs_ctx* ctx, const float* d_pixels, uint8_t* d_rgb, int64_t n_pixels,
                      void* stream);
+
+/* The whole passes loop of the CLI (src/bin/raysnail.rs:379-427) in one call, device-resident between
+ * passes: old = [0,0,0,1]; for pass in 0..n_passes { new = shot_to_target(mask); old = combine_pixels(old,
+ * new, pass); noise = calc_noise(old); redo = noise >= noise_threshold }.  Pass k renders with the Philox
+ * key rs_pass_seed(params->seed, k) (the reference gets fresh RNG state on every shot_to_target call).
+ *   RS_REDO_REFERENCE: what the reference does — its RedoController holds a stale clone of the all-ones
+ *                      map (raysnail.rs:369-372), so every pass re-renders every pixel; the map is only counted;
+ *   RS_REDO_NOISE:     opt-in, the map is used: pass k+1 renders only pixels with noise >= threshold
+ *                      (noise computed like the reference, `x = y` indexing quirk included);
+ *   RS_REDO_NOISE_FIXED: as RS_REDO_NOISE with the noise window centred on (x, y).
+ * The reference's threshold is 0.01 (raysnail.rs:404).  out_rgba: host, W*H*[f32;4] (the final old_pixels);
+ * out_rgb8: host, W*H*3 PNG bytes (raysnail.rs:431-441) or NULL; redo_counts: host, n_passes entries
+ * ("oversampling N pixels", raysnail.rs:424) or NULL. */
+#define RS_REDO_REFERENCE 0
+#define RS_REDO_NOISE 1
+#define RS_REDO_NOISE_FIXED 2
+int rs_render_passes(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* params, int32_t n_passes,
+                     int32_t redo_mode, float noise_threshold, float* out_rgba, uint8_t* out_rgb8,
+                     int64_t* redo_counts);
+/* Philox key of pass k: seed + k * 0x9E3779B97F4A7C15 (wrapping); pass 0 renders with `seed` itself. */
+uint64_t rs_pass_seed(uint64_t seed, int32_t pass);
+
+/* ---- the RNG, for host harnesses (replaces FastRng, src/prelude/random.rs:109-145) ---------------
+ * Philox4x32-10 (Salmon et al., SC'11) exactly as the kernels evaluate it, so that a host-side harness
+ * (the Rust reference with its RNG swapped, or a test) can draw the very numbers a path sees.  Plain CPU
+ * integer code, no GPU needed.  Stream layout: key = (seed lo, seed hi), counter = (pixel, sample, depth,
+ * purpose | call << 8); uniform = (word >> 8) * 2^-24.  Purposes: RS_RNG_*; `depth` is 0 for the camera
+ * ray and b + 1 for everything drawn at the b-th hit of the path. */
+#define RS_RNG_PIXEL 0u   /* words 0,1: jitter x,y (painter.rs:169-170); word 2: shutter time (camera.rs:84) */
+#define RS_RNG_LENS 1u    /* random_unit_disk rejection loop (vec3.rs:140-147): iteration k = word pair k&1 of call k>>1 */
+#define RS_RNG_SCATTER 2u /* word 0: light/BRDF branch (camera.rs:198); 1: light pick (list.rs:49-52); 2: MixedMaterial level 0; 3: Dielectric */
+#define RS_RNG_MIXED 3u   /* call = nesting level >= 1 of a MixedMaterial (mixed_material.rs:44), word 0 */
+#define RS_RNG_LIGHT 4u   /* Hittable::random of the picked light (sphere.rs:153-163 loop / rect.rs:149-150) */
+#define RS_RNG_BRDF 5u    /* PDF::generate (pdf.rs) */
+#define RS_RNG_MEDIUM 6u  /* ConstantMedium free flight (constant.rs:62), call = node index of the medium */
+int rs_philox4x32_10(const uint32_t counter[4], const uint32_t key[2], uint32_t out[4]);
+int rs_philox_uniform(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t depth, uint32_t purpose,
+                      uint32_t call, double out4[4]);
 
 /* ---- parity probes (host output buffers, one entry per pixel) ------------------------------*/
 /* Primary ray of sample `sample_index` (= s_j*sqrt_spp + s_i) of every pixel: closest hit.

@@ -1440,7 +1440,28 @@ struct ScatterProbe {  // filled for the first bounce when non-null
 };
 
 // camera.rs:156-255
-Vec3 ray_color(const Ray& ray, const Scene& world, int depth, Rng rng, Counters& cnt, ScatterProbe* probe) {
+// pdf.rs:237-269.  `value` is what the reference's type computes today: the `objects.pdf_value` call is
+// commented out there (no Hittable has a pdf_value), it evaluates a CosinePdf about the stored normal.
+struct HittablePdf : PDF {
+    const Scene* world;
+    Vec3 origin, normal;
+    HittablePdf(const Scene* w, const Vec3& o, const Vec3& n) : world(w), origin(o), normal(n) {}
+    double value(const Vec3& direction) const override { return CosinePdf(normal).value(direction); }
+    Vec3 generate(const Rng& rng) const override { return unit(world->lights_random(origin, rng)); }
+};
+// pdf.rs:271-307; the selector draw is word 0 of the P_SCATTER call (the draw of camera.rs:198)
+struct MixturePdf : PDF {
+    const PDF *p0, *p1;
+    MixturePdf(const PDF* a, const PDF* b) : p0(a), p1(b) {}
+    double value(const Vec3& direction) const override { return 0.5 * p0->value(direction) + 0.5 * p1->value(direction); }
+    Vec3 generate(const Rng& rng) const override {
+        uint32_t w[4];
+        rng.words(P_SCATTER, 0, w);
+        return u01(w[0]) < 0.5 ? p0->generate(rng) : p1->generate(rng);
+    }
+};
+
+Vec3 ray_color(const Ray& ray, const Scene& world, int depth, Rng rng, Counters& cnt, ScatterProbe* probe, uint32_t flags) {
     if (depth == 0) return Vec3();
     rng.depth += 1;  // shading depth index of the hit that ends this segment
     HitRecord hit;
@@ -1455,7 +1476,7 @@ Vec3 ray_color(const Ray& ray, const Scene& world, int depth, Rng rng, Counters&
             if (srec.skip_pdf) {
                 if (srec.has_ray) {
                     if (probe) { probe->kind = 2; probe->next_o = srec.ray.origin; probe->next_d = srec.ray.direction; probe->weight = to_vec3(srec.color); probe->emitted = emitted; return Vec3(); }
-                    return emitted + srec.color * ray_color(srec.ray, world, depth - 1, rng, cnt, nullptr);
+                    return emitted + srec.color * ray_color(srec.ray, world, depth - 1, rng, cnt, nullptr, flags);
                 }
                 return emitted + srec.color * Vec3(1.0, 1.0, 1.0);
             }
@@ -1465,7 +1486,18 @@ Vec3 ray_color(const Ray& ray, const Scene& world, int depth, Rng rng, Counters&
             uint32_t w[4];
             rng.words(P_SCATTER, 0, w);
             bool light_branch = u01(w[0]) < 0.5;
-            if (light_branch) {
+            if (flags & RS_FLAG_MIS) {
+                // the integrator the reference keeps commented out (camera.rs:188-192, 222-225): direction from
+                // MixturePdf(HittablePdf(lights), srec.pdf), density = the mixture's value, where the second
+                // HittablePdf is built with `normal = scattered.direction`; the ray starts at the hit point
+                HittablePdf light_pdf(&world, hit.point, hit.normal);
+                MixturePdf mixture(&light_pdf, srec.pdf.get());
+                Vec3 scatter_direction = mixture.generate(rng);
+                scattered = Ray{hit.point, scatter_direction, ray.departure_time};
+                HittablePdf light_pdf2(&world, hit.point, scattered.direction);
+                MixturePdf mixture2(&light_pdf2, srec.pdf.get());
+                pdf_val = mixture2.value(scattered.direction);
+            } else if (light_branch) {
                 pdf_val = 0.3183098861837907;
                 Vec3 dir_to_light = unit(world.lights_random(hit.point, rng));
                 Settings settings = material->settings();
@@ -1488,7 +1520,7 @@ Vec3 ray_color(const Ray& ray, const Scene& world, int depth, Rng rng, Counters&
                 probe->emitted = emitted;
                 return Vec3();
             }
-            Vec3 sample_color = light_multi * ray_color(scattered, world, depth - 1, rng, cnt, nullptr);
+            Vec3 sample_color = light_multi * ray_color(scattered, world, depth - 1, rng, cnt, nullptr, flags);
             Vec3 color_from_scatter = (srec.color * sample_color) * pdf_multiplicator;
             return emitted + color_from_scatter;
         }
@@ -1567,6 +1599,17 @@ int rso_marcher_log(const double* x, int64_t n, double* out) {
     return 0;
 }
 
+// test hook: Texture::color of texture `tex` at n points (u, v, p.xyz as 5 doubles each) -> n x rgba f32
+int rso_texture_color(const rso_world* w, int32_t tex, const double* uvp, int64_t n, float* out) {
+    if (tex < 0 || tex >= (int)w->scene.textures.size()) return RS_ERR_INVALID_ARGUMENT;
+    for (int64_t i = 0; i < n; ++i) {
+        const double* q = uvp + 5 * i;
+        Color c = w->scene.textures[tex]->color(q[0], q[1], Vec3(q[2], q[3], q[4]));
+        out[4 * i] = c.r; out[4 * i + 1] = c.g; out[4 * i + 2] = c.b; out[4 * i + 3] = c.a;
+    }
+    return RS_OK;
+}
+
 int rso_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
     philox4x32_10(ctr, key, out);
     return 0;
@@ -1594,7 +1637,7 @@ int rso_render(const rso_world* w, const rs_camera* cam_in, const rs_render_para
                 for (int s_j = p->stratum_row_begin; s_j < p->stratum_row_end; ++s_j)
                     for (int s_i = 0; s_i < p->sqrt_spp; ++s_i) {
                         Ray r = sample_ray(cam, *p, row, col, s_i, s_j, rng);
-                        color_vec = color_vec + ray_color(r, w->scene, p->depth, rng, cnt, nullptr);
+                        color_vec = color_vec + ray_color(r, w->scene, p->depth, rng, cnt, nullptr, p->flags);
                         ++samples;
                     }
                 // Vec3::into_color (vec3.rs:227-240)
@@ -1659,7 +1702,7 @@ int rso_debug_scatter(const rso_world* w, const rs_camera* cam_in, const rs_rend
             size_t i = (size_t)row * cam.width + col;
             Ray r = sample_ray(cam, *p, row, col, s_i, s_j, rng);
             ScatterProbe probe;
-            ray_color(r, w->scene, p->depth, rng, cnt, &probe);
+            ray_color(r, w->scene, p->depth, rng, cnt, &probe, p->flags);
             if (kind) kind[i] = probe.kind;
             if (next_od6) { double* o = next_od6 + 6 * i; o[0] = probe.next_o.x; o[1] = probe.next_o.y; o[2] = probe.next_o.z; o[3] = probe.next_d.x; o[4] = probe.next_d.y; o[5] = probe.next_d.z; }
             if (weight3) { weight3[3 * i] = probe.weight.x; weight3[3 * i + 1] = probe.weight.y; weight3[3 * i + 2] = probe.weight.z; }
@@ -1700,6 +1743,32 @@ int rso_noise_map(const float* px, float* noise, int32_t width, int32_t height, 
                 }
             noise[(size_t)y0 * width + x0] = diff;
         }
+    return RS_OK;
+}
+
+// src/bin/raysnail.rs:379-427: the passes loop.  redo_mode as RS_REDO_* of include/raysnail_b200.h; pass k
+// renders with key seed + k * 0x9E3779B97F4A7C15 (the reference's RNG is freshly seeded per pass).
+int rso_render_passes(const rso_world* w, const rs_camera* cam, const rs_render_params* p, int32_t n_passes, int32_t redo_mode,
+                      float threshold, int n_threads, float* out, int64_t* redo_counts) {
+    const size_t np = (size_t)cam->width * cam->height;
+    std::vector<float> old_px(4 * np), new_px(4 * np), comb(4 * np), noise(np);
+    std::vector<uint8_t> redo(np, 1);
+    for (size_t i = 0; i < np; ++i) { old_px[4 * i] = 0.f; old_px[4 * i + 1] = 0.f; old_px[4 * i + 2] = 0.f; old_px[4 * i + 3] = 1.f; }  // :318-326
+    for (int pass = 0; pass < n_passes; ++pass) {
+        rs_render_params pp = *p;
+        pp.seed = p->seed + (uint64_t)(int64_t)pass * 0x9E3779B97F4A7C15ull;
+        // :369-372: the controller holds a clone of the initial all-ones map; the opt-in modes use the live one
+        const uint8_t* mask = (redo_mode != RS_REDO_REFERENCE && pass > 0) ? redo.data() : nullptr;
+        int rc = rso_render(w, cam, &pp, mask, new_px.data(), n_threads, nullptr);
+        if (rc != RS_OK) return rc;
+        rso_combine_passes(old_px.data(), new_px.data(), comb.data(), (int64_t)np, (float)pass);  // :388
+        rso_noise_map(comb.data(), noise.data(), cam->width, cam->height, redo_mode == RS_REDO_NOISE_FIXED ? 0 : 1);
+        int64_t count = 0;
+        for (size_t i = 0; i < np; ++i) { redo[i] = noise[i] >= threshold ? 1 : 0; count += redo[i]; }  // :408-423
+        if (redo_counts) redo_counts[pass] = count;
+        old_px.swap(comb);  // :426
+    }
+    std::memcpy(out, old_px.data(), 4 * np * sizeof(float));
     return RS_OK;
 }
 

@@ -16,6 +16,8 @@ LIB_PATH = os.environ.get("RAYSNAIL_B200_LIB") or os.path.join(_HERE, "libraysna
 RS_OK = 0
 RS_FLAG_PIXEL_CENTRE = 1
 RS_FLAG_KERNEL_TIMING = 2
+RS_FLAG_MIS = 4
+RS_REDO_REFERENCE, RS_REDO_NOISE, RS_REDO_NOISE_FIXED = 0, 1, 2
 
 # every symbol include/raysnail_b200.h declares
 CORE_SYMBOLS = [
@@ -23,6 +25,7 @@ CORE_SYMBOLS = [
     "rs_render_accumulate", "rs_finalize", "rs_combine_passes", "rs_noise_map", "rs_quantize_rgb8",
     "rs_debug_primary", "rs_debug_scatter", "rs_get_stats",
     "rs_device_alloc", "rs_device_free", "rs_ipc_export", "rs_ipc_open", "rs_ipc_close", "rs_finalize_peers",
+    "rs_render_passes", "rs_pass_seed", "rs_philox4x32_10", "rs_philox_uniform",
 ]
 # every symbol include/raysnail_b200_host.h declares
 HOST_SYMBOLS = [
@@ -140,6 +143,10 @@ def load() -> C.CDLL:
     proto("rs_ipc_open", C.c_int, vp, vp, P(vp))
     proto("rs_ipc_close", C.c_int, vp, vp)
     proto("rs_finalize_peers", C.c_int, vp, P(vp), i32, vp, vp, C.c_int64, C.c_int64, i32, i32, vp)
+    proto("rs_render_passes", C.c_int, vp, P(RsCamera), P(RsRenderParams), i32, i32, f32, vp, vp, vp)
+    proto("rs_pass_seed", C.c_uint64, C.c_uint64, i32)
+    proto("rs_philox4x32_10", C.c_int, vp, vp, vp)
+    proto("rs_philox_uniform", C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp)
 
     proto("rs_host_last_error", C.c_char_p)
     proto("rs_host_scene_from_sdl_file", C.c_int, C.c_char_p, P(vp))

@@ -353,6 +353,17 @@ class Renderer:
         self._ck(self._lib.rs_finalize_peers(self._ctx, arr, len(d_accums), d_mask, d_out, int(pixel_begin), int(pixel_end), int(n_samples),
                                              int(gamma), stream), "rs_finalize_peers")
 
+    def render_passes(self, cam: RsCamera, params: RsRenderParams, n_passes: int, redo_mode: int = 0, threshold: float = 0.01,
+                      want_rgb8: bool = False):
+        """The CLI's passes loop (src/bin/raysnail.rs:379-427) in one call: (image, redo count per pass[, rgb8])."""
+        h, w = cam.height, cam.width
+        out = np.empty((h, w, 4), dtype=np.float32)
+        rgb = np.empty((h, w, 3), dtype=np.uint8) if want_rgb8 else None
+        counts = np.zeros(max(n_passes, 1), dtype=np.int64)
+        self._ck(self._lib.rs_render_passes(self._ctx, C.byref(cam), C.byref(params), int(n_passes), int(redo_mode), float(threshold),
+                                            out.ctypes.data, rgb.ctypes.data if want_rgb8 else None, counts.ctypes.data), "rs_render_passes")
+        return (out, counts[:n_passes], rgb) if want_rgb8 else (out, counts[:n_passes])
+
     def combine_passes(self, d_old, d_new, d_out, n_pixels, pass_index: float, stream: int = 0):
         self._ck(self._lib.rs_combine_passes(self._ctx, d_old, d_new, d_out, n_pixels, pass_index, stream), "rs_combine_passes")
 
@@ -417,3 +428,28 @@ class TakePhotoSettings:
 
 def take_photo(cam: RsCamera, renderer: Renderer) -> TakePhotoSettings:
     return TakePhotoSettings(cam, renderer)
+
+
+def pass_seed(seed: int, pass_index: int) -> int:
+    """Philox key of pass k of the passes loop (`rs_pass_seed`)."""
+    return int(_abi.load().rs_pass_seed(C.c_uint64(seed & 0xFFFFFFFFFFFFFFFF), int(pass_index)))
+
+
+def philox4x32_10(counter: Sequence[int], key: Sequence[int]) -> np.ndarray:
+    """`rs_philox4x32_10`: the kernels' counter-based RNG, evaluated on the host (for harnesses)."""
+    c = np.asarray(counter, dtype=np.uint32)
+    k = np.asarray(key, dtype=np.uint32)
+    out = np.zeros(4, dtype=np.uint32)
+    rc = _abi.load().rs_philox4x32_10(c.ctypes.data, k.ctypes.data, out.ctypes.data)
+    if rc != 0:
+        raise RaysnailError(f"rs_philox4x32_10 failed ({rc})")
+    return out
+
+
+def philox_uniform(seed: int, pixel: int, sample: int, depth: int, purpose: int, call: int = 0) -> np.ndarray:
+    """`rs_philox_uniform`: the four uniforms of one draw site of a path."""
+    out = np.zeros(4, dtype=np.float64)
+    rc = _abi.load().rs_philox_uniform(C.c_uint64(seed), pixel, sample, depth, purpose, call, out.ctypes.data)
+    if rc != 0:
+        raise RaysnailError(f"rs_philox_uniform failed ({rc})")
+    return out

@@ -95,13 +95,14 @@ struct rs_ctx {
     int wave_streams = 2;
     cudaStream_t aux_stream[kMaxSets - 1] = {};
     cudaEvent_t ev_fork = nullptr, ev_join[kMaxSets - 1] = {}, ev_acc[kMaxSets] = {};
-    int extend_grid = 148, shade_grid = 148, shade_grid_lambert = 148, extend_dyn_grid = 148;
+    int extend_grid = 148, shade_grid = 148, shade_grid_lambert = 148;
     int extend_first_grid = 148;
     int fuse_raygen = 1;  // bounce 0 of a render without pixel mask generates its camera rays inside extend
-    int dyn_from = -1;  // first bounce that uses the dynamic-fetch extend kernel (lean scenes, binary BVH); -1 = never
 
     // scratch for rs_render / probes
     DevBuf d_accum, d_out, d_mask, d_dbg[11];
+    DevBuf d_pass_old, d_pass_comb, d_noise, d_redo_count;  // rs_render_passes
+    bool stats_final = false;  // `stats` already holds the device counters (rs_render_passes sums them over its passes)
 
     // timing
     std::vector<cudaEvent_t> events;
@@ -506,6 +507,7 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
     const uint32_t np = (uint32_t)cam->width * (uint32_t)cam->height;
     const uint32_t s_total = (uint32_t)(p->stratum_row_end - p->stratum_row_begin) * (uint32_t)p->sqrt_spp;
     ctx->stats = rs_stats{};
+    ctx->stats_final = false;
     if (s_total == 0 || np == 0) return RS_OK;
     uint32_t cap = p->max_wave_paths > 0 ? (uint32_t)p->max_wave_paths : (1u << 23);
     cap = std::max(cap, 1024u);
@@ -558,8 +560,6 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
                 tm.mark(1);
                 if (b == 0 && fused_first)
                     launch_extend_first(ctx->scene, fp, ws, ctx->extend_mode, ctx->extend_first_grid, st);
-                else if (ctx->dyn_from >= 0 && b >= ctx->dyn_from && ctx->extend_mode < 2 && ctx->bvh_width == 2)
-                    launch_extend_dyn(ctx->scene, fp, ws, b, ctx->extend_mode, 1, ctx->extend_dyn_grid, st);
                 else
                     launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
                 tm.mark(2);
@@ -714,12 +714,16 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
                 return fail(ctx, RS_ERR_INVALID_ARGUMENT, "perlin tables out of range");
         }
     }
+    std::vector<int> mixed_depth(s->n_materials, 0);
     for (int i = 0; i < s->n_materials; ++i) {
         const rs_material& m = s->materials[i];
         if (m.type < RS_MAT_LAMBERTIAN || m.type > RS_MAT_MIXED) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad material type");
         bool needs_tex = m.type == RS_MAT_LAMBERTIAN || m.type == RS_MAT_METAL || m.type == RS_MAT_DIFFUSE_METAL || m.type == RS_MAT_DIFFUSE_LIGHT || m.type == RS_MAT_BLINN_PHONG;
         if (needs_tex && (m.texture < 0 || m.texture >= s->n_textures)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "material texture out of range");
         if (m.type == RS_MAT_MIXED && (m.mat1 < 0 || m.mat1 >= i || m.mat2 < 0 || m.mat2 >= i)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "mixed material children must precede it");
+        // the kernels resolve a MixedMaterial chain (mixed_material.rs:43-51) in at most RS_MAX_MIXED_DEPTH draws
+        mixed_depth[i] = m.type == RS_MAT_MIXED ? 1 + std::max(mixed_depth[m.mat1], mixed_depth[m.mat2]) : 0;
+        if (mixed_depth[i] > RS_MAX_MIXED_DEPTH) return fail(ctx, RS_ERR_UNSUPPORTED, "MixedMaterial nested deeper than RS_MAX_MIXED_DEPTH (8)");
     }
     std::vector<rs_node> nodes(s->nodes, s->nodes + s->n_nodes);
     std::vector<XformPre> xf;
@@ -847,9 +851,6 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4);
     ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, ctx->shade_generic == 2 ? 0 : 2);
     ctx->shade_grid_lambert = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic == 2 ? 0 : ctx->shade_generic, 1);
-    ctx->extend_dyn_grid = ctx->sm_count * extend_dyn_blocks_per_sm(ctx->extend_mode < 2 ? ctx->extend_mode : 0);
-    ctx->dyn_from = -1;
-    if (const char* e = std::getenv("RAYSNAIL_B200_DYN_FROM")) ctx->dyn_from = std::atoi(e);
     ctx->extend_first_grid = ctx->sm_count * extend_first_blocks_per_sm(ctx->extend_mode);
     if (const char* e = std::getenv("RAYSNAIL_B200_FUSE_RAYGEN")) ctx->fuse_raygen = std::atoi(e);
     // tuning hooks: fewer resident blocks per SM than the occupancy limit (profiling experiments)
@@ -1118,6 +1119,96 @@ int rs_quantize_rgb8(rs_ctx* ctx, const float* d_pixels, uint8_t* d_rgb, int64_t
     return RS_OK;
 }
 
+uint64_t rs_pass_seed(uint64_t seed, int32_t pass) { return seed + (uint64_t)(int64_t)pass * 0x9E3779B97F4A7C15ull; }
+
+// The passes loop of the CLI (raysnail.rs:379-427), device-resident: render -> combine -> noise -> redo map.
+int rs_render_passes(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, int32_t n_passes, int32_t redo_mode, float noise_threshold,
+                     float* out_rgba, uint8_t* out_rgb8, int64_t* redo_counts) {
+    int rc = check_render_args(ctx, cam, p);
+    if (rc != RS_OK) return rc;
+    if (!out_rgba || n_passes < 0 || redo_mode < RS_REDO_REFERENCE || redo_mode > RS_REDO_NOISE_FIXED)
+        return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad rs_render_passes arguments");
+    CK(cudaSetDevice(ctx->device));
+    const size_t np = (size_t)cam->width * cam->height;
+    CK(ctx->d_accum.ensure(np * sizeof(float4)));
+    CK(ctx->d_out.ensure(np * sizeof(float4)));
+    CK(ctx->d_pass_old.ensure(np * sizeof(float4)));
+    CK(ctx->d_pass_comb.ensure(np * sizeof(float4)));
+    CK(ctx->d_noise.ensure(np * sizeof(float)));
+    CK(ctx->d_mask.ensure(np));
+    CK(ctx->d_redo_count.ensure((size_t)std::max(n_passes, 1) * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(ctx->d_redo_count.p, 0, (size_t)std::max(n_passes, 1) * sizeof(unsigned long long), 0));
+    float4* d_old = ctx->d_pass_old.as<float4>();
+    float4* d_comb = ctx->d_pass_comb.as<float4>();
+    // "in the first pass all pixels must be calculated": old = [0,0,0,1], redo = 1 (raysnail.rs:318-326)
+    launch_fill(d_old, (int64_t)np, make_float4(0.f, 0.f, 0.f, 1.f), 0);
+    const int n = (p->stratum_row_end - p->stratum_row_begin) * p->sqrt_spp;
+    rs_stats total{};
+    for (int pass = 0; pass < n_passes; ++pass) {
+        rs_render_params pp = *p;
+        pp.seed = rs_pass_seed(p->seed, pass);
+        pp.flags &= ~RS_FLAG_KERNEL_TIMING;
+        // RS_REDO_REFERENCE: the controller's map is the stale all-ones clone => every pixel, every pass
+        const unsigned char* d_mask = (redo_mode != RS_REDO_REFERENCE && pass > 0) ? ctx->d_mask.as<unsigned char>() : nullptr;
+        CK(cudaMemsetAsync(ctx->d_accum.p, 0, np * sizeof(float4), 0));
+        rc = render_into(ctx, cam, &pp, d_mask, ctx->d_accum.as<float4>(), 0, false);
+        if (rc != RS_OK) return rc;
+        total.n_launches += ctx->stats.n_launches + 5;
+        launch_finalize(ctx->d_accum.as<float4>(), d_mask, ctx->d_out.as<float4>(), (int64_t)np, std::max(n, 1), p->gamma, 0);
+        launch_combine(d_old, ctx->d_out.as<float4>(), d_comb, (int64_t)np, (float)pass, 0);
+        launch_noise(d_comb, ctx->d_noise.as<float>(), cam->width, cam->height, redo_mode == RS_REDO_NOISE_FIXED ? 0 : 1, 0);
+        launch_redo_mask(ctx->d_noise.as<float>(), ctx->d_mask.as<unsigned char>(), (int64_t)np, noise_threshold,
+                         ctx->d_redo_count.as<unsigned long long>() + pass, 0);
+        std::swap(d_old, d_comb);
+        CK(cudaGetLastError());
+        DeviceStats ds;  // the per-pass path counters (also orders the host loop behind the device: one pass in flight)
+        CK(cudaMemcpyAsync(&ds, ctx->ws.stats, sizeof(ds), cudaMemcpyDeviceToHost, 0));
+        CK(cudaStreamSynchronize(0));
+        total.n_samples += ds.n_samples;
+        total.n_segments += ds.n_segments;
+    }
+    CK(cudaMemcpyAsync(out_rgba, d_old, np * sizeof(float4), cudaMemcpyDeviceToHost, 0));
+    if (out_rgb8) {
+        unsigned char* d_rgb = reinterpret_cast<unsigned char*>(ctx->d_out.p);  // W*H*3 <= W*H*16 bytes: reuse
+        launch_quantize(d_old, d_rgb, (int64_t)np, 0);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(out_rgb8, d_rgb, np * 3, cudaMemcpyDeviceToHost, 0));
+    }
+    if (redo_counts && n_passes > 0) {
+        std::vector<unsigned long long> c((size_t)n_passes);
+        CK(cudaMemcpyAsync(c.data(), ctx->d_redo_count.p, (size_t)n_passes * sizeof(unsigned long long), cudaMemcpyDeviceToHost, 0));
+        CK(cudaStreamSynchronize(0));
+        for (int k = 0; k < n_passes; ++k) redo_counts[k] = (int64_t)c[(size_t)k];
+    }
+    CK(cudaStreamSynchronize(0));
+    ctx->stats = total;
+    ctx->stats_final = true;
+    return RS_OK;
+}
+
+// Philox4x32-10 on the host: the same definition as rt_math.cuh's philox4x32_10 (integer arithmetic only)
+int rs_philox4x32_10(const uint32_t counter[4], const uint32_t key[2], uint32_t out[4]) {
+    if (!counter || !key || !out) return RS_ERR_INVALID_ARGUMENT;
+    uint32_t c0 = counter[0], c1 = counter[1], c2 = counter[2], c3 = counter[3], k0 = key[0], k1 = key[1];
+    for (int r = 0; r < 10; ++r) {
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t)p1, n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+    return RS_OK;
+}
+
+int rs_philox_uniform(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t depth, uint32_t purpose, uint32_t call, double out4[4]) {
+    if (!out4 || purpose > 0xffu || call > 0xffffffu) return RS_ERR_INVALID_ARGUMENT;
+    const uint32_t ctr[4] = {pixel, sample, depth, purpose | (call << 8)}, key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    uint32_t w[4];
+    rs_philox4x32_10(ctr, key, w);
+    for (int k = 0; k < 4; ++k) out4[k] = (double)(w[k] >> 8) * (1.0 / 16777216.0);
+    return RS_OK;
+}
+
 static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, int32_t sample_index, bool shade, void* host_out[11],
                      const size_t elem_bytes[11]) {
     int rc = check_render_args(ctx, cam, p);
@@ -1186,7 +1277,7 @@ int rs_debug_scatter(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
 int rs_get_stats(const rs_ctx* ctx, rs_stats* out) {
     if (!ctx || !out) return RS_ERR_INVALID_ARGUMENT;
     rs_ctx* c = const_cast<rs_ctx*>(ctx);
-    if (c->capacity) {
+    if (c->capacity && !c->stats_final) {
         cudaSetDevice(c->device);
         DeviceStats ds;
         if (cudaMemcpy(&ds, c->ws.stats, sizeof(ds), cudaMemcpyDeviceToHost) == cudaSuccess) {

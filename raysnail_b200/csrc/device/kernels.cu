@@ -516,7 +516,7 @@ __device__ __forceinline__ int root_material(const DScene& S, const Closest& bes
 // MixedMaterial::scatter (mixed_material.rs:43-51) resolved ahead of shading, so that the
 // class buckets hold concrete materials.  Level 0 uses word 2 of the P_SCATTER call.
 __device__ __forceinline__ int resolve_mixed(const DScene& S, int m, const RngCtx& rng) {
-    for (uint32_t level = 0; level < 8 && RS_MATHOT_TYPE(S.mat_hot[m]) == RS_MAT_MIXED; ++level) {
+    for (uint32_t level = 0; level < RS_MAX_MIXED_DEPTH && RS_MATHOT_TYPE(S.mat_hot[m]) == RS_MAT_MIXED; ++level) {
         const rs_material& mm = S.materials[m];
         uint32_t word = level == 0 ? rng_words(rng, P_SCATTER, 0).z : rng_words(rng, P_MIXED, level).x;
         m = ((double)word < 4294967295.0 * mm.a) ? mm.mat1 : mm.mat2;
@@ -609,7 +609,14 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                 const MatHot& mh = S.mat_hot[leaf];
                 const int tf = mh.type_flags;
                 cls = 1 + (tf & 0xff);
-                if (miss_in_extend && (tf & 0x3ff) == RS_MAT_DIFFUSE_LIGHT) {
+                if (miss_in_extend && (tf & 0xff) == RS_MAT_DIFFUSE_LIGHT && leaf != top) {
+                    // a DiffuseLight reached THROUGH a MixedMaterial: `emitted` is asked of the hit's
+                    // own (top) material, and MixedMaterial::emitted is None (mixed_material.rs:53-55,
+                    // camera.rs:172-174); the light's `scatter` is None as well (material/mod.rs:59-61), so the
+                    // path ends here and adds nothing
+                    if constexpr (FIRST) ws.contrib[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    cls = -1;
+                } else if (miss_in_extend && (tf & 0x3ff) == RS_MAT_DIFFUSE_LIGHT) {
                     // a DiffuseLight never scatters (light.rs:33-35): the path ends here with
                     // T * colour * multiplier.  With a solid colour (tex_mode 0) nothing about the
                     // hit point is needed, so it is finished on the spot like a miss — no hit
@@ -692,226 +699,6 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                 *queue_slot = make_uint2(i, out_pos);
             }
         }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// extend with dynamic ray fetch (lean scenes; chosen per scene, see rs_upload_scene)
-// ---------------------------------------------------------------------------------------------
-// After the first bounce the rays of a warp can need very different numbers of node visits (ncu,
-// 1 M-triangle mesh, bounce 1 of the batch kernel: 7.4 of 32 lanes active per instruction): in a
-// batch-at-a-time kernel the warp runs as long as its slowest ray.  Here a warp owns a POOL of
-// ray indices and every lane keeps its own traversal state; whenever at least RS_TUNE_DYN_REFILL
-// lanes have finished their ray, those lanes TOGETHER run the epilogue of their rays (finish
-// misses and light hits, resolve the material, bucket the hit by class, reserve the output slot)
-// and take new rays from the pool, so the traversal loop keeps most lanes busy and the epilogue
-// still runs with many lanes at a time.  The pool is refilled 32 indices at a time with one atomic
-// on the cursor, issued one chunk ahead.  (On the sphere scenes, whose rays differ far less, this
-// kernel is 5-15 % slower than the batch kernel: measured, DESIGN.md.)
-#ifndef RS_TUNE_DYN_REFILL
-#define RS_TUNE_DYN_REFILL 12
-#endif
-#ifndef RS_TUNE_DYN_BLOCKS
-#define RS_TUNE_DYN_BLOCKS 4
-#endif
-template <int MODE>
-__global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_DYN_BLOCKS) extend_dyn_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
-                                                                                  const __grid_constant__ WaveState ws, const int bounce,
-                                                                                  const int miss_in_extend) {
-    static_assert(MODE < 2, "lean scenes only");
-    const uint32_t nf = ws.ctr->n_rays[bounce], nb = ws.ctr->n_back[bounce];
-    const uint32_t nf32 = (nf + 31u) & ~31u;
-    const uint32_t n = nf32 + nb;
-    const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
-    const uint32_t lane_zero = RS_LANE_ZERO(ws);
-    const PathBuf& in = ws.buf[bounce & 1];
-    uint32_t* head = &ws.ctr->extend_head[bounce];
-    uint32_t* class_count = ws.ctr->class_count[bounce];
-    const bool last_bounce = bounce + 1 >= fp.depth;
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_segments, (unsigned long long)(nf + nb));
-    const double inf = __longlong_as_double(0x7ff0000000000000LL);
-    const float tmin_f = (float)RS_TMIN * (1.0f - 2.0f * RS_SLAB_EPS);
-    const float slack = (1.0f + RS_SLAB_EPS) * (1.0f + RS_SLAB_EPS);
-
-    // per-lane traversal state
-    unsigned long long stack[RS_STACK];
-    int sp = 0, node = RS_BVH_SENTINEL;  // sentinel = idle
-    bool has_ray = false;
-    uint32_t i = 0, slot = 0;
-    Ray ray;
-    ray.o = v3(0, 0, 0); ray.d = v3(0, 0, 1); ray.time = 0.0;
-    float idx = 0.f, idy = 0.f, idz = 0.f, oodx = 0.f, oody = 0.f, oodz = 0.f, tmax_f = FLT_MAX;
-    Closest best;
-    best.t = inf; best.end_then = inf; best.root = -1; best.material = -1;
-    // the warp's pool of virtual ray indices [pool_next, pool_end) + the chunk fetched ahead
-    uint32_t pool_next = 0, pool_end = 0, pend = 0;
-    bool exhausted = false;
-    if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
-    RngCtx no_rng;
-    no_rng.key = fp.key; no_rng.pixel = 0; no_rng.sample = 0; no_rng.depth = 0;
-
-    while (true) {
-        const uint32_t idle = __ballot_sync(0xffffffffu, node == RS_BVH_SENTINEL);
-        if (idle == 0xffffffffu || (!exhausted && __popc(idle) >= RS_TUNE_DYN_REFILL)) {
-            // ---- epilogue of the finished rays (all 32 lanes take part in the collectives) ----
-            const bool fin = has_ray && node == RS_BVH_SENTINEL;
-            int cls = -1;
-            RngCtx rng;
-            rng.key = fp.key; rng.pixel = 0; rng.sample = 0; rng.depth = (uint32_t)bounce + 1;
-            if (fin) {
-                decode_slot(fp, slot, rng.pixel, rng.sample);
-                HitA h;
-                h.t = best.t; h.root = best.root; h.matinfo = 0;
-                cls = 0;
-                if (best.root >= 0) {
-                    int top = root_material<MODE>(S, best);
-                    int leaf = resolve_mixed(S, top, rng);
-                    h.matinfo = (uint32_t)leaf | ((uint32_t)top << 16);
-                    const MatHot& mh = S.mat_hot[leaf];
-                    const int tf = mh.type_flags;
-                    cls = 1 + (tf & 0xff);
-                    if (miss_in_extend && (tf & 0x3ff) == RS_MAT_DIFFUSE_LIGHT) {  // see extend_kernel
-                        const float4 c = mh.c0;
-                        const double mul = mh.a;
-                        const uint4 q3 = in.rec[4 * (size_t)i + 3];
-                        ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * (float)((double)c.x * mul), __uint_as_float(q3.y) * (float)((double)c.y * mul),
-                                                       __uint_as_float(q3.z) * (float)((double)c.z * mul), 0.f);
-                        cls = -1;
-                    } else {
-                        ws.hit[i] = h;
-                    }
-                } else if (miss_in_extend) {
-                    const float4 bg = background(S, ray.d);
-                    const uint4 q3 = in.rec[4 * (size_t)i + 3];
-                    ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * bg.x, __uint_as_float(q3.y) * bg.y, __uint_as_float(q3.z) * bg.z, 0.f);
-                    cls = -1;
-                } else {
-                    ws.hit[i] = h;
-                }
-            }
-            const bool queued = fin && cls >= 0;
-            const uint32_t active = __ballot_sync(0xffffffffu, queued);
-            constexpr bool RESERVE = RS_TUNE_RESERVE != 0;
-            bool reserve = false, res_front = false;
-            uint32_t mf = 0, mb = 0, bf = 0, bb = 0, lf = 0, lb = 0;
-            if constexpr (RESERVE) {
-                if (queued && !last_bounce && RS_ALWAYS_CONTINUES(cls)) {
-                    reserve = true;
-                    res_front = cls != 1 + RS_MAT_DIELECTRIC && u01(rng_words(rng, P_SCATTER, 0).x) < 0.5;
-                }
-                mf = __ballot_sync(0xffffffffu, reserve && res_front);
-                mb = __ballot_sync(0xffffffffu, reserve && !res_front);
-                lf = mf ? (uint32_t)(__ffs(mf) - 1) : 0u;
-                lb = mb ? (uint32_t)(__ffs(mb) - 1) : 0u;
-                if (mf && lane == lf) bf = atomic_add_async(&ws.ctr->n_rays[bounce + 1], __popc(mf), lane_zero);
-                if (mb && lane == lb) bb = atomic_add_async(&ws.ctr->n_back[bounce + 1], __popc(mb), lane_zero);
-            }
-            uint2* queue_slot = nullptr;
-            if (queued) {
-                const int key = (RESERVE && res_front) ? RS_FRONT_CLASS(cls) : cls;
-                const uint32_t peers = __match_any_sync(active, key);
-                const uint32_t leader = __ffs(peers) - 1;
-                uint32_t qbase = 0;
-                if (lane == leader) qbase = atomic_add_async(&class_count[key * RS_COUNTER_STRIDE], __popc(peers), lane_zero);
-                qbase = __shfl_sync(peers, qbase, leader);
-                queue_slot = ws.class_queue + ((size_t)key * ws.capacity + qbase + __popc(peers & lt));
-                if constexpr (!RESERVE) *queue_slot = make_uint2(i, 0xffffffffu);
-            }
-            if constexpr (RESERVE) {
-                bf = __shfl_sync(0xffffffffu, bf, lf);
-                bb = __shfl_sync(0xffffffffu, bb, lb);
-                if (queued) {
-                    const uint32_t out_pos = !reserve ? 0xffffffffu : (res_front ? bf + __popc(mf & lt) : ws.capacity - 1u - (bb + __popc(mb & lt)));
-                    *queue_slot = make_uint2(i, out_pos);
-                }
-            }
-            // ---- refill the idle lanes from the pool ----
-            const bool want = node == RS_BVH_SENTINEL;
-            if (want) has_ray = false;
-            if (!exhausted) {
-                const uint32_t need = __popc(idle), avail = pool_end - pool_next, rank = __popc(idle & lt);
-                uint32_t v;
-                if (need > avail) {  // warp-uniform: cross into the chunk fetched ahead
-                    const uint32_t nextb = __shfl_sync(0xffffffffu, pend, 0);
-                    v = rank < avail ? pool_next + rank : nextb + (rank - avail);
-                    pool_next = nextb + (need - avail);
-                    pool_end = nextb + 32u;
-                    if (nextb >= n) exhausted = true;
-                    else if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
-                } else {
-                    v = pool_next + rank;
-                    pool_next += need;
-                }
-                if (want && (v < nf32 ? v < nf : v < n)) {
-                    i = v < nf32 ? v : ws.capacity - 1u - (v - nf32);
-                    const uint4* rec = in.rec + 4 * (size_t)i;
-                    const uint4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
-                    slot = rec[3].w;
-                    ray.o = v3(__hiloint2double((int)q0.y, (int)q0.x), __hiloint2double((int)q0.w, (int)q0.z), __hiloint2double((int)q1.y, (int)q1.x));
-                    ray.d = v3(__hiloint2double((int)q1.w, (int)q1.z), __hiloint2double((int)q2.y, (int)q2.x), __hiloint2double((int)q2.w, (int)q2.z));
-                    const float ox = (float)ray.o.x, oy = (float)ray.o.y, oz = (float)ray.o.z;
-                    float dx = (float)ray.d.x, dy = (float)ray.d.y, dz = (float)ray.d.z;
-                    const float tiny = 1e-20f;
-                    dx = fabsf(dx) > tiny ? dx : copysignf(tiny, dx);
-                    dy = fabsf(dy) > tiny ? dy : copysignf(tiny, dy);
-                    dz = fabsf(dz) > tiny ? dz : copysignf(tiny, dz);
-                    idx = 1.0f / dx; idy = 1.0f / dy; idz = 1.0f / dz;
-                    oodx = ox * idx; oody = oy * idy; oodz = oz * idz;
-                    tmax_f = FLT_MAX;
-                    best.t = inf; best.root = -1;
-                    has_ray = true;
-                    stack[0] = (unsigned long long)(uint32_t)RS_BVH_SENTINEL;
-                    sp = 1;
-                    node = S.n_roots ? S.bvh_root : RS_BVH_SENTINEL;
-                }
-            }
-            if (__ballot_sync(0xffffffffu, has_ray) == 0u) {
-                if (exhausted) break;
-                continue;  // a chunk of padding only
-            }
-        }
-#define RS_POP()                                                                   \
-    do {                                                                           \
-        const unsigned long long e_ = stack[--sp];                                 \
-        node = (int)(uint32_t)e_;                                                  \
-        if (!(__uint_as_float((uint32_t)(e_ >> 32) & ~3u) > tmax_f)) break;        \
-    } while (true)
-        // ---- one round of while-while: every busy lane walks to its next leaf, then tests it ----
-        while (node >= 0) {
-            const float4* np = reinterpret_cast<const float4*>(S.bvh2 + node);
-            const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
-            const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
-            float a0 = fmaf(bx.x, idx, -oodx), a1 = fmaf(bx.y, idx, -oodx);
-            float b0 = fmaf(bx.z, idy, -oody), b1 = fmaf(bx.w, idy, -oody);
-            float c0 = fmaf(bz.x, idz, -oodz), c1 = fmaf(bz.y, idz, -oodz);
-            const float near0 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), tmin_f));
-            const float far0 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), tmax_f));
-            a0 = fmaf(by.x, idx, -oodx); a1 = fmaf(by.y, idx, -oodx);
-            b0 = fmaf(by.z, idy, -oody); b1 = fmaf(by.w, idy, -oody);
-            c0 = fmaf(bz.z, idz, -oodz); c1 = fmaf(bz.w, idz, -oodz);
-            const float near1 = fmaxf(fmaxf(fminf(a0, a1), fminf(b0, b1)), fmaxf(fminf(c0, c1), tmin_f));
-            const float far1 = fminf(fminf(fmaxf(a0, a1), fmaxf(b0, b1)), fminf(fmaxf(c0, c1), tmax_f));
-            const bool h0 = near0 <= far0 * slack, h1 = near1 <= far1 * slack;
-            if (h0 && h1) {
-                const bool swap = near1 < near0;
-                const int second = swap ? ch.x : ch.y;
-                const float second_near = swap ? near0 : near1;
-                if (sp < RS_STACK) stack[sp++] = ((unsigned long long)__float_as_uint(second_near) << 32) | (unsigned long long)(uint32_t)second;
-                node = swap ? ch.y : ch.x;
-            } else if (h0) {
-                node = ch.x;
-            } else if (h1) {
-                node = ch.y;
-            } else {
-                RS_POP();
-            }
-        }
-        if (node != RS_BVH_SENTINEL) {
-            test_root<MODE>(S, ~node, ray, no_rng, best);
-            tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
-            RS_POP();
-        }
-#undef RS_POP
     }
 }
 
@@ -1303,7 +1090,10 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
                 V3 reflected = v3(0, 0, 0);
                 switch (mat_type) {
                     case RS_MAT_DIFFUSE_LIGHT: {  // light.rs:33-35: emitted = colour * multiplier, no scatter
-                        add = make_float3((float)((double)col.x * mat.a), (float)((double)col.y * mat.a), (float)((double)col.z * mat.a));
+                        // `emitted` is asked of the hit's own material (camera.rs:172-174): a light that was
+                        // selected THROUGH a MixedMaterial emits nothing (mixed_material.rs:53-55)
+                        if ((ha.matinfo >> 16) == (ha.matinfo & 0xffffu))
+                            add = make_float3((float)((double)col.x * mat.a), (float)((double)col.y * mat.a), (float)((double)col.z * mat.a));
                         break;
                     }
                     case RS_MAT_LAMBERTIAN: {  // lambertian.rs:39-50
@@ -1380,6 +1170,7 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
                     P.r_w = (P.kind == 1 || P.kind == 2) ? unit_fast(reflected) : v3(0, 0, 0);
                     double light_multi = 1.0, pdf_val;
                     const uint4 w = rng_words(rng, P_SCATTER, 0);
+                    const bool mis = (fp.flags & RS_FLAG_MIS) != 0;
                     if (u01(w.x) < 0.5) {  // camera.rs:198-213
                         kind = 3;
                         pdf_val = 0.3183098861837907;
@@ -1392,9 +1183,9 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
                             to_light = ln.type == RS_NODE_SPHERE ? sphere_random(ln, h.point, rng) : rect_random(ln, h.point, rng);
                         }
                         V3 dir_to_light = unit_fast(to_light);
-                        if (smat.phong_factor > 0.0)
+                        if (!mis && smat.phong_factor > 0.0)
                             light_multi += phong_highlight(-dir_to_light, p.ray.d, h.normal, smat.phong_exponent, smat.phong_factor);
-                        next_o = ray_at(p.ray, h.t1 - 0.0002);
+                        next_o = mis ? h.point : ray_at(p.ray, h.t1 - 0.0002);
                         next_d = dir_to_light;
                     } else {  // camera.rs:214-218
                         kind = 4;
@@ -1408,9 +1199,19 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
                         pdf_val = pdf_value(P, next_d);
                         next_o = h.point;
                     }
-                    if (pdf_val <= 0.0 || pdf_val != pdf_val) pdf_val = 1e-5;  // camera.rs:236-238
-                    // BRDF branch: the two values are the same number, x / x == 1 exactly
-                    const double ratio = (kind == 4 && pdf_val > 0.0 && pdf_val < RS_F64_MAX) ? 1.0 : pdf_value(P, next_d) / pdf_val;
+                    if (mis) {
+                        // RS_FLAG_MIS: the integrator the reference keeps commented out (camera.rs:188-192,
+                        // 222-225): density of MixturePdf(HittablePdf, srec.pdf) (pdf.rs:237-307), where
+                        // HittablePdf::value is a CosinePdf about ITS normal, and that normal is the sampled direction
+                        const double c = dot(next_d, unit_fast(next_d));
+                        pdf_val = 0.5 * (c < 0.0 ? 0.0 : c * RS_INV_PI) + 0.5 * pdf_value(P, next_d);
+                    }
+                    // camera.rs:236-243: a pdf value that is <= 0 or NaN is replaced by 1e-5 and the
+                    // (unchanged) scattering value is divided by it: 0, a large negative number or NaN
+                    const bool degenerate = pdf_val <= 0.0 || pdf_val != pdf_val;
+                    if (degenerate) pdf_val = 1e-5;
+                    // BRDF branch with a regular value: the two values are the same number, x / x == 1 exactly
+                    const double ratio = (kind == 4 && !mis && !degenerate && pdf_val < RS_F64_MAX) ? 1.0 : pdf_value(P, next_d) / pdf_val;
                     const double mult = light_multi * ratio;
                     w_r = (double)col.x * mult; w_g = (double)col.y * mult; w_b = (double)col.z * mult;
                 }
@@ -1514,13 +1315,15 @@ __global__ void __launch_bounds__(RS_BLOCK) accumulate_kernel(const __grid_const
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < fp.n_pixels; p += gridDim.x * blockDim.x) {
         const uint32_t pixel = fp.pixel0 + p;
         if (fp.mask && fp.mask[pixel] == 0) continue;
-        float sx = 0.f, sy = 0.f, sz = 0.f;
+        // the reference sums `color_vec` in f64 (painter.rs:163-176): the samples of a wave are summed in
+        // f64 and rounded once into the f32 accumulator
+        double sx = 0.0, sy = 0.0, sz = 0.0;
         for (uint32_t k = 0; k < fp.n_samples; ++k) {
             const float4 c = ws.contrib[(size_t)k * fp.n_pixels + p];
-            sx += c.x; sy += c.y; sz += c.z;
+            sx += (double)c.x; sy += (double)c.y; sz += (double)c.z;
         }
         float4 a = accum[pixel];
-        a.x += sx; a.y += sy; a.z += sz; a.w += (float)fp.n_samples;
+        a.x = (float)((double)a.x + sx); a.y = (float)((double)a.y + sy); a.z = (float)((double)a.z + sz); a.w += (float)fp.n_samples;
         accum[pixel] = a;
     }
 }
@@ -1589,6 +1392,23 @@ __global__ void noise_kernel(const float4* __restrict__ px, float* __restrict__ 
     }
 }
 
+// the redo map of the passes loop (raysnail.rs:408-423): 1 where noise >= t; *count += number of ones
+__global__ void __launch_bounds__(RS_BLOCK) redo_mask_kernel(const float* __restrict__ noise, unsigned char* __restrict__ mask, int64_t n, float t,
+                                                             unsigned long long* __restrict__ count) {
+    unsigned int mine = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const bool redo = noise[i] >= t;
+        mask[i] = redo ? 1 : 0;
+        mine += redo ? 1u : 0u;
+    }
+    mine = __reduce_add_sync(0xffffffffu, mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(count, (unsigned long long)mine);
+}
+
+__global__ void fill_kernel(float4* __restrict__ p, int64_t n, float4 v) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
 // (clamp(c,0,1) * 255.5) as u8 (raysnail.rs:437-439)
 __device__ __forceinline__ unsigned char quant(float c) {
     double v = (double)c;
@@ -1637,16 +1457,6 @@ static const void* extend_fn_for(int mode, int wide) {
     if (wide) return mode == 0 ? extend_fn<0, true>() : (mode == 1 ? extend_fn<1, true>() : (mode == 2 ? extend_fn<2, true>() : extend_fn<3, true>()));
     return mode == 0 ? extend_fn<0, false>() : (mode == 1 ? extend_fn<1, false>() : (mode == 2 ? extend_fn<2, false>() : extend_fn<3, false>()));
 }
-void launch_extend_dyn(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int miss_in_extend, int grid, cudaStream_t s) {
-    if (mode == 0) extend_dyn_kernel<0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, miss_in_extend);
-    else extend_dyn_kernel<1><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, miss_in_extend);
-}
-int extend_dyn_blocks_per_sm(int mode) {
-    int n = 0;
-    if (mode == 0) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_dyn_kernel<0>, RS_BLOCK, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_dyn_kernel<1>, RS_BLOCK, 0);
-    return n > 0 ? n : 1;
-}
 void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int miss_in_extend, int grid,
                    cudaStream_t s) {
     void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
@@ -1683,6 +1493,10 @@ void launch_combine(const float4* old_px, const float4* new_px, float4* out, int
 void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s) {
     noise_kernel<<<grid_for((int64_t)w * h), RS_BLOCK, 0, s>>>(px, noise, w, h, quirk);
 }
+void launch_redo_mask(const float* noise, unsigned char* mask, int64_t n, float t, unsigned long long* count, cudaStream_t s) {
+    redo_mask_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(noise, mask, n, t, count);
+}
+void launch_fill(float4* p, int64_t n, float4 v, cudaStream_t s) { fill_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(p, n, v); }
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s) {
     quantize_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(px, rgb, n);
 }

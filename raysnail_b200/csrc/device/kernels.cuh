@@ -9,6 +9,7 @@
 namespace rsd {
 
 #define RS_MAX_DEPTH 64   // TakePhotoSettings::depth upper bound supported by the counter block
+#define RS_MAX_MIXED_DEPTH 8  // MixedMaterial nesting the kernels resolve (resolve_mixed); deeper scenes are rejected at upload
 #define RS_TRAVERSAL_STACK 96  // per-thread QBVH traversal stack entries (3 pushes per level at most)
 // Shade work classes: 0 = miss, 1 + rs_material_type for the resolved (non-mixed) material, and —
 // lean kernels, where extend already knows the light/BRDF branch draw — 8, 9, 10 = the hits of
@@ -122,8 +123,8 @@ void launch_finalize_peers(const PeerAccums& peers, const unsigned char* mask, f
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s);
 void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s);
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);
-void launch_extend_dyn(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int miss_in_extend, int grid, cudaStream_t s);
-int extend_dyn_blocks_per_sm(int mode);
+void launch_redo_mask(const float* noise, unsigned char* mask, int64_t n, float t, unsigned long long* count, cudaStream_t s);
+void launch_fill(float4* p, int64_t n, float4 v, cudaStream_t s);
 void launch_extend_first(const DScene& S, const FrameParams& fp, const WaveState& ws, int mode, int grid, cudaStream_t s);
 int extend_first_blocks_per_sm(int mode);
 int extend_blocks_per_sm(int mode, int wide);

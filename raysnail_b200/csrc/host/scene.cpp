@@ -283,7 +283,7 @@ int MixedMaterial::flatten(FlatScene& fs) const {
     return cached(fs.material_cache, this, [&] {
         int m1 = material_1->flatten(fs), m2 = material_2->flatten(fs);
         // MixedMaterial::settings() returns material_1's settings (mixed_material.rs:56-58)
-        rs_material m = blank_material(RS_MAT_MIXED, material_1->settings);
+        rs_material m = blank_material(RS_MAT_MIXED, effective_settings());
         m.mat1 = m1; m.mat2 = m2; m.a = probability_1;
         return push_material(fs, m);
     });

@@ -153,6 +153,8 @@ struct Material {
     CommonMaterialSettings settings;
     virtual ~Material() = default;
     void set(const CommonMaterialSettings& s) { settings = s; }
+    // `Material::settings()` (material/mod.rs:63-65); MixedMaterial forwards to material_1 (mixed_material.rs:56-58)
+    virtual CommonMaterialSettings effective_settings() const { return settings; }
     virtual int flatten(FlatScene& fs) const = 0;
 };
 using MaterialPtr = std::shared_ptr<const Material>;
@@ -204,6 +206,7 @@ struct MixedMaterial : Material {
     double probability_1;
     MixedMaterial(MaterialPtr m1, MaterialPtr m2, double p)
         : material_1(std::move(m1)), material_2(std::move(m2)), probability_1(p) {}
+    CommonMaterialSettings effective_settings() const override { return material_1->effective_settings(); }
     int flatten(FlatScene& fs) const override;
 };
 

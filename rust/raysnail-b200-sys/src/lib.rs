@@ -8,7 +8,7 @@
 
 use std::os::raw::{c_char, c_int, c_void};
 
-pub const RS_ABI_VERSION: c_int = 1;
+pub const RS_ABI_VERSION: c_int = 2;
 
 // rs_status
 pub const RS_OK: c_int = 0;
@@ -54,6 +54,17 @@ pub const RS_TEX_PERLIN: i32 = 3;
 
 pub const RS_FLAG_PIXEL_CENTRE: u32 = 1;
 pub const RS_FLAG_KERNEL_TIMING: u32 = 2;
+pub const RS_FLAG_MIS: u32 = 4;
+pub const RS_REDO_REFERENCE: i32 = 0;
+pub const RS_REDO_NOISE: i32 = 1;
+pub const RS_REDO_NOISE_FIXED: i32 = 2;
+pub const RS_RNG_PIXEL: u32 = 0;
+pub const RS_RNG_LENS: u32 = 1;
+pub const RS_RNG_SCATTER: u32 = 2;
+pub const RS_RNG_MIXED: u32 = 3;
+pub const RS_RNG_LIGHT: u32 = 4;
+pub const RS_RNG_BRDF: u32 = 5;
+pub const RS_RNG_MEDIUM: u32 = 6;
 pub const RS_OPT_BVH_WIDTH: c_int = 1;
 pub const RS_OPT_WAVE_STREAMS: c_int = 2;
 pub const RS_IPC_HANDLE_BYTES: usize = 64;
@@ -218,6 +229,10 @@ extern "C" {
     pub fn rs_debug_primary(ctx: *mut rs_ctx, cam: *const rs_camera, params: *const rs_render_params, sample_index: i32, obj_id: *mut i32, t: *mut f64, normal3: *mut f64, point3: *mut f64, front: *mut i32, material: *mut i32, ray_od6: *mut f64) -> c_int;
     pub fn rs_debug_scatter(ctx: *mut rs_ctx, cam: *const rs_camera, params: *const rs_render_params, sample_index: i32, kind: *mut i32, next_od6: *mut f64, weight3: *mut f64, emitted3: *mut f64) -> c_int;
     pub fn rs_get_stats(ctx: *const rs_ctx, out: *mut rs_stats) -> c_int;
+    pub fn rs_render_passes(ctx: *mut rs_ctx, cam: *const rs_camera, params: *const rs_render_params, n_passes: i32, redo_mode: i32, noise_threshold: f32, out_rgba: *mut f32, out_rgb8: *mut u8, redo_counts: *mut i64) -> c_int;
+    pub fn rs_pass_seed(seed: u64, pass: i32) -> u64;
+    pub fn rs_philox4x32_10(counter: *const u32, key: *const u32, out: *mut u32) -> c_int;
+    pub fn rs_philox_uniform(seed: u64, pixel: u32, sample: u32, depth: u32, purpose: u32, call: u32, out4: *mut f64) -> c_int;
 }
 
 /// Compares `size_of` of every `#[repr(C)]` struct with what the loaded library was compiled

@@ -113,7 +113,13 @@ impl SceneBuilder {
 /// One CUDA device.  Not `Sync`: one host thread at a time (include/raysnail_b200.h).
 pub struct Context {
     ctx: *mut sys::rs_ctx,
+    /// Base Philox key.  Render call k uses `rs_pass_seed(seed, k)`, so that consecutive
+    /// `shot_to_target` calls (the passes loop, raysnail.rs:379-427) see fresh random numbers the way
+    /// the reference's freshly seeded FastRng does — with a constant key every pass would return
+    /// bit-identical pixels and averaging them would never reduce the noise.
     pub seed: u64,
+    /// number of `render` calls so far (the pass index mixed into the key)
+    pub pass: i32,
 }
 
 impl Context {
@@ -125,7 +131,7 @@ impl Context {
         if rc != sys::RS_OK {
             return Err(Error { status: rc, message: last_error(ptr::null()) });
         }
-        Ok(Context { ctx, seed: 0x5EED_0007 })
+        Ok(Context { ctx, seed: 0x5EED_0007, pass: 0 })
     }
     fn check(&self, rc: i32) -> Result<(), Error> {
         if rc == sys::RS_OK {
@@ -152,7 +158,7 @@ impl Context {
             stratum_row_begin: 0,
             stratum_row_end: sqrt_spp,
             max_wave_paths: 0,
-            seed: self.seed,
+            seed: unsafe { sys::rs_pass_seed(self.seed, self.pass) },
             flags: 0,
             reserved: 0,
         };
@@ -165,7 +171,20 @@ impl Context {
         let mut out = vec![[0f32; 4]; n];
         let rc = unsafe { sys::rs_render(self.ctx, cam, &params, mask.map_or(ptr::null(), |m| m.as_ptr()), out.as_mut_ptr() as *mut f32) };
         self.check(rc)?;
+        self.pass += 1;
         Ok(out)
+    }
+    /// The whole passes loop (raysnail.rs:379-427) on the device; `redo_mode`: `sys::RS_REDO_*`.
+    pub fn render_passes(&mut self, cam: &sys::rs_camera, samples: usize, depth: usize, passes: usize, redo_mode: i32, threshold: f32) -> Result<(Vec<[f32; 4]>, Vec<i64>), Error> {
+        let sqrt_spp = (samples as f64).sqrt().floor() as i32;
+        let params = sys::rs_render_params { sqrt_spp, depth: depth as i32, gamma: 1, stratum_row_begin: 0, stratum_row_end: sqrt_spp, max_wave_paths: 0, seed: self.seed, flags: 0, reserved: 0 };
+        let n = cam.width as usize * cam.height as usize;
+        let mut out = vec![[0f32; 4]; n];
+        let mut counts = vec![0i64; passes.max(1)];
+        let rc = unsafe { sys::rs_render_passes(self.ctx, cam, &params, passes as i32, redo_mode, threshold, out.as_mut_ptr() as *mut f32, ptr::null_mut(), counts.as_mut_ptr()) };
+        self.check(rc)?;
+        counts.truncate(passes);
+        Ok((out, counts))
     }
     pub fn stats(&self) -> sys::rs_stats {
         let mut s = sys::rs_stats::default();
@@ -190,4 +209,26 @@ fn last_error(ctx: *const sys::rs_ctx) -> String {
     } else {
         unsafe { CStr::from_ptr(p) }.to_string_lossy().into_owned()
     }
+}
+
+
+/// Philox4x32-10 exactly as the kernels evaluate it (`rs_philox4x32_10`), in plain Rust: a reference
+/// harness that swaps `FastRng` (src/prelude/random.rs:109-145) for this draws the very numbers a
+/// GPU path sees.  Stream layout: key = (seed lo, seed hi), counter = (pixel, sample, depth,
+/// purpose | call << 8); see the RS_RNG_* purposes in include/raysnail_b200.h.
+pub fn philox4x32_10(counter: [u32; 4], key: [u32; 2]) -> [u32; 4] {
+    let (mut c, mut k) = (counter, key);
+    for _ in 0..10 {
+        let p0 = 0xD251_1F53u64 * c[0] as u64;
+        let p1 = 0xCD9E_8D57u64 * c[2] as u64;
+        c = [(p1 >> 32) as u32 ^ c[1] ^ k[0], p1 as u32, (p0 >> 32) as u32 ^ c[3] ^ k[1], p0 as u32];
+        k = [k[0].wrapping_add(0x9E37_79B9), k[1].wrapping_add(0xBB67_AE85)];
+    }
+    c
+}
+
+/// The four uniforms of one draw site: `(word >> 8) * 2^-24`, exact in f32 and f64.
+pub fn philox_uniform(seed: u64, pixel: u32, sample: u32, depth: u32, purpose: u32, call: u32) -> [f64; 4] {
+    let w = philox4x32_10([pixel, sample, depth, purpose | (call << 8)], [seed as u32, (seed >> 32) as u32]);
+    [w[0], w[1], w[2], w[3]].map(|x| (x >> 8) as f64 * (1.0 / 16_777_216.0))
 }

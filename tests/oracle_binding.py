@@ -38,6 +38,8 @@ def load():
     lib.rso_combine_passes.argtypes = [vp, vp, vp, C.c_int64, C.c_float]
     lib.rso_noise_map.argtypes = [vp, vp, i32, i32, i32]
     lib.rso_quantize_rgb8.argtypes = [vp, vp, C.c_int64]
+    lib.rso_render_passes.argtypes = [vp, P(RsCamera), P(RsRenderParams), i32, i32, C.c_float, C.c_int, vp, vp]
+    lib.rso_texture_color.argtypes = [vp, i32, vp, C.c_int64, vp]
     _lib = lib
     return lib
 
@@ -76,6 +78,25 @@ class OracleWorld:
         if rc != 0:
             raise RuntimeError(f"rso_render failed: {rc}")
         return out, stats
+
+    def render_passes(self, cam, params, n_passes, redo_mode=0, threshold=0.01, threads=0):
+        """The CLI's passes loop (src/bin/raysnail.rs:379-427): (final old_pixels, redo count per pass)."""
+        out = np.empty((cam.height, cam.width, 4), dtype=np.float32)
+        counts = np.zeros(max(n_passes, 1), dtype=np.int64)
+        rc = self._lib.rso_render_passes(self._w, C.byref(cam), C.byref(params), n_passes, redo_mode, threshold, threads, out.ctypes.data,
+                                         counts.ctypes.data)
+        if rc != 0:
+            raise RuntimeError(f"rso_render_passes failed: {rc}")
+        return out, counts[:n_passes]
+
+    def texture_color(self, tex, uvp):
+        """Texture::color of texture index `tex` at rows (u, v, x, y, z) -> (n, 4) f32."""
+        uvp = np.ascontiguousarray(uvp, dtype=np.float64).reshape(-1, 5)
+        out = np.empty((uvp.shape[0], 4), dtype=np.float32)
+        rc = self._lib.rso_texture_color(self._w, int(tex), uvp.ctypes.data, uvp.shape[0], out.ctypes.data)
+        if rc != 0:
+            raise RuntimeError(f"rso_texture_color failed: {rc}")
+        return out
 
     def debug_primary(self, cam, params, sample_index=0):
         n = cam.width * cam.height

@@ -65,7 +65,7 @@ def test_structs_match_the_header_field_for_field():
 def c_functions():
     text = " ".join(strip_comments(HEADER).split())
     out = {}
-    for m in re.finditer(r"(?:int|void|const char\*) (rs_\w+)\((.*?)\);", text):
+    for m in re.finditer(r"(?:int|void|uint64_t|const char\*) (rs_\w+)\((.*?)\);", text):
         args = m.group(2).strip()
         out[m.group(1)] = 0 if args in ("", "void") else len(args.split(","))
     return out
