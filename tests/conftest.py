@@ -8,6 +8,10 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 SDL_DIR = os.path.join(ROOT, "tests", "golden", "sdl")
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+# `all_feature_scene` reads examples/earth-map.png (examples/common/scene.rs:425-431); the committed copy
+# under tests/golden/ travels to the GPU box, /root/reference does not
+os.environ.setdefault("RAYSNAIL_ASSETS", GOLDEN_DIR)
 
 
 def pytest_configure(config):

@@ -21,6 +21,14 @@ def copy_sdl():
             shutil.copyfile(os.path.join(src, f), os.path.join(dst, f))
 
 
+def copy_assets():
+    """The reference's two binary assets: the earth texture of `all_feature_scene`
+    (examples/common/scene.rs:425-431) and the one image the reference's authors rendered with it
+    (examples/sdl_quadrics.jpg = sdl/quadric.sdl at 800x500), used as an image-level pin of the oracle."""
+    for f in ("earth-map.png", "sdl_quadrics.jpg"):
+        shutil.copyfile(os.path.join("/root/reference/examples", f), os.path.join(HERE, f))
+
+
 def oracle_vectors():
     import numpy as np
     from conftest import load_scene
@@ -55,6 +63,9 @@ def raymarching_vectors():
 
 if __name__ == "__main__":
     copy_sdl()
+    copy_assets()
+    if "--only-copies" in sys.argv:
+        sys.exit(0)
     if "--only-raymarching" not in sys.argv:
         oracle_vectors()
     raymarching_vectors()

@@ -230,7 +230,7 @@ def test_checker_sign_table_and_image_lookup():
 
 def test_sphere_uv_and_earth_texture_lookup():
     """Image texel lookup on the reference's earth-map.png (1920x960), read by the host PNG reader."""
-    path = "/root/reference/examples/earth-map.png"
+    path = os.path.join(HERE, "golden", "earth-map.png")  # the reference's examples/earth-map.png (tests/golden/make_fixtures.py)
     if not os.path.exists(path):
         pytest.skip("reference assets are not on this machine")
     from PIL import Image
