@@ -25,6 +25,12 @@
 //    (quadric +-100 box, Intersection::bbox z quirk).
 //  * Exact ties in t between two world objects: the reference keeps whichever its (randomly
 //    built) BVH visits first (collection/bvh.rs:184-191); here the lower object id wins.
+//  * Limit seen by a world object: the reference hands every BVH leaf the limit as shrunk by the hits found
+//    before it in ITS (random) visiting order (collection/bvh.rs:180-187).  For a Box the far face may then
+//    fall outside the limit (one-face record with the real `outside` instead of the two-face record with
+//    `outside = true`, box.rs:131-146), and a Difference / Intersection can return another surface or none.
+//    Canonical, order-independent rule used by oracle and GPU alike: a world object is evaluated over
+//    [limit.start, +inf) — as if it were the first one visited — and its hit competes with t1.
 //  * `assert!`s that abort the reference (pdf.rs:38 etc., box.rs:129) do not abort here.
 #include <algorithm>
 #include <atomic>
@@ -1163,8 +1169,14 @@ struct BVHNode : Hittable {
     bool hit(const Ray& ray, const Range& limit, const Rng& rng, HitRecord& out) const override {  // :173-192
         if (gate_leaf) {
             if (!box.hit(ray, Range{limit.start, INF})) return false;
-            if (!left->hit(ray, limit, rng, out)) return false;
-            out.u = out.u;  // no-op; the id travels separately
+            // The object is evaluated over [limit.start, +inf) and its hit is accepted if it lies inside the
+            // (shrunk) limit.  For spheres, rects, quadrics, triangles and media that is what evaluating under
+            // the shrunk limit returns anyway; for a Box (which of its faces count, hence `outside` of the
+            // two-face record, box.rs:125-150) and for CSG objects the reference's answer depends on how far
+            // the limit had shrunk when its randomly built tree reached the object — canonical rule: as if
+            // the object were visited first (see the header).
+            if (!left->hit(ray, Range{limit.start, INF}, rng, out)) return false;
+            if (!(out.t1 < limit.end)) return false;
             last_leaf_hit(leaf_id);
             return true;
         }

@@ -84,7 +84,7 @@ struct rs_ctx {
     // every persistent kernel of one wave (SMs going idle as its last batches finish) is filled by
     // blocks of the other wave's kernel (RS_OPT_WAVE_STREAMS; `ws` is set 0 and the one the probes use)
     struct WaveSet {
-        DevBuf d_rec[2], d_time[2], d_hit, d_hit_end, d_cq, d_contrib, d_ctr;
+        DevBuf d_rec[2], d_time[2], d_hit, d_cq, d_contrib, d_ctr;
         uint32_t capacity = 0;
     };
     static constexpr int kMaxSets = 4;
@@ -425,12 +425,10 @@ int ensure_wave_set(rs_ctx* ctx, int k, uint32_t cap) {
         ws.buf[b].time = w.d_time[b].as<double>();
     }
     CK(w.d_hit.ensure((size_t)cap * sizeof(HitA)));
-    CK(w.d_hit_end.ensure((size_t)cap * sizeof(double)));
     CK(w.d_cq.ensure((size_t)cap * RS_NUM_CLASSES * sizeof(uint2)));
     CK(w.d_contrib.ensure((size_t)cap * sizeof(float4)));
     CK(w.d_ctr.ensure(sizeof(WaveCounters)));
     ws.hit = w.d_hit.as<HitA>();
-    ws.hit_end = w.d_hit_end.as<double>();
     ws.class_queue = w.d_cq.as<uint2>();
     ws.contrib = w.d_contrib.as<float4>();
     ws.ctr = w.d_ctr.as<WaveCounters>();

@@ -230,7 +230,6 @@ __global__ void __launch_bounds__(RS_BLOCK) raygen_kernel(const __grid_constant_
 // =============================================================================================
 struct Closest {
     double t;        // current limit end / best t
-    double end_then; // limit the winning generic object was evaluated under
     int root;
     int material;
 };
@@ -277,20 +276,22 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
             r.d = xf_apply(x.inv, ray.d, 0.0);
             n = S.nodes + n->child0;
         }
-        const double hi = next_up(best.t);
+        // a world object is evaluated over [tmin, +inf) — as if it were the first one visited — and its hit then
+        // competes with t1: which faces of a Box count (box.rs:125-150: `outside` of the record), and what a CSG
+        // object returns, must not depend on the order in which the tree reaches the objects
+        const double inf = __longlong_as_double(0x7ff0000000000000LL);
+        const double hi = inf;
         double t;
         bool hit;
         if (MODE >= RS_QUADRIC_MODE && n->type == RS_NODE_QUADRIC) {
             // quadric.rs:191-196: the surface is unbounded, the reference clips it with its +-100 bbox
-            const double inf = __longlong_as_double(0x7ff0000000000000LL);
             if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
             hit = quadric_t(n->p, r, RS_TMIN, hi, t);
         } else {
             hit = n->type == RS_NODE_BOX ? box_t(n->p, r, RS_TMIN, hi, t)
                                          : rect_t(n->rect_axis, n->p[0], n->p[1], n->p[2], n->p[3], n->p[4], r, RS_TMIN, hi, t);
         }
-        if (hit && (t < best.t || root < best.root)) {
-            best.end_then = hi;
+        if (hit && (t < best.t || (t == best.t && root < best.root))) {
             best.t = t;
             best.root = root;
             best.material = -2;
@@ -301,9 +302,8 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
             if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
         }
         HitRec h;
-        const double hi = next_up(best.t);
-        if (TreeTop::hit<false>(S, __ldg(&S.root_node[root]), ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || root < best.root)) {
-            best.end_then = hi;
+        const double hi = __longlong_as_double(0x7ff0000000000000LL);  // see ROOT_FLAT
+        if (TreeTop::hit<false>(S, __ldg(&S.root_node[root]), ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || (h.t1 == best.t && root < best.root))) {
             best.t = h.t1;
             best.root = root;
             best.material = h.material;
@@ -386,7 +386,6 @@ template <int MODE, bool WIDE>
 __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, Closest& best) {
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     best.t = inf;
-    best.end_then = inf;
     best.root = -1;
     best.material = -1;
     if (S.n_roots == 0) return;
@@ -628,7 +627,6 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                                                    __uint_as_float(q3.z) * (float)((double)c.z * mul), 0.f);
                     cls = -1;
                 } else {
-                    if (MODE >= 2 && S.root_kind[best.root] >= ROOT_GENERIC) ws.hit_end[i] = best.end_then;
                     ws.hit[i] = h;
                 }
             } else if (miss_in_extend) {
@@ -708,8 +706,9 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
 // GENERIC = false: the scene holds only static spheres and triangles and its lights are plain
 // spheres/rects, so no expression-tree code is compiled into the kernel.
 template <bool GENERIC, bool TREES>
-__device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, const RngCtx& rng, const HitA& ha, double end_then,
-                                            bool want_uv, HitRec& h) {
+__device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, const RngCtx& rng, const HitA& ha, bool want_uv, HitRec& h) {
+    // world objects are evaluated over [tmin, +inf) (see test_root): the same call returns the same record here
+    const double end_then = __longlong_as_double(0x7ff0000000000000LL);
     // static spheres: centre and 1/r straight from the per-root tables (one level of loads
     // instead of root -> node index -> node)
     const int kind = (!GENERIC && S.all_spheres) ? (int)ROOT_SPHERE : __ldg(&S.root_kind[ha.root]);
@@ -1077,9 +1076,7 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
                 const int mat_type = SET == 1 ? (int)RS_MAT_LAMBERTIAN : RS_MATHOT_TYPE(mat);
                 const bool want_uv = RS_MATHOT_NEEDS_UV(mat);
                 HitRec h;
-                double end_then = 0.0;
-                if constexpr (GENERIC) end_then = S.root_kind[ha.root] >= ROOT_GENERIC ? ws.hit_end[i] : 0.0;
-                rebuild_hit<GENERIC, TREES>(S, p.ray, rng, ha, end_then, want_uv, h);
+                rebuild_hit<GENERIC, TREES>(S, p.ray, rng, ha, want_uv, h);
 
                 const float4 col = material_color(S, mat, h.u, h.v, h.point);
 
@@ -1294,8 +1291,7 @@ __global__ void __launch_bounds__(RS_BLOCK) probe_primary_kernel(const __grid_co
         RngCtx rng;
         rng.key = fp.key; rng.pixel = p.pixel; rng.sample = p.sample; rng.depth = 1;
         HitRec h;
-        const double end_then = S.root_kind[ha.root] >= ROOT_GENERIC ? ws.hit_end[i] : 0.0;
-        rebuild_hit<true, true>(S, p.ray, rng, ha, end_then, true, h);
+        rebuild_hit<true, true>(S, p.ray, rng, ha, true, h);
         if (dbg.t) dbg.t[px] = h.t1;
         dbg_store3(dbg.normal3, px, h.normal);
         dbg_store3(dbg.point3, px, h.point);

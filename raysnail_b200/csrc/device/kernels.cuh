@@ -31,8 +31,7 @@ struct PathBuf {
     double* time;  // capacity (used when WaveState::uses_time)
 };
 
-// closest-hit record written by extend, read by shade (16 B) + the limit the object was
-// evaluated under (only meaningful for ROOT_GENERIC)
+// closest-hit record written by extend, read by shade (16 B)
 struct __align__(16) HitA {
     double t;
     int root;          // -1 = miss
@@ -63,7 +62,6 @@ struct DeviceStats {
 struct WaveState {
     PathBuf buf[2];
     HitA* hit;
-    double* hit_end;
     uint2* class_queue;     // RS_NUM_CLASSES * capacity entries of (path index, output slot reserved by extend or ~0)
     float4* contrib;        // per slot: radiance of the finished path
     WaveCounters* ctr;
