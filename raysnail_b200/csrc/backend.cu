@@ -84,7 +84,7 @@ struct rs_ctx {
     // every persistent kernel of one wave (SMs going idle as its last batches finish) is filled by
     // blocks of the other wave's kernel (RS_OPT_WAVE_STREAMS; `ws` is set 0 and the one the probes use)
     struct WaveSet {
-        DevBuf d_rec[2], d_time[2], d_hit, d_cq, d_contrib, d_ctr;
+        DevBuf d_rec[2], d_time[2], d_hit, d_cq, d_contrib, d_ctr, d_dbg_cost;
         uint32_t capacity = 0;
     };
     static constexpr int kMaxSets = 4;
@@ -432,6 +432,11 @@ int ensure_wave_set(rs_ctx* ctx, int k, uint32_t cap) {
     ws.class_queue = w.d_cq.as<uint2>();
     ws.contrib = w.d_contrib.as<float4>();
     ws.ctr = w.d_ctr.as<WaveCounters>();
+#if defined(RS_TUNE_COST_DUMP) && RS_TUNE_COST_DUMP
+    CK(w.d_dbg_cost.ensure((size_t)cap * sizeof(int2)));
+    CK(cudaMemset(w.d_dbg_cost.p, 0, (size_t)cap * sizeof(int2)));
+    ws.dbg_cost = w.d_dbg_cost.as<int2>();
+#endif
     ws.capacity = cap;
     w.capacity = cap;
     return RS_OK;
@@ -560,6 +565,32 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
                     launch_extend_first(ctx->scene, fp, ws, ctx->extend_mode, ctx->extend_first_grid, st);
                 else
                     launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
+#if defined(RS_TUNE_COST_DUMP) && RS_TUNE_COST_DUMP
+                // profiling builds: RAYSNAIL_B200_COST_DUMP=<file>:<bounce> writes the rays of that bounce of wave 0
+                // and their traversal costs: header (cap, nf, nb), cap x 64-byte records, cap x int2
+                if (const char* spec = std::getenv("RAYSNAIL_B200_COST_DUMP")) {
+                    std::string sp(spec);
+                    const size_t colon = sp.rfind(':');
+                    const int want = colon == std::string::npos ? 1 : std::atoi(sp.c_str() + colon + 1);
+                    if (wave == 0 && b == want && ws.dbg_cost) {
+                        CK(cudaStreamSynchronize(st));
+                        WaveCounters hc;
+                        CK(cudaMemcpy(&hc, ws.ctr, sizeof(hc), cudaMemcpyDeviceToHost));
+                        const uint32_t capn = ws.capacity, nf = (b == 0 && fused_first) ? fp.n_pixels * fp.n_samples : hc.n_rays[b], nb = (b == 0 && fused_first) ? 0u : hc.n_back[b];
+                        std::vector<uint4> rec((size_t)capn * 4);
+                        std::vector<int2> cost(capn);
+                        CK(cudaMemcpy(rec.data(), ws.buf[b & 1].rec, rec.size() * sizeof(uint4), cudaMemcpyDeviceToHost));
+                        CK(cudaMemcpy(cost.data(), ws.dbg_cost, cost.size() * sizeof(int2), cudaMemcpyDeviceToHost));
+                        if (FILE* f = std::fopen(sp.substr(0, colon).c_str(), "wb")) {
+                            const uint32_t hdr[4] = {capn, nf, nb, (uint32_t)b};
+                            std::fwrite(hdr, sizeof(hdr), 1, f);
+                            std::fwrite(rec.data(), sizeof(uint4), rec.size(), f);
+                            std::fwrite(cost.data(), sizeof(int2), cost.size(), f);
+                            std::fclose(f);
+                        }
+                    }
+                }
+#endif
                 tm.mark(2);
                 if (ctx->shade_generic == 2) {
                     launch_shade(ctx->scene, fp, ws, b, 2, 0, ctx->shade_grid, nullptr, st);

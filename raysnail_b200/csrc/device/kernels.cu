@@ -228,7 +228,13 @@ __global__ void __launch_bounds__(RS_BLOCK) raygen_kernel(const __grid_constant_
 // =============================================================================================
 // extend
 // =============================================================================================
+#ifndef RS_TUNE_COST_DUMP
+#define RS_TUNE_COST_DUMP 0  // 1 (profiling builds only): extend records per-ray node visits / leaf tests (profiles/cost_dump.py)
+#endif
 struct Closest {
+#if RS_TUNE_COST_DUMP
+    int n_nodes, n_leaves;
+#endif
     double t;        // current limit end / best t
     int root;
     int material;
@@ -388,6 +394,10 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
     best.t = inf;
     best.root = -1;
     best.material = -1;
+#if RS_TUNE_COST_DUMP
+    best.n_nodes = 0;
+    best.n_leaves = 0;
+#endif
     if (S.n_roots == 0) return;
     // f32 copy of the ray for the slab tests
     const float ox = (float)ray.o.x, oy = (float)ray.o.y, oz = (float)ray.o.z;
@@ -417,6 +427,9 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
     } while (true)
     while (true) {
         while (!WIDE && node >= 0) {
+#if RS_TUNE_COST_DUMP
+            ++best.n_nodes;
+#endif
             // one 64-byte node: two children with their boxes, four 128-bit ld.global.nc
             const float4* np = reinterpret_cast<const float4*>(S.bvh2 + node);
             const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
@@ -458,6 +471,9 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
             }
         }
         while (WIDE && node >= 0) {
+#if RS_TUNE_COST_DUMP
+            ++best.n_nodes;
+#endif
             // one 128-byte QBVH node: seven 128-bit ld.global.nc
             const float4* np = reinterpret_cast<const float4*>(S.bvh + node);
             const float4 lox = __ldg(np), hix = __ldg(np + 1), loy = __ldg(np + 2), hiy = __ldg(np + 3), loz = __ldg(np + 4), hiz = __ldg(np + 5);
@@ -497,6 +513,9 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
 #undef RS_CHILD
         }
         if (node == RS_BVH_SENTINEL) break;
+#if RS_TUNE_COST_DUMP
+        ++best.n_leaves;
+#endif
         test_root<MODE>(S, ~node, ray, rng, best);
         // shrink the f32 limit (rounded up) so farther boxes are culled
         tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
@@ -596,6 +615,9 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
             if constexpr (RS_TUNE_RESERVE && MODE < 2) rng_of_lane = rng;
             Closest best;
             closest_hit<MODE, WIDE>(S, ray, rng, best);
+#if RS_TUNE_COST_DUMP
+            if (ws.dbg_cost) ws.dbg_cost[i] = make_int2(best.n_nodes, best.n_leaves);
+#endif
             HitA h;
             h.t = best.t;
             h.root = best.root;

@@ -67,6 +67,9 @@ struct WaveState {
     WaveCounters* ctr;
     DeviceStats* stats;
     uint32_t capacity;
+#if defined(RS_TUNE_COST_DUMP) && RS_TUNE_COST_DUMP
+    int2* dbg_cost;  // profiling builds: per ray index (node visits, leaf tests) of the last extend launch
+#endif
     int uses_time;  // the scene holds moving spheres: rays carry their shutter time (sphere.rs:50-53)
 };
 
