@@ -66,6 +66,7 @@ struct rs_ctx {
     // scene (device)
     DevBuf d_nodes, d_xf, d_bvh, d_root_node, d_root_kind, d_root_sphere, d_root_bbox, d_root_gate;
     DevBuf d_mat_hot, d_root_inv_r, d_root_material, d_light_nodes;
+    DevBuf d_prog, d_cprog, d_csg, d_root_prog;  // object programs (expression-tree roots)
     DevBuf d_tri_geom, d_tri_normals, d_tri_material, d_lights, d_materials, d_textures, d_texels, d_perm, d_values;
     DScene scene{};
     // scene (host side, kept to re-pad the f32 boxes when the camera moves far away)
@@ -84,7 +85,7 @@ struct rs_ctx {
     // every persistent kernel of one wave (SMs going idle as its last batches finish) is filled by
     // blocks of the other wave's kernel (RS_OPT_WAVE_STREAMS; `ws` is set 0 and the one the probes use)
     struct WaveSet {
-        DevBuf d_rec[2], d_time[2], d_hit, d_cq, d_contrib, d_ctr, d_dbg_cost;
+        DevBuf d_rec[2], d_time[2], d_hit, d_hit_src, d_cq, d_contrib, d_ctr, d_dbg_cost;
         uint32_t capacity = 0;
     };
     static constexpr int kMaxSets = 4;
@@ -411,6 +412,91 @@ void mat3x4_mul(const long double* a, const double* b16, long double* out) {  //
         }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Object programs (rt_scene.cuh "Object programs"): post-order flattening of a world object's expression tree
+// ---------------------------------------------------------------------------------------------
+struct ProgramBuilder {
+    const std::vector<rs_node>& nodes;
+    std::vector<XformPre>& xf;  // per-TfFacade pre-multiplied stacks, composed world -> leaf chains are appended
+    std::vector<ObjInstr> prog;
+    std::vector<int2> cprog;
+    std::vector<CsgInfo> csg;
+    int max_stack = 0;
+    bool nested_medium = false;
+
+    // (parent chain `outer`, TfFacade `inner` below it): inv = inner.inv o outer.inv, fwd = outer.fwd o inner.fwd
+    int compose(int outer, int inner) {
+        if (outer < 0) return inner;
+        XformPre r;
+        auto mul = [](const double* a, const double* b, double* out) {  // out = a o b (apply b first)
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 4; ++j) {
+                    long double acc = j == 3 ? (long double)a[4 * i + 3] : 0.0L;
+                    for (int k = 0; k < 3; ++k) acc += (long double)a[4 * i + k] * (long double)b[4 * k + j];
+                    out[4 * i + j] = (double)acc;
+                }
+        };
+        mul(xf[inner].inv, xf[outer].inv, r.inv);
+        mul(xf[outer].fwd, xf[inner].fwd, r.fwd);
+        xf.push_back(r);
+        return (int)xf.size() - 1;
+    }
+    static bool primitive(int type) {
+        return type == RS_NODE_SPHERE || type == RS_NODE_BOX || type == RS_NODE_RECT || type == RS_NODE_QUADRIC || type == RS_NODE_RAYMARCHER;
+    }
+    void cemit(int ni, int cur) {  // `Hittable::contains`
+        const rs_node& n = nodes[ni];
+        if (n.type == RS_NODE_TRANSFORM) { cemit(n.child0, compose(cur, n.first_xform)); return; }
+        if (n.type == RS_NODE_DIFFERENCE || n.type == RS_NODE_INTERSECTION) {
+            cemit(n.child0, cur);
+            cemit(n.child1, cur);
+            cprog.push_back(make_int2((int)(((uint32_t)(n.type == RS_NODE_INTERSECTION ? RS_C_AND : RS_C_ANDNOT)) << 28), -1));
+            return;
+        }
+        if (primitive(n.type) && n.type != RS_NODE_RECT) cprog.push_back(make_int2(ni | (RS_C_LEAF << 28), cur));
+        else cprog.push_back(make_int2((int)((uint32_t)RS_C_FALSE << 28), -1));  // rect, medium (hit.rs default / unimplemented)
+    }
+    // returns the operand stack depth the subtree needs
+    int emit(int ni, int cur, bool in_medium) {
+        const rs_node& n = nodes[ni];
+        switch (n.type) {
+            case RS_NODE_TRANSFORM: return emit(n.child0, compose(cur, n.first_xform), in_medium);
+            case RS_NODE_DIFFERENCE:
+            case RS_NODE_INTERSECTION: {
+                const int d0 = emit(n.child0, cur, in_medium);
+                const size_t jm = prog.size();
+                prog.push_back(ObjInstr{OP_JMISS, ni, -1, 0});
+                const int d1 = emit(n.child1, cur, in_medium);
+                CsgInfo ci;
+                ci.c0_off = (int)cprog.size();
+                cemit(n.child0, cur);
+                ci.c0_len = (int)cprog.size() - ci.c0_off;
+                ci.c1_off = (int)cprog.size();
+                cemit(n.child1, cur);
+                ci.c1_len = (int)cprog.size() - ci.c1_off;
+                csg.push_back(ci);
+                prog.push_back(ObjInstr{n.type == RS_NODE_DIFFERENCE ? OP_DIFF : OP_INTER, ni, cur, (int)csg.size() - 1});
+                prog[jm].aux = (int)(prog.size() - 1 - jm);  // pc += aux, then ++pc: the instruction after the combiner
+                return std::max(d0, 1 + d1);
+            }
+            case RS_NODE_MEDIUM: {
+                if (in_medium) nested_medium = true;
+                prog.push_back(ObjInstr{OP_MED_BEGIN, ni, cur, 0});
+                const int d0 = emit(n.child0, cur, true);
+                const size_t mid = prog.size();
+                prog.push_back(ObjInstr{OP_MED_MID, ni, cur, 0});
+                emit(n.child0, cur, true);
+                prog.push_back(ObjInstr{OP_MED_END, ni, cur, 0});
+                prog[mid].aux = (int)(prog.size() - 1 - mid);
+                return d0;
+            }
+            default:
+                prog.push_back(ObjInstr{OP_LEAF, ni, cur, 0});
+                return 1;
+        }
+    }
+};
+
 int ensure_wave_set(rs_ctx* ctx, int k, uint32_t cap) {
     rs_ctx::WaveSet& w = ctx->wset[k];
     WaveState& ws = k == 0 ? ctx->ws : ctx->ws_aux[k - 1];
@@ -425,10 +511,12 @@ int ensure_wave_set(rs_ctx* ctx, int k, uint32_t cap) {
         ws.buf[b].time = w.d_time[b].as<double>();
     }
     CK(w.d_hit.ensure((size_t)cap * sizeof(HitA)));
+    CK(w.d_hit_src.ensure((size_t)cap * sizeof(int2)));
     CK(w.d_cq.ensure((size_t)cap * RS_NUM_CLASSES * sizeof(uint2)));
     CK(w.d_contrib.ensure((size_t)cap * sizeof(float4)));
     CK(w.d_ctr.ensure(sizeof(WaveCounters)));
     ws.hit = w.d_hit.as<HitA>();
+    ws.hit_src = w.d_hit_src.as<int2>();
     ws.class_queue = w.d_cq.as<uint2>();
     ws.contrib = w.d_contrib.as<float4>();
     ws.ctr = w.d_ctr.as<WaveCounters>();
@@ -887,6 +975,18 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid = std::min(ctx->shade_grid, ctx->sm_count * v); }
     if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_LAMBERT_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid_lambert = std::min(ctx->shade_grid_lambert, ctx->sm_count * v); }
 
+    // object programs of the expression-tree roots
+    ProgramBuilder pb{nodes, xf};
+    std::vector<int2> root_prog(std::max(s->n_roots, 1), make_int2(0, 0));
+    for (int i = 0; i < s->n_roots; ++i) {
+        if (root_kind[i] != ROOT_GENERIC) continue;
+        const int first = (int)pb.prog.size();
+        const int depth = pb.emit(s->roots[i], -1, false);
+        if (depth > RS_EVAL_STACK) return fail(ctx, RS_ERR_UNSUPPORTED, "object tree needs more than RS_EVAL_STACK operands");
+        root_prog[i] = make_int2(first, (int)pb.prog.size() - first);
+    }
+    if (pb.nested_medium) return fail(ctx, RS_ERR_UNSUPPORTED, "a ConstantMedium inside the boundary of another ConstantMedium is not supported");
+
     // triangles: p0, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56)
     std::vector<double> tri_geom((size_t)s->n_tris * 9);
     for (int i = 0; i < s->n_tris; ++i) {
@@ -901,6 +1001,10 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     int rc;
     if ((rc = upload(ctx, ctx->d_nodes, nodes.data(), nodes.size())) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_xf, xf.data(), xf.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_prog, pb.prog.data(), pb.prog.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_cprog, pb.cprog.data(), pb.cprog.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_csg, pb.csg.data(), pb.csg.size())) != RS_OK) return rc;
+    if ((rc = upload(ctx, ctx->d_root_prog, root_prog.data(), root_prog.size())) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_root_node, s->roots, (size_t)s->n_roots)) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_root_kind, root_kind.data(), root_kind.size())) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_root_sphere, root_sphere.data(), root_sphere.size())) != RS_OK) return rc;
@@ -992,6 +1096,10 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     S.root_sphere = ctx->d_root_sphere.as<double4>();
     S.root_bbox = ctx->d_root_bbox.as<double>();
     S.root_gate = ctx->d_root_gate.as<unsigned char>();
+    S.obj.prog = ctx->d_prog.as<ObjInstr>();
+    S.obj.cprog = ctx->d_cprog.as<int2>();
+    S.obj.csg = ctx->d_csg.as<CsgInfo>();
+    S.obj.root_prog = ctx->d_root_prog.as<int2>();
     S.tri_geom = ctx->d_tri_geom.as<double>();
     S.tri_normals = ctx->d_tri_normals.as<double>();
     S.tri_material = ctx->d_tri_material.as<int>();

@@ -238,6 +238,7 @@ struct Closest {
     double t;        // current limit end / best t
     int root;
     int material;
+    int src, flavor;  // ROOT_GENERIC: what the record is rebuilt from (object_record)
 };
 
 // smallest double above x (x > 0); +inf stays +inf
@@ -307,12 +308,15 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
             const double inf = __longlong_as_double(0x7ff0000000000000LL);
             if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
         }
-        HitRec h;
+        const int2 pr = __ldg(&S.obj.root_prog[root]);
+        ObjHit h;
         const double hi = __longlong_as_double(0x7ff0000000000000LL);  // see ROOT_FLAT
-        if (TreeTop::hit<false>(S, __ldg(&S.root_node[root]), ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || (h.t1 == best.t && root < best.root))) {
+        if (eval_object(S.nodes, S.xf, S.obj, pr.x, pr.y, ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || (h.t1 == best.t && root < best.root))) {
             best.t = h.t1;
             best.root = root;
-            best.material = h.material;
+            best.material = h.mat;
+            best.src = h.src;
+            best.flavor = h.flavor;
         }
     }
 }
@@ -649,6 +653,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
                                                    __uint_as_float(q3.z) * (float)((double)c.z * mul), 0.f);
                     cls = -1;
                 } else {
+                    if (MODE >= 3 && S.root_kind[best.root] == ROOT_GENERIC) ws.hit_src[i] = make_int2(best.src, best.flavor);
                     ws.hit[i] = h;
                 }
             } else if (miss_in_extend) {
@@ -728,7 +733,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
 // GENERIC = false: the scene holds only static spheres and triangles and its lights are plain
 // spheres/rects, so no expression-tree code is compiled into the kernel.
 template <bool GENERIC, bool TREES>
-__device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, const RngCtx& rng, const HitA& ha, bool want_uv, HitRec& h) {
+__device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, const HitA& ha, int2 src, bool want_uv, HitRec& h) {
     // world objects are evaluated over [tmin, +inf) (see test_root): the same call returns the same record here
     const double end_then = __longlong_as_double(0x7ff0000000000000LL);
     // static spheres: centre and 1/r straight from the per-root tables (one level of loads
@@ -764,20 +769,9 @@ __device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, con
             else ok = n->type == RS_NODE_BOX ? hit_box(*n, r, RS_TMIN, end_then, h)
                                              : hit_rect(n->rect_axis, n->p[0], n->p[1], n->p[2], n->p[3], n->p[4], n->material, r, RS_TMIN, end_then, h);
             if (ok && x) h.point = xf_apply(x->fwd, h.point, 1.0);
-        } else if (S.nodes[rn].type == RS_NODE_RAYMARCHER) {
-            // a bare RayMarcher root: the record follows from the distance extend found (the same
-            // t1 the full search would return), without marching the ray a second time
-            h.point = ray_at(ray, ha.t);
-            V3 nn = marcher_normal(h.point);
-            h.outside = dot(ray.d, nn) < 0.0;
-            h.normal = h.outside ? nn : -nn;
-            h.material = S.nodes[rn].material;
-            h.t1 = ha.t; h.t2 = ha.t;
-            h.u = 0.0; h.v = 0.0;
-            if (want_uv) sphere_uv(v3(0.0, 0.0, 0.0), h.point, h.u, h.v);
-            ok = true;
         } else {
-            ok = TreeTop::hit(S, rn, ray, RS_TMIN, end_then, rng, h);
+            object_record(S.nodes, S.xf, S.obj.prog, src.x, src.y, ha.t, ray, want_uv, h);
+            ok = true;
         }
         if (!ok) {
             h.point = ray_at(ray, ha.t);
@@ -1098,7 +1092,9 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
                 const int mat_type = SET == 1 ? (int)RS_MAT_LAMBERTIAN : RS_MATHOT_TYPE(mat);
                 const bool want_uv = RS_MATHOT_NEEDS_UV(mat);
                 HitRec h;
-                rebuild_hit<GENERIC, TREES>(S, p.ray, rng, ha, want_uv, h);
+                int2 src = make_int2(0, 0);
+                if constexpr (TREES) { if (S.root_kind[ha.root] == ROOT_GENERIC) src = ws.hit_src[i]; }
+                rebuild_hit<GENERIC, TREES>(S, p.ray, ha, src, want_uv, h);
 
                 const float4 col = material_color(S, mat, h.u, h.v, h.point);
 
@@ -1196,7 +1192,7 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
                         const uint32_t light_k = S.n_lights == 1 ? 0u : w.y % (uint32_t)S.n_lights;  // list.rs:49-52
                         V3 to_light;
                         if (TREES) {
-                            to_light = TreeTop::random(S, S.lights[light_k], h.point, rng);
+                            to_light = light_random(S.nodes, S.xf, S.lights[light_k], h.point, rng);
                         } else {
                             const rs_node& ln = S.light_nodes[light_k];
                             to_light = ln.type == RS_NODE_SPHERE ? sphere_random(ln, h.point, rng) : rect_random(ln, h.point, rng);
@@ -1313,7 +1309,8 @@ __global__ void __launch_bounds__(RS_BLOCK) probe_primary_kernel(const __grid_co
         RngCtx rng;
         rng.key = fp.key; rng.pixel = p.pixel; rng.sample = p.sample; rng.depth = 1;
         HitRec h;
-        rebuild_hit<true, true>(S, p.ray, rng, ha, true, h);
+        const int2 src = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_src[i] : make_int2(0, 0);
+        rebuild_hit<true, true>(S, p.ray, ha, src, true, h);
         if (dbg.t) dbg.t[px] = h.t1;
         dbg_store3(dbg.normal3, px, h.normal);
         dbg_store3(dbg.point3, px, h.point);

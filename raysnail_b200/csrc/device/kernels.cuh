@@ -62,6 +62,7 @@ struct DeviceStats {
 struct WaveState {
     PathBuf buf[2];
     HitA* hit;
+    int2* hit_src;          // ROOT_GENERIC hits: (source instruction, flavor) the record is rebuilt from (object_record)
     uint2* class_queue;     // RS_NUM_CLASSES * capacity entries of (path index, output slot reserved by extend or ~0)
     float4* contrib;        // per slot: radiance of the finished path
     WaveCounters* ctr;

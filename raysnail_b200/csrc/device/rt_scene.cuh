@@ -2,10 +2,9 @@
 // every Hittable of the reference, textures and material helpers.  Used by the extend, shade
 // and probe kernels (kernels.cu).
 //
-// Object expression trees (CSG, TfFacade, ConstantMedium) are evaluated by depth-templated,
-// non-inlined functions (eval<D> calls eval<D-1>): a static call graph instead of device
-// recursion, so ptxas can size the stack.  RS_MAX_TREE_DEPTH bounds the nesting; the host
-// rejects deeper scenes at upload.
+// Object expression trees (CSG, TfFacade, ConstantMedium) are flattened at upload into post-order
+// programs that one loop evaluates (see "Object programs" below).  RS_MAX_TREE_DEPTH bounds the
+// nesting (operand stack); the host rejects deeper scenes at upload.
 #pragma once
 
 #include "../../../include/raysnail_b200.h"
@@ -71,6 +70,20 @@ struct __align__(16) MatHot {
     int pad;
 };
 
+// object programs (see "Object programs" below)
+struct __align__(16) ObjInstr {
+    int op, node, xf, aux;
+};
+struct __align__(16) CsgInfo {
+    int c0_off, c0_len, c1_off, c1_len;  // `contains` programs of child0 / child1 in the space of the CSG node
+};
+struct ObjPrograms {
+    const ObjInstr* prog;
+    const int2* cprog;
+    const CsgInfo* csg;
+    const int2* root_prog;  // per root: (first instruction, count); count 0 = not a ROOT_GENERIC object
+};
+
 struct DScene {
     const rs_node* nodes;
     const XformPre* xf;          // indexed by rs_node.first_xform (rewritten at upload)
@@ -88,6 +101,7 @@ struct DScene {
     const rs_node* light_nodes;  // copy of nodes[lights[k]]: the lean shade kernel samples plain sphere / rect lights
     const double* root_bbox;     // 6 per root (reference bbox, for the gate)
     const unsigned char* root_gate;
+    ObjPrograms obj;             // programs of the ROOT_GENERIC objects (expression trees)
     const double* tri_geom;      // 9 per triangle: p0.xyz, (a,b,c) = p0-p1, (d,e,f) = p0-p2
     const double* tri_normals;   // 9 per triangle
     const int* tri_material;
@@ -616,155 +630,364 @@ __device__ __forceinline__ V3 xf_apply(const double* m, V3 p, double w) {
               m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11] * w);
 }
 
-template <int D>
-struct Tree {
-    // `Hittable::contains`
-    static __device__ __noinline__ bool contains(const DScene& S, int ni, V3 p) {
-        const rs_node& n = S.nodes[ni];
-        switch (n.type) {
-            case RS_NODE_SPHERE: {  // sphere.rs:111-115
-                V3 r = v3(n.p[0], n.p[1], n.p[2]) - p;
-                return length_squared(r) < n.p[3] * n.p[3];
-            }
-            case RS_NODE_BOX:  // box.rs:152-157
-                return p.x >= n.p[0] && p.x <= n.p[3] && p.y >= n.p[1] && p.y <= n.p[4] && p.z >= n.p[2] && p.z <= n.p[5];
-            case RS_NODE_QUADRIC: {  // quadric.rs:184-189
-                const double* q = n.p;
-                return (p.x * (q[0] * p.x + q[1] * p.y + q[3]) + p.y * (q[4] * p.y + q[5] * p.z + q[6]) + p.z * (q[7] * p.z + q[2] * p.x + q[8]) + q[9]) <= 0.0;
-            }
-            case RS_NODE_DIFFERENCE: return Tree<D - 1>::contains(S, n.child0, p) && !Tree<D - 1>::contains(S, n.child1, p);
-            case RS_NODE_INTERSECTION: return Tree<D - 1>::contains(S, n.child0, p) && Tree<D - 1>::contains(S, n.child1, p);
-            case RS_NODE_TRANSFORM: return Tree<D - 1>::contains(S, n.child0, xf_apply(S.xf[n.first_xform].inv, p, 1.0));
-            case RS_NODE_RAYMARCHER: return marcher_inside(p, (int)n.p[0]);  // raymarching.rs:167-170
-            default: return false;  // rect, medium
+// ---------------------------------------------------------------------------------------------
+// Object programs: a world object that is an expression tree (CSG, TfFacade, ConstantMedium, any nesting)
+// is flattened at upload into a post-order program, evaluated by ONE loop with a small operand stack —
+// no recursion, no per-depth copies of the code.  What makes this possible:
+//   * a TfFacade keeps the ray parameter (tf_facade.rs:41-56: the child is hit with the transformed ray,
+//     only the hit POINT is mapped back), so the transforms above a primitive compose into one 3x4
+//     world -> leaf matrix per LEAF instruction, and a hit is fully described by (t1, t2, material, source);
+//   * the points CSG rules ask `contains` about are ray points: p = ray.at(t) (difference.rs:68-75,
+//     intersection.rs:66-83), evaluated through the composed world -> leaf matrices as well.
+// The record of the winning hit is rebuilt by shade from (source instruction, flavor, t1): see object_record.
+// ---------------------------------------------------------------------------------------------
+enum ObjOp : int {
+    OP_LEAF = 0,       // node = primitive, xf = composed world -> leaf transform (-1: none): push its hit under the current limits
+    OP_JMISS = 1,      // if the top of the stack is a miss, skip `aux` instructions (second operand + combiner: a miss stays a miss)
+    OP_DIFF = 2,       // node = Difference, aux = its CsgInfo: pop minus, pop plus, push the result (difference.rs:57-107)
+    OP_INTER = 3,      // node = Intersection (intersection.rs:58-96)
+    OP_MED_BEGIN = 4,  // ConstantMedium (constant.rs:42-80): the boundary is hit over (-inf, +inf) ...
+    OP_MED_MID = 5,    // ... then again from t1 + 0.0001 (the boundary's program follows twice); aux = skip when the first search misses
+    OP_MED_END = 6,    // node = the medium, xf = its space: free-flight sample, push the result
+};
+enum ObjFlavor : int {
+    FLAVOR_LEAF = 0,       // HitRecord::new of the primitive at `src` (hit.rs:32-53)
+    FLAVOR_SYNTHETIC = 1,  // Difference's inner surface: normal = -minus.normal(p), outside = true (difference.rs:86-103); src = the OP_DIFF
+    FLAVOR_MEDIUM = 2,     // ConstantMedium: normal (1,0,0), outside = false (constant.rs:72-79); src = the OP_MED_END
+};
+// `contains` programs (boolean post-order): x = node | op << 28, y = xf
+#define RS_C_LEAF 0
+#define RS_C_AND 1      // Intersection::contains
+#define RS_C_ANDNOT 2   // Difference::contains: plus && !minus
+#define RS_C_FALSE 3    // rect, medium
+#define RS_EVAL_STACK 9  // operands: a tree of depth RS_MAX_TREE_DEPTH needs at most depth + 1
+
+struct ObjHit {
+    double t1, t2;
+    int mat;   // -1 = None
+    int src;   // index of the instruction the record is rebuilt from
+    int flavor;
+    bool hit;
+};
+
+__device__ __forceinline__ Ray xf_ray(const double* inv, const Ray& ray) {
+    Ray r;
+    r.o = xf_apply(inv, ray.o, 1.0);
+    r.d = xf_apply(inv, ray.d, 0.0);
+    r.time = ray.time;
+    return r;
+}
+
+// box.rs:125-150, distances only: t1 = the nearer of the first two faces hit (order back, front, left, right, down,
+// up), t2 = the other one or f64::MAX
+__device__ __forceinline__ bool box_t2(const double* p, const Ray& ray, double lo, double hi, double& t1, double& t2) {
+    const double mnx = p[0], mny = p[1], mnz = p[2], mxx = p[3], mxy = p[4], mxz = p[5];
+    double first = 0.0, second = 0.0, cur;
+    int count = 0;
+#define RS_BOX_FACE_T(kind, k, a0, a1, b0, b1)                                  \
+    if (count < 2 && rect_t(kind, k, a0, a1, b0, b1, ray, lo, hi, cur)) {       \
+        if (count == 0) first = cur; else second = cur;                         \
+        ++count;                                                                \
+    }
+    RS_BOX_FACE_T(RS_RECT_XY, mnz, mnx, mxx, mny, mxy)
+    RS_BOX_FACE_T(RS_RECT_XY, mxz, mnx, mxx, mny, mxy)
+    RS_BOX_FACE_T(RS_RECT_YZ, mnx, mny, mxy, mnz, mxz)
+    RS_BOX_FACE_T(RS_RECT_YZ, mxx, mny, mxy, mnz, mxz)
+    RS_BOX_FACE_T(RS_RECT_XZ, mny, mnx, mxx, mnz, mxz)
+    RS_BOX_FACE_T(RS_RECT_XZ, mxy, mnx, mxx, mnz, mxz)
+#undef RS_BOX_FACE_T
+    if (count == 0) return false;
+    const bool take_first = count == 1 || first < second;
+    t1 = take_first ? first : second;
+    t2 = count == 2 ? (take_first ? second : first) : RS_F64_MAX;
+    return true;
+}
+
+// quadric.rs:112-182, distances only
+__device__ __forceinline__ bool quadric_t2(const double* q, const Ray& ray, double lo, double hi, double& t1, double& t2) {
+    const double qa = q[0], qb = q[1], qc = q[2], qd = q[3], qe = q[4], qf = q[5], qg = q[6], qh = q[7], qi = q[8], qj = q[9];
+    const double xo = ray.o.x, yo = ray.o.y, zo = ray.o.z, xd = ray.d.x, yd = ray.d.y, zd = ray.d.z;
+    double a = xd * (qa * xd + qb * yd + qc * zd) + yd * (qe * yd + qf * zd) + zd * qh * zd;
+    double b = xd * (qa * xo + 0.5 * (qb * yo + qc * zo + qd)) + yd * (qe * yo + 0.5 * (qb * xo + qf * zo + qg)) +
+               zd * (qh * zo + 0.5 * (qc * xo + qf * yo + qi));
+    double c = xo * (qa * xo + qb * yo + qc * zo + qd) + yo * (qe * yo + qf * zo + qg) + zo * (qh * zo + qi) + qj;
+    if (a == 0.0) {
+        if (b == 0.0) return false;
+        t1 = -0.5 * c / b;
+        t2 = RS_F64_MAX;
+        return in_range(t1, lo, hi);
+    }
+    double d = b * b - a * c;
+    if (d <= 0.0) return false;
+    double dr = sqrt(d);
+    double ta = (-b - dr) / a, tb = (-b + dr) / a;
+    if (in_range(ta, lo, hi)) { t1 = ta; t2 = tb; return true; }
+    if (in_range(tb, lo, hi)) { t1 = tb; t2 = RS_F64_MAX; return true; }
+    return false;
+}
+
+// `Hittable::hit` of a primitive, distances only
+static __device__ __noinline__ bool leaf_hit(const rs_node& n, const Ray& ray, double lo, double hi, double& t1, double& t2) {
+    switch (n.type) {
+        case RS_NODE_SPHERE: {
+            V3 c = v3(n.p[0], n.p[1], n.p[2]);
+            if (n.p[4] != 0.0 || n.p[5] != 0.0 || n.p[6] != 0.0) c = c + v3(n.p[4], n.p[5], n.p[6]) * ray.time;  // center_at
+            return sphere_roots(c, n.p[3] * n.p[3], ray, lo, hi, t1, t2);
+        }
+        case RS_NODE_BOX: return box_t2(n.p, ray, lo, hi, t1, t2);
+        case RS_NODE_RECT: t2 = RS_F64_MAX; return rect_t(n.rect_axis, n.p[0], n.p[1], n.p[2], n.p[3], n.p[4], ray, lo, hi, t1);
+        case RS_NODE_QUADRIC: return quadric_t2(n.p, ray, lo, hi, t1, t2);
+        case RS_NODE_RAYMARCHER: {
+            HitRec h;
+            if (!hit_marcher<false>(n, ray, lo, hi, h)) return false;
+            t1 = h.t1; t2 = h.t2;
+            return true;
+        }
+        default: return false;
+    }
+}
+
+// `Hittable::contains` of a primitive
+__device__ __forceinline__ bool leaf_contains(const rs_node& n, V3 p) {
+    switch (n.type) {
+        case RS_NODE_SPHERE: {  // sphere.rs:111-115
+            V3 r = v3(n.p[0], n.p[1], n.p[2]) - p;
+            return length_squared(r) < n.p[3] * n.p[3];
+        }
+        case RS_NODE_BOX:  // box.rs:152-157
+            return p.x >= n.p[0] && p.x <= n.p[3] && p.y >= n.p[1] && p.y <= n.p[4] && p.z >= n.p[2] && p.z <= n.p[5];
+        case RS_NODE_QUADRIC: {  // quadric.rs:184-189
+            const double* q = n.p;
+            return (p.x * (q[0] * p.x + q[1] * p.y + q[3]) + p.y * (q[4] * p.y + q[5] * p.z + q[6]) + p.z * (q[7] * p.z + q[2] * p.x + q[8]) + q[9]) <= 0.0;
+        }
+        case RS_NODE_RAYMARCHER: return marcher_inside(p, (int)n.p[0]);  // raymarching.rs:167-170
+        default: return false;  // rect
+    }
+}
+
+// `contains` of a subtree for the world-space point p
+__device__ __forceinline__ bool contains_prog(const rs_node* nodes, const XformPre* xf, const int2* cprog, int off, int len, V3 p) {
+    uint32_t bits = 0;  // boolean stack, top = bit 0
+    for (int k = off; k < off + len; ++k) {
+        const int2 c = __ldg(cprog + k);
+        const int op = (int)((uint32_t)c.x >> 28);
+        if (op == RS_C_LEAF) {
+            const V3 q = c.y >= 0 ? xf_apply(xf[c.y].inv, p, 1.0) : p;
+            bits = (bits << 1) | (leaf_contains(nodes[c.x & 0x0fffffff], q) ? 1u : 0u);
+        } else if (op == RS_C_FALSE) {
+            bits <<= 1;
+        } else {
+            const uint32_t b = bits & 1u, a = (bits >> 1) & 1u;
+            bits = ((bits >> 2) << 1) | (op == RS_C_AND ? (a & b) : (a & (b ^ 1u)));
         }
     }
+    return bits & 1u;
+}
 
-    // `Hittable::hit`
-    template <bool FULL = true>
-    static __device__ __noinline__ bool hit(const DScene& S, int ni, const Ray& ray, double lo, double hi, const RngCtx& rng, HitRec& h) {
-        const rs_node& n = S.nodes[ni];
-        switch (n.type) {
-            case RS_NODE_SPHERE: return hit_sphere_node<FULL>(n, ray, lo, hi, h);
-            case RS_NODE_BOX: return hit_box<FULL>(n, ray, lo, hi, h);
-            case RS_NODE_RECT: return hit_rect<FULL>(n.rect_axis, n.p[0], n.p[1], n.p[2], n.p[3], n.p[4], n.material, ray, lo, hi, h);
-            case RS_NODE_QUADRIC: return hit_quadric<FULL>(n, ray, lo, hi, h);
-            case RS_NODE_RAYMARCHER: return hit_marcher<FULL>(n, ray, lo, hi, h);
-            case RS_NODE_DIFFERENCE: {  // difference.rs:57-107
-                HitRec hp, hm;
-                bool has_p = Tree<D - 1>::template hit<FULL>(S, n.child0, ray, lo, hi, rng, hp);
-                if (!has_p) return false;
-                bool has_m = Tree<D - 1>::template hit<FULL>(S, n.child1, ray, lo, hi, rng, hm);
-                if (!has_m) { h = hp; return true; }
-                if (hp.t1 < hm.t1) {
-                    if (!Tree<D - 1>::contains(S, n.child1, hp.point)) {
-                        h = hp;
-                        if (h.material < 0) h.material = n.material;
-                        return true;
+// `Hittable::hit` of a world object through its program.  Limits [lo, hi) as for any hit call.
+static __device__ __noinline__ bool eval_object(const rs_node* nodes, const XformPre* xf, const ObjPrograms P, int first, int count, const Ray& ray,
+                                                double lo, double hi, const RngCtx& rng, ObjHit& out) {
+    ObjHit stack[RS_EVAL_STACK];
+    int sp = 0;
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    double lo0 = lo, hi0 = hi, med_t1 = 0.0;
+    for (int pc = first; pc < first + count; ++pc) {
+        const int4 raw = __ldg(reinterpret_cast<const int4*>(P.prog + pc));
+        const int op = raw.x, ni = raw.y, xi = raw.z, aux = raw.w;
+        if (op == OP_LEAF) {
+            const rs_node& n = nodes[ni];
+            const Ray r = xi >= 0 ? xf_ray(xf[xi].inv, ray) : ray;
+            ObjHit e;
+            e.hit = leaf_hit(n, r, lo, hi, e.t1, e.t2);
+            e.mat = n.material;
+            e.src = pc;
+            e.flavor = FLAVOR_LEAF;
+            stack[sp++] = e;
+        } else if (op == OP_JMISS) {
+            if (!stack[sp - 1].hit) pc += aux;
+        } else if (op == OP_DIFF) {  // difference.rs:57-107
+            const ObjHit hm = stack[--sp];
+            const ObjHit hp = stack[sp - 1];
+            const rs_node& n = nodes[ni];
+            ObjHit res = hp;
+            if (!hp.hit) {
+                res.hit = false;
+            } else if (!hm.hit) {
+                // only the plus object is hit: its record as it is
+            } else if (hp.t1 < hm.t1) {
+                const CsgInfo ci = P.csg[aux];
+                if (contains_prog(nodes, xf, P.cprog, ci.c1_off, ci.c1_len, ray_at(ray, hp.t1))) res.hit = false;
+                else if (res.mat < 0) res.mat = n.material;
+            } else if (hm.t2 < hp.t1) {
+                if (res.mat < 0) res.mat = n.material;
+            } else if (hm.t2 < hp.t2) {
+                // the ray leaves the minus object inside the plus object: the cavity's surface
+                const rs_node& m = nodes[n.child1];
+                const bool primitive = m.type == RS_NODE_SPHERE || m.type == RS_NODE_BOX || m.type == RS_NODE_RECT || m.type == RS_NODE_QUADRIC ||
+                                       m.type == RS_NODE_RAYMARCHER;  // only these implement normal() / material() (hit.rs:82-93)
+                res.t1 = hm.t2;
+                res.t2 = hp.t2;
+                res.mat = (primitive && m.material >= 0) ? m.material : n.material;
+                res.src = pc;
+                res.flavor = FLAVOR_SYNTHETIC;
+            } else {
+                res.hit = false;
+            }
+            stack[sp - 1] = res;
+        } else if (op == OP_INTER) {  // intersection.rs:58-96
+            const ObjHit h2 = stack[--sp];
+            const ObjHit h1 = stack[sp - 1];
+            const rs_node& n = nodes[ni];
+            ObjHit res = h1;
+            if (!h1.hit || !h2.hit) {
+                res.hit = false;
+            } else {
+                const CsgInfo ci = P.csg[aux];
+                const bool first_is_1 = h1.t1 < h2.t1;
+                const ObjHit& near = first_is_1 ? h1 : h2;
+                const ObjHit& far = first_is_1 ? h2 : h1;
+                // contains(the other object, the hit point), nearest hit first
+                const int far_off = first_is_1 ? ci.c1_off : ci.c0_off, far_len = first_is_1 ? ci.c1_len : ci.c0_len;
+                const int near_off = first_is_1 ? ci.c0_off : ci.c1_off, near_len = first_is_1 ? ci.c0_len : ci.c1_len;
+                if (contains_prog(nodes, xf, P.cprog, far_off, far_len, ray_at(ray, near.t1))) res = near;
+                else if (contains_prog(nodes, xf, P.cprog, near_off, near_len, ray_at(ray, far.t1))) res = far;
+                else res.hit = false;
+                if (res.hit && res.mat < 0) res.mat = n.material;
+            }
+            stack[sp - 1] = res;
+        } else if (op == OP_MED_BEGIN) {  // constant.rs:45
+            lo0 = lo; hi0 = hi;
+            lo = -inf; hi = inf;
+        } else if (op == OP_MED_MID) {  // constant.rs:46-49
+            const ObjHit r1 = stack[sp - 1];
+            if (!r1.hit) {
+                lo = lo0; hi = hi0;
+                pc += aux;  // past the OP_MED_END: the miss stays as the result
+            } else {
+                --sp;
+                med_t1 = r1.t1;
+                lo = r1.t1 + 0.0001; hi = inf;
+            }
+        } else {  // OP_MED_END: constant.rs:50-79
+            const ObjHit r2 = stack[--sp];
+            const rs_node& n = nodes[ni];
+            lo = lo0; hi = hi0;
+            ObjHit res;
+            res.hit = false;
+            res.t1 = 0.0; res.t2 = 0.0; res.mat = n.material; res.src = pc; res.flavor = FLAVOR_MEDIUM;
+            if (r2.hit) {
+                double a = med_t1, b = r2.t1;
+                if (a < lo) a = lo;
+                if (b > hi) b = hi;
+                if (a < b) {
+                    if (a < 0.0) a = 0.0;
+                    const Ray r = xi >= 0 ? xf_ray(xf[xi].inv, ray) : ray;
+                    const double length_per_unit = length(r.d);
+                    const double distance_inside = (b - a) * length_per_unit;
+                    const uint4 w = rng_words(rng, P_MEDIUM, (uint32_t)ni);
+                    const double hit_distance = (-1.0 / n.p[0]) * log(u01(w.x));
+                    if (!(hit_distance > distance_inside)) {
+                        res.hit = true;
+                        res.t1 = a + hit_distance / length_per_unit;
+                        res.t2 = res.t1;
                     }
-                    return false;
                 }
-                if (hm.t2 < hp.t1) {
-                    h = hp;
-                    if (h.material < 0) h.material = n.material;
-                    return true;
-                }
-                if (hm.t2 < hp.t2) {
-                    const rs_node& m = S.nodes[n.child1];
-                    V3 p = ray_at(ray, hm.t2);
-                    // minus.normal(p) / minus.material(): only primitives implement them
-                    V3 nn = v3(0.0, 0.0, 0.0);
-                    int mm = -1;
-                    if (m.type == RS_NODE_SPHERE) { if (FULL) nn = vdiv(p - v3(m.p[0], m.p[1], m.p[2]), m.p[3]); mm = m.material; }
-                    else if (m.type == RS_NODE_BOX) { nn = v3(0.0, 1.0, 0.0); mm = m.material; }
-                    else if (m.type == RS_NODE_RECT) { int a, b, c; rect_axes(m.rect_axis, a, b, c); set_comp(nn, c, 1.0); mm = m.material; }
-                    else if (m.type == RS_NODE_QUADRIC) { if (FULL) nn = quadric_normal(m.p, p); mm = m.material; }
-                    else if (m.type == RS_NODE_RAYMARCHER) { if (FULL) nn = marcher_normal(p); mm = m.material; }
-                    h.point = p;
-                    h.normal = -nn;
-                    h.material = mm >= 0 ? mm : n.material;
-                    h.u = 0.0; h.v = 0.0;
-                    h.t1 = hm.t2; h.t2 = hp.t2;
-                    h.outside = true;
-                    return true;
-                }
-                return false;
             }
-            case RS_NODE_INTERSECTION: {  // intersection.rs:58-96
-                HitRec h1, h2;
-                if (!Tree<D - 1>::template hit<FULL>(S, n.child0, ray, lo, hi, rng, h1)) return false;
-                if (!Tree<D - 1>::template hit<FULL>(S, n.child1, ray, lo, hi, rng, h2)) return false;
-                bool first_is_1 = h1.t1 < h2.t1;
-                const HitRec& near = first_is_1 ? h1 : h2;
-                const HitRec& far = first_is_1 ? h2 : h1;
-                int obj_near = first_is_1 ? n.child0 : n.child1, obj_far = first_is_1 ? n.child1 : n.child0;
-                if (Tree<D - 1>::contains(S, obj_far, near.point)) h = near;
-                else if (Tree<D - 1>::contains(S, obj_near, far.point)) h = far;
-                else return false;
-                if (h.material < 0) h.material = n.material;
-                return true;
-            }
-            case RS_NODE_TRANSFORM: {  // tf_facade.rs:41-56: only the hit point goes back to world space
-                const XformPre& x = S.xf[n.first_xform];
-                Ray r;
-                r.o = xf_apply(x.inv, ray.o, 1.0);
-                r.d = xf_apply(x.inv, ray.d, 0.0);
-                r.time = ray.time;
-                if (!Tree<D - 1>::template hit<FULL>(S, n.child0, r, lo, hi, rng, h)) return false;
-                h.point = xf_apply(x.fwd, h.point, 1.0);
-                return true;
-            }
-            case RS_NODE_MEDIUM: {  // constant.rs:42-80
-                HitRec r1, r2;
-                const double inf = __longlong_as_double(0x7ff0000000000000LL);
-                if (!Tree<D - 1>::template hit<FULL>(S, n.child0, ray, -inf, inf, rng, r1)) return false;
-                if (!Tree<D - 1>::template hit<FULL>(S, n.child0, ray, r1.t1 + 0.0001, inf, rng, r2)) return false;
-                if (r1.t1 < lo) r1.t1 = lo;
-                if (r2.t1 > hi) r2.t1 = hi;
-                if (r1.t1 >= r2.t1) return false;
-                if (r1.t1 < 0.0) r1.t1 = 0.0;
-                double length_per_unit = length(ray.d);
-                double distance_inside = (r2.t1 - r1.t1) * length_per_unit;
-                uint4 w = rng_words(rng, P_MEDIUM, (uint32_t)ni);
-                double hit_distance = (-1.0 / n.p[0]) * log(u01(w.x));
-                if (hit_distance > distance_inside) return false;
-                double t = r1.t1 + hit_distance / length_per_unit;
-                h.point = ray_at(ray, t);
-                h.normal = v3(1.0, 0.0, 0.0);
-                h.material = n.material;
-                h.t1 = t; h.t2 = t; h.u = 0.0; h.v = 0.0;
-                h.outside = false;
-                return true;
-            }
-            default: return false;
+            stack[sp++] = res;
         }
     }
+    out = stack[0];
+    return sp > 0 && out.hit;
+}
 
-    // `Hittable::random` (light sampling)
-    static __device__ __noinline__ V3 random(const DScene& S, int ni, V3 origin, const RngCtx& rng) {
-        const rs_node& n = S.nodes[ni];
+// `Hittable::normal` of a primitive (hit.rs:82-87; only primitives implement it)
+__device__ __forceinline__ V3 leaf_normal(const rs_node& m, V3 p) {
+    V3 nn = v3(0.0, 0.0, 0.0);
+    if (m.type == RS_NODE_SPHERE) nn = vdiv(p - v3(m.p[0], m.p[1], m.p[2]), m.p[3]);
+    else if (m.type == RS_NODE_BOX) nn = v3(0.0, 1.0, 0.0);  // box.rs:107-109
+    else if (m.type == RS_NODE_RECT) { int a, b, c; rect_axes(m.rect_axis, a, b, c); set_comp(nn, c, 1.0); }
+    else if (m.type == RS_NODE_QUADRIC) nn = quadric_normal(m.p, p);
+    else if (m.type == RS_NODE_RAYMARCHER) nn = marcher_normal(p);
+    return nn;
+}
+
+// The full HitRecord of the hit (src, flavor, t1) that eval_object reported for this ray.
+static __device__ __noinline__ void object_record(const rs_node* nodes, const XformPre* xf, const ObjInstr* prog, int src, int flavor, double t1,
+                                                  const Ray& ray, bool want_uv, HitRec& h) {
+    const int4 raw = __ldg(reinterpret_cast<const int4*>(prog + src));
+    const rs_node& n = nodes[raw.y];
+    const XformPre* x = raw.z >= 0 ? xf + raw.z : nullptr;
+    const Ray r = x ? xf_ray(x->inv, ray) : ray;
+    h.t1 = t1; h.t2 = t1; h.u = 0.0; h.v = 0.0; h.material = n.material;
+    if (flavor == FLAVOR_LEAF) {
+        // the primitive, in its own space, over the root limits [tmin, +inf) it was searched with
+        const double inf = __longlong_as_double(0x7ff0000000000000LL);
+        bool ok;
+        switch (n.type) {
+            case RS_NODE_SPHERE: {
+                h.point = ray_at(r, t1);
+                V3 nn = (h.point - v3(n.p[0], n.p[1], n.p[2])) * n.p[7];  // static centre (sphere.rs:56-58); p[7] = 1 / r
+                h.outside = dot(r.d, nn) < 0.0;
+                h.normal = h.outside ? nn : -nn;
+                if (want_uv) sphere_uv(v3(n.p[0], n.p[1], n.p[2]), h.point, h.u, h.v);
+                ok = true;
+                break;
+            }
+            case RS_NODE_BOX: ok = hit_box<true>(n, r, 0.0001, inf, h); break;
+            case RS_NODE_RECT: ok = hit_rect<true>(n.rect_axis, n.p[0], n.p[1], n.p[2], n.p[3], n.p[4], n.material, r, 0.0001, inf, h); break;
+            case RS_NODE_QUADRIC: ok = hit_quadric<true>(n, r, 0.0001, inf, h); break;
+            default: {  // RayMarcher: the record follows from the distance, without marching again
+                h.point = ray_at(r, t1);
+                V3 nn = marcher_normal(h.point);
+                h.outside = dot(r.d, nn) < 0.0;
+                h.normal = h.outside ? nn : -nn;
+                if (want_uv) sphere_uv(v3(0.0, 0.0, 0.0), h.point, h.u, h.v);
+                ok = true;
+                break;
+            }
+        }
+        if (!ok || h.t1 != t1) {
+            // the primitive was searched under other limits (inside a ConstantMedium's boundary search never ends
+            // here; a CSG operand always uses the root limits): keep the distance, generic record
+            h.point = ray_at(r, t1);
+            V3 nn = leaf_normal(n, h.point);
+            h.outside = dot(r.d, nn) < 0.0;
+            h.normal = h.outside ? nn : -nn;
+            h.t1 = t1; h.t2 = t1;
+        }
+    } else if (flavor == FLAVOR_SYNTHETIC) {  // difference.rs:86-103; n = the Difference
+        const rs_node& m = nodes[n.child1];
+        h.point = ray_at(r, t1);
+        h.normal = -leaf_normal(m, h.point);
+        h.outside = true;
+    } else {  // FLAVOR_MEDIUM (constant.rs:72-79)
+        h.point = ray_at(r, t1);
+        h.normal = v3(1.0, 0.0, 0.0);
+        h.outside = false;
+    }
+    if (x) h.point = xf_apply(x->fwd, h.point, 1.0);  // tf_facade.rs:52-55: only the point goes back to world space
+}
+
+// `Hittable::random` of a light (HittableList::random picks it, list.rs:49-52)
+static __device__ __noinline__ V3 light_random(const rs_node* nodes, const XformPre* xf, int ni, V3 origin, const RngCtx& rng) {
+    for (int guard = 0; guard <= RS_MAX_TREE_DEPTH; ++guard) {
+        const rs_node& n = nodes[ni];
         switch (n.type) {
             case RS_NODE_SPHERE: return sphere_random(n, origin, rng);
             case RS_NODE_RECT: return rect_random(n, origin, rng);
             case RS_NODE_QUADRIC: return -origin;  // quadric.rs:202-205
             case RS_NODE_RAYMARCHER: return marcher_random(rng);
             case RS_NODE_DIFFERENCE:
-            case RS_NODE_INTERSECTION: return Tree<D - 1>::random(S, n.child0, origin, rng);
-            case RS_NODE_TRANSFORM: return Tree<D - 1>::random(S, n.child0, xf_apply(S.xf[n.first_xform].inv, origin, 1.0), rng);
+            case RS_NODE_INTERSECTION: ni = n.child0; break;  // difference.rs:118-120, intersection.rs:120-122
+            case RS_NODE_TRANSFORM:  // tf_facade.rs:89-93: the origin goes to object space, the result is not mapped back
+                origin = xf_apply(xf[n.first_xform].inv, origin, 1.0);
+                ni = n.child0;
+                break;
             default: return v3(1.0, 0.0, 0.0);  // box, medium
         }
     }
-};
-
-template <>
-struct Tree<0> {
-    static __device__ __forceinline__ bool contains(const DScene&, int, V3) { return false; }
-    template <bool FULL = true>
-    static __device__ __forceinline__ bool hit(const DScene&, int, const Ray&, double, double, const RngCtx&, HitRec&) { return false; }
-    static __device__ __forceinline__ V3 random(const DScene&, int, V3, const RngCtx&) { return v3(1.0, 0.0, 0.0); }
-};
-
-using TreeTop = Tree<RS_MAX_TREE_DEPTH>;
+    return v3(1.0, 0.0, 0.0);
+}
 
 // ---------------------------------------------------------------------------------------------
 // Textures
