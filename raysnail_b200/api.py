@@ -295,6 +295,12 @@ class Renderer:
         if self._scene is not None:
             self.upload(self._scene)
 
+    def set_list_max(self, n: int):
+        """RS_OPT_LIST_MAX: worlds of at most n objects are searched as a list, not a tree (0 = always the tree)."""
+        self._ck(self._lib.rs_set_option(self._ctx, 3, int(n)), "rs_set_option")
+        if self._scene is not None:
+            self.upload(self._scene)
+
     def set_wave_streams(self, n: int):
         """RS_OPT_WAVE_STREAMS: 2 = consecutive waves overlap on two streams (default), 1 = one stream."""
         self._ck(self._lib.rs_set_option(self._ctx, 2, int(n)), "rs_set_option")

@@ -66,13 +66,17 @@ struct rs_ctx {
     // scene (device)
     DevBuf d_nodes, d_xf, d_bvh, d_root_node, d_root_kind, d_root_sphere, d_root_bbox, d_root_gate;
     DevBuf d_mat_hot, d_root_inv_r, d_root_material, d_light_nodes;
-    DevBuf d_prog, d_cprog, d_csg, d_root_prog;  // object programs (expression-tree roots)
+    DevBuf d_prog, d_cprog, d_csg, d_root_prog, d_root_list;  // object programs (expression-tree roots)
     DevBuf d_tri_geom, d_tri_normals, d_tri_material, d_lights, d_materials, d_textures, d_texels, d_perm, d_values;
     DScene scene{};
     // scene (host side, kept to re-pad the f32 boxes when the camera moves far away)
     std::vector<HostBvhNode> bvh_host;
     std::vector<HostBvhNode4> bvh4_host;
     std::vector<int> root_kind_host;
+    struct ListEntry { double box[6]; int root; bool noclip; };
+    std::vector<ListEntry> list_host;  // the world objects with a proper bbox, ascending ids
+    bool use_list = false;             // small worlds: the kernels walk the object list instead of the tree (RS_OPT_LIST_MAX)
+    int list_max = 12;
     int bvh_root = 0;
     int bvh_width = 2;       // RS_OPT_BVH_WIDTH: 2 = binary 64-byte nodes (default), 4 = QBVH 128-byte nodes
     int extend_mode = 3;     // 0 static spheres only, 1 + triangles, 2 + flat roots (rect / box), 3 everything
@@ -134,6 +138,72 @@ int upload(rs_ctx* ctx, DevBuf& buf, const T* src, size_t n) {
 // ---------------------------------------------------------------------------------------------
 // BVH build: binned SAH over the reference bounding boxes of the world objects
 // ---------------------------------------------------------------------------------------------
+// Conservative bound of the SURFACE of object `ni` (all the points a hit can report), or false
+// when there is none (a quadric) or none is known.  It is not the reference's bbox: that one is
+// restated by the host layer and is what the BVH leaf gates the object with (bvh.rs:173-176);
+// a rotated Intersection, for one, reaches outside it.  The tree may drop a box that lies
+// beyond the closest hit so far only if the box holds every hit of its objects, so the tree is
+// built over (reference bbox ∪ this bound) and objects without a bound stay out of the tree.
+bool geom_bound(const std::vector<rs_node>& nodes, const std::vector<XformPre>& xf, int ni, double* lo, double* hi) {
+    const rs_node& n = nodes[ni];
+    switch (n.type) {
+    case RS_NODE_SPHERE:
+        if (n.p[4] != 0.0 || n.p[5] != 0.0 || n.p[6] != 0.0) return false;  // moving: the time range is not known here
+        for (int a = 0; a < 3; ++a) { lo[a] = n.p[a] - std::fabs(n.p[3]); hi[a] = n.p[a] + std::fabs(n.p[3]); }
+        return true;
+    case RS_NODE_BOX:
+        for (int a = 0; a < 3; ++a) { lo[a] = std::min(n.p[a], n.p[3 + a]); hi[a] = std::max(n.p[a], n.p[3 + a]); }
+        return true;
+    case RS_NODE_RECT: {
+        // rect.rs: plane `k` on the axis the other two span (RS_RECT_XY: a = x, b = y, k = z, ...)
+        const int ax[3][3] = {{0, 1, 2}, {0, 2, 1}, {1, 2, 0}};
+        const int* m = ax[n.rect_axis];
+        lo[m[0]] = std::min(n.p[1], n.p[2]); hi[m[0]] = std::max(n.p[1], n.p[2]);
+        lo[m[1]] = std::min(n.p[3], n.p[4]); hi[m[1]] = std::max(n.p[3], n.p[4]);
+        lo[m[2]] = n.p[0]; hi[m[2]] = n.p[0];
+        return true;
+    }
+    case RS_NODE_DIFFERENCE:  // every hit lies on or inside the first operand
+    case RS_NODE_MEDIUM:      // inside the boundary
+        return geom_bound(nodes, xf, n.child0, lo, hi);
+    case RS_NODE_INTERSECTION: {
+        double l1[3], h1[3];
+        const bool b0 = geom_bound(nodes, xf, n.child0, lo, hi), b1 = geom_bound(nodes, xf, n.child1, l1, h1);
+        if (!b0 && !b1) return false;
+        if (!b0) { std::memcpy(lo, l1, sizeof(l1)); std::memcpy(hi, h1, sizeof(h1)); return true; }
+        if (!b1) return true;
+        bool empty = false;
+        for (int a = 0; a < 3; ++a) empty |= std::max(lo[a], l1[a]) > std::min(hi[a], h1[a]);
+        if (!empty)
+            for (int a = 0; a < 3; ++a) { lo[a] = std::max(lo[a], l1[a]); hi[a] = std::min(hi[a], h1[a]); }
+        return true;  // (disjoint operands: no hits at all; the first operand's bound will do)
+    }
+    case RS_NODE_TRANSFORM: {
+        double l0[3], h0[3];
+        if (!geom_bound(nodes, xf, n.child0, l0, h0)) return false;
+        const double* F = xf[n.first_xform].fwd;  // pre-multiplied stack, 3x4 row-major
+        for (int a = 0; a < 3; ++a) { lo[a] = INFINITY; hi[a] = -INFINITY; }
+        for (int c = 0; c < 8; ++c) {
+            const double x = (c & 1) ? h0[0] : l0[0], y = (c & 2) ? h0[1] : l0[1], z = (c & 4) ? h0[2] : l0[2];
+            for (int a = 0; a < 3; ++a) {
+                const double v = F[4 * a] * x + F[4 * a + 1] * y + F[4 * a + 2] * z + F[4 * a + 3];
+                lo[a] = std::min(lo[a], v);
+                hi[a] = std::max(hi[a], v);
+            }
+        }
+        return true;
+    }
+    case RS_NODE_RAYMARCHER:
+        // a reported point is within one search step (0.05) of a point that has not escaped |v|^2 <= 8
+        // after >= 1 iteration, the first of which is the point itself (raymarching.rs:59-76, 202-241)
+        if (n.p[0] < 1.0) return false;
+        for (int a = 0; a < 3; ++a) { lo[a] = -3.0; hi[a] = 3.0; }
+        return true;
+    default:  // RS_NODE_QUADRIC: unbounded
+        return false;
+    }
+}
+
 struct BuildPrim {
     double lo[3], hi[3], c[3];
     int root;
@@ -283,6 +353,26 @@ float f32_up(double v) {
 // bound itself (DESIGN.md "conservative f32 traversal").
 int upload_bvh(rs_ctx* ctx, double omax) {
     const double k = 1.0 / 2097152.0;  // 2^-21
+    {
+        // small worlds: the object list the kernels walk instead of a tree (same outward padding as the node boxes)
+        std::vector<float4> list;
+        for (const auto& e : ctx->list_host) {
+                float lo[3], hi[3];
+                for (int a = 0; a < 3; ++a) {
+                    lo[a] = f32_down(e.box[a] - k * (omax + std::fabs(e.box[a])) - 1e-7);
+                    hi[a] = f32_up(e.box[3 + a] + k * (omax + std::fabs(e.box[3 + a])) + 1e-7);
+                }
+                const int ref = (e.root << 2) | ctx->root_kind_host[e.root];
+                float refbits;
+                std::memcpy(&refbits, &ref, 4);
+                list.push_back(make_float4(lo[0], lo[1], lo[2], refbits));
+                list.push_back(make_float4(hi[0], hi[1], hi[2], e.noclip ? 1.f : 0.f));
+        }
+        int rcl = upload(ctx, ctx->d_root_list, list.data(), list.size());
+        if (rcl != RS_OK) return rcl;
+        ctx->scene.root_list = ctx->d_root_list.as<float4>();
+        ctx->scene.n_list = (int)(list.size() / 2);
+    }
     if (ctx->bvh_width != 4) {  // binary tree, 64-byte nodes
         std::vector<BvhNode> dev2(std::max<size_t>(ctx->bvh_host.size(), 1));
         for (size_t i = 0; i < ctx->bvh_host.size(); ++i) {
@@ -680,7 +770,7 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
                 }
 #endif
                 tm.mark(2);
-                if (ctx->shade_generic == 2) {
+                if (ctx->shade_generic == 2 && !shade_split_trees()) {
                     launch_shade(ctx->scene, fp, ws, b, 2, 0, ctx->shade_grid, nullptr, st);
                 } else {  // lean / flat scenes: the Lambertian hits, then the other classes (see shade_kernel)
                     launch_shade(ctx->scene, fp, ws, b, ctx->shade_generic, 1, ctx->shade_grid_lambert, nullptr, st);
@@ -802,6 +892,11 @@ int rs_set_option(rs_ctx* ctx, int option, int value) {
         ctx->bvh_width = value;
         return RS_OK;
     }
+    if (option == RS_OPT_LIST_MAX && value >= 0 && value <= 64) {
+        if (ctx->list_max != value) ctx->has_scene = false;
+        ctx->list_max = value;
+        return RS_OK;
+    }
     if (option == RS_OPT_WAVE_STREAMS && value >= 1 && value <= rs_ctx::kMaxSets) {
         ctx->wave_streams = value;
         return RS_OK;
@@ -889,7 +984,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     bool any_quadric_root = false;
     std::vector<double> root_sphere((size_t)s->n_roots * 4, 0.0);
     std::vector<unsigned char> root_gate(s->n_roots, 0);
-    std::vector<BuildPrim> prims;
+    std::vector<BuildPrim> prims, loose;  // loose: no bound on the surface; searched as a list, never dropped by distance
     prims.reserve(s->n_roots);
     double omax = 1.0;
     for (int i = 0; i < s->n_roots; ++i) {
@@ -929,13 +1024,52 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
             p.c[a] = 0.5 * (lo + hi);
         }
         if (degenerate) continue;
-        for (int a = 0; a < 3; ++a) omax = std::max(omax, std::max(std::fabs(p.lo[a]), std::fabs(p.hi[a])));
         p.root = i;
-        prims.push_back(p);
+        // objects the bbox gates (not a bare sphere / box / rect): their surface may reach outside it (geom_bound)
+        bool bounded = true;
+        if (r >= 0 && root_gate[i]) {
+            double glo[3], ghi[3];
+            bounded = geom_bound(nodes, xf, r, glo, ghi);
+            if (bounded)
+                for (int a = 0; a < 3; ++a) {
+                    p.lo[a] = std::min(p.lo[a], std::max(glo[a], -1e30));
+                    p.hi[a] = std::max(p.hi[a], std::min(ghi[a], 1e30));
+                    p.c[a] = 0.5 * (p.lo[a] + p.hi[a]);
+                }
+        }
+        for (int a = 0; a < 3; ++a) omax = std::max(omax, std::max(std::fabs(p.lo[a]), std::fabs(p.hi[a])));
+        (bounded ? prims : loose).push_back(p);
     }
+    // small worlds are searched as one list (RS_OPT_LIST_MAX); otherwise only the loose objects are
+    if (const char* e = std::getenv("RAYSNAIL_B200_LIST_MAX")) ctx->list_max = std::atoi(e);
+    bool flat_or_tree = !loose.empty();
+    for (const BuildPrim& p : prims) flat_or_tree |= root_kind[p.root] == ROOT_FLAT || root_kind[p.root] == ROOT_GENERIC;
+    ctx->use_list = flat_or_tree && ctx->bvh_width == 2 && (int)(prims.size() + loose.size()) <= ctx->list_max;
+    ctx->list_host.clear();
+    auto list_add = [&](const BuildPrim& p, bool noclip) {
+        rs_ctx::ListEntry e;
+        for (int a = 0; a < 3; ++a) { e.box[a] = p.lo[a]; e.box[3 + a] = p.hi[a]; }
+        e.root = p.root;
+        e.noclip = noclip;
+        ctx->list_host.push_back(e);
+    };
+    for (const BuildPrim& p : loose) list_add(p, true);
+    if (ctx->use_list) {
+        for (const BuildPrim& p : prims) list_add(p, false);
+        prims.clear();  // no tree
+    }
+    // any fixed order gives the same hit (the tie rule does not depend on it).  Objects that are tested whatever
+    // the closest hit is come first, then the others by the cost of their test, so that the cheap ones'
+    // hits spare the dear ones: sphere, rect / box, expression tree
+    auto list_rank = [&](const rs_ctx::ListEntry& e) { return e.noclip ? -1 : root_kind[e.root] == ROOT_SPHERE ? 0 : root_kind[e.root] == ROOT_GENERIC ? 2 : 1; };
+    std::sort(ctx->list_host.begin(), ctx->list_host.end(), [&](const rs_ctx::ListEntry& a, const rs_ctx::ListEntry& b) {
+        const int ra = list_rank(a), rb = list_rank(b);
+        return ra != rb ? ra < rb : a.root < b.root;
+    });
+    const bool any_object = !prims.empty() || !ctx->list_host.empty();
     ctx->bvh_host.clear();
     ctx->root_kind_host = root_kind;
-    int bvh_root = 0x7fffffff;
+    int bvh_root = (int)0x80000000;  // RS_BVH_SENTINEL: no tree
     if (!prims.empty()) bvh_root = build_bvh(prims, 0, prims.size(), 0, ctx->bvh_host);
     ctx->bvh4_host.clear();
     if (!prims.empty() && bvh_root < 0) {
@@ -950,11 +1084,13 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     ctx->scene_omax = omax;
     // which kernel specialisations this scene needs
     bool any_tri = false, any_flat = false, any_tree = RS_TUNE_QUADRIC_FLAT ? false : any_quadric_root;
-    for (const BuildPrim& p : prims) {
-        any_tri |= root_kind[p.root] == ROOT_TRIANGLE;
-        any_flat |= root_kind[p.root] == ROOT_FLAT;
-        any_tree |= root_kind[p.root] == ROOT_GENERIC;
-    }
+    auto needs = [&](int root) {
+        any_tri |= root_kind[root] == ROOT_TRIANGLE;
+        any_flat |= root_kind[root] == ROOT_FLAT;
+        any_tree |= root_kind[root] == ROOT_GENERIC;
+    };
+    for (const BuildPrim& p : prims) needs(p.root);
+    for (const auto& e : ctx->list_host) needs(e.root);
     ctx->extend_mode = any_tree ? 3 : (any_flat ? 2 : (any_tri ? 1 : 0));
     ctx->uses_time = false;
     for (const rs_node& n : nodes)
@@ -966,8 +1102,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     }
     ctx->shade_generic = (any_tree || !lights_simple) ? 2 : (any_flat ? 1 : 0);
     ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4);
-    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, ctx->shade_generic == 2 ? 0 : 2);
-    ctx->shade_grid_lambert = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic == 2 ? 0 : ctx->shade_generic, 1);
+    const bool one_shade = ctx->shade_generic == 2 && !shade_split_trees();
+    ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, one_shade ? 0 : 2);
+    ctx->shade_grid_lambert = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, one_shade ? 0 : 1);
     ctx->extend_first_grid = ctx->sm_count * extend_first_blocks_per_sm(ctx->extend_mode);
     if (const char* e = std::getenv("RAYSNAIL_B200_FUSE_RAYGEN")) ctx->fuse_raygen = std::atoi(e);
     // tuning hooks: fewer resident blocks per SM than the occupancy limit (profiling experiments)
@@ -1089,8 +1226,8 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     DScene& S = ctx->scene;
     S.nodes = ctx->d_nodes.as<rs_node>();
     S.xf = ctx->d_xf.as<XformPre>();
-    S.bvh_root = prims.empty() ? 0 : bvh_root;
-    S.n_roots = prims.empty() ? 0 : s->n_roots;
+    S.bvh_root = bvh_root;
+    S.n_roots = any_object ? s->n_roots : 0;
     S.root_node = ctx->d_root_node.as<int>();
     S.root_kind = ctx->d_root_kind.as<int>();
     S.root_sphere = ctx->d_root_sphere.as<double4>();
@@ -1384,12 +1521,15 @@ static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), 0));
     launch_raygen(fp, ctx->ws, 0);
     launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->bvh_width == 4, 0, ctx->extend_grid, 0);  // probes: misses stay visible to shade
-    if (shade && ctx->shade_generic == 2) launch_shade(ctx->scene, fp, ctx->ws, 0, 2, 0, ctx->shade_grid, &dbg, 0);
-    if (shade && ctx->shade_generic != 2) {
+    const bool one_shade = ctx->shade_generic == 2 && !shade_split_trees();
+    if (shade && one_shade) {
+        launch_shade(ctx->scene, fp, ctx->ws, 0, 2, 0, ctx->shade_grid, &dbg, 0);
+    } else if (shade) {
         launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic, 1, ctx->shade_grid_lambert, &dbg, 0);
         launch_shade(ctx->scene, fp, ctx->ws, 0, ctx->shade_generic, 2, ctx->shade_grid, &dbg, 0);
+    } else {
+        launch_probe_primary(ctx->scene, fp, ctx->ws, dbg, 0);
     }
-    else launch_probe_primary(ctx->scene, fp, ctx->ws, dbg, 0);
     CK(cudaGetLastError());
     for (int i = 0; i < 11; ++i)
         if (host_out[i]) CK(cudaMemcpyAsync(host_out[i], dev[i], (size_t)np * elem_bytes[i], cudaMemcpyDeviceToHost, 0));

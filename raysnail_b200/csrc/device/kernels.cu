@@ -134,8 +134,17 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // staging slots per lane of shade: the 4 path elements + the hit record; double buffered
 #define RS_SHADE_STAGE 5
 // per warp: two record buffers + two 32-entry queue-entry buffers (uint2) + two 32-entry buffers
-// of reserved output slots
-#define RS_SHADE_WARP_SMEM (2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 8 + 2 * 32 * 4)
+// of reserved output slots + two 32-entry buffers of path indices
+#define RS_SHADE_WARP_SMEM (2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 8 + 2 * 32 * 4 + 2 * 32 * 4)
+// highest shade tier that runs the staged (cp.async) pipeline; 0 = lean scenes only
+#ifndef RS_TUNE_STAGE_TIERS
+#define RS_TUNE_STAGE_TIERS 0
+#endif
+// 1: scenes with expression trees (tier 2) also shade their Lambertian hits in a kernel of their own
+#ifndef RS_TUNE_SPLIT_TREES
+#define RS_TUNE_SPLIT_TREES 1
+#endif
+#define RS_SHADE_STAGED(TIER) ((TIER) <= RS_TUNE_STAGE_TIERS)
 #define RS_SHADE_SMEM (RS_WARPS * RS_SHADE_WARP_SMEM)
 
 // =============================================================================================
@@ -304,14 +313,13 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
             best.material = -2;
         }
     } else if (MODE >= 3) {
-        if (__ldg(&S.root_gate[root])) {
-            const double inf = __longlong_as_double(0x7ff0000000000000LL);
-            if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
-        }
         const int2 pr = __ldg(&S.obj.root_prog[root]);
         ObjHit h;
         const double hi = __longlong_as_double(0x7ff0000000000000LL);  // see ROOT_FLAT
-        if (eval_object(S.nodes, S.xf, S.obj, pr.x, pr.y, ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || (h.t1 == best.t && root < best.root))) {
+        // the object only counts when the ray passes AABB::hit on its reference bbox (bvh.rs:173-176 on the leaf's box)
+        if (__ldg(&S.root_gate[root]) && !aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, hi)) return;
+        const bool hit = eval_object(S.nodes, S.xf, S.obj, pr.x, pr.y, ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || (h.t1 == best.t && root < best.root));
+        if (hit) {
             best.t = h.t1;
             best.root = root;
             best.material = h.mat;
@@ -414,6 +422,34 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
     const float oodx = ox * idx, oody = oy * idy, oodz = oz * idz;
     const float tmin_f = (float)RS_TMIN * (1.0f - 2.0f * RS_SLAB_EPS);
     float tmax_f = FLT_MAX;
+    const float slack = (1.0f + RS_SLAB_EPS) * (1.0f + RS_SLAB_EPS);
+
+    // The object list, walked before the tree.  It holds
+    //  - the objects whose surface has no bound (quadrics): the reference visits them whenever the ray
+    //    passes their bbox at all, wherever the hit then lies, so no closest hit may drop them (hi.w = 1);
+    //  - in worlds of a few objects (the .sdl scenes, the Cornell box) every object, and there is no tree:
+    //    all lanes walk the SAME objects in the same order, so the object test a warp runs in an iteration is
+    //    one object's code for all its lanes (a tree hands every lane another object first and the kinds —
+    //    sphere, box, expression tree — serialise: 12 of 32 lanes per instruction on bounce 1 of quadric.sdl).
+    // Same conservative f32 slab test as a tree node; the tie rule (lower id wins) is order-independent.
+    if constexpr (MODE >= 2) {
+        for (int k = 0; k < S.n_list; ++k) {
+            const float4 lo = __ldg(S.root_list + 2 * k), hi = __ldg(S.root_list + 2 * k + 1);
+            const float x0 = fmaf(lo.x, idx, -oodx), x1 = fmaf(hi.x, idx, -oodx);
+            const float y0 = fmaf(lo.y, idy, -oody), y1 = fmaf(hi.y, idy, -oody);
+            const float z0 = fmaf(lo.z, idz, -oodz), z1 = fmaf(hi.z, idz, -oodz);
+            const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin_f));
+            const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), hi.w != 0.f ? FLT_MAX : tmax_f));
+            if (tn <= tf * slack) {
+#if RS_TUNE_COST_DUMP
+                ++best.n_leaves;
+#endif
+                test_root<MODE>(S, __float_as_int(lo.w), ray, rng, best);
+                tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
+            }
+        }
+    }
+    if (S.bvh_root == RS_BVH_SENTINEL) return;
 
     // stack entries carry the entry distance of the child (its sort key) next to the reference,
     // so entries that fell behind the closest hit found meanwhile are dropped when popped —
@@ -422,7 +458,6 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
     int sp = 0;
     stack[sp++] = (unsigned long long)(uint32_t)RS_BVH_SENTINEL;  // key 0: never dropped
     int node = S.bvh_root;  // may itself be a leaf (single object)
-    const float slack = (1.0f + RS_SLAB_EPS) * (1.0f + RS_SLAB_EPS);
 #define RS_POP()                                                                   \
     do {                                                                           \
         const unsigned long long e_ = stack[--sp];                                 \
@@ -884,7 +919,7 @@ __device__ __forceinline__ void dbg_store3(double* p, uint32_t i, V3 v) {
 // TIER: 0 = lean scenes (spheres, triangles; staged pipeline), 1 = + ROOT_FLAT objects, lights are plain
 // spheres / rects (no expression-tree code), 2 = everything
 template <int TIER, int SET>
-__global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? RS_TUNE_SHADE_GENERIC : (SET == 1 ? RS_TUNE_SHADE_LAMBERT : RS_TUNE_SHADE_LEAN)) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+__global__ void __launch_bounds__(RS_SHADE_STAGED(TIER) ? RS_TUNE_SHADE_BLOCK : RS_BLOCK, TIER ? RS_TUNE_SHADE_GENERIC : (SET == 1 ? RS_TUNE_SHADE_LAMBERT : RS_TUNE_SHADE_LEAN)) shade_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                             const __grid_constant__ WaveState ws, const int bounce,
                                                             const __grid_constant__ DebugOut dbg, const int has_dbg) {
     constexpr bool GENERIC = TIER >= 1, TREES = TIER >= 2;
@@ -902,6 +937,7 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
     uint4* const stage = reinterpret_cast<uint4*>(warp_smem) + lane;
     uint2* const idxq = reinterpret_cast<uint2*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16) + lane;                   // [2][32]
     uint32_t* const outq = reinterpret_cast<uint32_t*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 8) + lane;  // [2][32]
+    uint32_t* const pidx = reinterpret_cast<uint32_t*>(warp_smem + 2 * RS_SHADE_STAGE * 32 * 16 + 2 * 32 * 8 + 2 * 32 * 4) + lane;  // [2][32]
 
     // virtual index space: each class padded to a multiple of 32 so a warp never mixes classes.
     // The table is spread over the lanes of the warp (lane c holds class c: two registers instead
@@ -986,6 +1022,7 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
     auto stage_item = [&](int buf, uint2 entry) {  // entry = (path index, output slot reserved by extend)
         const uint32_t i = entry.x;
         outq[buf * 32] = entry.y;
+        if constexpr (GENERIC) pidx[buf * 32] = i;
         uint4* s = stage + buf * (RS_SHADE_STAGE * 32);
         const uint4* r = in.rec + 4 * (size_t)i;
         cp_async16(s, r);
@@ -1003,7 +1040,7 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
     // Generic scenes keep the plain loads: their kernel is register-bound (expression-tree
     // interpreter) and the extra pipeline state costs more in spills than the latency it hides
     // (measured on the Cornell box).
-    constexpr bool STAGED = !GENERIC;
+    constexpr bool STAGED = RS_SHADE_STAGED(TIER);
     uint32_t base0 = 0, base1 = 0;
     int cls0 = 0, cls1 = 0;
     bool live0 = false, live1 = false;
@@ -1069,6 +1106,10 @@ __global__ void __launch_bounds__(TIER ? RS_BLOCK : RS_TUNE_SHADE_BLOCK, TIER ? 
                 ha.t = __hiloint2double((int)hh.y, (int)hh.x);
                 ha.root = (int)hh.z;
                 ha.matinfo = hh.w;
+                if constexpr (GENERIC) {
+                    i = pidx[buf * 32];
+                    if (ws.uses_time) p.ray.time = in.time[i];
+                }
             } else {
                 load_path(fp, ws, in, i, p);
                 ha = ws.hit[i];
@@ -1477,17 +1518,37 @@ void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, 
     void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
     cudaLaunchKernel(extend_fn_for(mode, wide), dim3(grid), dim3(RS_BLOCK), args, 0, s);
 }
+template <int TIER, int SET>
+static void launch_shade_t(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int grid, const DebugOut& d, int has_dbg, cudaStream_t s) {
+    if constexpr (RS_SHADE_STAGED(TIER)) shade_kernel<TIER, SET><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, has_dbg);
+    else shade_kernel<TIER, SET><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, has_dbg);
+}
+template <int TIER, int SET>
+static int shade_occupancy_t() {
+    int n = 0;
+    if constexpr (RS_SHADE_STAGED(TIER)) {
+        cudaFuncSetAttribute(shade_kernel<TIER, SET>, cudaFuncAttributeMaxDynamicSharedMemorySize, RS_SHADE_SMEM);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<TIER, SET>, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM);
+    } else {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<TIER, SET>, RS_BLOCK, 0);
+    }
+    return n > 0 ? n : 1;
+}
+#define RS_SHADE_DISPATCH(FN, ...)                                                                   \
+    do {                                                                                             \
+        if (generic == 2) { if (set == 1) return FN<2, 1>(__VA_ARGS__); if (set == 2) return FN<2, 2>(__VA_ARGS__); return FN<2, 0>(__VA_ARGS__); } \
+        if (generic == 1) { if (set == 1) return FN<1, 1>(__VA_ARGS__); if (set == 2) return FN<1, 2>(__VA_ARGS__); return FN<1, 0>(__VA_ARGS__); } \
+        if (set == 1) return FN<0, 1>(__VA_ARGS__);                                                  \
+        if (set == 2) return FN<0, 2>(__VA_ARGS__);                                                  \
+        return FN<0, 0>(__VA_ARGS__);                                                                \
+    } while (0)
 void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int set, int grid, const DebugOut* dbg, cudaStream_t s) {
     DebugOut d = {};
     if (dbg) d = *dbg;
-    if (generic == 2) shade_kernel<2, 0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else if (generic == 1 && set == 1) shade_kernel<1, 1><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else if (generic == 1 && set == 2) shade_kernel<1, 2><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else if (generic == 1) shade_kernel<1, 0><<<grid, RS_BLOCK, 0, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else if (set == 1) shade_kernel<0, 1><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else if (set == 2) shade_kernel<0, 2><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
-    else shade_kernel<0, 0><<<grid, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM, s>>>(S, fp, ws, bounce, d, dbg ? 1 : 0);
+    const int has_dbg = dbg ? 1 : 0;
+    RS_SHADE_DISPATCH(launch_shade_t, S, fp, ws, bounce, grid, d, has_dbg, s);
 }
+int shade_split_trees() { return RS_TUNE_SPLIT_TREES; }
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s) {
     probe_primary_kernel<<<grid_for((int64_t)fp.n_pixels * fp.n_samples), RS_BLOCK, 0, s>>>(S, fp, ws, dbg);
 }
@@ -1520,19 +1581,6 @@ int extend_blocks_per_sm(int mode, int wide) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_fn_for(mode, wide), RS_BLOCK, 0);
     return n > 0 ? n : 1;
 }
-int shade_blocks_per_sm(int generic, int set) {
-    int n = 0;
-    if (generic) {
-        if (generic == 2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<2, 0>, RS_BLOCK, 0);
-        else if (set == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<1, 1>, RS_BLOCK, 0);
-        else if (set == 2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<1, 2>, RS_BLOCK, 0);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shade_kernel<1, 0>, RS_BLOCK, 0);
-    } else {
-        const void* fn = set == 1 ? (const void*)shade_kernel<0, 1> : (set == 2 ? (const void*)shade_kernel<0, 2> : (const void*)shade_kernel<0, 0>);
-        cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, RS_SHADE_SMEM);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, RS_TUNE_SHADE_BLOCK, RS_SHADE_SMEM);
-    }
-    return n > 0 ? n : 1;
-}
+int shade_blocks_per_sm(int generic, int set) { RS_SHADE_DISPATCH(shade_occupancy_t); }
 
 }  // namespace rsd

@@ -131,5 +131,6 @@ void launch_extend_first(const DScene& S, const FrameParams& fp, const WaveState
 int extend_first_blocks_per_sm(int mode);
 int extend_blocks_per_sm(int mode, int wide);
 int shade_blocks_per_sm(int generic, int set);
+int shade_split_trees();  // tier-2 scenes launch the Lambertian hits separately (RS_TUNE_SPLIT_TREES)
 
 }  // namespace rsd

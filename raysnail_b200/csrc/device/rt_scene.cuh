@@ -91,6 +91,8 @@ struct DScene {
     const BvhNode* bvh2;         // binary tree (default)
     int bvh_root;                // >= 0 node, < 0 single leaf ref
     int n_roots;
+    const float4* root_list;     // objects searched as a list before the tree: (lo.xyz, bits of the leaf ref), (hi.xyz, 1 = never dropped by distance)
+    int n_list;                  // unbounded objects; in small worlds every object (then bvh_root is the sentinel: no tree)
     const int* root_node;        // node index or ~triangle
     const int* root_kind;        // RootKind
     const double4* root_sphere;  // ROOT_SPHERE: (cx, cy, cz, r)
@@ -791,12 +793,17 @@ static __device__ __noinline__ bool eval_object(const rs_node* nodes, const Xfor
     int sp = 0;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     double lo0 = lo, hi0 = hi, med_t1 = 0.0;
+    int cur_xi = -1;  // the space `r` is in: consecutive operands usually share it (the operands of one CSG node)
+    Ray r = ray;
     for (int pc = first; pc < first + count; ++pc) {
         const int4 raw = __ldg(reinterpret_cast<const int4*>(P.prog + pc));
         const int op = raw.x, ni = raw.y, xi = raw.z, aux = raw.w;
         if (op == OP_LEAF) {
             const rs_node& n = nodes[ni];
-            const Ray r = xi >= 0 ? xf_ray(xf[xi].inv, ray) : ray;
+            if (xi != cur_xi) {
+                r = xi >= 0 ? xf_ray(xf[xi].inv, ray) : ray;
+                cur_xi = xi;
+            }
             ObjHit e;
             e.hit = leaf_hit(n, r, lo, hi, e.t1, e.t2);
             e.mat = n.material;
@@ -881,7 +888,10 @@ static __device__ __noinline__ bool eval_object(const rs_node* nodes, const Xfor
                 if (b > hi) b = hi;
                 if (a < b) {
                     if (a < 0.0) a = 0.0;
-                    const Ray r = xi >= 0 ? xf_ray(xf[xi].inv, ray) : ray;
+                    if (xi != cur_xi) {
+                        r = xi >= 0 ? xf_ray(xf[xi].inv, ray) : ray;
+                        cur_xi = xi;
+                    }
                     const double length_per_unit = length(r.d);
                     const double distance_inside = (b - a) * length_per_unit;
                     const uint4 w = rng_words(rng, P_MEDIUM, (uint32_t)ni);

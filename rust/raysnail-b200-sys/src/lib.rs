@@ -67,6 +67,7 @@ pub const RS_RNG_BRDF: u32 = 5;
 pub const RS_RNG_MEDIUM: u32 = 6;
 pub const RS_OPT_BVH_WIDTH: c_int = 1;
 pub const RS_OPT_WAVE_STREAMS: c_int = 2;
+pub const RS_OPT_LIST_MAX: c_int = 3;
 pub const RS_IPC_HANDLE_BYTES: usize = 64;
 pub const RS_MAX_PEERS: usize = 16;
 

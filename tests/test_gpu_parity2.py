@@ -14,8 +14,8 @@ import pytest
 
 from conftest import load_scene
 from oracle_binding import OracleWorld
-from raysnail_b200 import (RS_FLAG_MIS, RS_FLAG_PIXEL_CENTRE, RS_REDO_NOISE, RS_REDO_NOISE_FIXED, RS_REDO_REFERENCE, RsCamera, Scene,
-                           make_params, pass_seed)
+from raysnail_b200 import (RS_FLAG_MIS, RS_FLAG_PIXEL_CENTRE, RS_REDO_NOISE, RS_REDO_NOISE_FIXED, RS_REDO_REFERENCE, CameraBuilder, RsCamera,
+                           Scene, make_params, pass_seed)
 
 pytestmark = pytest.mark.gpu
 
@@ -333,3 +333,34 @@ def test_config4_one_million_triangles(renderer, bvh_width):
         assert float(diff.mean()) <= 1e-3 * scale
     finally:
         renderer.set_bvh_width(2)
+
+
+def test_surfaces_outside_their_reference_bbox_are_found_by_list_and_trees(renderer):
+    """csg.sdl's rotated Intersection reaches outside the bbox the reference computes for it.  The canonical
+    rule (oracle header) visits an object whenever the ray passes that bbox over [tmin, inf), wherever the
+    hit lies, so neither tree may drop it behind a closer hit found first: the trees are built over
+    (reference bbox ∪ bound of the surface), the object list and both trees must return the oracle's hit."""
+    scene = load_scene("csg")
+    oracle = OracleWorld(scene)
+    o3 = np.array([-0.67466441, -0.99993399, -2.40198036])
+    d3 = np.array([0.42554444, 0.63877392, 0.64099907])
+    probe = CameraBuilder().look_from(o3).look_at(o3 + d3).vup((0.123, 1, 0.0456)).fov(1.0).aperture(0.0).focus(1.0).width(1).height(1).build()
+    pp = make_params(sqrt_spp=1, depth=1, flags=RS_FLAG_PIXEL_CENTRE)
+    cam = scene.camera(96, 60)
+    params = make_params(samples=9)
+    expect = oracle.debug_primary(probe, pp, 0)
+    assert expect["obj_id"][0] == 1  # the Intersection, in front of the box (object 2) the ray reaches later
+    imgs = []
+    try:
+        for list_max, width in ((12, 2), (0, 2), (0, 4)):
+            renderer.set_list_max(list_max)
+            renderer.set_bvh_width(width)
+            renderer.upload(scene)
+            g = renderer.debug_primary(probe, pp, 0)
+            assert g["obj_id"][0] == 1 and math.isclose(g["t"][0], expect["t"][0], rel_tol=1e-13), (list_max, width)
+            imgs.append((g["t"][0], renderer.render(cam, params)))
+    finally:
+        renderer.set_list_max(12)
+        renderer.set_bvh_width(2)
+    assert imgs[0][0] == imgs[1][0] == imgs[2][0]
+    assert np.array_equal(imgs[0][1], imgs[1][1]) and np.array_equal(imgs[0][1], imgs[2][1])
