@@ -72,7 +72,7 @@ struct rs_ctx {
     // scene (host side, kept to re-pad the f32 boxes when the camera moves far away)
     std::vector<HostBvhNode> bvh_host;
     std::vector<HostBvhNode4> bvh4_host;
-    std::vector<int> root_kind_host;
+    std::vector<int> root_kind_host, root_node_host;
     struct ListEntry { double box[6]; int root; bool noclip; };
     std::vector<ListEntry> list_host;  // the world objects with a proper bbox, ascending ids
     bool use_list = false;             // small worlds: the kernels walk the object list instead of the tree (RS_OPT_LIST_MAX)
@@ -102,6 +102,10 @@ struct rs_ctx {
     cudaEvent_t ev_fork = nullptr, ev_join[kMaxSets - 1] = {}, ev_acc[kMaxSets] = {};
     int extend_grid = 148, shade_grid = 148, shade_grid_lambert = 148;
     int extend_first_grid = 148;
+    bool use_stream = false;  // bounces >= 1 run extend_stream_kernel (triangle-mesh scenes)
+    int extend_stream_grid = 148;
+    int stage_bounces = 1 << 30, extend_grid_global = 148;  // bounces >= stage_bounces run the unstaged kernel
+    int stage_bytes = 0;  // > 0: extend keeps the binary tree + sphere table in shared memory (that many bytes per block)
     int fuse_raygen = 1;  // bounce 0 of a render without pixel mask generates its camera rays inside extend
 
     // scratch for rs_render / probes
@@ -351,6 +355,13 @@ float f32_up(double v) {
 // f32 node boxes padded outward so that the f32 slab test never rejects a box the f64 ray
 // enters: the absolute pad covers the rounding of the ray origin (|o| <= omax) and of the
 // bound itself (DESIGN.md "conservative f32 traversal").
+// what a leaf holds: the object's id and kind — for a triangle its index in the triangle table instead (the
+// record there names the object), so that the test needs no look-up in between
+int leaf_ref(const rs_ctx* ctx, int root) {
+    const int kind = ctx->root_kind_host[root];
+    return ((kind == ROOT_TRIANGLE ? ~ctx->root_node_host[root] : root) << 2) | kind;
+}
+
 int upload_bvh(rs_ctx* ctx, double omax) {
     const double k = 1.0 / 2097152.0;  // 2^-21
     {
@@ -362,7 +373,7 @@ int upload_bvh(rs_ctx* ctx, double omax) {
                     lo[a] = f32_down(e.box[a] - k * (omax + std::fabs(e.box[a])) - 1e-7);
                     hi[a] = f32_up(e.box[3 + a] + k * (omax + std::fabs(e.box[3 + a])) + 1e-7);
                 }
-                const int ref = (e.root << 2) | ctx->root_kind_host[e.root];
+                const int ref = leaf_ref(ctx, e.root);
                 float refbits;
                 std::memcpy(&refbits, &ref, 4);
                 list.push_back(make_float4(lo[0], lo[1], lo[2], refbits));
@@ -389,7 +400,7 @@ int upload_bvh(rs_ctx* ctx, double omax) {
             d.by = make_float4(lo[1][0], hi[1][0], lo[1][1], hi[1][1]);
             d.bz = make_float4(lo[0][2], hi[0][2], lo[1][2], hi[1][2]);
             // leaf references carry the root kind in their low bits: ~(root << 2 | kind)
-            auto enc = [&](int c) { return c >= 0 ? c : ~((~c << 2) | ctx->root_kind_host[~c]); };
+            auto enc = [&](int c) { return c >= 0 ? c : ~leaf_ref(ctx, ~c); };
             d.ch = make_int4(enc(h.child[0]), enc(h.child[1]), 0, 0);
         }
         int rc2 = upload(ctx, ctx->d_bvh, dev2.data(), dev2.size());
@@ -418,7 +429,7 @@ int upload_bvh(rs_ctx* ctx, double omax) {
             }
             // leaf references carry the root kind in their low bits: ~(root << 2 | kind)
             const int r = h.child[c];
-            child[c] = r >= 0 ? r : ~((~r << 2) | ctx->root_kind_host[~r]);
+            child[c] = r >= 0 ? r : ~leaf_ref(ctx, ~r);
         }
         BvhNode4& d = dev[i];
         d.lox = make_float4(lo[0][0], lo[1][0], lo[2][0], lo[3][0]);
@@ -740,9 +751,13 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
             for (int b = 0; b < p->depth; ++b) {
                 tm.mark(1);
                 if (b == 0 && fused_first)
-                    launch_extend_first(ctx->scene, fp, ws, ctx->extend_mode, ctx->extend_first_grid, st);
+                    launch_extend_first(ctx->scene, fp, ws, ctx->extend_mode, ctx->extend_first_grid, ctx->stage_bytes, st);
                 else
-                    launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, ctx->extend_grid, st);
+                    if (ctx->use_stream)
+                        launch_extend_stream(ctx->scene, fp, ws, b, ctx->extend_mode, 1, ctx->extend_stream_grid, st);
+                    else
+                        launch_extend(ctx->scene, fp, ws, b, ctx->extend_mode, ctx->bvh_width == 4, 1, b < ctx->stage_bounces ? ctx->extend_grid : ctx->extend_grid_global,
+                                      b < ctx->stage_bounces ? ctx->stage_bytes : 0, st);
 #if defined(RS_TUNE_COST_DUMP) && RS_TUNE_COST_DUMP
                 // profiling builds: RAYSNAIL_B200_COST_DUMP=<file>:<bounce> writes the rays of that bounce of wave 0
                 // and their traversal costs: header (cap, nf, nb), cap x 64-byte records, cap x int2
@@ -864,7 +879,7 @@ int rs_create(rs_ctx** out, int device) {
     rs_ctx* ctx = new rs_ctx();
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
-    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(3, 0);
+    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(3, 0, 0);
     ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(2, 0);
     *out = ctx;
     return RS_OK;
@@ -1069,11 +1084,12 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     const bool any_object = !prims.empty() || !ctx->list_host.empty();
     ctx->bvh_host.clear();
     ctx->root_kind_host = root_kind;
+    ctx->root_node_host.assign(s->roots, s->roots + s->n_roots);
     int bvh_root = (int)0x80000000;  // RS_BVH_SENTINEL: no tree
     if (!prims.empty()) bvh_root = build_bvh(prims, 0, prims.size(), 0, ctx->bvh_host);
     ctx->bvh4_host.clear();
     if (!prims.empty() && bvh_root < 0) {
-        bvh_root = ~((~bvh_root << 2) | root_kind[~bvh_root]);  // single object
+        bvh_root = ~leaf_ref(ctx, ~bvh_root);  // single object
     } else if (!prims.empty() && ctx->bvh_width == 4) {
         int need = 0;
         bvh_root = collapse_bvh4(ctx->bvh_host, bvh_root, ctx->bvh4_host, need);
@@ -1101,11 +1117,31 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
         lights_simple &= (n.type == RS_NODE_SPHERE || n.type == RS_NODE_RECT);
     }
     ctx->shade_generic = (any_tree || !lights_simple) ? 2 : (any_flat ? 1 : 0);
-    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4);
+    // lean scenes whose binary tree and sphere table fit: the staged extend kernels (tree in shared memory)
+    ctx->stage_bytes = 0;
+    {
+        const size_t tree_bytes = ctx->bvh_host.size() * sizeof(BvhNode), sphere_bytes = (size_t)s->n_roots * sizeof(double4);
+        int want = 1;
+        if (const char* e = std::getenv("RAYSNAIL_B200_STAGE_TREE")) want = std::atoi(e);
+        if (want && ctx->extend_mode <= 1 && ctx->bvh_width == 2 && !ctx->bvh_host.empty() && tree_bytes + sphere_bytes <= (size_t)RS_STAGE_MAX_BYTES) {
+            const int bytes = (int)(tree_bytes + sphere_bytes);
+            const int b0 = extend_blocks_per_sm(ctx->extend_mode, 0, bytes), b1 = extend_first_blocks_per_sm(ctx->extend_mode, bytes);
+            if (b0 > 0 && b1 > 0) ctx->stage_bytes = bytes;
+        }
+    }
+    ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4, ctx->stage_bytes);
+    {
+        int want = ctx->extend_mode == 1 ? 1 : 0;  // meshes: per-ray cost varies by orders of magnitude
+        if (const char* e = std::getenv("RAYSNAIL_B200_STREAM")) want = std::atoi(e);
+        ctx->use_stream = want && ctx->extend_mode <= 1 && ctx->bvh_width == 2 && !ctx->bvh_host.empty() && bvh_root >= 0;
+        if (ctx->use_stream) ctx->extend_stream_grid = ctx->sm_count * extend_stream_blocks_per_sm(ctx->extend_mode);
+    }
+    ctx->extend_grid_global = ctx->sm_count * extend_blocks_per_sm(ctx->extend_mode, ctx->bvh_width == 4, 0);
+    if (const char* e = std::getenv("RAYSNAIL_B200_STAGE_BOUNCES")) ctx->stage_bounces = std::atoi(e);
     const bool one_shade = ctx->shade_generic == 2 && !shade_split_trees();
     ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, one_shade ? 0 : 2);
     ctx->shade_grid_lambert = ctx->sm_count * shade_blocks_per_sm(ctx->shade_generic, one_shade ? 0 : 1);
-    ctx->extend_first_grid = ctx->sm_count * extend_first_blocks_per_sm(ctx->extend_mode);
+    ctx->extend_first_grid = ctx->sm_count * extend_first_blocks_per_sm(ctx->extend_mode, ctx->stage_bytes);
     if (const char* e = std::getenv("RAYSNAIL_B200_FUSE_RAYGEN")) ctx->fuse_raygen = std::atoi(e);
     // tuning hooks: fewer resident blocks per SM than the occupancy limit (profiling experiments)
     if (const char* e = std::getenv("RAYSNAIL_B200_EXTEND_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->extend_grid = std::min(ctx->extend_grid, ctx->sm_count * v); }
@@ -1125,14 +1161,26 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if (pb.nested_medium) return fail(ctx, RS_ERR_UNSUPPORTED, "a ConstantMedium inside the boundary of another ConstantMedium is not supported");
 
     // triangles: p0, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56)
-    std::vector<double> tri_geom((size_t)s->n_tris * 9);
+    // 80-byte records (five 128-bit loads); the spare word names the world object the triangle is
+    std::vector<double> tri_geom((size_t)s->n_tris * 10, 0.0);
     for (int i = 0; i < s->n_tris; ++i) {
         const double* v = s->tri_verts + 9 * (size_t)i;
-        double* g = &tri_geom[9 * (size_t)i];
+        double* g = &tri_geom[10 * (size_t)i];
         g[0] = v[0]; g[1] = v[1]; g[2] = v[2];
         g[3] = v[0] - v[3]; g[4] = v[1] - v[4]; g[5] = v[2] - v[5];
         g[6] = v[0] - v[6]; g[7] = v[1] - v[7]; g[8] = v[2] - v[8];
+        const int64_t none = -1;
+        std::memcpy(&g[9], &none, 8);
     }
+    for (int i = 0; i < s->n_roots; ++i)
+        if (s->roots[i] < 0) {
+            double& slot = tri_geom[10 * (size_t)(~s->roots[i]) + 9];
+            int64_t root;
+            std::memcpy(&root, &slot, 8);
+            if (root != -1) return fail(ctx, RS_ERR_UNSUPPORTED, "a triangle is listed as two world objects");
+            root = i;
+            std::memcpy(&slot, &root, 8);
+        }
 
     // ---- upload -------------------------------------------------------------------------------
     int rc;
@@ -1227,6 +1275,8 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     S.nodes = ctx->d_nodes.as<rs_node>();
     S.xf = ctx->d_xf.as<XformPre>();
     S.bvh_root = bvh_root;
+    S.bvh2_bytes = ctx->stage_bytes ? (uint32_t)(ctx->bvh_host.size() * sizeof(BvhNode)) : 0u;
+    S.sphere_bytes = ctx->stage_bytes ? (uint32_t)((size_t)s->n_roots * sizeof(double4)) : 0u;
     S.n_roots = any_object ? s->n_roots : 0;
     S.root_node = ctx->d_root_node.as<int>();
     S.root_kind = ctx->d_root_kind.as<int>();
@@ -1237,7 +1287,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     S.obj.cprog = ctx->d_cprog.as<int2>();
     S.obj.csg = ctx->d_csg.as<CsgInfo>();
     S.obj.root_prog = ctx->d_root_prog.as<int2>();
-    S.tri_geom = ctx->d_tri_geom.as<double>();
+    S.tri_geom = ctx->d_tri_geom.as<double2>();
     S.tri_normals = ctx->d_tri_normals.as<double>();
     S.tri_material = ctx->d_tri_material.as<int>();
     S.lights = ctx->d_lights.as<int>();
@@ -1520,7 +1570,7 @@ static int run_probe(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     CK(cudaMemsetAsync(ctx->ws.ctr, 0, sizeof(WaveCounters), 0));
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), 0));
     launch_raygen(fp, ctx->ws, 0);
-    launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->bvh_width == 4, 0, ctx->extend_grid, 0);  // probes: misses stay visible to shade
+    launch_extend(ctx->scene, fp, ctx->ws, 0, ctx->extend_mode, ctx->bvh_width == 4, 0, ctx->extend_grid, ctx->stage_bytes, 0);  // probes: misses stay visible to shade
     const bool one_shade = ctx->shade_generic == 2 && !shade_split_trees();
     if (shade && one_shade) {
         launch_shade(ctx->scene, fp, ctx->ws, 0, 2, 0, ctx->shade_grid, &dbg, 0);

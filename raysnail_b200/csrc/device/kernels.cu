@@ -123,6 +123,51 @@ __device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
+// ---- 1-D bulk copy global -> shared (TMA, `cp.async.bulk`) completing on an mbarrier -----------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");  // visible to the async proxy
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];\n" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ int4 lds_i4(uint32_t a) {
+    int4 v;
+    asm("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];\n" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ double2 lds_d2(uint32_t a) {
+    double2 v;
+    asm("ld.shared.v2.f64 {%0, %1}, [%2];\n" : "=d"(v.x), "=d"(v.y) : "r"(a));
+    return v;
+}
+// where the staged kernels keep the tree and the sphere table (shared-space addresses)
+struct Staged {
+    uint32_t nodes, spheres;
+};
+
 #ifndef RS_TUNE_FIRST_LATE_FETCH
 #define RS_TUNE_FIRST_LATE_FETCH 1
 #endif
@@ -262,13 +307,19 @@ __device__ __forceinline__ double next_up(double x) {
 // lean kernel without the expression-tree code: 0 = static spheres, 1 = + triangles, 2 = + rects and
 // boxes, bare or under one TfFacade (ROOT_FLAT: still no expression-tree code), 3 = everything.
 // `ref` is the decoded leaf reference (root << 2 | kind).
-template <int MODE>
-__device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& ray, const RngCtx& rng, Closest& best) {
+template <int MODE, bool STAGE = false>
+__device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& ray, const RngCtx& rng, Closest& best, const Staged st = Staged{0, 0}) {
     const int kind = MODE == 0 ? (int)ROOT_SPHERE : (ref & 3);
     const int root = ref >> 2;
     if (kind == ROOT_SPHERE) {
-        const double2* sp = reinterpret_cast<const double2*>(S.root_sphere + root);
-        double2 c01 = __ldg(sp), c23 = __ldg(sp + 1);  // two 128-bit ld.global.nc
+        double2 c01, c23;
+        if constexpr (STAGE) {
+            c01 = lds_d2(st.spheres + 32u * (uint32_t)root);
+            c23 = lds_d2(st.spheres + 32u * (uint32_t)root + 16u);
+        } else {
+            const double2* sp = reinterpret_cast<const double2*>(S.root_sphere + root);
+            c01 = __ldg(sp), c23 = __ldg(sp + 1);  // two 128-bit ld.global.nc
+        }
         double t1;
         if (sphere_nearest(v3(c01.x, c01.y, c23.x), c23.y * c23.y, ray, RS_TMIN, next_up(best.t), t1) && (t1 < best.t || root < best.root)) {
             best.t = t1;
@@ -276,11 +327,12 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
             if (MODE >= 2) best.material = -2;  // look it up in root_material
         }
     } else if (MODE >= 1 && kind == ROOT_TRIANGLE) {
-        const int tri = ~__ldg(&S.root_node[root]);
+        // (a triangle's leaf reference holds its index in the triangle table, the record names the world object)
+        const TriGeom T = load_triangle(S.tri_geom, root);
         double t, beta, gamma;
-        if (triangle_test(S.tri_geom + 9 * (size_t)tri, ray, RS_TMIN, best.t, t, beta, gamma) && (t < best.t || root < best.root)) {
+        if (triangle_test<true>(T, ray, RS_TMIN, best.t, t, beta, gamma) && (t < best.t || T.root < best.root)) {
             best.t = t;
-            best.root = root;
+            best.root = T.root;
             if (MODE >= 2) best.material = -2;
         }
     } else if (MODE >= 2 && kind == ROOT_FLAT) {
@@ -393,15 +445,18 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
 #ifndef RS_TUNE_EXTEND_FLAT
 #define RS_TUNE_EXTEND_FLAT 3
 #endif
-#define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) == 3 ? RS_TUNE_EXTEND_GENERIC : ((MODE) == 2 ? RS_TUNE_EXTEND_FLAT : RS_TUNE_EXTEND_LEAN))
+#ifndef RS_TUNE_EXTEND_TRI
+#define RS_TUNE_EXTEND_TRI RS_TUNE_EXTEND_LEAN
+#endif
+#define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) == 3 ? RS_TUNE_EXTEND_GENERIC : ((MODE) == 2 ? RS_TUNE_EXTEND_FLAT : ((MODE) == 1 ? RS_TUNE_EXTEND_TRI : RS_TUNE_EXTEND_LEAN)))
 
 // while-while traversal: every lane first walks inner nodes until it holds a leaf (or is done),
 // the warp reconverges, then the lanes holding leaves run the (expensive, f64) object test
 // together.
 // WIDE = false: binary tree of 64-byte nodes (the default: fewest instructions per ray on
 // these cache-resident scenes); WIDE = true: the 4-wide QBVH of 128-byte nodes.
-template <int MODE, bool WIDE>
-__device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, Closest& best) {
+template <int MODE, bool WIDE, bool STAGE = false>
+__device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, Closest& best, const Staged st = Staged{0, 0}) {
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     best.t = inf;
     best.root = -1;
@@ -470,9 +525,17 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
             ++best.n_nodes;
 #endif
             // one 64-byte node: two children with their boxes, four 128-bit ld.global.nc
-            const float4* np = reinterpret_cast<const float4*>(S.bvh2 + node);
-            const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
-            const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+            float4 bx, by, bz;
+            int4 ch;
+            if constexpr (STAGE) {  // the tree sits in shared memory: four ld.shared.v4
+                const uint32_t na = st.nodes + 64u * (uint32_t)node;
+                bx = lds_f4(na), by = lds_f4(na + 16u), bz = lds_f4(na + 32u);
+                ch = lds_i4(na + 48u);
+            } else {
+                const float4* np = reinterpret_cast<const float4*>(S.bvh2 + node);
+                bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
+                ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+            }
 #if RS_TUNE_FFMA2
             const float2 ix2 = make_float2(idx, idx), iy2 = make_float2(idy, idy), iz2 = make_float2(idz, idz);
             const float2 ox2 = make_float2(-oodx, -oodx), oy2 = make_float2(-oody, -oody), oz2 = make_float2(-oodz, -oodz);
@@ -555,7 +618,7 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
 #if RS_TUNE_COST_DUMP
         ++best.n_leaves;
 #endif
-        test_root<MODE>(S, ~node, ray, rng, best);
+        test_root<MODE, STAGE>(S, ~node, ray, rng, best, st);
         // shrink the f32 limit (rounded up) so farther boxes are culled
         tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
         RS_POP();
@@ -585,10 +648,42 @@ __device__ __forceinline__ int resolve_mixed(const DScene& S, int m, const RngCt
 // (raygen fused in: Camera::ray + the strata loop of painter.rs:154-187) instead of reading a
 // record raygen wrote — one kernel, one 64-byte record read per path less, and a path that ends on
 // its first segment (sky, light) never gets a record at all.
-template <int MODE, bool WIDE, bool FIRST>
-__global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
-                                                                                     const __grid_constant__ WaveState ws, const int bounce,
-                                                                                     const int miss_in_extend) {
+// STAGE = true (lean scenes whose binary tree + sphere table fit, rs_upload_scene decides): every persistent
+// block first copies the tree and the sphere table into shared memory — two 1-D bulk copies (TMA,
+// cp.async.bulk) completing on one mbarrier — and the traversal reads them with ld.shared: a node fetch
+// no longer competes with the streaming ray / hit / stack traffic for L1 lines (ncu, headline scene:
+// L1 hit 75-78 % on a 61 KB tree; every miss is an L2 round trip on the critical path of the walk).
+// MEASURED SLOWER (profiles/r02_ab_stage.txt: headline extend 30.5 vs 29.2 ms at 64 spp; 512 x 2 and 1024 x 1
+// blocks, all or only the first bounces staged): the walk is issue- and divergence-bound, an L1 hit costs
+// what an LDS costs, and 76 KB per block per launch is a fixed ~10 us the small late-bounce launches cannot
+// amortise.  Kept as a build option (RS_TUNE_STAGE_TREE=1 compiles the kernels, RAYSNAIL_B200_STAGE_TREE=0/1 and
+// RAYSNAIL_B200_STAGE_BOUNCES=k then choose at run time); the default build does not instantiate them.
+#ifndef RS_TUNE_STAGE_TREE
+#define RS_TUNE_STAGE_TREE 0
+#endif
+#ifndef RS_TUNE_STAGE_BLOCK
+#define RS_TUNE_STAGE_BLOCK 512  // threads per block of the staged kernels (x 1024 / block per SM)
+#endif
+template <int MODE, bool WIDE, bool FIRST, bool STAGE = false>
+__global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE ? 1024 / RS_TUNE_STAGE_BLOCK : RS_EXTEND_MIN_BLOCKS(MODE))
+    extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp, const __grid_constant__ WaveState ws, const int bounce,
+                  const int miss_in_extend) {
+    Staged st{0, 0};
+    if constexpr (STAGE) {
+        extern __shared__ __align__(128) unsigned char stage_smem[];
+        __shared__ __align__(8) unsigned long long stage_bar;
+        st.nodes = smem_u32(stage_smem);
+        st.spheres = st.nodes + S.bvh2_bytes;
+        const uint32_t bar = smem_u32(&stage_bar);
+        if (threadIdx.x == 0) {
+            mbar_init(bar, 1);
+            mbar_expect_tx(bar, S.bvh2_bytes + S.sphere_bytes);
+            bulk_g2s(st.nodes, S.bvh2, S.bvh2_bytes, bar);
+            bulk_g2s(st.spheres, S.root_sphere, S.sphere_bytes, bar);
+        }
+        __syncthreads();  // the barrier is initialised for everyone
+        mbar_wait(bar, 0);
+    }
     // virtual index space: [0, nf32) = the front stack padded to a multiple of 32 (so that no warp
     // mixes the two kinds of rays), [nf32, nf32 + nb) = the back stack, top first
     const uint32_t nf = FIRST ? fp.n_pixels * fp.n_samples : ws.ctr->n_rays[bounce], nb = FIRST ? 0u : ws.ctr->n_back[bounce];
@@ -607,8 +702,8 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
     // atomic's round trip to L2 overlaps with the traversal instead of heading every batch
 #if RS_TUNE_EXTEND_STATIC
     (void)head;
-    uint32_t next_base = (blockIdx.x * (RS_BLOCK / 32) + (threadIdx.x >> 5)) * 32u;
-    const uint32_t base_stride = gridDim.x * (RS_BLOCK / 32) * 32u;
+    uint32_t next_base = (blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5)) * 32u;
+    const uint32_t base_stride = gridDim.x * (blockDim.x / 32) * 32u;
 #else
     uint32_t pend = 0;
     if (lane_id() == 0) pend = atomic_add_async(head, 32u, lane_zero);
@@ -653,7 +748,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
             rng.depth = (uint32_t)bounce + 1;
             if constexpr (RS_TUNE_RESERVE && MODE < 2) rng_of_lane = rng;
             Closest best;
-            closest_hit<MODE, WIDE>(S, ray, rng, best);
+            closest_hit<MODE, WIDE, STAGE>(S, ray, rng, best, st);
 #if RS_TUNE_COST_DUMP
             if (ws.dbg_cost) ws.dbg_cost[i] = make_int2(best.n_nodes, best.n_leaves);
 #endif
@@ -762,6 +857,279 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_EXTEND_MIN_BLOCKS(MODE)) extend_k
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// extend, streaming form (triangle-mesh scenes, bounces >= 1; chosen per scene in rs_upload_scene)
+// ---------------------------------------------------------------------------------------------
+// After the first bounce the rays of a warp need wildly different numbers of node visits on a mesh
+// (1 M triangles, bounce 1: median 4, mean 18, 99th percentile 90) and extend_kernel's warp, which
+// takes 32 rays and walks them to the end — every round of its while-while loop as long as the
+// slowest lane's walk to its next leaf — issues with 6-7 of its 32 lanes.  Here
+//  - every lane owns its traversal state, and one loop iteration is ONE node step for the lanes that
+//    hold an inner node;
+//  - lanes that reached a leaf wait until RS_TUNE_STREAM_LEAF lanes hold one (or no lane walks any
+//    more), then test their triangles together;
+//  - lanes whose ray is done park (ray, t, object) in a per-warp shared-memory queue and, once
+//    RS_TUNE_STREAM_REFILL lanes are idle, take new rays from the warp's pool (32 indices per atomic,
+//    fetched one chunk ahead);
+//  - the epilogue of a ray (material, miss / light contribution, class bucket, output slot) runs off
+//    that queue 32 rays at a time, i.e. with full warps.
+// The f64 ray is not kept in registers: a leaf test reloads it from the path record (three 128-bit
+// loads that hit L1), which is what lets the per-lane state fit the 64-register budget.
+#ifndef RS_TUNE_STREAM_REFILL
+#define RS_TUNE_STREAM_REFILL 8
+#endif
+#ifndef RS_TUNE_STREAM_LEAF
+#define RS_TUNE_STREAM_LEAF 8
+#endif
+#ifndef RS_TUNE_STREAM_BLOCKS
+#define RS_TUNE_STREAM_BLOCKS 4
+#endif
+template <int MODE>
+__global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
+                                                                                        const __grid_constant__ WaveState ws, const int bounce,
+                                                                                        const int miss_in_extend) {
+    static_assert(MODE < 2, "lean scenes only");
+    __shared__ uint4 done_queue[RS_BLOCK / 32][64];  // (ray index, object, t) of finished rays awaiting their epilogue
+    uint4* const queue = done_queue[threadIdx.x >> 5];
+    const uint32_t nf = ws.ctr->n_rays[bounce], nb = ws.ctr->n_back[bounce];
+    const uint32_t nf32 = (nf + 31u) & ~31u;
+    const uint32_t n = nf32 + nb;
+    const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
+    const uint32_t lane_zero = RS_LANE_ZERO(ws);
+    const PathBuf& in = ws.buf[bounce & 1];
+    uint32_t* head = &ws.ctr->extend_head[bounce];
+    uint32_t* class_count = ws.ctr->class_count[bounce];
+    const bool last_bounce = bounce + 1 >= fp.depth;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ws.stats->n_segments, (unsigned long long)(nf + nb));
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    const float tmin_f = (float)RS_TMIN * (1.0f - 2.0f * RS_SLAB_EPS);
+    const float slack = (1.0f + RS_SLAB_EPS) * (1.0f + RS_SLAB_EPS);
+
+    // per-lane traversal state
+    unsigned long long stack[RS_STACK];
+    int sp = 0, node = RS_BVH_SENTINEL;
+    bool has_ray = false;
+    uint32_t i = 0;
+    float idx = 0.f, idy = 0.f, idz = 0.f, oodx = 0.f, oody = 0.f, oodz = 0.f, tmax_f = FLT_MAX;
+    Closest best;
+    best.t = inf; best.root = -1; best.material = -1;
+    // the warp's pool of virtual ray indices [pool_next, pool_end) + the chunk fetched ahead
+    uint32_t pool_next = 0, pool_end = 0, pend = 0, queued = 0;
+    bool exhausted = false;
+    if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
+    RngCtx no_rng;
+    no_rng.key = fp.key; no_rng.pixel = 0; no_rng.sample = 0; no_rng.depth = 0;
+
+    // epilogue of up to 32 queued rays (extend_kernel's, for a ray that came from the path buffer)
+    auto epilogue = [&](const bool live, const uint4 e) {
+        const uint32_t ri = e.x;
+        int cls = -1;
+        RngCtx rng;
+        rng.key = fp.key; rng.pixel = 0; rng.sample = 0; rng.depth = (uint32_t)bounce + 1;
+        if (live) {
+            const uint4 q3 = in.rec[4 * (size_t)ri + 3];  // (T, slot)
+            decode_slot(fp, q3.w, rng.pixel, rng.sample);
+            Closest b;
+            b.t = __hiloint2double((int)e.w, (int)e.z);
+            b.root = (int)e.y;
+            b.material = -1;
+            HitA h;
+            h.t = b.t; h.root = b.root; h.matinfo = 0;
+            cls = 0;
+            if (b.root >= 0) {
+                const int top = root_material<MODE>(S, b);
+                const int leaf = resolve_mixed(S, top, rng);
+                h.matinfo = (uint32_t)leaf | ((uint32_t)top << 16);
+                const MatHot& mh = S.mat_hot[leaf];
+                const int tf = mh.type_flags;
+                cls = 1 + (tf & 0xff);
+                if (miss_in_extend && (tf & 0xff) == RS_MAT_DIFFUSE_LIGHT && leaf != top) {
+                    cls = -1;  // a light behind a MixedMaterial neither emits nor scatters (see extend_kernel)
+                } else if (miss_in_extend && (tf & 0x3ff) == RS_MAT_DIFFUSE_LIGHT) {
+                    const float4 c = mh.c0;
+                    const double mul = mh.a;
+                    ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * (float)((double)c.x * mul), __uint_as_float(q3.y) * (float)((double)c.y * mul),
+                                                   __uint_as_float(q3.z) * (float)((double)c.z * mul), 0.f);
+                    cls = -1;
+                } else {
+                    ws.hit[ri] = h;
+                }
+            } else if (miss_in_extend) {
+                const uint4 q1 = in.rec[4 * (size_t)ri + 1], q2 = in.rec[4 * (size_t)ri + 2];
+                const V3 d = v3(__hiloint2double((int)q1.w, (int)q1.z), __hiloint2double((int)q2.y, (int)q2.x), __hiloint2double((int)q2.w, (int)q2.z));
+                const float4 bg = background(S, d);
+                ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * bg.x, __uint_as_float(q3.y) * bg.y, __uint_as_float(q3.z) * bg.z, 0.f);
+                cls = -1;
+            } else {
+                ws.hit[ri] = h;
+            }
+        }
+        const bool go = live && cls >= 0;
+        const uint32_t active = __ballot_sync(0xffffffffu, go);
+        constexpr bool RESERVE = RS_TUNE_RESERVE != 0;
+        bool reserve = false, res_front = false;
+        uint32_t mf = 0, mb = 0, bf = 0, bb = 0, lf = 0, lb = 0;
+        if constexpr (RESERVE) {
+            if (go && !last_bounce && RS_ALWAYS_CONTINUES(cls)) {
+                reserve = true;
+                res_front = cls != 1 + RS_MAT_DIELECTRIC && u01(rng_words(rng, P_SCATTER, 0).x) < 0.5;
+            }
+            mf = __ballot_sync(0xffffffffu, reserve && res_front);
+            mb = __ballot_sync(0xffffffffu, reserve && !res_front);
+            lf = mf ? (uint32_t)(__ffs(mf) - 1) : 0u;
+            lb = mb ? (uint32_t)(__ffs(mb) - 1) : 0u;
+            if (mf && lane == lf) bf = atomic_add_async(&ws.ctr->n_rays[bounce + 1], __popc(mf), lane_zero);
+            if (mb && lane == lb) bb = atomic_add_async(&ws.ctr->n_back[bounce + 1], __popc(mb), lane_zero);
+        }
+        uint2* queue_slot = nullptr;
+        if (go) {
+            const int key = (RESERVE && res_front) ? RS_FRONT_CLASS(cls) : cls;
+            const uint32_t peers = __match_any_sync(active, key);
+            const uint32_t leader = __ffs(peers) - 1;
+            uint32_t qbase = 0;
+            if (lane == leader) qbase = atomic_add_async(&class_count[key * RS_COUNTER_STRIDE], __popc(peers), lane_zero);
+            qbase = __shfl_sync(peers, qbase, leader);
+            queue_slot = ws.class_queue + ((size_t)key * ws.capacity + qbase + __popc(peers & lt));
+            if constexpr (!RESERVE) *queue_slot = make_uint2(ri, 0xffffffffu);
+        }
+        if constexpr (RESERVE) {
+            bf = __shfl_sync(0xffffffffu, bf, lf);
+            bb = __shfl_sync(0xffffffffu, bb, lb);
+            if (go) {
+                const uint32_t out_pos = !reserve ? 0xffffffffu : (res_front ? bf + __popc(mf & lt) : ws.capacity - 1u - (bb + __popc(mb & lt)));
+                *queue_slot = make_uint2(ri, out_pos);
+            }
+        }
+    };
+
+#define RS_POP()                                                                   \
+    do {                                                                           \
+        const unsigned long long e_ = stack[--sp];                                 \
+        node = (int)(uint32_t)e_;                                                  \
+        if (!(__uint_as_float((uint32_t)(e_ >> 32) & ~3u) > tmax_f)) break;        \
+    } while (true)
+    while (true) {
+        // ---- lanes whose ray is done hand it to the queue ----
+        {
+            const bool fin = has_ray && node == RS_BVH_SENTINEL;
+            const uint32_t fm = __ballot_sync(0xffffffffu, fin);
+            if (fm) {
+                if (fin) {
+                    queue[queued + __popc(fm & lt)] = make_uint4(i, (uint32_t)best.root, (uint32_t)__double2loint(best.t), (uint32_t)__double2hiint(best.t));
+                    has_ray = false;
+                }
+                queued += __popc(fm);
+                __syncwarp();
+                if (queued >= 32u) {
+                    queued -= 32u;
+                    const uint4 e = queue[queued + lane];
+                    __syncwarp();
+                    epilogue(true, e);
+                }
+            }
+        }
+        // ---- idle lanes take new rays from the pool ----
+        const uint32_t idle = __ballot_sync(0xffffffffu, !has_ray);
+        if (!exhausted && __popc(idle) >= RS_TUNE_STREAM_REFILL) {
+            const uint32_t need = __popc(idle), avail = pool_end - pool_next, rank = __popc(idle & lt);
+            uint32_t v;
+            if (need > avail) {  // warp-uniform: cross into the chunk fetched ahead
+                const uint32_t nextb = __shfl_sync(0xffffffffu, pend, 0);
+                v = rank < avail ? pool_next + rank : nextb + (rank - avail);
+                pool_next = nextb + (need - avail);
+                pool_end = nextb + 32u;
+                if (nextb >= n) exhausted = true;
+                else if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
+            } else {
+                v = pool_next + rank;
+                pool_next += need;
+            }
+            if (!has_ray && (v < nf32 ? v < nf : v < n)) {
+                i = v < nf32 ? v : ws.capacity - 1u - (v - nf32);
+                const uint4* rec = in.rec + 4 * (size_t)i;
+                const uint4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
+                const float ox = (float)__hiloint2double((int)q0.y, (int)q0.x), oy = (float)__hiloint2double((int)q0.w, (int)q0.z),
+                            oz = (float)__hiloint2double((int)q1.y, (int)q1.x);
+                float dx = (float)__hiloint2double((int)q1.w, (int)q1.z), dy = (float)__hiloint2double((int)q2.y, (int)q2.x),
+                      dz = (float)__hiloint2double((int)q2.w, (int)q2.z);
+                const float tiny = 1e-20f;
+                dx = fabsf(dx) > tiny ? dx : copysignf(tiny, dx);
+                dy = fabsf(dy) > tiny ? dy : copysignf(tiny, dy);
+                dz = fabsf(dz) > tiny ? dz : copysignf(tiny, dz);
+                idx = 1.0f / dx; idy = 1.0f / dy; idz = 1.0f / dz;
+                oodx = ox * idx; oody = oy * idy; oodz = oz * idz;
+                tmax_f = FLT_MAX;
+                best.t = inf; best.root = -1;
+                has_ray = true;
+                stack[0] = (unsigned long long)(uint32_t)RS_BVH_SENTINEL;
+                sp = 1;
+                node = S.n_roots ? S.bvh_root : RS_BVH_SENTINEL;
+            }
+        }
+        if (__ballot_sync(0xffffffffu, has_ray) == 0u) {
+            if (exhausted) break;
+            continue;  // a chunk of padding only
+        }
+        // ---- node steps and batched leaf tests until enough lanes are done ----
+        while (true) {
+            if (node >= 0) {
+                const float4* np = reinterpret_cast<const float4*>(S.bvh2 + node);
+                const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
+                const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+                const float2 ix2 = make_float2(idx, idx), iy2 = make_float2(idy, idy), iz2 = make_float2(idz, idz);
+                const float2 ox2 = make_float2(-oodx, -oodx), oy2 = make_float2(-oody, -oody), oz2 = make_float2(-oodz, -oodz);
+                float2 ta = ffma2(make_float2(bx.x, bx.y), ix2, ox2), tb = ffma2(make_float2(bx.z, bx.w), iy2, oy2), tc = ffma2(make_float2(bz.x, bz.y), iz2, oz2);
+                const float near0 = fmaxf(fmaxf(fminf(ta.x, ta.y), fminf(tb.x, tb.y)), fmaxf(fminf(tc.x, tc.y), tmin_f));
+                const float far0 = fminf(fminf(fmaxf(ta.x, ta.y), fmaxf(tb.x, tb.y)), fminf(fmaxf(tc.x, tc.y), tmax_f));
+                ta = ffma2(make_float2(by.x, by.y), ix2, ox2); tb = ffma2(make_float2(by.z, by.w), iy2, oy2); tc = ffma2(make_float2(bz.z, bz.w), iz2, oz2);
+                const float near1 = fmaxf(fmaxf(fminf(ta.x, ta.y), fminf(tb.x, tb.y)), fmaxf(fminf(tc.x, tc.y), tmin_f));
+                const float far1 = fminf(fminf(fmaxf(ta.x, ta.y), fmaxf(tb.x, tb.y)), fminf(fmaxf(tc.x, tc.y), tmax_f));
+                const bool h0 = near0 <= far0 * slack, h1 = near1 <= far1 * slack;
+                if (h0 && h1) {
+                    const bool swap = near1 < near0;
+                    const int second = swap ? ch.x : ch.y;
+                    const float second_near = swap ? near0 : near1;
+                    if (sp < RS_STACK) stack[sp++] = ((unsigned long long)__float_as_uint(second_near) << 32) | (unsigned long long)(uint32_t)second;
+                    node = swap ? ch.y : ch.x;
+                } else if (h0) {
+                    node = ch.x;
+                } else if (h1) {
+                    node = ch.y;
+                } else {
+                    RS_POP();
+                }
+            }
+            const bool at_leaf = node < 0 && node != RS_BVH_SENTINEL;
+            const uint32_t lm = __ballot_sync(0xffffffffu, at_leaf), im = __ballot_sync(0xffffffffu, node >= 0);
+            if (lm && (__popc(lm) >= RS_TUNE_STREAM_LEAF || im == 0u)) {
+                if (at_leaf) {
+                    const uint4* rec = in.rec + 4 * (size_t)i;
+                    const uint4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
+                    Ray ray;
+                    ray.o = v3(__hiloint2double((int)q0.y, (int)q0.x), __hiloint2double((int)q0.w, (int)q0.z), __hiloint2double((int)q1.y, (int)q1.x));
+                    ray.d = v3(__hiloint2double((int)q1.w, (int)q1.z), __hiloint2double((int)q2.y, (int)q2.x), __hiloint2double((int)q2.w, (int)q2.z));
+                    ray.time = 0.0;
+                    test_root<MODE>(S, ~node, ray, no_rng, best);
+                    tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
+                    RS_POP();
+                }
+                continue;  // (lanes may have popped another leaf: look again before deciding to leave)
+            }
+            const uint32_t busy = im | lm;
+            if (busy == 0u) break;
+            if (!exhausted && 32 - __popc(busy) >= RS_TUNE_STREAM_REFILL) break;
+            if (exhausted && __popc(__ballot_sync(0xffffffffu, has_ray && node == RS_BVH_SENTINEL)) + (int)queued >= 32) break;  // a full epilogue is ready
+        }
+    }
+#undef RS_POP
+    // the rays still queued
+    if (queued) {
+        const bool live = lane < queued;
+        const uint4 e = live ? queue[lane] : make_uint4(0u, 0u, 0u, 0u);
+        epilogue(live, e);
+    }
+}
+
 // =============================================================================================
 // shade
 // =============================================================================================
@@ -785,7 +1153,7 @@ __device__ __forceinline__ void rebuild_hit(const DScene& S, const Ray& ray, con
     if (kind == ROOT_TRIANGLE) {
         double t, beta, gamma;
         const double inf = __longlong_as_double(0x7ff0000000000000LL);
-        triangle_test(S.tri_geom + 9 * (size_t)(~rn), ray, -inf, inf, t, beta, gamma);
+        triangle_test(load_triangle(S.tri_geom, ~rn), ray, -inf, inf, t, beta, gamma);
         triangle_record(S, ~rn, ray, ha.t, beta, gamma, h);
     } else if (GENERIC) {
         // same limit as in extend => bit-identical record
@@ -1495,28 +1863,59 @@ void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s) {
 }
 template <int MODE, bool WIDE>
 static const void* extend_fn() { return (const void*)extend_kernel<MODE, WIDE, false>; }
-static const void* extend_first_fn_for(int mode) {
+static const void* extend_first_fn_for(int mode, int stage) {
+#if RS_TUNE_STAGE_TREE
+    if (stage) return mode == 0 ? (const void*)extend_kernel<0, false, true, true> : (const void*)extend_kernel<1, false, true, true>;
+#endif
     return mode == 0 ? (const void*)extend_kernel<0, false, true> : (mode == 1 ? (const void*)extend_kernel<1, false, true>
                      : (mode == 2 ? (const void*)extend_kernel<2, false, true> : (const void*)extend_kernel<3, false, true>));
 }
-void launch_extend_first(const DScene& S, const FrameParams& fp, const WaveState& ws, int mode, int grid, cudaStream_t s) {
-    int bounce = 0, miss_in_extend = 1;
-    void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
-    cudaLaunchKernel(extend_first_fn_for(mode), dim3(grid), dim3(RS_BLOCK), args, 0, s);
-}
-int extend_first_blocks_per_sm(int mode) {
-    int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_first_fn_for(mode), RS_BLOCK, 0);
-    return n > 0 ? n : 1;
-}
-static const void* extend_fn_for(int mode, int wide) {
+static const void* extend_fn_for(int mode, int wide, int stage) {
+#if RS_TUNE_STAGE_TREE
+    if (stage) return mode == 0 ? (const void*)extend_kernel<0, false, false, true> : (const void*)extend_kernel<1, false, false, true>;
+#endif
     if (wide) return mode == 0 ? extend_fn<0, true>() : (mode == 1 ? extend_fn<1, true>() : (mode == 2 ? extend_fn<2, true>() : extend_fn<3, true>()));
     return mode == 0 ? extend_fn<0, false>() : (mode == 1 ? extend_fn<1, false>() : (mode == 2 ? extend_fn<2, false>() : extend_fn<3, false>()));
 }
-void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int miss_in_extend, int grid,
-                   cudaStream_t s) {
+// stage_bytes > 0: the staged kernels (lean modes, binary tree), with that much dynamic shared memory
+void launch_extend_first(const DScene& S, const FrameParams& fp, const WaveState& ws, int mode, int grid, int stage_bytes, cudaStream_t s) {
+    int bounce = 0, miss_in_extend = 1;
     void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
-    cudaLaunchKernel(extend_fn_for(mode, wide), dim3(grid), dim3(RS_BLOCK), args, 0, s);
+    cudaLaunchKernel(extend_first_fn_for(mode, stage_bytes > 0), dim3(grid), dim3(stage_bytes > 0 ? RS_TUNE_STAGE_BLOCK : RS_BLOCK), args, (size_t)stage_bytes, s);
+}
+void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int miss_in_extend, int grid,
+                   int stage_bytes, cudaStream_t s) {
+    void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
+    cudaLaunchKernel(extend_fn_for(mode, wide, stage_bytes > 0), dim3(grid), dim3(stage_bytes > 0 ? RS_TUNE_STAGE_BLOCK : RS_BLOCK), args, (size_t)stage_bytes, s);
+}
+// resident blocks per SM of the kernel the scene will use; staged kernels are first given their dynamic shared memory
+static int extend_occupancy(const void* fn, int stage_bytes) {
+    int n = 0;
+    if (stage_bytes > 0 && !RS_TUNE_STAGE_TREE) return 0;  // not compiled in
+    if (stage_bytes > 0) {
+        if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, stage_bytes) != cudaSuccess) { cudaGetLastError(); return 0; }
+        cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    }
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, fn, stage_bytes > 0 ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, (size_t)stage_bytes);
+    if (stage_bytes > 0 && n < 1024 / RS_TUNE_STAGE_BLOCK) return 0;  // staging must not cost resident warps
+    return n;
+}
+int extend_first_blocks_per_sm(int mode, int stage_bytes) {
+    const int n = extend_occupancy(extend_first_fn_for(mode, stage_bytes > 0), stage_bytes);
+    return n > 0 ? n : (stage_bytes > 0 ? 0 : 1);
+}
+int extend_blocks_per_sm(int mode, int wide, int stage_bytes) {
+    const int n = extend_occupancy(extend_fn_for(mode, wide, stage_bytes > 0), stage_bytes);
+    return n > 0 ? n : (stage_bytes > 0 ? 0 : 1);
+}
+void launch_extend_stream(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int miss_in_extend, int grid, cudaStream_t s) {
+    void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
+    cudaLaunchKernel(mode == 0 ? (const void*)extend_stream_kernel<0> : (const void*)extend_stream_kernel<1>, dim3(grid), dim3(RS_BLOCK), args, 0, s);
+}
+int extend_stream_blocks_per_sm(int mode) {
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, mode == 0 ? (const void*)extend_stream_kernel<0> : (const void*)extend_stream_kernel<1>, RS_BLOCK, 0);
+    return n > 0 ? n : 1;
 }
 template <int TIER, int SET>
 static void launch_shade_t(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int grid, const DebugOut& d, int has_dbg, cudaStream_t s) {
@@ -1575,11 +1974,6 @@ void launch_redo_mask(const float* noise, unsigned char* mask, int64_t n, float 
 void launch_fill(float4* p, int64_t n, float4 v, cudaStream_t s) { fill_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(p, n, v); }
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s) {
     quantize_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(px, rgb, n);
-}
-int extend_blocks_per_sm(int mode, int wide) {
-    int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_fn_for(mode, wide), RS_BLOCK, 0);
-    return n > 0 ? n : 1;
 }
 int shade_blocks_per_sm(int generic, int set) { RS_SHADE_DISPATCH(shade_occupancy_t); }
 

@@ -111,7 +111,7 @@ inline uint32_t div_magic(uint32_t d) { return d <= 1u ? 0xffffffffu : (uint32_t
 // launchers (kernels.cu)
 void launch_raygen(const FrameParams& fp, const WaveState& ws, cudaStream_t s);
 void launch_extend(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int wide, int miss_in_extend, int grid,
-                   cudaStream_t s);
+                   int stage_bytes, cudaStream_t s);
 void launch_shade(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int generic, int set, int grid, const DebugOut* dbg, cudaStream_t s);
 void launch_probe_primary(const DScene& S, const FrameParams& fp, const WaveState& ws, const DebugOut& dbg, cudaStream_t s);
 void launch_accumulate(const FrameParams& fp, const WaveState& ws, float4* accum, cudaStream_t s);
@@ -127,9 +127,14 @@ void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaS
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);
 void launch_redo_mask(const float* noise, unsigned char* mask, int64_t n, float t, unsigned long long* count, cudaStream_t s);
 void launch_fill(float4* p, int64_t n, float4 v, cudaStream_t s);
-void launch_extend_first(const DScene& S, const FrameParams& fp, const WaveState& ws, int mode, int grid, cudaStream_t s);
-int extend_first_blocks_per_sm(int mode);
-int extend_blocks_per_sm(int mode, int wide);
+void launch_extend_first(const DScene& S, const FrameParams& fp, const WaveState& ws, int mode, int grid, int stage_bytes, cudaStream_t s);
+#define RS_STAGE_MAX_BYTES (100 * 1024)  // tree + sphere table a staged block may hold (two blocks of 512 threads per SM)
+// stage_bytes > 0 selects the kernels that keep the tree + sphere table in shared memory; 0 blocks = they do not fit
+int extend_first_blocks_per_sm(int mode, int stage_bytes);
+int extend_blocks_per_sm(int mode, int wide, int stage_bytes);
+// the streaming form of extend (lean modes, binary tree, bounces >= 1): per-lane traversal state, dynamic ray fetch
+void launch_extend_stream(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int miss_in_extend, int grid, cudaStream_t s);
+int extend_stream_blocks_per_sm(int mode);
 int shade_blocks_per_sm(int generic, int set);
 int shade_split_trees();  // tier-2 scenes launch the Lambertian hits separately (RS_TUNE_SPLIT_TREES)
 

@@ -91,6 +91,8 @@ struct DScene {
     const BvhNode* bvh2;         // binary tree (default)
     int bvh_root;                // >= 0 node, < 0 single leaf ref
     int n_roots;
+    uint32_t bvh2_bytes;         // size of the binary tree and of the sphere table (16-byte multiples): what the
+    uint32_t sphere_bytes;       // staged extend kernels copy into shared memory (0 = not staged)
     const float4* root_list;     // objects searched as a list before the tree: (lo.xyz, bits of the leaf ref), (hi.xyz, 1 = never dropped by distance)
     int n_list;                  // unbounded objects; in small worlds every object (then bvh_root is the sentinel: no tree)
     const int* root_node;        // node index or ~triangle
@@ -104,7 +106,7 @@ struct DScene {
     const double* root_bbox;     // 6 per root (reference bbox, for the gate)
     const unsigned char* root_gate;
     ObjPrograms obj;             // programs of the ROOT_GENERIC objects (expression trees)
-    const double* tri_geom;      // 9 per triangle: p0.xyz, (a,b,c) = p0-p1, (d,e,f) = p0-p2
+    const double2* tri_geom;     // RS_TRI_STRIDE per triangle (load_triangle)
     const double* tri_normals;   // 9 per triangle
     const int* tri_material;
     const int* lights;
@@ -415,17 +417,46 @@ static __device__ __noinline__ bool hit_quadric(const rs_node& n, const Ray& ray
     return true;
 }
 
-// triangle_mesh.rs:85-131.  g = p0,(a,b,c),(d,e,f).  Returns t, beta, gamma.
-__device__ __forceinline__ bool triangle_test(const double* g, const Ray& ray, double lo, double hi, double& t, double& beta, double& gamma) {
-    const double a = g[3], b = g[4], c = g[5], d = g[6], e = g[7], f = g[8];
+// One triangle: 80 bytes read as five 128-bit ld.global.nc — p0.xyz, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2
+// (triangle_mesh.rs:51-56) and, in the spare word, the world object the triangle is (its root id).
+#define RS_TRI_STRIDE 5  // double2 per triangle
+struct TriGeom {
+    double p0x, p0y, p0z, a, b, c, d, e, f;
+    int root;
+};
+__device__ __forceinline__ TriGeom load_triangle(const double2* tri_geom, int tri) {
+    const double2* g = tri_geom + (size_t)RS_TRI_STRIDE * (size_t)tri;
+    const double2 q0 = __ldg(g), q1 = __ldg(g + 1), q2 = __ldg(g + 2), q3 = __ldg(g + 3), q4 = __ldg(g + 4);
+    TriGeom T;
+    T.p0x = q0.x; T.p0y = q0.y; T.p0z = q1.x;
+    T.a = q1.y; T.b = q2.x; T.c = q2.y;
+    T.d = q3.x; T.e = q3.y; T.f = q4.x;
+    T.root = __double2loint(q4.y);
+    return T;
+}
+
+// triangle_mesh.rs:85-131.  Returns t, beta, gamma.
+// QUICK = true (extend; most tested triangles are missed) first rejects on the SIGNS and MAGNITUDES of the
+// numerators, without a division: for finite, nonzero operands fl(n / d) < 0 <=> n, d differ in sign and
+// fl(n / d) >= 1 <=> |n| >= |d| (two doubles n < d differ by at least half an ulp of 1 in ratio, and such a
+// quotient never rounds up to 1), so the outcome is the reference's.  Whatever is not rejected that way runs the
+// reference's own sequence (divide, then compare) unchanged.
+template <bool QUICK = false>
+__device__ __forceinline__ bool triangle_test(const TriGeom& T, const Ray& ray, double lo, double hi, double& t, double& beta, double& gamma) {
+    const double a = T.a, b = T.b, c = T.c, d = T.d, e = T.e, f = T.f;
     const double gg = ray.d.x, hh = ray.d.y, ii = ray.d.z;
-    const double j = g[0] - ray.o.x, k = g[1] - ray.o.y, l = g[2] - ray.o.z;
+    const double j = T.p0x - ray.o.x, k = T.p0y - ray.o.y, l = T.p0z - ray.o.z;
     double eihf = e * ii - hh * f, gfdi = gg * f - d * ii, dheg = d * hh - e * gg;
     double denom = a * eihf + b * gfdi + c * dheg;
-    beta = (j * eihf + k * gfdi + l * dheg) / denom;
-    if (beta < 0.0 || beta >= 1.0) return false;
+    const double nb = j * eihf + k * gfdi + l * dheg;
+    const bool plain = denom != 0.0 && fabs(denom) <= RS_F64_MAX;  // (false for NaN too)
+    if (QUICK && plain && nb != 0.0 && fabs(nb) <= RS_F64_MAX && ((nb < 0.0) != (denom < 0.0) || fabs(nb) >= fabs(denom))) return false;
     double akjb = a * k - j * b, jcal = j * c - a * l, blkc = b * l - k * c;
-    gamma = (ii * akjb + hh * jcal + gg * blkc) / denom;
+    const double ng = ii * akjb + hh * jcal + gg * blkc;
+    if (QUICK && plain && fabs(ng) <= RS_F64_MAX && (ng == 0.0 || (ng < 0.0) != (denom < 0.0))) return false;
+    beta = nb / denom;
+    if (beta < 0.0 || beta >= 1.0) return false;
+    gamma = ng / denom;
     if (gamma <= 0.0 || beta + gamma >= 1.0) return false;
     t = -(f * akjb + e * jcal + d * blkc) / denom;
     return t >= lo && t <= hi;  // inclusive on both ends (triangle_mesh.rs:114)
@@ -1117,7 +1148,10 @@ __device__ __forceinline__ float4 background(const DScene& S, V3 dir) {
     double slide = (dir.y + 1.0) * 0.5;
     float a = (float)fmin(fmax(slide, 0.0), 1.0);
     float b = 1.0f - a;
-    return make_float4(S.bg0.x * b + S.bg1.x * a, S.bg0.y * b + S.bg1.y * a, S.bg0.z * b + S.bg1.z * a, 1.0f);
+    // two products and a sum, each rounded (Rust never fuses; left to the compiler, which product of `x*b + y*a` ends
+    // up inside the FMA depends on the kernel the function is inlined into)
+    return make_float4(__fadd_rn(__fmul_rn(S.bg0.x, b), __fmul_rn(S.bg1.x, a)), __fadd_rn(__fmul_rn(S.bg0.y, b), __fmul_rn(S.bg1.y, a)),
+                       __fadd_rn(__fmul_rn(S.bg0.z, b), __fmul_rn(S.bg1.z, a)), 1.0f);
 }
 
 }  // namespace rsd
