@@ -167,6 +167,9 @@ def scene_bytes(desc):
             d.n_materials * C.sizeof(_abi.RsMaterial) + d.n_textures * C.sizeof(_abi.RsTexture) + d.n_texel_bytes + d.n_perlin_perm * 4 + d.n_perlin_values * 8)
 
 
+DEFAULT_WAVE_PATHS = 1 << 25  # csrc/backend.cu render_into: paths in flight per wave when rs_render_params.max_wave_paths is 0
+
+
 def load_bench_scene(name):
     """rtow_final (the headline workload) or another BASELINE.json config: an .sdl file name under
     tests/golden/sdl (example, quadric, csg, declares, transforms), cornell, mesh:<grid>, mesh_blinn:<grid>."""
@@ -311,7 +314,7 @@ def run_gpu(args):
         shares = {"extend": kt.ms_extend, "shade": kt.ms_shade, "raygen": kt.ms_raygen, "accumulate": kt.ms_accumulate}
         dom = max(("extend", "shade"), key=lambda k: shares[k])
         # waves of one render (the partition of render_into, csrc/backend.cu): P pixels x K samples each
-        cap = max(args.wave or (1 << 23), 1024)
+        cap = max(args.wave or DEFAULT_WAVE_PATHS, 1024)
         s_total = (r1 - r0) * q
         P = min(width * height, cap)
         K = max(1, min(s_total, cap // P))
@@ -330,8 +333,8 @@ def run_gpu(args):
                        else f"{args.scene} {width}x{height} {q * q} spp depth 8 (not the headline workload)",
                        "parallelism": f"strata-rows x{world_size}",
                        "combine": ("none (single GPU: finalize only)" if world_size == 1 else
-                                   ("fused reduce+finalize kernel over NVLink peer memory" if args.reduce == "peer" else "ncclReduce + finalize")), "l2": "path/ray/hit buffers of one wave (>1.5 GB) exceed the 126 MB L2; no flush needed",
-                       "wave_paths": args.wave or (1 << 23)},
+                                   ("fused reduce+finalize kernel over NVLink peer memory" if args.reduce == "peer" else "ncclReduce + finalize")), "l2": "path/ray/hit buffers of one wave (> 6 GB at 32 Mi paths) exceed the 126 MB L2; no flush needed",
+                       "wave_paths": args.wave or DEFAULT_WAVE_PATHS, "wave_streams": args.wave_streams},
             "mrays_per_s": n_segments / (ms_total / args.steps / 1e3) / 1e6,
             "segments_per_sample": n_segments / max(n_samples, 1.0),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
@@ -371,7 +374,7 @@ def main():
     ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"],
                     help="N > 1 combine step: peer = fused reduce+finalize kernel over NVLink peer memory (default); nccl = ncclReduce + finalize")
     ap.add_argument("--bvh-width", type=int, default=2, choices=[2, 4], help="world BVH: 2 = binary (default), 4 = QBVH")
-    ap.add_argument("--wave-streams", type=int, default=2, choices=[1, 2, 3, 4], help="streams consecutive waves rotate over")
+    ap.add_argument("--wave-streams", type=int, default=4, choices=[1, 2, 3, 4], help="streams consecutive waves rotate over")
     ap.add_argument("--scene", default="rtow_final", help="other BASELINE.json configs (see load_bench_scene); default = headline")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -163,6 +163,7 @@ __device__ __forceinline__ double2 lds_d2(uint32_t a) {
     asm("ld.shared.v2.f64 {%0, %1}, [%2];\n" : "=d"(v.x), "=d"(v.y) : "r"(a));
     return v;
 }
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];\n" ::"l"(p)); }
 // where the staged kernels keep the tree and the sphere table (shared-space addresses)
 struct Staged {
     uint32_t nodes, spheres;
@@ -884,13 +885,28 @@ __global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE 
 #ifndef RS_TUNE_STREAM_BLOCKS
 #define RS_TUNE_STREAM_BLOCKS 4
 #endif
+#ifndef RS_TUNE_STREAM_PREFETCH
+#define RS_TUNE_STREAM_PREFETCH 0
+#endif
+#ifndef RS_TUNE_STREAM_SSTACK
+#define RS_TUNE_STREAM_SSTACK 8  // stack entries per thread kept in shared memory (power of two)
+#endif
+#define RS_STREAM_SMEM ((RS_BLOCK / 32) * 64 * sizeof(uint4) + 6 * RS_BLOCK * sizeof(double) + RS_TUNE_STREAM_SSTACK * RS_BLOCK * sizeof(unsigned long long))
 template <int MODE>
 __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp,
                                                                                         const __grid_constant__ WaveState ws, const int bounce,
                                                                                         const int miss_in_extend) {
     static_assert(MODE < 2, "lean scenes only");
-    __shared__ uint4 done_queue[RS_BLOCK / 32][64];  // (ray index, object, t) of finished rays awaiting their epilogue
-    uint4* const queue = done_queue[threadIdx.x >> 5];
+    // shared memory of a block: the queues of finished rays awaiting their epilogue (per warp: 64 x (ray index,
+    // object, t)), every thread's f64 ray (what a triangle test needs) and the TOP RS_TUNE_STREAM_SSTACK entries of
+    // every thread's traversal stack.  All per-thread arrays are laid out [entry][thread]: a lane owns its banks,
+    // so a warp's access is conflict-free whatever entry each lane is at — where the same stack in local memory
+    // costs one L1 sector access per lane and push or pop (ncu, 1 M-triangle mesh: 22 % of all L1 sector accesses,
+    // on a kernel whose L1 runs at 76 % of peak).
+    extern __shared__ __align__(16) unsigned char stream_smem[];
+    uint4* const queue = reinterpret_cast<uint4*>(stream_smem) + 64 * (threadIdx.x >> 5);
+    double* const sray = reinterpret_cast<double*>(stream_smem + (RS_BLOCK / 32) * 64 * sizeof(uint4)) + threadIdx.x;  // [6][RS_BLOCK]
+    unsigned long long* const sstack = reinterpret_cast<unsigned long long*>(stream_smem + (RS_BLOCK / 32) * 64 * sizeof(uint4) + 6 * RS_BLOCK * sizeof(double)) + threadIdx.x;  // [SSTACK][RS_BLOCK]
     const uint32_t nf = ws.ctr->n_rays[bounce], nb = ws.ctr->n_back[bounce];
     const uint32_t nf32 = (nf + 31u) & ~31u;
     const uint32_t n = nf32 + nb;
@@ -906,8 +922,9 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
     const float slack = (1.0f + RS_SLAB_EPS) * (1.0f + RS_SLAB_EPS);
 
     // per-lane traversal state
+    // entries [lo, sp) of the stack live in shared memory (slot = index mod RS_TUNE_STREAM_SSTACK), [0, lo) in local memory
     unsigned long long stack[RS_STACK];
-    int sp = 0, node = RS_BVH_SENTINEL;
+    int sp = 0, lo = 0, node = RS_BVH_SENTINEL;
     bool has_ray = false;
     uint32_t i = 0;
     float idx = 0.f, idy = 0.f, idz = 0.f, oodx = 0.f, oody = 0.f, oodz = 0.f, tmax_f = FLT_MAX;
@@ -1002,9 +1019,18 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
         }
     };
 
+#define RS_SSLOT(k) sstack[((k) & (RS_TUNE_STREAM_SSTACK - 1)) * RS_BLOCK]
+#define RS_PUSH(e)                                                                 \
+    do {                                                                           \
+        if (sp - lo == RS_TUNE_STREAM_SSTACK) { stack[lo] = RS_SSLOT(lo); ++lo; }  \
+        RS_SSLOT(sp) = (e);                                                        \
+        ++sp;                                                                      \
+    } while (false)
 #define RS_POP()                                                                   \
     do {                                                                           \
-        const unsigned long long e_ = stack[--sp];                                 \
+        --sp;                                                                      \
+        const unsigned long long e_ = RS_SSLOT(sp);                                \
+        if (sp == lo && lo > 0) { --lo; RS_SSLOT(lo) = stack[lo]; }                \
         node = (int)(uint32_t)e_;                                                  \
         if (!(__uint_as_float((uint32_t)(e_ >> 32) & ~3u) > tmax_f)) break;        \
     } while (true)
@@ -1048,10 +1074,12 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
                 i = v < nf32 ? v : ws.capacity - 1u - (v - nf32);
                 const uint4* rec = in.rec + 4 * (size_t)i;
                 const uint4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
-                const float ox = (float)__hiloint2double((int)q0.y, (int)q0.x), oy = (float)__hiloint2double((int)q0.w, (int)q0.z),
-                            oz = (float)__hiloint2double((int)q1.y, (int)q1.x);
-                float dx = (float)__hiloint2double((int)q1.w, (int)q1.z), dy = (float)__hiloint2double((int)q2.y, (int)q2.x),
-                      dz = (float)__hiloint2double((int)q2.w, (int)q2.z);
+                const double o0 = __hiloint2double((int)q0.y, (int)q0.x), o1 = __hiloint2double((int)q0.w, (int)q0.z), o2 = __hiloint2double((int)q1.y, (int)q1.x);
+                const double d0 = __hiloint2double((int)q1.w, (int)q1.z), d1 = __hiloint2double((int)q2.y, (int)q2.x), d2 = __hiloint2double((int)q2.w, (int)q2.z);
+                sray[0] = o0; sray[RS_BLOCK] = o1; sray[2 * RS_BLOCK] = o2;
+                sray[3 * RS_BLOCK] = d0; sray[4 * RS_BLOCK] = d1; sray[5 * RS_BLOCK] = d2;
+                const float ox = (float)o0, oy = (float)o1, oz = (float)o2;
+                float dx = (float)d0, dy = (float)d1, dz = (float)d2;
                 const float tiny = 1e-20f;
                 dx = fabsf(dx) > tiny ? dx : copysignf(tiny, dx);
                 dy = fabsf(dy) > tiny ? dy : copysignf(tiny, dy);
@@ -1061,8 +1089,9 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
                 tmax_f = FLT_MAX;
                 best.t = inf; best.root = -1;
                 has_ray = true;
-                stack[0] = (unsigned long long)(uint32_t)RS_BVH_SENTINEL;
+                RS_SSLOT(0) = (unsigned long long)(uint32_t)RS_BVH_SENTINEL;
                 sp = 1;
+                lo = 0;
                 node = S.n_roots ? S.bvh_root : RS_BVH_SENTINEL;
             }
         }
@@ -1089,7 +1118,13 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
                     const bool swap = near1 < near0;
                     const int second = swap ? ch.x : ch.y;
                     const float second_near = swap ? near0 : near1;
-                    if (sp < RS_STACK) stack[sp++] = ((unsigned long long)__float_as_uint(second_near) << 32) | (unsigned long long)(uint32_t)second;
+                    if (sp < RS_STACK) RS_PUSH(((unsigned long long)__float_as_uint(second_near) << 32) | (unsigned long long)(uint32_t)second);
+#if RS_TUNE_STREAM_PREFETCH
+                    // the walk is bound by the latency of its dependent node fetches (ncu: long_scoreboard 56 % of the
+                    // stall samples at 8 warps per scheduler): start the fetch of the postponed child now
+                    if (second >= 0) prefetch_l1(S.bvh2 + second);
+                    else if (RS_TUNE_STREAM_PREFETCH >= 2 && MODE == 1 && ((~second) & 3) == ROOT_TRIANGLE) prefetch_l1(S.tri_geom + (size_t)RS_TRI_STRIDE * (size_t)((~second) >> 2));
+#endif
                     node = swap ? ch.y : ch.x;
                 } else if (h0) {
                     node = ch.x;
@@ -1103,11 +1138,9 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
             const uint32_t lm = __ballot_sync(0xffffffffu, at_leaf), im = __ballot_sync(0xffffffffu, node >= 0);
             if (lm && (__popc(lm) >= RS_TUNE_STREAM_LEAF || im == 0u)) {
                 if (at_leaf) {
-                    const uint4* rec = in.rec + 4 * (size_t)i;
-                    const uint4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
                     Ray ray;
-                    ray.o = v3(__hiloint2double((int)q0.y, (int)q0.x), __hiloint2double((int)q0.w, (int)q0.z), __hiloint2double((int)q1.y, (int)q1.x));
-                    ray.d = v3(__hiloint2double((int)q1.w, (int)q1.z), __hiloint2double((int)q2.y, (int)q2.x), __hiloint2double((int)q2.w, (int)q2.z));
+                    ray.o = v3(sray[0], sray[RS_BLOCK], sray[2 * RS_BLOCK]);
+                    ray.d = v3(sray[3 * RS_BLOCK], sray[4 * RS_BLOCK], sray[5 * RS_BLOCK]);
                     ray.time = 0.0;
                     test_root<MODE>(S, ~node, ray, no_rng, best);
                     tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
@@ -1122,6 +1155,8 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
         }
     }
 #undef RS_POP
+#undef RS_PUSH
+#undef RS_SSLOT
     // the rays still queued
     if (queued) {
         const bool live = lane < queued;
@@ -1908,13 +1943,16 @@ int extend_blocks_per_sm(int mode, int wide, int stage_bytes) {
     const int n = extend_occupancy(extend_fn_for(mode, wide, stage_bytes > 0), stage_bytes);
     return n > 0 ? n : (stage_bytes > 0 ? 0 : 1);
 }
+static const void* extend_stream_fn(int mode) { return mode == 0 ? (const void*)extend_stream_kernel<0> : (const void*)extend_stream_kernel<1>; }
 void launch_extend_stream(const DScene& S, const FrameParams& fp, const WaveState& ws, int bounce, int mode, int miss_in_extend, int grid, cudaStream_t s) {
     void* args[] = {(void*)&S, (void*)&fp, (void*)&ws, (void*)&bounce, (void*)&miss_in_extend};
-    cudaLaunchKernel(mode == 0 ? (const void*)extend_stream_kernel<0> : (const void*)extend_stream_kernel<1>, dim3(grid), dim3(RS_BLOCK), args, 0, s);
+    cudaLaunchKernel(extend_stream_fn(mode), dim3(grid), dim3(RS_BLOCK), args, RS_STREAM_SMEM, s);
 }
 int extend_stream_blocks_per_sm(int mode) {
     int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, mode == 0 ? (const void*)extend_stream_kernel<0> : (const void*)extend_stream_kernel<1>, RS_BLOCK, 0);
+    cudaFuncSetAttribute(extend_stream_fn(mode), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_STREAM_SMEM);
+    cudaFuncSetAttribute(extend_stream_fn(mode), cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, extend_stream_fn(mode), RS_BLOCK, RS_STREAM_SMEM);
     return n > 0 ? n : 1;
 }
 template <int TIER, int SET>

@@ -1,0 +1,12 @@
+#!/bin/bash
+# headline A/B with extra bench args at 64 spp: "label|ENV|_variant|args"
+for spec in "$@"; do
+  IFS='|' read -r label envs variant extra <<< "$spec"
+  L=$PWD/raysnail_b200/libraysnail_b200$variant.so
+  env $envs RAYSNAIL_B200_LIB=$L python bench.py --steps 3 --warmup 2 --no-cpu --sqrt-spp 8 $extra 2>&1 | tail -1 | python -c "
+import json,sys
+try:
+    d=json.loads(sys.stdin.read()); k=d['roofline']['kernel_ms_per_step']
+    print('[head $label]', round(d['value']/1e6,1), 'Msamples/s', round(d['ms_per_step'],2), 'ms/step', {a:round(b,2) for a,b in k.items()})
+except Exception as e: print('[head $label] FAILED', e)"
+done
