@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RS_ABI_VERSION 2
+#define RS_ABI_VERSION 3
 
 typedef enum rs_status {
     RS_OK = 0,
@@ -240,7 +240,7 @@ const char* rs_last_error(const rs_ctx* ctx);
  * 64-byte nodes, 4 = QBVH of 128-byte nodes (both give identical hits; see DESIGN.md for the
  * measured trade-off).  */
 #define RS_OPT_BVH_WIDTH 1
-/* RS_OPT_WAVE_STREAMS: n in 1..4 (default 2) = consecutive waves rotate over the caller's stream and
+/* RS_OPT_WAVE_STREAMS: n in 1..4 (default 4) = consecutive waves rotate over the caller's stream and
  * n-1 internal ones, so the tail of each persistent kernel overlaps with another wave's work (the image
  * is bit-identical: accumulation stays in wave order); 1 = every kernel on the caller's stream. */
 #define RS_OPT_WAVE_STREAMS 2
@@ -359,6 +359,30 @@ int rs_debug_primary(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
 int rs_debug_scatter(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* params,
                      int32_t sample_index, int32_t* kind, double* next_od6, double* weight3,
                      double* emitted3);
+
+/* ---- several devices behind one call (replaces the caller-side fan-out a multi-GPU
+ * `Camera::take_photo` — camera.rs:283-330 is the single-device loop — would otherwise need) ------------
+ * One process, one host thread per device.  The scene is replicated; the strata rows
+ * [stratum_row_begin, stratum_row_end) of `params` are split evenly over the devices, every device
+ * sum-reduces and finalizes its slice of the pixels out of all accumulators (NVLink peer memory) into
+ * device 0's image.  The devices order themselves with arrival counters in device 0's memory — no host
+ * barrier between render and combine.  device_ids may name a device twice (separate contexts on one GPU). */
+typedef struct rs_multi rs_multi;
+int rs_create_multi(rs_multi** out, const int32_t* device_ids, int32_t n);
+void rs_destroy_multi(rs_multi* m);
+const char* rs_multi_last_error(const rs_multi* m); /* m may be NULL: error of the last failed rs_create_multi */
+int rs_multi_device_count(const rs_multi* m);
+int rs_multi_set_option(rs_multi* m, int option, int value);
+int rs_multi_upload_scene(rs_multi* m, const rs_scene_desc* scene);
+/* out_rgba: HOST, width*height*4 floats (as rs_render).  stats_sum (may be NULL): counters summed over devices. */
+int rs_multi_render(rs_multi* m, const rs_camera* cam, const rs_render_params* params, const uint8_t* pixel_mask,
+                    float* out_rgba, rs_stats* stats_sum);
+/* The counters themselves, for callers that run one PROCESS per device (torchrun): d_counter is a uint32 in
+ * memory every rank mapped (rs_device_alloc on one rank + rs_ipc_export / rs_ipc_open on the others).
+ * rs_signal: when everything queued on `stream` so far is done and visible system-wide, counter += 1.
+ * rs_wait_counter: work queued on `stream` after this call starts once counter >= expect (wrap-safe). */
+int rs_signal(rs_ctx* ctx, uint32_t* d_counter, void* stream);
+int rs_wait_counter(rs_ctx* ctx, const uint32_t* d_counter, uint32_t expect, void* stream);
 
 int rs_get_stats(const rs_ctx* ctx, rs_stats* out);
 

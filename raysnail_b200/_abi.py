@@ -26,6 +26,8 @@ CORE_SYMBOLS = [
     "rs_debug_primary", "rs_debug_scatter", "rs_get_stats",
     "rs_device_alloc", "rs_device_free", "rs_ipc_export", "rs_ipc_open", "rs_ipc_close", "rs_finalize_peers",
     "rs_render_passes", "rs_pass_seed", "rs_philox4x32_10", "rs_philox_uniform",
+    "rs_create_multi", "rs_destroy_multi", "rs_multi_last_error", "rs_multi_device_count", "rs_multi_set_option",
+    "rs_multi_upload_scene", "rs_multi_render", "rs_signal", "rs_wait_counter",
 ]
 # every symbol include/raysnail_b200_host.h declares
 HOST_SYMBOLS = [
@@ -145,6 +147,15 @@ def load() -> C.CDLL:
     proto("rs_finalize_peers", C.c_int, vp, P(vp), i32, vp, vp, C.c_int64, C.c_int64, i32, i32, vp)
     proto("rs_render_passes", C.c_int, vp, P(RsCamera), P(RsRenderParams), i32, i32, f32, vp, vp, vp)
     proto("rs_pass_seed", C.c_uint64, C.c_uint64, i32)
+    proto("rs_create_multi", C.c_int, P(vp), P(i32), i32)
+    proto("rs_destroy_multi", None, vp)
+    proto("rs_multi_last_error", C.c_char_p, vp)
+    proto("rs_multi_device_count", i32, vp)
+    proto("rs_multi_set_option", C.c_int, vp, C.c_int, C.c_int)
+    proto("rs_multi_upload_scene", C.c_int, vp, P(RsSceneDesc))
+    proto("rs_multi_render", C.c_int, vp, P(RsCamera), P(RsRenderParams), vp, vp, P(RsStats))
+    proto("rs_signal", C.c_int, vp, vp, vp)
+    proto("rs_wait_counter", C.c_int, vp, vp, C.c_uint32, vp)
     proto("rs_philox4x32_10", C.c_int, vp, vp, vp)
     proto("rs_philox_uniform", C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp)
 

@@ -359,6 +359,14 @@ class Renderer:
         self._ck(self._lib.rs_finalize_peers(self._ctx, arr, len(d_accums), d_mask, d_out, int(pixel_begin), int(pixel_end), int(n_samples),
                                              int(gamma), stream), "rs_finalize_peers")
 
+    def signal(self, d_counter: int, stream: int = 0):
+        """rs_signal: counter += 1 (release, system scope) once the work queued on `stream` so far is done."""
+        self._ck(self._lib.rs_signal(self._ctx, int(d_counter), stream), "rs_signal")
+
+    def wait_counter(self, d_counter: int, expect: int, stream: int = 0):
+        """rs_wait_counter: work queued on `stream` after this starts once the counter has reached `expect`."""
+        self._ck(self._lib.rs_wait_counter(self._ctx, int(d_counter), int(expect) & 0xffffffff, stream), "rs_wait_counter")
+
     def render_passes(self, cam: RsCamera, params: RsRenderParams, n_passes: int, redo_mode: int = 0, threshold: float = 0.01,
                       want_rgb8: bool = False):
         """The CLI's passes loop (src/bin/raysnail.rs:379-427) in one call: (image, redo count per pass[, rgb8])."""
@@ -400,6 +408,61 @@ class Renderer:
         self._ck(self._lib.rs_get_stats(self._ctx, C.byref(s)), "rs_get_stats")
         return s
 
+
+
+class MultiRenderer:
+    """Several CUDA devices behind one call (`rs_multi`): the scene is replicated, the strata rows are
+    split over the devices, the image is combined on device 0 over NVLink peer memory."""
+
+    def __init__(self, devices: Sequence[int]):
+        self._lib = _abi.load()
+        self._m = C.c_void_p()
+        ids = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+        rc = self._lib.rs_create_multi(C.byref(self._m), ids, len(devices))
+        if rc != 0:
+            raise RaysnailError(f"rs_create_multi failed ({rc}): {self._lib.rs_multi_last_error(None).decode()}")
+        self._scene = None
+        self.stats = RsStats()
+
+    def close(self):
+        if getattr(self, "_m", None) and self._m.value:
+            self._lib.rs_destroy_multi(self._m)
+            self._m = C.c_void_p(None)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise RaysnailError(f"{what} failed ({rc}): {self._lib.rs_multi_last_error(self._m).decode()}")
+
+    @property
+    def device_count(self) -> int:
+        return int(self._lib.rs_multi_device_count(self._m))
+
+    def set_option(self, option: int, value: int):
+        self._ck(self._lib.rs_multi_set_option(self._m, int(option), int(value)), "rs_multi_set_option")
+
+    def upload(self, scene: Scene):
+        self._ck(self._lib.rs_multi_upload_scene(self._m, scene.desc), "rs_multi_upload_scene")
+        self._scene = scene
+
+    def render(self, cam: RsCamera, params: RsRenderParams, mask: Optional[np.ndarray] = None, out: Optional[np.ndarray] = None) -> np.ndarray:
+        h, w = cam.height, cam.width
+        if out is None:
+            out = np.empty((h, w, 4), dtype=np.float32)
+        mptr = None
+        if mask is not None:
+            mask = np.ascontiguousarray(mask, dtype=np.uint8)
+            mptr = mask.ctypes.data
+        self._ck(self._lib.rs_multi_render(self._m, C.byref(cam), C.byref(params), mptr, out.ctypes.data, C.byref(self.stats)), "rs_multi_render")
+        return out
+
+    def render_to_ptr(self, cam, params, mask_ptr, out_ptr):
+        self._ck(self._lib.rs_multi_render(self._m, C.byref(cam), C.byref(params), mask_ptr, out_ptr, C.byref(self.stats)), "rs_multi_render")
 
 class TakePhotoSettings:
     """`TakePhotoSettings` (src/camera.rs:103-154): camera.take_photo().samples(n).depth(d).shot(world)."""

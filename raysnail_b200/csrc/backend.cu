@@ -14,6 +14,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/raysnail_b200.h"
@@ -1600,6 +1601,249 @@ int rs_debug_scatter(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* 
     void* host[11] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, kind, next_od6, weight3, emitted3};
     const size_t eb[11] = {4, 8, 24, 24, 4, 4, 48, 4, 48, 24, 24};
     return run_probe(ctx, cam, p, sample_index, true, host, eb);
+}
+
+// ---------------------------------------------------------------------------------------------
+// several devices behind one call: the scene is replicated, the strata rows of
+// every pixel are split across the devices, every device sum-reduces + finalizes its slice of
+// the pixels out of all accumulators over NVLink peer memory into device 0's image.  One host
+// thread per device enqueues; the devices order themselves with arrival counters in device 0's
+// memory (signal_kernel / wait_counter_kernel) — no host barrier between render and combine.
+// ---------------------------------------------------------------------------------------------
+}  // extern "C"
+
+struct rs_multi {
+    std::vector<rs_ctx*> ctx;
+    std::vector<int> device;
+    std::vector<cudaStream_t> stream;
+    std::vector<DevBuf> accum, mask;
+    DevBuf out0, counters;  // device 0: the image; [0] = accumulators complete, [1] = slices written
+    uint32_t epoch = 0;
+    std::string error;
+};
+
+namespace {
+int multi_fail(rs_multi* m, int code, const std::string& msg) {
+    if (m) m->error = msg;
+    else g_create_error = msg;
+    return code;
+}
+// run f(k) for every device on its own host thread; first non-zero return wins
+template <class F>
+int for_each_device(rs_multi* m, F f) {
+    const int n = (int)m->ctx.size();
+    std::vector<int> rc(n, RS_OK);
+    std::vector<std::thread> th;
+    for (int k = 1; k < n; ++k) th.emplace_back([&, k] { rc[k] = f(k); });
+    rc[0] = f(0);
+    for (auto& t : th) t.join();
+    for (int k = 0; k < n; ++k)
+        if (rc[k] != RS_OK) return multi_fail(m, rc[k], "device " + std::to_string(m->device[k]) + ": " + rs_last_error(m->ctx[k]));
+    return RS_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int rs_create_multi(rs_multi** out, const int32_t* device_ids, int32_t n) {
+    if (!out || !device_ids || n <= 0 || n > RS_MAX_PEERS) return multi_fail(nullptr, RS_ERR_INVALID_ARGUMENT, "rs_create_multi: 1..16 devices");
+    *out = nullptr;
+    rs_multi* m = new rs_multi();
+    m->device.assign(device_ids, device_ids + n);
+    m->ctx.assign(n, nullptr);
+    m->stream.assign(n, nullptr);
+    m->accum.resize(n);
+    m->mask.resize(n);
+    for (int k = 0; k < n; ++k) {
+        int rc = rs_create(&m->ctx[k], m->device[k]);
+        if (rc != RS_OK) {
+            const std::string why = g_create_error;
+            rs_destroy_multi(m);
+            return multi_fail(nullptr, rc, why);
+        }
+    }
+    // every device reads every accumulator and writes device 0's image and counters
+    for (int a = 0; a < n; ++a)
+        for (int b = 0; b < n; ++b) {
+            if (m->device[a] == m->device[b]) continue;  // (the same device listed twice: separate contexts, no peer mapping needed)
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, m->device[a], m->device[b]);
+            if (!can) {
+                rs_destroy_multi(m);
+                return multi_fail(nullptr, RS_ERR_UNSUPPORTED, "devices " + std::to_string(device_ids[a]) + " and " + std::to_string(device_ids[b]) + " are not peers");
+            }
+            cudaSetDevice(m->device[a]);
+            cudaError_t e = cudaDeviceEnablePeerAccess(m->device[b], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                rs_destroy_multi(m);
+                return multi_fail(nullptr, RS_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+            }
+            cudaGetLastError();
+        }
+    // A device listed more than once (a test set-up): its contexts share the device's hardware queues, and a
+    // wait kernel that spins at the head of a queue another context's render also maps to would never see
+    // that render finish.  One stream per such context keeps every stream on a queue of its own
+    // (8 per device by default).
+    for (int k = 0; k < n; ++k) {
+        int same = 0;
+        for (int j = 0; j < n; ++j) same += m->device[j] == m->device[k];
+        if (same > 4) {
+            rs_destroy_multi(m);
+            return multi_fail(nullptr, RS_ERR_INVALID_ARGUMENT, "rs_create_multi: a device may be listed at most 4 times");
+        }
+        if (same > 1) rs_set_option(m->ctx[k], RS_OPT_WAVE_STREAMS, 1);
+    }
+    for (int k = 0; k < n; ++k) {
+        cudaSetDevice(m->device[k]);
+        if (cudaStreamCreateWithFlags(&m->stream[k], cudaStreamNonBlocking) != cudaSuccess) {
+            rs_destroy_multi(m);
+            return multi_fail(nullptr, RS_ERR_CUDA, "cudaStreamCreate failed");
+        }
+    }
+    cudaSetDevice(m->device[0]);
+    if (m->counters.ensure(2 * sizeof(uint32_t)) != cudaSuccess || cudaMemset(m->counters.p, 0, 2 * sizeof(uint32_t)) != cudaSuccess) {
+        rs_destroy_multi(m);
+        return multi_fail(nullptr, RS_ERR_CUDA, "counter allocation failed");
+    }
+    *out = m;
+    return RS_OK;
+}
+
+void rs_destroy_multi(rs_multi* m) {
+    if (!m) return;
+    for (size_t k = 0; k < m->ctx.size(); ++k) {
+        cudaSetDevice(m->device[k]);
+        if (m->stream[k]) { cudaStreamSynchronize(m->stream[k]); cudaStreamDestroy(m->stream[k]); }
+        m->accum[k].release();
+        m->mask[k].release();
+    }
+    if (!m->device.empty()) {
+        cudaSetDevice(m->device[0]);
+        m->out0.release();
+        m->counters.release();
+    }
+    for (rs_ctx* c : m->ctx) rs_destroy(c);
+    delete m;
+}
+
+const char* rs_multi_last_error(const rs_multi* m) { return m ? m->error.c_str() : g_create_error.c_str(); }
+int rs_multi_device_count(const rs_multi* m) { return m ? (int)m->ctx.size() : 0; }
+
+int rs_multi_set_option(rs_multi* m, int option, int value) {
+    if (!m) return RS_ERR_INVALID_ARGUMENT;
+    for (size_t k = 0; k < m->ctx.size(); ++k) {
+        if (option == RS_OPT_WAVE_STREAMS) {  // contexts that share a device keep their single stream (rs_create_multi)
+            int same = 0;
+            for (size_t j = 0; j < m->ctx.size(); ++j) same += m->device[j] == m->device[k];
+            if (same > 1) continue;
+        }
+        int rc = rs_set_option(m->ctx[k], option, value);
+        if (rc != RS_OK) return multi_fail(m, rc, rs_last_error(m->ctx[k]));
+    }
+    return RS_OK;
+}
+
+int rs_multi_upload_scene(rs_multi* m, const rs_scene_desc* s) {
+    if (!m || !s) return multi_fail(m, RS_ERR_INVALID_ARGUMENT, "null scene");
+    return for_each_device(m, [&](int k) { return rs_upload_scene(m->ctx[k], s); });
+}
+
+int rs_multi_render(rs_multi* m, const rs_camera* cam, const rs_render_params* p, const uint8_t* pixel_mask, float* out_rgba, rs_stats* stats_sum) {
+    if (!m || !cam || !p || !out_rgba) return multi_fail(m, RS_ERR_INVALID_ARGUMENT, "bad rs_multi_render arguments");
+    const int n = (int)m->ctx.size();
+    for (int k = 0; k < n; ++k) {
+        int rc = check_render_args(m->ctx[k], cam, p);
+        if (rc != RS_OK) return multi_fail(m, rc, rs_last_error(m->ctx[k]));
+    }
+    const size_t np = (size_t)cam->width * cam->height;
+    const int rows0 = p->stratum_row_begin, rows = p->stratum_row_end - p->stratum_row_begin;
+    const int n_total = std::max(rows * p->sqrt_spp, 1);
+    // buffers first (allocation synchronises), so that nothing but launches follows
+    for (int k = 0; k < n; ++k) {
+        cudaSetDevice(m->device[k]);
+        if (m->accum[k].ensure(np * sizeof(float4)) != cudaSuccess || (pixel_mask && m->mask[k].ensure(np) != cudaSuccess))
+            return multi_fail(m, RS_ERR_OUT_OF_MEMORY, "accumulator allocation failed");
+    }
+    cudaSetDevice(m->device[0]);
+    if (m->out0.ensure(np * sizeof(float4)) != cudaSuccess) return multi_fail(m, RS_ERR_OUT_OF_MEMORY, "image allocation failed");
+    const uint32_t expect = (uint32_t)n * ++m->epoch;
+    uint32_t* const arrived = m->counters.as<uint32_t>();
+    uint32_t* const written = arrived + 1;
+    PeerAccums pa;
+    std::memset(&pa, 0, sizeof(pa));
+    pa.n = n;
+    for (int k = 0; k < n; ++k) pa.p[k] = m->accum[k].as<float4>();
+    // Phase 1, every device: enqueue the render.  Whatever allocates happens here (the wave buffers on a first
+    // call): with peer access enabled cudaMalloc synchronises with the peer devices, and it would wait forever for
+    // a peer that already spins in phase 2's wait kernel.  The host threads join before phase 2 — they wait for
+    // each other's ENQUEUE only, the devices keep running.
+    int rc = for_each_device(m, [&](int k) -> int {
+        rs_ctx* ctx = m->ctx[k];
+        cudaStream_t st = m->stream[k];
+        CK(cudaSetDevice(m->device[k]));
+        const unsigned char* d_mask = nullptr;
+        if (pixel_mask) {
+            CK(cudaMemcpyAsync(m->mask[k].p, pixel_mask, np, cudaMemcpyHostToDevice, st));
+            d_mask = m->mask[k].as<unsigned char>();
+        }
+        CK(cudaMemsetAsync(m->accum[k].p, 0, np * sizeof(float4), st));
+        rs_render_params pk = *p;  // this device's strata rows: contiguous, balanced (the split of distributed.py)
+        pk.stratum_row_begin = rows0 + (int)(((int64_t)rows * k) / n);
+        pk.stratum_row_end = rows0 + (int)(((int64_t)rows * (k + 1)) / n);
+        pk.flags &= ~RS_FLAG_KERNEL_TIMING;
+        return render_into(ctx, cam, &pk, d_mask, m->accum[k].as<float4>(), st, false);
+    });
+    if (rc != RS_OK) return rc;
+    // Phase 2, every device: arrive, wait for all accumulators, reduce + finalize this device's slice of the pixels
+    // into device 0's image, arrive again; device 0 waits for all slices and copies the image out.
+    rc = for_each_device(m, [&](int k) -> int {
+        rs_ctx* ctx = m->ctx[k];
+        cudaStream_t st = m->stream[k];
+        CK(cudaSetDevice(m->device[k]));
+        const unsigned char* d_mask = pixel_mask ? m->mask[k].as<unsigned char>() : nullptr;
+        launch_signal(arrived, st);
+        launch_wait_counter(arrived, expect, st);
+        const int64_t per = ((((int64_t)np + n - 1) / n) + 15) / 16 * 16;
+        const int64_t b = std::min<int64_t>((int64_t)np, k * per), e = std::min<int64_t>((int64_t)np, (k + 1) * per);
+        launch_finalize_peers(pa, d_mask, m->out0.as<float4>(), b, e, n_total, p->gamma, st);
+        launch_signal(written, st);
+        CK(cudaGetLastError());
+        if (k == 0) {
+            launch_wait_counter(written, expect, st);
+            CK(cudaMemcpyAsync(out_rgba, m->out0.p, np * sizeof(float4), cudaMemcpyDeviceToHost, st));
+        }
+        CK(cudaStreamSynchronize(st));
+        return fetch_device_stats(ctx, st);
+    });
+    if (rc != RS_OK) return rc;
+    if (stats_sum) {
+        *stats_sum = rs_stats{};
+        for (int k = 0; k < n; ++k) {
+            rs_stats sk;
+            rs_get_stats(m->ctx[k], &sk);
+            stats_sum->n_samples += sk.n_samples;
+            stats_sum->n_segments += sk.n_segments;
+            stats_sum->n_launches += sk.n_launches + 4;
+        }
+    }
+    return RS_OK;
+}
+
+// the same counters for callers that run one PROCESS per device (torchrun): the counter lives in memory
+// every rank mapped (rs_ipc_open)
+int rs_signal(rs_ctx* ctx, uint32_t* d_counter, void* stream) {
+    if (!ctx || !d_counter) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "null counter");
+    CK(cudaSetDevice(ctx->device));
+    launch_signal(d_counter, (cudaStream_t)stream);
+    CK(cudaGetLastError());
+    return RS_OK;
+}
+int rs_wait_counter(rs_ctx* ctx, const uint32_t* d_counter, uint32_t expect, void* stream) {
+    if (!ctx || !d_counter) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "null counter");
+    CK(cudaSetDevice(ctx->device));
+    launch_wait_counter(d_counter, expect, (cudaStream_t)stream);
+    CK(cudaGetLastError());
+    return RS_OK;
 }
 
 int rs_get_stats(const rs_ctx* ctx, rs_stats* out) {

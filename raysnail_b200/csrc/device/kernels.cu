@@ -1821,6 +1821,27 @@ __global__ void __launch_bounds__(RS_BLOCK) finalize_peers_kernel(const __grid_c
     }
 }
 
+// Device-side arrival counters in peer memory (multi-GPU combine without a host barrier).
+// signal: everything this stream did before is visible system-wide, then counter += 1.
+__global__ void signal_kernel(uint32_t* counter) {
+    __threadfence_system();
+    asm volatile("red.release.sys.global.add.u32 [%0], 1;\n" ::"l"(counter) : "memory");
+}
+// wait: ONE warp polls (ld.acquire.sys) until the counter reaches `expect`; the kernels queued behind it on
+// the stream then see what the signalling devices wrote.  (The poll sits in its own one-warp kernel rather than
+// at the top of the reduce kernel: a whole grid of spinning blocks could keep co-resident work — another
+// context's render on the same device — from ever running.)
+__global__ void wait_counter_kernel(const uint32_t* counter, uint32_t expect) {
+    if (threadIdx.x == 0) {
+        uint32_t v;
+        while (true) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(counter) : "memory");
+            if ((int32_t)(v - expect) >= 0) break;
+            __nanosleep(500);
+        }
+    }
+}
+
 // combine_pixel (raysnail.rs:176-193)
 __global__ void combine_kernel(const float4* __restrict__ old_px, const float4* __restrict__ new_px, float4* __restrict__ out, int64_t n, float pass) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -2000,6 +2021,8 @@ void launch_finalize_peers(const PeerAccums& peers, const unsigned char* mask, f
     if (end <= begin) return;
     finalize_peers_kernel<<<grid_for(end - begin), RS_BLOCK, 0, s>>>(peers, mask, out, begin, end, 1.0f / (float)n_samples, gamma);
 }
+void launch_signal(uint32_t* counter, cudaStream_t s) { signal_kernel<<<1, 1, 0, s>>>(counter); }
+void launch_wait_counter(const uint32_t* counter, uint32_t expect, cudaStream_t s) { wait_counter_kernel<<<1, 32, 0, s>>>(counter, expect); }
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s) {
     combine_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(old_px, new_px, out, n, pass);
 }

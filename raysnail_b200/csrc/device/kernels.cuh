@@ -122,6 +122,8 @@ struct PeerAccums {
 };
 void launch_finalize_peers(const PeerAccums& peers, const unsigned char* mask, float4* out, int64_t begin, int64_t end, int n_samples, int gamma,
                            cudaStream_t s);
+void launch_signal(uint32_t* counter, cudaStream_t s);
+void launch_wait_counter(const uint32_t* counter, uint32_t expect, cudaStream_t s);
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s);
 void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s);
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);

@@ -60,7 +60,11 @@ class PeerImage:
         dev = torch.device("cuda", torch.cuda.current_device())
         self.accum_t = device_view(self.accum, (height, width, 4), dev)  # torch views for zero_() / copies
         self.out_t = device_view(self.out, (height, width, 4), dev) if self.rank == 0 else None
-        mine = {"accum": renderer.ipc_export(self.accum), "out": renderer.ipc_export(self.out) if self.rank == 0 else None}
+        # arrival counters in rank 0's memory: [0] accumulators complete, [1] image slices written (rs_signal / rs_wait_counter)
+        self.counters = renderer.device_alloc(256) if self.rank == 0 else 0
+        self.epoch = 0
+        mine = {"accum": renderer.ipc_export(self.accum), "out": renderer.ipc_export(self.out) if self.rank == 0 else None,
+                "counters": renderer.ipc_export(self.counters) if self.rank == 0 else None}
         handles = [None] * self.world
         dist.all_gather_object(handles, mine)
         self._opened = []
@@ -74,22 +78,29 @@ class PeerImage:
                 self.peer_accums.append(p)
         if self.rank == 0:
             self.out_on_rank0 = self.out
+            self.counters_on_rank0 = self.counters
         else:
             self.out_on_rank0 = renderer.ipc_open(handles[0]["out"])
-            self._opened.append(self.out_on_rank0)
+            self.counters_on_rank0 = renderer.ipc_open(handles[0]["counters"])
+            self._opened += [self.out_on_rank0, self.counters_on_rank0]
 
     def reduce_finalize(self, n_samples: int, gamma: bool, stream: int = 0, d_mask=None):
-        """Call after this rank's render was enqueued on `stream`.  Barrier (every accumulator is
-        complete), fused sum + finalize of this rank's pixel slice into rank 0's image, barrier
-        (rank 0's image is complete)."""
-        import torch
-        import torch.distributed as dist
-        torch.cuda.synchronize()
-        dist.barrier()
+        """Call after this rank's render was enqueued on `stream`; everything here is enqueued on `stream` too
+        and nothing blocks the host.  signal(arrived) -> wait(arrived == world) -> fused sum + finalize of this
+        rank's pixel slice into rank 0's image -> signal(written) -> wait(written == world), so work queued
+        afterwards sees the complete image (rank 0) and may reuse the accumulator (every rank).  The ranks order
+        themselves on the devices; there is no host barrier (the two of round 1 are gone)."""
+        self.epoch += 1
+        expect = self.world * self.epoch
+        arrived, written = self.counters_on_rank0, self.counters_on_rank0 + 4
+        self.r.signal(arrived, stream)
+        self.r.wait_counter(arrived, expect, stream)
         b, e = pixel_slice(self.rank, self.world, self.n_pixels)
         self.r.finalize_peers(self.peer_accums, d_mask, self.out_on_rank0, b, e, n_samples, gamma, stream)
-        torch.cuda.synchronize()
-        dist.barrier()
+        self.r.signal(written, stream)
+        # every rank: nobody reads this rank's accumulator any more (it may be cleared for the next frame), and
+        # on rank 0 the image is complete
+        self.r.wait_counter(written, expect, stream)
 
     def close(self):
         for p in self._opened:
@@ -98,6 +109,8 @@ class PeerImage:
         self.r.device_free(self.accum)
         if self.rank == 0 and self.out:
             self.r.device_free(self.out)
+        if self.rank == 0 and self.counters:
+            self.r.device_free(self.counters)
 
 
 def env_world() -> Tuple[int, int, int]:

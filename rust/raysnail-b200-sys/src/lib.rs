@@ -8,7 +8,7 @@
 
 use std::os::raw::{c_char, c_int, c_void};
 
-pub const RS_ABI_VERSION: c_int = 2;
+pub const RS_ABI_VERSION: c_int = 3;
 
 // rs_status
 pub const RS_OK: c_int = 0;
@@ -201,6 +201,12 @@ pub struct rs_stats {
     pub ms_total: f64,
 }
 
+/// Opaque handle of `rs_create_multi` (several devices behind one call).
+#[repr(C)]
+pub struct rs_multi {
+    _private: [u8; 0],
+}
+
 /// Opaque context: one CUDA device, one host thread at a time.
 #[repr(C)]
 pub struct rs_ctx {
@@ -234,6 +240,15 @@ extern "C" {
     pub fn rs_pass_seed(seed: u64, pass: i32) -> u64;
     pub fn rs_philox4x32_10(counter: *const u32, key: *const u32, out: *mut u32) -> c_int;
     pub fn rs_philox_uniform(seed: u64, pixel: u32, sample: u32, depth: u32, purpose: u32, call: u32, out4: *mut f64) -> c_int;
+    pub fn rs_create_multi(out: *mut *mut rs_multi, device_ids: *const i32, n: i32) -> c_int;
+    pub fn rs_destroy_multi(m: *mut rs_multi);
+    pub fn rs_multi_last_error(m: *const rs_multi) -> *const c_char;
+    pub fn rs_multi_device_count(m: *const rs_multi) -> c_int;
+    pub fn rs_multi_set_option(m: *mut rs_multi, option: c_int, value: c_int) -> c_int;
+    pub fn rs_multi_upload_scene(m: *mut rs_multi, scene: *const rs_scene_desc) -> c_int;
+    pub fn rs_multi_render(m: *mut rs_multi, cam: *const rs_camera, params: *const rs_render_params, pixel_mask: *const u8, out_rgba: *mut f32, stats_sum: *mut rs_stats) -> c_int;
+    pub fn rs_signal(ctx: *mut rs_ctx, d_counter: *mut u32, stream: *mut c_void) -> c_int;
+    pub fn rs_wait_counter(ctx: *mut rs_ctx, d_counter: *const u32, expect: u32, stream: *mut c_void) -> c_int;
 }
 
 /// Compares `size_of` of every `#[repr(C)]` struct with what the loaded library was compiled

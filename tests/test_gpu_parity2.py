@@ -364,3 +364,46 @@ def test_surfaces_outside_their_reference_bbox_are_found_by_list_and_trees(rende
         renderer.set_bvh_width(2)
     assert imgs[0][0] == imgs[1][0] == imgs[2][0]
     assert np.array_equal(imgs[0][1], imgs[1][1]) and np.array_equal(imgs[0][1], imgs[2][1])
+
+
+def _device_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("devices", [(0,), (0, 0), (0, 0, 0), (0, 1), (0, 1, 2, 3)])
+def test_rs_multi_render_equals_the_one_device_image(renderer, devices):
+    """rs_create_multi / rs_multi_render: strata rows split over the contexts, arrival counters instead of host
+    barriers, fused reduce + finalize of pixel slices into device 0's image.  The union of the shards is the
+    one-device sample set; every pixel is a sum of the same per-sample values, grouped per shard, so the
+    image may differ from rs_render's by the rounding of that grouping only.  A device listed twice gives
+    separate contexts on one GPU, which exercises all of it on a one-GPU box."""
+    from raysnail_b200 import MultiRenderer
+    if max(devices) >= _device_count():
+        pytest.skip(f"needs {max(devices) + 1} CUDA devices")
+    scene = load_scene("cornell")
+    cam = scene.camera(160, 120)
+    params = make_params(sqrt_spp=6, depth=8)
+    renderer.upload(scene)
+    ref = renderer.render(cam, params)
+    mask = np.ones((120, 160), np.uint8)
+    mask[10:40, 20:90] = 0
+    ref_masked = renderer.render(cam, params, mask=mask)
+    m = MultiRenderer(devices)
+    try:
+        assert m.device_count == len(devices)
+        m.upload(scene)
+        for rep in range(3):  # the counters are epochs: calls may follow each other without a reset
+            img = m.render(cam, params)
+            np.testing.assert_allclose(img, ref, rtol=2e-6, atol=1e-7)
+            assert m.stats.n_samples == 160 * 120 * 36
+        if len(devices) == 1:
+            assert np.array_equal(img, ref)
+        img_m = m.render(cam, params, mask=mask)
+        np.testing.assert_allclose(img_m, ref_masked, rtol=2e-6, atol=1e-7)
+        assert not img_m[10:40, 20:90].any()
+        # more devices than strata rows: the extra ones get an empty range
+        p1 = make_params(sqrt_spp=1, depth=4)
+        np.testing.assert_allclose(m.render(cam, p1), renderer.render(cam, p1), rtol=2e-6, atol=1e-7)
+    finally:
+        m.close()

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), f"{name} is declared in include/ but not exported"
     assert sorted(declared) == sorted(_abi.CORE_SYMBOLS + _abi.HOST_SYMBOLS)
-    assert lib.rs_abi_version() == 2
+    assert lib.rs_abi_version() == 3
 
 
 def test_ctypes_layouts_match_the_compiled_structs():
