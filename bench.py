@@ -99,18 +99,22 @@ def measured_peak_gbs():
 
 
 def ncu_traffic(kernel):
-    """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of one launch of the dominant
-    kernel from the committed `ncu --set full` capture (profiles/traffic.json, written by
-    profiles/ncu_metrics.py): the bounce-0 launch of one full 8.29 M-path wave, i.e. the largest
-    launch — compare it with that launch's algorithmic bytes (roofline.traffic_launch), not with
-    the average over all bounces in algorithmic_bytes_per_launch."""
+    """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of one launch of the dominant kernel, from the
+    `ncu --set full` capture profiles/capture.sh made (profiles/traffic.json, written by profiles/ncu_metrics.py with
+    the commit it ran and the paths of the captured wave): the bounce-0 launch of one wave, i.e. the largest launch —
+    to be compared with THAT launch's algorithmic bytes (roofline.traffic_launch), not with the average over all
+    bounces in algorithmic_bytes_per_launch.  Returns (bytes, description) or (None, None)."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         try:
-            return float(json.load(open(p))[kernel + "_kernel"]["per_launch_bytes"][0])
+            e = json.load(open(p))[kernel + "_kernel"]
+            paths = float(e.get("paths_per_wave") or 8294400)
+            return float(e["per_launch_bytes"][0]), {
+                "what": f"bounce 0 of one wave of {int(paths)} paths (profiles/traffic.json: {e.get('source')}, commit {e.get('commit', 'r01')})",
+                "algorithmic_bytes": BYTES_PER_SEGMENT[kernel] * paths}
         except Exception:
-            return None
-    return None
+            return None, None
+    return None, None
 
 
 # ---------------------------------------------------------------------------------------------
@@ -181,6 +185,102 @@ def load_bench_scene(name):
         kind, _, grid = name.partition(":")
         return Scene.builtin(kind, SCENE_SEED, int(grid or 708))
     return Scene.builtin(name, SCENE_SEED)
+
+
+# BASELINE.json's other configs (driver-visible numbers next to the headline line): name, scene, frame, sqrt(spp)
+OTHER_CONFIGS_1GPU = [
+    ("C1 sdl/example.sdl 800x500 64 spp (--samples 65 -> 8x8 strata)", "example", 800, 500, 8),
+    ("C3a sdl/quadric.sdl 1920x1080 256 spp", "quadric", 1920, 1080, 16),
+    ("C3b sdl/csg.sdl 1920x1080 256 spp", "csg", 1920, 1080, 16),
+    ("C4 1M-triangle mesh (mesh_blinn:708, 1 001 112 triangles), Blinn-Phong, 2048x2048 64 spp", "mesh_blinn:708", 2048, 2048, 8),
+    ("C5 Cornell box 3840x2160 256 spp (the 4096 spp of the config on N > 1)", "cornell", 3840, 2160, 16),
+]
+OTHER_CONFIGS_NGPU = [("C5 Cornell box 3840x2160 4096 spp", "cornell", 3840, 2160, 64)]
+
+
+def measure_config(renderer, dev, label, scene_name, width, height, q, steps, world_size, rank, peak):
+    """One BASELINE.json config through the same sharded step as the headline: `steps` timed frames (CUDA events,
+    barrier + synchronize on both sides, max over ranks) after one warm-up frame, then one frame with per-kernel
+    event timing for the breakdown.  All ranks call this; every rank returns the same dict."""
+    import torch
+    import torch.distributed as dist
+    from raysnail_b200 import RS_FLAG_KERNEL_TIMING, make_params
+    from raysnail_b200.distributed import PeerImage, stratum_rows
+    scene = load_bench_scene(scene_name)
+    renderer.upload(scene)
+    cam = scene.camera(width, height)
+    stream = torch.cuda.current_stream().cuda_stream
+    r0, r1 = stratum_rows(rank, world_size, q)
+    params = make_params(sqrt_spp=q, depth=DEPTH, rows=(r0, r1))
+    params_t = make_params(sqrt_spp=q, depth=DEPTH, rows=(r0, r1), flags=RS_FLAG_KERNEL_TIMING)
+    peer = PeerImage(renderer, width, height) if world_size > 1 else None
+    if peer is not None:
+        accum, out = peer.accum_t, peer.out_t
+    else:
+        accum = torch.zeros((height, width, 4), dtype=torch.float32, device=dev)
+        out = torch.empty_like(accum)
+
+    def step(p):
+        accum.zero_()
+        renderer.render_accumulate(cam, p, None, accum.data_ptr(), stream)
+        if peer is not None:
+            peer.reduce_finalize(q * q, True, stream, None)
+        else:
+            renderer.finalize(accum.data_ptr(), None, out.data_ptr(), width, height, q * q, True, stream)
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    step(params)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        step(params)
+    ev1.record()
+    barrier()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+    st = renderer.stats()
+    seg = torch.tensor([float(st.n_segments), float(st.n_samples)], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(seg, op=dist.ReduceOp.SUM)
+    ms_step = float(ms.item()) / steps
+    n_segments, n_samples = [float(x) for x in seg.tolist()]
+    step(params_t)
+    barrier()
+    kt = renderer.stats()
+    shares = {"extend": kt.ms_extend, "shade": kt.ms_shade, "raygen": kt.ms_raygen, "accumulate": kt.ms_accumulate}
+    dom = max(("extend", "shade"), key=lambda k: shares[k])
+    # the dominant kernel's algorithmic bytes over its own summed launch time (rank 0's share of the segments)
+    achieved = BYTES_PER_SEGMENT[dom] * float(kt.n_segments) / (shares[dom] * 1e-3) / 1e9 if shares[dom] > 0 else 0.0
+    e2e = None
+    if world_size == 1:
+        # the reference-facing call with HOST buffers: rs_upload_scene + rs_render (host mask in, host image out)
+        host_img = torch.empty((height, width, 4), dtype=torch.float32).pin_memory()
+        host_mask = torch.ones((height, width), dtype=torch.uint8).pin_memory()
+        p_all = make_params(sqrt_spp=q, depth=DEPTH)
+
+        def e2e_step():
+            renderer.upload(scene)
+            renderer.render_to_ptr(cam, p_all, host_mask.data_ptr(), host_img.data_ptr())
+
+        e2e_step()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            e2e_step()
+        dt = (time.perf_counter() - t0) / steps
+        e2e = {"value": width * height * q * q / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "h2d_bytes_per_step": int(scene_bytes(scene.desc) + height * width),
+               "d2h_bytes_per_step": height * width * 16}
+    if peer is not None:
+        barrier()
+        peer.close()
+    return {"workload": label, "e2e": e2e, "value": n_samples / (ms_step / 1e3), "unit": UNIT, "mrays_per_s": n_segments / (ms_step / 1e3) / 1e6, "ms_per_step": ms_step,
+            "steps": steps, "segments_per_sample": n_segments / max(n_samples, 1.0),
+            "roofline": {"bound": "hbm", "kernel": dom + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "kernel_ms_per_step": shares}}
 
 
 def run_gpu(args):
@@ -307,6 +407,22 @@ def run_gpu(args):
     total_samples_per_step = float(width * height * q * q)
     e2e_value = total_samples_per_step * e2e_steps / (float(e2e_ms.item()) / 1e3)
 
+    # the other BASELINE.json configs, outside the timed headline region (all ranks take part; N = 1: C1, C3a, C3b, C4, C5
+    # at 256 spp; N > 1: C5 at its full 4096 spp)
+    others, others_clocks = [], None
+    if not (args.no_cpu or args.no_others) and (args.scene, width, height, q) == ("rtow_final", WIDTH, HEIGHT, SQRT_SPP):
+        peak0 = measured_peak_gbs()[0]
+        osampler = ClockSampler(local_rank)
+        if rank == 0:
+            osampler.start()
+        for label, name, w_, h_, q_ in (OTHER_CONFIGS_1GPU if world_size == 1 else OTHER_CONFIGS_NGPU):
+            try:
+                others.append(measure_config(renderer, dev, label, name, w_, h_, q_, 2, world_size, rank, peak0))
+            except Exception as exc:  # a config that cannot run is reported, not hidden
+                others.append({"workload": label, "error": f"{type(exc).__name__}: {exc}"})
+        if rank == 0:
+            others_clocks = osampler.stop()
+
     if rank == 0:
         value = total_samples_per_step * args.steps / (ms_total / 1e3)
         peak, peak_src = measured_peak_gbs()
@@ -340,9 +456,8 @@ def run_gpu(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(n_launches * args.steps),
             "roofline": {"bound": "hbm", "kernel": dom + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic(dom),
-                         "traffic_launch": {"what": "bounce 0 of one wave of 1920x1080x4 = 8294400 paths (profiles/traffic.json)",
-                                            "algorithmic_bytes": BYTES_PER_SEGMENT[dom] * 8294400.0},
+                         "traffic": ncu_traffic(dom)[0],
+                         "traffic_launch": ncu_traffic(dom)[1],
                          "peak_source": peak_src, "avg_launch_ms": avg_ms,
                          "algorithmic_bytes_per_launch": alg_bytes_per_launch,
                          "pipeline": {"bytes_per_step": pipeline_bytes, "achieved": pipeline_bytes / (ms_total / args.steps / 1e3) / 1e9 / world_size,
@@ -350,6 +465,9 @@ def run_gpu(args):
                          "kernel_ms_per_step": shares},
             "clocks": clocks,
         }
+        if others:
+            line["other_configs"] = others
+            line["other_configs_clocks"] = others_clocks
         if world_size == 1 and not args.no_cpu:
             c = cpu_render_sample(2)
             line["cpu_baseline"] = {"value": c["samples_per_s"], "unit": UNIT, "cores": c["cores"], "kind": "port", "sample": c["sample"],
@@ -370,7 +488,8 @@ def main():
     ap.add_argument("--height", type=int, default=HEIGHT)
     ap.add_argument("--sqrt-spp", type=int, default=SQRT_SPP)
     ap.add_argument("--wave", type=int, default=0, help="max paths in flight per wave (0 = library default)")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (and the other configs)")
+    ap.add_argument("--no-others", action="store_true", help="skip the other BASELINE.json configs (other_configs)")
     ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"],
                     help="N > 1 combine step: peer = fused reduce+finalize kernel over NVLink peer memory (default); nccl = ncclReduce + finalize")
     ap.add_argument("--bvh-width", type=int, default=2, choices=[2, 4], help="world BVH: 2 = binary (default), 4 = QBVH")

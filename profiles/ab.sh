@@ -4,7 +4,7 @@
 for spec in "$@"; do
   IFS='|' read -r label envs variant extra <<< "$spec"
   L=$PWD/raysnail_b200/libraysnail_b200$variant.so
-  env $envs RAYSNAIL_B200_LIB=$L python bench.py --steps 3 --warmup 2 --sqrt-spp 8 --no-cpu $extra 2>&1 | tail -1 | python -c "
+  env $envs RAYSNAIL_B200_LIB=$L python bench.py --steps 3 --warmup 2 --sqrt-spp 8 --no-cpu --no-others $extra 2>&1 | tail -1 | python -c "
 import json,sys
 try:
     d=json.loads(sys.stdin.read()); k=d['roofline']['kernel_ms_per_step']

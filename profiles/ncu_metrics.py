@@ -4,7 +4,8 @@ Writes the counters DESIGN.md cites (warp execution efficiency, pipe utilisation
 rates, DRAM bytes, stall mix) and, with --traffic-json, the per-launch DRAM traffic of each
 kernel for bench.py's `roofline.traffic`.
 
-usage: ncu_metrics.py report.ncu-rep [--traffic-json profiles/traffic.json]"""
+usage: ncu_metrics.py report.ncu-rep [--traffic-json profiles/traffic.json --paths N --commit HASH]
+(--paths: camera paths of the captured wave; --commit: the commit the capture ran — both recorded in the json)"""
 import csv
 import io
 import json
@@ -63,6 +64,9 @@ for k, v in traffic.items():
     print(f"dram bytes per launch, {k}: " + ", ".join(f"{x/1e6:.1f} MB" for x in v))
 if "--traffic-json" in sys.argv:
     out = sys.argv[sys.argv.index("--traffic-json") + 1]
-    json.dump({k: {"per_launch_bytes": v, "max": max(v), "source": rep.split("/")[-1],
-                   "note": "dram__bytes_read.sum + dram__bytes_write.sum, one wave of 8.29 M paths (1920x1080x4), launches = bounce 0 and bounce 1"}
+    def arg(name, default):
+        return sys.argv[sys.argv.index(name) + 1] if name in sys.argv else default
+    paths, commit = int(arg("--paths", "0")), arg("--commit", "unknown")
+    json.dump({k: {"per_launch_bytes": v, "max": max(v), "source": rep.split("/")[-1], "commit": commit, "paths_per_wave": paths,
+                   "note": f"dram__bytes_read.sum + dram__bytes_write.sum per launch; one wave of {paths} paths of the headline scene; launches in capture order (bounce 0 first)"}
                for k, v in traffic.items()}, open(out, "w"), indent=1)

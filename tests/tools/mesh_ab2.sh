@@ -3,7 +3,7 @@
 for spec in "$@"; do
   IFS='|' read -r label envs variant extra <<< "$spec"
   L=$PWD/raysnail_b200/libraysnail_b200$variant.so
-  env $envs RAYSNAIL_B200_LIB=$L python bench.py --steps 2 --warmup 2 --no-cpu --scene mesh_blinn:708 --width 2048 --height 2048 --sqrt-spp 8 $extra 2>&1 | tail -1 | python -c "
+  env $envs RAYSNAIL_B200_LIB=$L python bench.py --steps 2 --warmup 2 --no-cpu --no-others --scene mesh_blinn:708 --width 2048 --height 2048 --sqrt-spp 8 $extra 2>&1 | tail -1 | python -c "
 import json,sys
 try:
     d=json.loads(sys.stdin.read()); k=d['roofline']['kernel_ms_per_step']
