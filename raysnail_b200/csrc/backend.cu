@@ -1277,6 +1277,8 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     S.nodes = ctx->d_nodes.as<rs_node>();
     S.xf = ctx->d_xf.as<XformPre>();
     S.bvh_root = bvh_root;
+    S.any_gate = 0;
+    for (unsigned char g : root_gate) S.any_gate |= g;
     S.bvh2_bytes = ctx->stage_bytes ? (uint32_t)(ctx->bvh_host.size() * sizeof(BvhNode)) : 0u;
     S.sphere_bytes = ctx->stage_bytes ? (uint32_t)((size_t)s->n_roots * sizeof(double4)) : 0u;
     S.n_roots = any_object ? s->n_roots : 0;
@@ -1405,6 +1407,9 @@ int rs_render(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, cons
     CK(ctx->d_accum.ensure(np * sizeof(float4)));
     CK(ctx->d_out.ensure(np * sizeof(float4)));
     const unsigned char* d_mask = nullptr;
+    // a mask that selects every pixel is no mask: the frame then takes the path that generates the camera rays
+    // inside extend instead of compacting the selected pixels first
+    if (pixel_mask && std::memchr(pixel_mask, 0, np) == nullptr) pixel_mask = nullptr;
     if (pixel_mask) {
         CK(ctx->d_mask.ensure(np));
         CK(cudaMemcpyAsync(ctx->d_mask.p, pixel_mask, np, cudaMemcpyHostToDevice, 0));
@@ -1756,6 +1761,7 @@ int rs_multi_render(rs_multi* m, const rs_camera* cam, const rs_render_params* p
         if (rc != RS_OK) return multi_fail(m, rc, rs_last_error(m->ctx[k]));
     }
     const size_t np = (size_t)cam->width * cam->height;
+    if (pixel_mask && std::memchr(pixel_mask, 0, np) == nullptr) pixel_mask = nullptr;  // (as rs_render)
     const int rows0 = p->stratum_row_begin, rows = p->stratum_row_end - p->stratum_row_begin;
     const int n_total = std::max(rows * p->sqrt_spp, 1);
     // buffers first (allocation synchronises), so that nothing but launches follows

@@ -309,7 +309,7 @@ __device__ __forceinline__ double next_up(double x) {
 // boxes, bare or under one TfFacade (ROOT_FLAT: still no expression-tree code), 3 = everything.
 // `ref` is the decoded leaf reference (root << 2 | kind).
 template <int MODE, bool STAGE = false>
-__device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& ray, const RngCtx& rng, Closest& best, const Staged st = Staged{0, 0}) {
+__device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& ray, const V3& inv_d, const RngCtx& rng, Closest& best, const Staged st = Staged{0, 0}) {
     const int kind = MODE == 0 ? (int)ROOT_SPHERE : (ref & 3);
     const int root = ref >> 2;
     if (kind == ROOT_SPHERE) {
@@ -354,7 +354,7 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
         bool hit;
         if (MODE >= RS_QUADRIC_MODE && n->type == RS_NODE_QUADRIC) {
             // quadric.rs:191-196: the surface is unbounded, the reference clips it with its +-100 bbox
-            if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, inf)) return;
+            if (!aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, inv_d, RS_TMIN, inf)) return;
             hit = quadric_t(n->p, r, RS_TMIN, hi, t);
         } else {
             hit = n->type == RS_NODE_BOX ? box_t(n->p, r, RS_TMIN, hi, t)
@@ -370,7 +370,7 @@ __device__ __forceinline__ void test_root(const DScene& S, int ref, const Ray& r
         ObjHit h;
         const double hi = __longlong_as_double(0x7ff0000000000000LL);  // see ROOT_FLAT
         // the object only counts when the ray passes AABB::hit on its reference bbox (bvh.rs:173-176 on the leaf's box)
-        if (__ldg(&S.root_gate[root]) && !aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, RS_TMIN, hi)) return;
+        if (__ldg(&S.root_gate[root]) && !aabb_hit_f64(S.root_bbox + 6 * (size_t)root, ray, inv_d, RS_TMIN, hi)) return;
         const bool hit = eval_object(S.nodes, S.xf, S.obj, pr.x, pr.y, ray, RS_TMIN, hi, rng, h) && (h.t1 < best.t || (h.t1 == best.t && root < best.root));
         if (hit) {
             best.t = h.t1;
@@ -479,6 +479,11 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
     const float tmin_f = (float)RS_TMIN * (1.0f - 2.0f * RS_SLAB_EPS);
     float tmax_f = FLT_MAX;
     const float slack = (1.0f + RS_SLAB_EPS) * (1.0f + RS_SLAB_EPS);
+    // 1 / direction in f64 for the bbox gates of the objects (AABB::hit divides per call; the quotient is the ray's)
+    V3 inv_d = v3(0.0, 0.0, 0.0);
+    if constexpr (MODE >= 2) {
+        if (S.any_gate) inv_d = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
+    }
 
     // The object list, walked before the tree.  It holds
     //  - the objects whose surface has no bound (quadrics): the reference visits them whenever the ray
@@ -500,7 +505,7 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
 #if RS_TUNE_COST_DUMP
                 ++best.n_leaves;
 #endif
-                test_root<MODE>(S, __float_as_int(lo.w), ray, rng, best);
+                test_root<MODE>(S, __float_as_int(lo.w), ray, inv_d, rng, best);
                 tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
             }
         }
@@ -619,7 +624,7 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
 #if RS_TUNE_COST_DUMP
         ++best.n_leaves;
 #endif
-        test_root<MODE, STAGE>(S, ~node, ray, rng, best, st);
+        test_root<MODE, STAGE>(S, ~node, ray, inv_d, rng, best, st);
         // shrink the f32 limit (rounded up) so farther boxes are culled
         tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
         RS_POP();
@@ -1142,7 +1147,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
                     ray.o = v3(sray[0], sray[RS_BLOCK], sray[2 * RS_BLOCK]);
                     ray.d = v3(sray[3 * RS_BLOCK], sray[4 * RS_BLOCK], sray[5 * RS_BLOCK]);
                     ray.time = 0.0;
-                    test_root<MODE>(S, ~node, ray, no_rng, best);
+                    test_root<MODE>(S, ~node, ray, v3(0.0, 0.0, 0.0), no_rng, best);
                     tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
                     RS_POP();
                 }

@@ -94,6 +94,7 @@ struct DScene {
     uint32_t bvh2_bytes;         // size of the binary tree and of the sphere table (16-byte multiples): what the
     uint32_t sphere_bytes;       // staged extend kernels copy into shared memory (0 = not staged)
     const float4* root_list;     // objects searched as a list before the tree: (lo.xyz, bits of the leaf ref), (hi.xyz, 1 = never dropped by distance)
+    int any_gate;                // some root is gated by its reference bbox (aabb_hit_f64 needs 1 / direction)
     int n_list;                  // unbounded objects; in small worlds every object (then bvh_root is the sentinel: no tree)
     const int* root_node;        // node index or ~triangle
     const int* root_kind;        // RootKind
@@ -130,24 +131,26 @@ struct HitRec {
 // [start, end) like std::ops::Range<f64>::contains
 __device__ __forceinline__ bool in_range(double t, double lo, double hi) { return t >= lo && t < hi; }
 
-// aabb.rs:20-38 in f64 (the gate for roots whose reference bbox does not contain them)
-__device__ __forceinline__ bool aabb_hit_f64(const double* b, const Ray& r, double lo, double hi) {
+// aabb.rs:20-38 in f64 (the gate for roots whose reference bbox does not contain them).  `inv` = 1.0 / direction per
+// axis, the quotient the reference computes inside the test: it depends on the ray alone, so the caller divides
+// once per ray, not once per object (three f64 divisions cost about what the rest of the test costs).
+__device__ __forceinline__ bool aabb_hit_f64(const double* b, const Ray& r, const V3& inv, double lo, double hi) {
     double t_min = lo, t_max = hi;
     {
-        double inv = 1.0 / r.d.x, t0 = (b[0] - r.o.x) * inv, t1 = (b[3] - r.o.x) * inv;
-        if (inv < 0.0) { double s = t0; t0 = t1; t1 = s; }
+        double t0 = (b[0] - r.o.x) * inv.x, t1 = (b[3] - r.o.x) * inv.x;
+        if (inv.x < 0.0) { double s = t0; t0 = t1; t1 = s; }
         t_min = fmax(t_min, t0); t_max = fmin(t_max, t1);
         if (t_max <= t_min) return false;
     }
     {
-        double inv = 1.0 / r.d.y, t0 = (b[1] - r.o.y) * inv, t1 = (b[4] - r.o.y) * inv;
-        if (inv < 0.0) { double s = t0; t0 = t1; t1 = s; }
+        double t0 = (b[1] - r.o.y) * inv.y, t1 = (b[4] - r.o.y) * inv.y;
+        if (inv.y < 0.0) { double s = t0; t0 = t1; t1 = s; }
         t_min = fmax(t_min, t0); t_max = fmin(t_max, t1);
         if (t_max <= t_min) return false;
     }
     {
-        double inv = 1.0 / r.d.z, t0 = (b[2] - r.o.z) * inv, t1 = (b[5] - r.o.z) * inv;
-        if (inv < 0.0) { double s = t0; t0 = t1; t1 = s; }
+        double t0 = (b[2] - r.o.z) * inv.z, t1 = (b[5] - r.o.z) * inv.z;
+        if (inv.z < 0.0) { double s = t0; t0 = t1; t1 = s; }
         t_min = fmax(t_min, t0); t_max = fmin(t_max, t1);
         if (t_max <= t_min) return false;
     }
