@@ -9,6 +9,7 @@
 //                     (src/painter.rs:256-336).
 #include <algorithm>
 #include <cfloat>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -50,6 +51,12 @@ struct HostBvhNode {  // binary SAH tree: two children with f64 boxes
     double box[2][6];
     int child[2];
 };
+// one member of the tree under construction: bounds, centroid and object id
+struct BuildPrim {
+    double lo[3], hi[3], c[3];
+    int root;
+    int pad;  // (kept zero: the records are compared bytewise by the tree cache of rs_upload_scene)
+};
 struct HostBvhNode4 {  // collapsed 4-wide tree (what the device traverses)
     double box[4][6];
     int child[4];
@@ -74,6 +81,22 @@ struct rs_ctx {
     std::vector<HostBvhNode> bvh_host;
     std::vector<HostBvhNode4> bvh4_host;
     std::vector<int> root_kind_host, root_node_host;
+    // what the kept tree was built from (bounds + object id of every tree member, before the build re-orders them):
+    // a re-upload of unchanged geometry — every pass of the passes loop, every frame over a fixed world — keeps the tree
+    std::vector<unsigned char> bvh_key;
+    int bvh_key_width = 0, bvh_key_root = 0;
+    bool bvh_reused = false;
+    // the device copy of the tree (f32 boxes padded for ray origins up to tree_dev_omax, leaf references) is kept with it
+    bool tree_dev_valid = false;
+    double tree_dev_omax = 0.0;
+    // host scratch of rs_upload_scene, kept between calls: a re-upload of a 1 M-triangle world fills ~300 MB of tables,
+    // and fresh vectors would page-fault and zero-fill all of it every time
+    struct UploadScratch {
+        std::vector<int> root_kind, root_material;
+        std::vector<double> root_sphere, root_inv_r, tri_geom;
+        std::vector<unsigned char> root_gate;
+        std::vector<BuildPrim> prims, loose, part[8], part_loose[8];
+    } scratch;
     struct ListEntry { double box[6]; int root; bool noclip; };
     std::vector<ListEntry> list_host;  // the world objects with a proper bbox, ascending ids
     bool use_list = false;             // small worlds: the kernels walk the object list instead of the tree (RS_OPT_LIST_MAX)
@@ -139,6 +162,21 @@ int upload(rs_ctx* ctx, DevBuf& buf, const T* src, size_t n) {
     CK(buf.ensure(std::max<size_t>(n, 1) * sizeof(T)));
     if (n) CK(cudaMemcpy(buf.p, src, n * sizeof(T), cudaMemcpyHostToDevice));
     return RS_OK;
+}
+
+// Host loops over a million world objects (the tables of rs_upload_scene): contiguous chunks on up to 8 threads.
+// f(chunk, begin, end); returns the number of chunks used (1 for small n: no thread is started).
+constexpr int kMaxChunks = 8;
+template <class F>
+int parallel_chunks(size_t n, F f) {
+    int t = 1;
+    if (n >= (size_t)1 << 16) t = (int)std::min<unsigned>(kMaxChunks, std::max(1u, std::thread::hardware_concurrency()));
+    if (t == 1) { f(0, (size_t)0, n); return 1; }
+    std::vector<std::thread> th;
+    for (int k = 1; k < t; ++k) th.emplace_back([&, k] { f(k, n * (size_t)k / (size_t)t, n * (size_t)(k + 1) / (size_t)t); });
+    f(0, (size_t)0, n / (size_t)t);
+    for (auto& x : th) x.join();
+    return t;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -210,10 +248,6 @@ bool geom_bound(const std::vector<rs_node>& nodes, const std::vector<XformPre>& 
     }
 }
 
-struct BuildPrim {
-    double lo[3], hi[3], c[3];
-    int root;
-};
 
 double half_area(const double* lo, const double* hi) {
     double dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
@@ -386,6 +420,14 @@ int upload_bvh(rs_ctx* ctx, double omax) {
         ctx->scene.root_list = ctx->d_root_list.as<float4>();
         ctx->scene.n_list = (int)(list.size() / 2);
     }
+    if (ctx->tree_dev_valid && ctx->tree_dev_omax >= omax) {
+        // same tree, same leaf references, boxes already padded for origins at least this far out (a wider pad is
+        // still conservative): the nodes in HBM stand
+        ctx->padded_omax = ctx->tree_dev_omax;
+        return RS_OK;
+    }
+    ctx->tree_dev_valid = true;
+    ctx->tree_dev_omax = omax;
     if (ctx->bvh_width != 4) {  // binary tree, 64-byte nodes
         std::vector<BvhNode> dev2(std::max<size_t>(ctx->bvh_host.size(), 1));
         for (size_t i = 0; i < ctx->bvh_host.size(); ++i) {
@@ -667,6 +709,7 @@ FrameParams make_frame(const rs_camera* cam, const rs_render_params* p) {
     fp.stratum_row_begin = p->stratum_row_begin;
     fp.flags = p->flags;
     fp.key = make_uint2((uint32_t)p->seed, (uint32_t)(p->seed >> 32));
+    for (uint32_t r = 0; r < 10; ++r) fp.rk.rk[r] = make_uint2(fp.key.x + r * 0x9E3779B9u, fp.key.y + r * 0xBB67AE85u);
     return fp;
 }
 
@@ -716,6 +759,12 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
     if (rc != RS_OK) return rc;
     FrameParams fp = make_frame(cam, p);
     fp.mask = d_mask;
+#if RS_CHECKED
+    // negative control of the checked build (tests/tools/checked_run.sh): the first 32 paths of every wave also try to
+    // store their record one whole buffer too far; RS_IN_BOUNDS must catch (and skip) the stores and the call must fail
+    static const bool selftest = [] { const char* e = std::getenv("RAYSNAIL_B200_CHECK_SELFTEST"); return e && std::atoi(e) != 0; }();
+    if (selftest) fp.flags |= 0x80000000u;
+#endif
     CK(cudaMemsetAsync(ctx->ws.stats, 0, sizeof(DeviceStats), stream));
     if (n_sets > 1) {
         if (!ctx->ev_fork) {
@@ -836,6 +885,11 @@ int fetch_device_stats(rs_ctx* ctx, cudaStream_t stream) {
     CK(cudaStreamSynchronize(stream));
     ctx->stats.n_samples = ds.n_samples;
     ctx->stats.n_segments = ds.n_segments;
+    if (RS_CHECKED) {  // the library's own memcheck (rt_math.cuh): a render with a failed bounds check is an error
+        CK(cudaDeviceSynchronize());
+        const unsigned long long v = read_violations();
+        if (v) return fail(ctx, RS_ERR_CUDA, "RS_CHECKED: " + std::to_string(v) + " out-of-bounds accesses caught on the device");
+    }
     return RS_OK;
 }
 
@@ -924,6 +978,15 @@ int rs_set_option(rs_ctx* ctx, int option, int value) {
 int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if (!ctx || !s) return RS_ERR_INVALID_ARGUMENT;
     CK(cudaSetDevice(ctx->device));
+    // RAYSNAIL_B200_UPLOAD_TRACE=1: wall time of every stage of the upload on stderr
+    static const bool trace = [] { const char* e = std::getenv("RAYSNAIL_B200_UPLOAD_TRACE"); return e && std::atoi(e) != 0; }();
+    auto t_last = std::chrono::steady_clock::now();
+    auto stage = [&](const char* what) {
+        if (!trace) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[rs_upload_scene] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
     ctx->has_scene = false;
     // ---- validation -------------------------------------------------------------------------
     if (s->n_nodes < 0 || s->n_roots < 0 || s->n_tris < 0 || s->n_materials <= 0 || s->n_textures < 0)
@@ -996,67 +1059,102 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     for (int i = 0; i < s->n_tris; ++i)
         if (s->tri_material[i] >= s->n_materials) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "triangle material out of range");
 
+    stage("validation");
     // ---- root tables + BVH ------------------------------------------------------------------
-    std::vector<int> root_kind(s->n_roots);
-    bool any_quadric_root = false;
-    std::vector<double> root_sphere((size_t)s->n_roots * 4, 0.0);
-    std::vector<unsigned char> root_gate(s->n_roots, 0);
-    std::vector<BuildPrim> prims, loose;  // loose: no bound on the surface; searched as a list, never dropped by distance
+    rs_ctx::UploadScratch& sc = ctx->scratch;
+    std::vector<int>& root_kind = sc.root_kind;
+    std::vector<double>& root_sphere = sc.root_sphere;
+    std::vector<unsigned char>& root_gate = sc.root_gate;
+    std::vector<BuildPrim>&prims = sc.prims, &loose = sc.loose;  // loose: no bound on the surface; searched as a list, never dropped by distance
+    root_kind.resize(s->n_roots);
+    root_sphere.resize((size_t)s->n_roots * 4);
+    root_gate.resize(s->n_roots);
+    prims.clear();
+    loose.clear();
     prims.reserve(s->n_roots);
+    bool any_quadric_root = false;
     double omax = 1.0;
-    for (int i = 0; i < s->n_roots; ++i) {
-        int r = s->roots[i];
-        const double* bb = s->root_bbox + 6 * (size_t)i;
-        if (r < 0) {
-            root_kind[i] = ROOT_TRIANGLE;
-        } else {
-            const rs_node& n = nodes[r];
-            bool static_sphere = n.type == RS_NODE_SPHERE && n.p[4] == 0.0 && n.p[5] == 0.0 && n.p[6] == 0.0;
-            if (static_sphere) {
-                root_kind[i] = ROOT_SPHERE;
-                for (int k = 0; k < 4; ++k) root_sphere[4 * (size_t)i + k] = n.p[k];
-            } else {
-                // rect / box, bare or under one TfFacade: inline distance tests in extend
-                const rs_node& inner = n.type == RS_NODE_TRANSFORM ? nodes[n.child0] : n;
-                // (a quadric root takes the same inline route, but only the generic-tier kernels hold its code)
-                root_kind[i] = (inner.type == RS_NODE_BOX || inner.type == RS_NODE_RECT || inner.type == RS_NODE_QUADRIC) ? ROOT_FLAT : ROOT_GENERIC;
-                any_quadric_root |= inner.type == RS_NODE_QUADRIC;
-                // spheres / boxes / rects always lie inside their reference bbox; everything
-                // else is clipped by it the way the reference's BVH leaf clips it
-                root_gate[i] = !(n.type == RS_NODE_SPHERE || n.type == RS_NODE_BOX || n.type == RS_NODE_RECT);
-            }
-        }
-        BuildPrim p;
-        bool degenerate = false;
-        for (int a = 0; a < 3; ++a) {
-            double lo = bb[a], hi = bb[3 + a];
-            if (!(lo == lo) || !(hi == hi)) degenerate = true;
-            lo = std::max(lo, -1e30);
-            hi = std::min(hi, 1e30);
-            // AABB::hit rejects t_max <= t_min (aabb.rs:33): a box with no thickness on an axis
-            // (e.g. an axis-aligned triangle, triangle_mesh.rs:43-45) is never hit
-            if (!(hi > lo)) degenerate = true;
-            p.lo[a] = lo;
-            p.hi[a] = hi;
-            p.c[a] = 0.5 * (lo + hi);
-        }
-        if (degenerate) continue;
-        p.root = i;
-        // objects the bbox gates (not a bare sphere / box / rect): their surface may reach outside it (geom_bound)
-        bool bounded = true;
-        if (r >= 0 && root_gate[i]) {
-            double glo[3], ghi[3];
-            bounded = geom_bound(nodes, xf, r, glo, ghi);
-            if (bounded)
-                for (int a = 0; a < 3; ++a) {
-                    p.lo[a] = std::min(p.lo[a], std::max(glo[a], -1e30));
-                    p.hi[a] = std::max(p.hi[a], std::min(ghi[a], 1e30));
-                    p.c[a] = 0.5 * (p.lo[a] + p.hi[a]);
+    {
+        bool anyq[kMaxChunks] = {};
+        double om[kMaxChunks];
+        for (double& v : om) v = 1.0;
+        // every chunk appends to its own lists; they are concatenated in chunk order, i.e. in ascending object id
+        const int chunks = parallel_chunks((size_t)s->n_roots, [&](int chunk, size_t begin, size_t end) {
+            std::vector<BuildPrim>&my = sc.part[chunk], &my_loose = sc.part_loose[chunk];
+            my.clear();
+            my_loose.clear();
+            for (size_t ii = begin; ii < end; ++ii) {
+                const int i = (int)ii;
+                int r = s->roots[i];
+                const double* bb = s->root_bbox + 6 * (size_t)i;
+                root_gate[i] = 0;
+                for (int k = 0; k < 4; ++k) root_sphere[4 * (size_t)i + k] = 0.0;
+                if (r < 0) {
+                    root_kind[i] = ROOT_TRIANGLE;
+                } else {
+                    const rs_node& n = nodes[r];
+                    bool static_sphere = n.type == RS_NODE_SPHERE && n.p[4] == 0.0 && n.p[5] == 0.0 && n.p[6] == 0.0;
+                    if (static_sphere) {
+                        root_kind[i] = ROOT_SPHERE;
+                        for (int k = 0; k < 4; ++k) root_sphere[4 * (size_t)i + k] = n.p[k];
+                    } else {
+                        // rect / box, bare or under one TfFacade: inline distance tests in extend
+                        const rs_node& inner = n.type == RS_NODE_TRANSFORM ? nodes[n.child0] : n;
+                        // (a quadric root takes the same inline route, but only the generic-tier kernels hold its code)
+                        root_kind[i] = (inner.type == RS_NODE_BOX || inner.type == RS_NODE_RECT || inner.type == RS_NODE_QUADRIC) ? ROOT_FLAT : ROOT_GENERIC;
+                        anyq[chunk] |= inner.type == RS_NODE_QUADRIC;
+                        // spheres / boxes / rects always lie inside their reference bbox; everything
+                        // else is clipped by it the way the reference's BVH leaf clips it
+                        root_gate[i] = !(n.type == RS_NODE_SPHERE || n.type == RS_NODE_BOX || n.type == RS_NODE_RECT);
+                    }
                 }
+                BuildPrim p;
+                p.pad = 0;
+                bool degenerate = false;
+                for (int a = 0; a < 3; ++a) {
+                    double lo = bb[a], hi = bb[3 + a];
+                    if (!(lo == lo) || !(hi == hi)) degenerate = true;
+                    lo = std::max(lo, -1e30);
+                    hi = std::min(hi, 1e30);
+                    // AABB::hit rejects t_max <= t_min (aabb.rs:33): a box with no thickness on an axis
+                    // (e.g. an axis-aligned triangle, triangle_mesh.rs:43-45) is never hit
+                    if (!(hi > lo)) degenerate = true;
+                    p.lo[a] = lo;
+                    p.hi[a] = hi;
+                    p.c[a] = 0.5 * (lo + hi);
+                }
+                if (degenerate) continue;
+                p.root = i;
+                // objects the bbox gates (not a bare sphere / box / rect): their surface may reach outside it (geom_bound)
+                bool bounded = true;
+                if (r >= 0 && root_gate[i]) {
+                    double glo[3], ghi[3];
+                    bounded = geom_bound(nodes, xf, r, glo, ghi);
+                    if (bounded)
+                        for (int a = 0; a < 3; ++a) {
+                            p.lo[a] = std::min(p.lo[a], std::max(glo[a], -1e30));
+                            p.hi[a] = std::max(p.hi[a], std::min(ghi[a], 1e30));
+                            p.c[a] = 0.5 * (p.lo[a] + p.hi[a]);
+                        }
+                }
+                for (int a = 0; a < 3; ++a) om[chunk] = std::max(om[chunk], std::max(std::fabs(p.lo[a]), std::fabs(p.hi[a])));
+                (bounded ? my : my_loose).push_back(p);
+            }
+        });
+        size_t off[kMaxChunks + 1] = {0};
+        for (int c = 0; c < chunks; ++c) {
+            off[c + 1] = off[c] + sc.part[c].size();
+            loose.insert(loose.end(), sc.part_loose[c].begin(), sc.part_loose[c].end());
+            any_quadric_root |= anyq[c];
+            omax = std::max(omax, om[c]);
         }
-        for (int a = 0; a < 3; ++a) omax = std::max(omax, std::max(std::fabs(p.lo[a]), std::fabs(p.hi[a])));
-        (bounded ? prims : loose).push_back(p);
+        prims.resize(off[chunks]);
+        parallel_chunks((size_t)chunks << 16, [&](int, size_t begin, size_t end) {  // (one chunk of this loop = one part)
+            for (size_t c = begin >> 16; c < (end >> 16); ++c)
+                if (!sc.part[c].empty()) std::memcpy(prims.data() + off[c], sc.part[c].data(), sc.part[c].size() * sizeof(BuildPrim));
+        });
     }
+    stage("root tables");
     // small worlds are searched as one list (RS_OPT_LIST_MAX); otherwise only the loose objects are
     if (const char* e = std::getenv("RAYSNAIL_B200_LIST_MAX")) ctx->list_max = std::atoi(e);
     bool flat_or_tree = !loose.empty();
@@ -1084,20 +1182,46 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
         return ra != rb ? ra < rb : a.root < b.root;
     });
     const bool any_object = !prims.empty() || !ctx->list_host.empty();
-    ctx->bvh_host.clear();
+    // (leaf references are made of the kinds and the node / triangle numbers of the objects)
+    const bool same_refs = ctx->root_kind_host == root_kind && ctx->root_node_host.size() == (size_t)s->n_roots &&
+                           (s->n_roots == 0 || std::memcmp(ctx->root_node_host.data(), s->roots, (size_t)s->n_roots * sizeof(int)) == 0);
     ctx->root_kind_host = root_kind;
     ctx->root_node_host.assign(s->roots, s->roots + s->n_roots);
     int bvh_root = (int)0x80000000;  // RS_BVH_SENTINEL: no tree
-    if (!prims.empty()) bvh_root = build_bvh(prims, 0, prims.size(), 0, ctx->bvh_host);
-    ctx->bvh4_host.clear();
-    if (!prims.empty() && bvh_root < 0) {
-        bvh_root = ~leaf_ref(ctx, ~bvh_root);  // single object
-    } else if (!prims.empty() && ctx->bvh_width == 4) {
-        int need = 0;
-        bvh_root = collapse_bvh4(ctx->bvh_host, bvh_root, ctx->bvh4_host, need);
-        if (need + 1 > RS_TRAVERSAL_STACK) return fail(ctx, RS_ERR_UNSUPPORTED, "world BVH too deep for the traversal stack");
-        std::vector<HostBvhNode>().swap(ctx->bvh_host);  // only the collapsed tree is kept
+    // The tree holds object ids and f64 bounds only (kinds and leaf references are filled in by upload_bvh), so it
+    // is a function of `prims` and the width alone: the SAH build (0.9 s for a 1 M-triangle mesh, the whole
+    // cost of a re-upload) is skipped when neither changed.  RAYSNAIL_B200_BVH_CACHE=0 always rebuilds.
+    static const bool cache_on = [] { const char* e = std::getenv("RAYSNAIL_B200_BVH_CACHE"); return !e || std::atoi(e) != 0; }();
+    const size_t key_bytes = prims.size() * sizeof(BuildPrim);
+    ctx->bvh_reused = cache_on && prims.size() > 1 && ctx->bvh_key_width == ctx->bvh_width && ctx->bvh_key.size() == key_bytes;
+    if (ctx->bvh_reused) {
+        bool differ[kMaxChunks] = {};
+        const int chunks = parallel_chunks(key_bytes, [&](int chunk, size_t begin, size_t end) {
+            differ[chunk] = std::memcmp(ctx->bvh_key.data() + begin, reinterpret_cast<const unsigned char*>(prims.data()) + begin, end - begin) != 0;
+        });
+        for (int c = 0; c < chunks; ++c) ctx->bvh_reused = ctx->bvh_reused && !differ[c];
     }
+    ctx->tree_dev_valid = ctx->tree_dev_valid && ctx->bvh_reused && same_refs;
+    if (ctx->bvh_reused) {
+        bvh_root = ctx->bvh_key_root;
+    } else {
+        ctx->bvh_key_width = 0;  // (nothing valid is kept while the build below can still fail)
+        ctx->bvh_host.clear();
+        ctx->bvh4_host.clear();
+        if (cache_on && prims.size() > 1) ctx->bvh_key.assign(reinterpret_cast<const unsigned char*>(prims.data()), reinterpret_cast<const unsigned char*>(prims.data()) + key_bytes);
+        else std::vector<unsigned char>().swap(ctx->bvh_key);
+        if (!prims.empty()) bvh_root = build_bvh(prims, 0, prims.size(), 0, ctx->bvh_host);
+        if (!prims.empty() && bvh_root < 0) {
+            bvh_root = ~leaf_ref(ctx, ~bvh_root);  // single object
+        } else if (!prims.empty() && ctx->bvh_width == 4) {
+            int need = 0;
+            bvh_root = collapse_bvh4(ctx->bvh_host, bvh_root, ctx->bvh4_host, need);
+            if (need + 1 > RS_TRAVERSAL_STACK) return fail(ctx, RS_ERR_UNSUPPORTED, "world BVH too deep for the traversal stack");
+            std::vector<HostBvhNode>().swap(ctx->bvh_host);  // only the collapsed tree is kept
+        }
+        if (!ctx->bvh_key.empty()) { ctx->bvh_key_width = ctx->bvh_width; ctx->bvh_key_root = bvh_root; }
+    }
+    stage(ctx->bvh_reused ? "tree (kept)" : "tree (built)");
     // (binary tree: depth <= 24 SAH levels + log2(n) median levels, one push per level: fits)
     ctx->scene_omax = omax;
     // which kernel specialisations this scene needs
@@ -1163,20 +1287,25 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if (pb.nested_medium) return fail(ctx, RS_ERR_UNSUPPORTED, "a ConstantMedium inside the boundary of another ConstantMedium is not supported");
 
     // triangles: p0, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56)
-    // 80-byte records (five 128-bit loads); the spare word names the world object the triangle is
-    std::vector<double> tri_geom((size_t)s->n_tris * 10, 0.0);
-    for (int i = 0; i < s->n_tris; ++i) {
-        const double* v = s->tri_verts + 9 * (size_t)i;
-        double* g = &tri_geom[10 * (size_t)i];
-        g[0] = v[0]; g[1] = v[1]; g[2] = v[2];
-        g[3] = v[0] - v[3]; g[4] = v[1] - v[4]; g[5] = v[2] - v[5];
-        g[6] = v[0] - v[6]; g[7] = v[1] - v[7]; g[8] = v[2] - v[8];
-        const int64_t none = -1;
-        std::memcpy(&g[9], &none, 8);
-    }
+    // RS_TRI_DOUBLES per record (load_triangle); word 9 names the world object the triangle is
+    constexpr size_t TD = RS_TRI_DOUBLES;
+    std::vector<double>& tri_geom = sc.tri_geom;
+    tri_geom.resize((size_t)s->n_tris * TD);
+    parallel_chunks((size_t)s->n_tris, [&](int, size_t begin, size_t end) {
+        for (size_t i = begin; i < end; ++i) {
+            const double* v = s->tri_verts + 9 * i;
+            double* g = &tri_geom[TD * i];
+            for (size_t k = 10; k < TD; ++k) g[k] = 0.0;
+            g[0] = v[0]; g[1] = v[1]; g[2] = v[2];
+            g[3] = v[0] - v[3]; g[4] = v[1] - v[4]; g[5] = v[2] - v[5];
+            g[6] = v[0] - v[6]; g[7] = v[1] - v[7]; g[8] = v[2] - v[8];
+            const int64_t none = -1;
+            std::memcpy(&g[9], &none, 8);
+        }
+    });
     for (int i = 0; i < s->n_roots; ++i)
         if (s->roots[i] < 0) {
-            double& slot = tri_geom[10 * (size_t)(~s->roots[i]) + 9];
+            double& slot = tri_geom[TD * (size_t)(~s->roots[i]) + 9];
             int64_t root;
             std::memcpy(&root, &slot, 8);
             if (root != -1) return fail(ctx, RS_ERR_UNSUPPORTED, "a triangle is listed as two world objects");
@@ -1184,6 +1313,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
             std::memcpy(&slot, &root, 8);
         }
 
+    stage("programs + triangle records");
     // ---- upload -------------------------------------------------------------------------------
     int rc;
     if ((rc = upload(ctx, ctx->d_nodes, nodes.data(), nodes.size())) != RS_OK) return rc;
@@ -1204,11 +1334,15 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if ((rc = upload(ctx, ctx->d_materials, s->materials, (size_t)s->n_materials)) != RS_OK) return rc;
     {
         // flattened per-root / per-material / per-light tables (see MatHot in rt_scene.cuh)
-        std::vector<double> root_inv_r(s->n_roots, 0.0);
-        std::vector<int> root_material(s->n_roots, -1);
+        std::vector<double>& root_inv_r = sc.root_inv_r;
+        std::vector<int>& root_material = sc.root_material;
+        root_inv_r.resize(s->n_roots);
+        root_material.resize(s->n_roots);
         bool all_spheres = s->n_roots > 0;
         for (int i = 0; i < s->n_roots; ++i) {
             const int r = s->roots[i];
+            root_inv_r[i] = 0.0;
+            root_material[i] = -1;
             if (root_kind[i] == ROOT_SPHERE) { root_inv_r[i] = nodes[r].p[7]; root_material[i] = nodes[r].material; }
             else if (root_kind[i] == ROOT_TRIANGLE) root_material[i] = s->tri_material[~r];
             else if (root_kind[i] == ROOT_FLAT) root_material[i] = (nodes[r].type == RS_NODE_TRANSFORM ? nodes[nodes[r].child0] : nodes[r]).material;
@@ -1273,6 +1407,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if ((rc = upload(ctx, ctx->d_perm, s->perlin_perm, (size_t)s->n_perlin_perm)) != RS_OK) return rc;
     if ((rc = upload(ctx, ctx->d_values, s->perlin_values, (size_t)s->n_perlin_values)) != RS_OK) return rc;
 
+    stage("uploads");
     DScene& S = ctx->scene;
     S.nodes = ctx->d_nodes.as<rs_node>();
     S.xf = ctx->d_xf.as<XformPre>();
@@ -1311,6 +1446,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     ctx->n_lights = s->n_lights;
     ctx->padded_omax = -1.0;
     if ((rc = upload_bvh(ctx, omax * 1.25)) != RS_OK) return rc;
+    stage("tree conversion + upload");
     ctx->has_scene = true;
     return RS_OK;
 }

@@ -18,6 +18,7 @@
 // ping-pong buffer with __ballot_sync-aggregated atomics.
 #include <cfloat>
 
+#define RS_DEFINE_VIOLATIONS 1
 #include "kernels.cuh"
 
 namespace rsd {
@@ -29,6 +30,29 @@ namespace rsd {
 // conversions of the ray; the absolute part (origin rounding) is folded into the padded boxes.
 #define RS_SLAB_EPS 9.5367431640625e-07f  // 2^-20
 
+// ---- 256-bit global loads / stores (sm_100: LDG.E.256 / STG.E.256, PTX ld.global.v8.b32) ---------------------------
+// A 64-byte BVH node or path record is two requests to L1 instead of four.  The walk of incoherent rays (every lane
+// of a warp at another node) is bound by L1 request throughput, not by bytes: ncu, 1 M-triangle mesh, bounce >= 1:
+// l1tex throughput 80 % of peak at 44 % hit rate.  RS_TUNE_LDG256=0 builds the 128-bit form for A/B.
+#ifndef RS_TUNE_LDG256
+#define RS_TUNE_LDG256 1
+#endif
+struct U8 { uint32_t v[8]; };
+__device__ __forceinline__ U8 ldg256_nc(const void* p) {  // read-only data (scene tables): ld.global.nc
+    U8 r;
+    asm("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+        : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7]) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ U8 ldg256(const void* p) {  // data another kernel wrote (path records)
+    U8 r;
+    asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+        : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7]) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void stg256(void* p, uint4 a, uint4 b) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};\n" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w) : "memory");
+}
 struct PathRec {
     Ray ray;
     float3 T;
@@ -58,24 +82,45 @@ __device__ __forceinline__ uint4 pack_d2(double a, double b) {
     return make_uint4((uint32_t)__double2loint(a), (uint32_t)__double2hiint(a), (uint32_t)__double2loint(b), (uint32_t)__double2hiint(b));
 }
 __device__ __forceinline__ void store_path(const WaveState& ws, const PathBuf& B, uint32_t i, const PathRec& p) {
+    if (!RS_IN_BOUNDS(i < ws.capacity)) return;
     uint4* r = B.rec + 4 * (size_t)i;
+#if RS_TUNE_LDG256
+    stg256(r, pack_d2(p.ray.o.x, p.ray.o.y), pack_d2(p.ray.o.z, p.ray.d.x));
+    stg256(r + 2, pack_d2(p.ray.d.y, p.ray.d.z), make_uint4(__float_as_uint(p.T.x), __float_as_uint(p.T.y), __float_as_uint(p.T.z), p.slot));
+#else
     r[0] = pack_d2(p.ray.o.x, p.ray.o.y);
     r[1] = pack_d2(p.ray.o.z, p.ray.d.x);
     r[2] = pack_d2(p.ray.d.y, p.ray.d.z);
     r[3] = make_uint4(__float_as_uint(p.T.x), __float_as_uint(p.T.y), __float_as_uint(p.T.z), p.slot);
+#endif
     if (ws.uses_time) B.time[i] = p.ray.time;
 }
 __device__ __forceinline__ void load_path(const FrameParams& fp, const WaveState& ws, const PathBuf& B, uint32_t i, PathRec& p) {
+    if (!RS_IN_BOUNDS(i < ws.capacity)) i = 0;
     const uint4* r = B.rec + 4 * (size_t)i;
+#if RS_TUNE_LDG256
+    const U8 a = ldg256(r), b = ldg256(r + 2);
+    const uint4 q0 = make_uint4(a.v[0], a.v[1], a.v[2], a.v[3]), q1 = make_uint4(a.v[4], a.v[5], a.v[6], a.v[7]);
+    const uint4 q2 = make_uint4(b.v[0], b.v[1], b.v[2], b.v[3]), q3 = make_uint4(b.v[4], b.v[5], b.v[6], b.v[7]);
+#else
     const uint4 q0 = r[0], q1 = r[1], q2 = r[2], q3 = r[3];
+#endif
     unpack_path(fp, q0, q1, q2, q3, p);
     if (ws.uses_time) p.ray.time = B.time[i];
 }
 __device__ __forceinline__ void load_ray_only(const FrameParams& fp, const WaveState& ws, const PathBuf& B, uint32_t i, Ray& r, uint32_t& pixel,
                                               uint32_t& sample) {
+    if (!RS_IN_BOUNDS(i < ws.capacity)) i = 0;
     const uint4* rec = B.rec + 4 * (size_t)i;
+#if RS_TUNE_LDG256
+    const U8 a = ldg256(rec), b = ldg256(rec + 2);
+    const uint4 q0 = make_uint4(a.v[0], a.v[1], a.v[2], a.v[3]), q1 = make_uint4(a.v[4], a.v[5], a.v[6], a.v[7]);
+    const uint4 q2 = make_uint4(b.v[0], b.v[1], b.v[2], b.v[3]);
+    const uint32_t slot = b.v[7];
+#else
     const uint4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
     const uint32_t slot = rec[3].w;
+#endif
     r.o = v3(__hiloint2double((int)q0.y, (int)q0.x), __hiloint2double((int)q0.w, (int)q0.z), __hiloint2double((int)q1.y, (int)q1.x));
     r.d = v3(__hiloint2double((int)q1.w, (int)q1.z), __hiloint2double((int)q2.y, (int)q2.x), __hiloint2double((int)q2.w, (int)q2.z));
     r.time = ws.uses_time ? B.time[i] : 0.0;
@@ -164,6 +209,21 @@ __device__ __forceinline__ double2 lds_d2(uint32_t a) {
     return v;
 }
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];\n" ::"l"(p)); }
+
+// one 64-byte node of the binary tree: two children with their boxes (BvhNode)
+__device__ __forceinline__ void load_node(const BvhNode* n, float4& bx, float4& by, float4& bz, int4& ch) {
+#if RS_TUNE_LDG256
+    const U8 a = ldg256_nc(n), b = ldg256_nc(reinterpret_cast<const unsigned char*>(n) + 32);
+    bx = make_float4(__uint_as_float(a.v[0]), __uint_as_float(a.v[1]), __uint_as_float(a.v[2]), __uint_as_float(a.v[3]));
+    by = make_float4(__uint_as_float(a.v[4]), __uint_as_float(a.v[5]), __uint_as_float(a.v[6]), __uint_as_float(a.v[7]));
+    bz = make_float4(__uint_as_float(b.v[0]), __uint_as_float(b.v[1]), __uint_as_float(b.v[2]), __uint_as_float(b.v[3]));
+    ch = make_int4((int)b.v[4], (int)b.v[5], (int)b.v[6], (int)b.v[7]);
+#else
+    const float4* np = reinterpret_cast<const float4*>(n);
+    bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
+    ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+#endif
+}
 // where the staged kernels keep the tree and the sphere table (shared-space addresses)
 struct Staged {
     uint32_t nodes, spheres;
@@ -257,7 +317,7 @@ __global__ void __launch_bounds__(RS_BLOCK) raygen_kernel(const __grid_constant_
                 uint32_t s_j = __umulhi(sample, fp.magic_q), s_i = sample - s_j * (uint32_t)fp.sqrt_spp;
                 if (s_i >= (uint32_t)fp.sqrt_spp) { ++s_j; s_i -= (uint32_t)fp.sqrt_spp; }
                 RngCtx rng;
-                rng.key = fp.key;
+                rng.key = &fp.rk;
                 rng.pixel = pixel;
                 rng.sample = sample;
                 rng.depth = 0;
@@ -538,9 +598,7 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
                 bx = lds_f4(na), by = lds_f4(na + 16u), bz = lds_f4(na + 32u);
                 ch = lds_i4(na + 48u);
             } else {
-                const float4* np = reinterpret_cast<const float4*>(S.bvh2 + node);
-                bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
-                ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+                load_node(S.bvh2 + node, bx, by, bz, ch);
             }
 #if RS_TUNE_FFMA2
             const float2 ix2 = make_float2(idx, idx), iy2 = make_float2(idy, idy), iz2 = make_float2(idz, idz);
@@ -569,6 +627,7 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
                 const int second = swap ? ch.x : ch.y;
                 const float second_near = swap ? near0 : near1;
                 if (sp < RS_STACK) stack[sp++] = ((unsigned long long)__float_as_uint(second_near) << 32) | (unsigned long long)(uint32_t)second;
+                else (void)RS_IN_BOUNDS(false);  // a dropped push would lose a subtree: upload bounds the depth so that it cannot happen
                 node = swap ? ch.y : ch.x;
             } else if (h0) {
                 node = ch.x;
@@ -733,14 +792,14 @@ __global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE 
         int cls = -1;
         uint2* queue_slot = nullptr;
         RngCtx rng_of_lane;
-        rng_of_lane.key = fp.key;
+        rng_of_lane.key = &fp.rk;
         rng_of_lane.pixel = 0;
         rng_of_lane.sample = 0;
         rng_of_lane.depth = (uint32_t)bounce + 1;
         if (live) {
             Ray ray;
             RngCtx rng;
-            rng.key = fp.key;
+            rng.key = &fp.rk;
             if constexpr (FIRST) {
                 decode_slot(fp, i, rng.pixel, rng.sample);
                 const uint32_t width = (uint32_t)fp.cam.width, row = rng.pixel / width, col = rng.pixel - row * width;
@@ -775,7 +834,7 @@ __global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE 
                     // own (top) material, and MixedMaterial::emitted is None (mixed_material.rs:53-55,
                     // camera.rs:172-174); the light's `scatter` is None as well (material/mod.rs:59-61), so the
                     // path ends here and adds nothing
-                    if constexpr (FIRST) ws.contrib[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if constexpr (FIRST) { if (RS_IN_BOUNDS(i < ws.capacity)) ws.contrib[i] = make_float4(0.f, 0.f, 0.f, 0.f); }
                     cls = -1;
                 } else if (miss_in_extend && (tf & 0x3ff) == RS_MAT_DIFFUSE_LIGHT) {
                     // a DiffuseLight never scatters (light.rs:33-35): the path ends here with
@@ -785,22 +844,22 @@ __global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE 
                     const float4 c = mh.c0;
                     const double mul = mh.a;
                     const uint4 q3 = FIRST ? make_uint4(0x3f800000u, 0x3f800000u, 0x3f800000u, i) : in.rec[4 * (size_t)i + 3];  // (T, slot)
-                    ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * (float)((double)c.x * mul), __uint_as_float(q3.y) * (float)((double)c.y * mul),
+                    if (RS_IN_BOUNDS(q3.w < ws.capacity)) ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * (float)((double)c.x * mul), __uint_as_float(q3.y) * (float)((double)c.y * mul),
                                                    __uint_as_float(q3.z) * (float)((double)c.z * mul), 0.f);
                     cls = -1;
                 } else {
-                    if (MODE >= 3 && S.root_kind[best.root] == ROOT_GENERIC) ws.hit_src[i] = make_int2(best.src, best.flavor);
-                    ws.hit[i] = h;
+                    if (MODE >= 3 && S.root_kind[best.root] == ROOT_GENERIC && RS_IN_BOUNDS(i < ws.capacity)) ws.hit_src[i] = make_int2(best.src, best.flavor);
+                    if (RS_IN_BOUNDS(i < ws.capacity && best.root < S.n_roots)) ws.hit[i] = h;
                 }
             } else if (miss_in_extend) {
                 // a miss ends the path with `world.background(ray)` (camera.rs:253-254): finish it
                 // here instead of sending it through a queue to the shade kernel
                 const float4 bg = background(S, ray.d);
                 const uint4 q3 = FIRST ? make_uint4(0x3f800000u, 0x3f800000u, 0x3f800000u, i) : in.rec[4 * (size_t)i + 3];  // (T, slot)
-                ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * bg.x, __uint_as_float(q3.y) * bg.y, __uint_as_float(q3.z) * bg.z, 0.f);
+                if (RS_IN_BOUNDS(q3.w < ws.capacity)) ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * bg.x, __uint_as_float(q3.y) * bg.y, __uint_as_float(q3.z) * bg.z, 0.f);
                 cls = -1;
             } else {
-                ws.hit[i] = h;
+                if (RS_IN_BOUNDS(i < ws.capacity)) ws.hit[i] = h;
             }
             if constexpr (FIRST) {
                 if (cls >= 0) {  // the path goes on to shade: now it needs its record (and a zeroed contribution)
@@ -809,7 +868,8 @@ __global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE 
                     p.T = make_float3(1.f, 1.f, 1.f);
                     p.slot = i;
                     store_path(ws, in, i, p);
-                    ws.contrib[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (RS_CHECKED && (fp.flags & 0x80000000u) && i < 32u) store_path(ws, in, ws.capacity + i, p);  // (checked builds: the negative control)
+                    if (RS_IN_BOUNDS(i < ws.capacity)) ws.contrib[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             }
         }
@@ -847,7 +907,8 @@ __global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE 
             if (lane_id() == leader) qbase = atomic_add_async(&class_count[key * RS_COUNTER_STRIDE], __popc(peers), lane_zero);
             qbase = __shfl_sync(peers, qbase, leader);
             const uint32_t rank = __popc(peers & ((1u << lane_id()) - 1u));
-            uint2* const slot = ws.class_queue + ((size_t)key * ws.capacity + qbase + rank);
+            (void)RS_IN_BOUNDS(key >= 0 && key < RS_NUM_CLASSES && qbase + rank < ws.capacity);
+            uint2* const slot = ws.class_queue + ((size_t)key * ws.capacity + (RS_CHECKED ? min(qbase + rank, ws.capacity - 1u) : qbase + rank));
             if constexpr (!RESERVE) *slot = make_uint2(i, 0xffffffffu);
             else queue_slot = slot;
         }
@@ -940,14 +1001,14 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
     bool exhausted = false;
     if (lane == 0) pend = atomic_add_async(head, 32u, lane_zero);
     RngCtx no_rng;
-    no_rng.key = fp.key; no_rng.pixel = 0; no_rng.sample = 0; no_rng.depth = 0;
+    no_rng.key = &fp.rk; no_rng.pixel = 0; no_rng.sample = 0; no_rng.depth = 0;
 
     // epilogue of up to 32 queued rays (extend_kernel's, for a ray that came from the path buffer)
     auto epilogue = [&](const bool live, const uint4 e) {
         const uint32_t ri = e.x;
         int cls = -1;
         RngCtx rng;
-        rng.key = fp.key; rng.pixel = 0; rng.sample = 0; rng.depth = (uint32_t)bounce + 1;
+        rng.key = &fp.rk; rng.pixel = 0; rng.sample = 0; rng.depth = (uint32_t)bounce + 1;
         if (live) {
             const uint4 q3 = in.rec[4 * (size_t)ri + 3];  // (T, slot)
             decode_slot(fp, q3.w, rng.pixel, rng.sample);
@@ -970,20 +1031,20 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
                 } else if (miss_in_extend && (tf & 0x3ff) == RS_MAT_DIFFUSE_LIGHT) {
                     const float4 c = mh.c0;
                     const double mul = mh.a;
-                    ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * (float)((double)c.x * mul), __uint_as_float(q3.y) * (float)((double)c.y * mul),
+                    if (RS_IN_BOUNDS(q3.w < ws.capacity)) ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * (float)((double)c.x * mul), __uint_as_float(q3.y) * (float)((double)c.y * mul),
                                                    __uint_as_float(q3.z) * (float)((double)c.z * mul), 0.f);
                     cls = -1;
                 } else {
-                    ws.hit[ri] = h;
+                    if (RS_IN_BOUNDS(ri < ws.capacity)) ws.hit[ri] = h;
                 }
             } else if (miss_in_extend) {
                 const uint4 q1 = in.rec[4 * (size_t)ri + 1], q2 = in.rec[4 * (size_t)ri + 2];
                 const V3 d = v3(__hiloint2double((int)q1.w, (int)q1.z), __hiloint2double((int)q2.y, (int)q2.x), __hiloint2double((int)q2.w, (int)q2.z));
                 const float4 bg = background(S, d);
-                ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * bg.x, __uint_as_float(q3.y) * bg.y, __uint_as_float(q3.z) * bg.z, 0.f);
+                if (RS_IN_BOUNDS(q3.w < ws.capacity)) ws.contrib[q3.w] = make_float4(__uint_as_float(q3.x) * bg.x, __uint_as_float(q3.y) * bg.y, __uint_as_float(q3.z) * bg.z, 0.f);
                 cls = -1;
             } else {
-                ws.hit[ri] = h;
+                if (RS_IN_BOUNDS(ri < ws.capacity)) ws.hit[ri] = h;
             }
         }
         const bool go = live && cls >= 0;
@@ -1011,7 +1072,8 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
             uint32_t qbase = 0;
             if (lane == leader) qbase = atomic_add_async(&class_count[key * RS_COUNTER_STRIDE], __popc(peers), lane_zero);
             qbase = __shfl_sync(peers, qbase, leader);
-            queue_slot = ws.class_queue + ((size_t)key * ws.capacity + qbase + __popc(peers & lt));
+            (void)RS_IN_BOUNDS(key >= 0 && key < RS_NUM_CLASSES && qbase + __popc(peers & lt) < ws.capacity);
+            queue_slot = ws.class_queue + ((size_t)key * ws.capacity + (RS_CHECKED ? min(qbase + (uint32_t)__popc(peers & lt), ws.capacity - 1u) : qbase + __popc(peers & lt)));
             if constexpr (!RESERVE) *queue_slot = make_uint2(ri, 0xffffffffu);
         }
         if constexpr (RESERVE) {
@@ -1107,9 +1169,9 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
         // ---- node steps and batched leaf tests until enough lanes are done ----
         while (true) {
             if (node >= 0) {
-                const float4* np = reinterpret_cast<const float4*>(S.bvh2 + node);
-                const float4 bx = __ldg(np), by = __ldg(np + 1), bz = __ldg(np + 2);
-                const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+                float4 bx, by, bz;
+                int4 ch;
+                load_node(S.bvh2 + node, bx, by, bz, ch);
                 const float2 ix2 = make_float2(idx, idx), iy2 = make_float2(idy, idy), iz2 = make_float2(idz, idz);
                 const float2 ox2 = make_float2(-oodx, -oodx), oy2 = make_float2(-oody, -oody), oz2 = make_float2(-oodz, -oodz);
                 float2 ta = ffma2(make_float2(bx.x, bx.y), ix2, ox2), tb = ffma2(make_float2(bx.z, bx.w), iy2, oy2), tc = ffma2(make_float2(bz.x, bz.y), iz2, oz2);
@@ -1124,6 +1186,7 @@ __global__ void __launch_bounds__(RS_BLOCK, RS_TUNE_STREAM_BLOCKS) extend_stream
                     const int second = swap ? ch.x : ch.y;
                     const float second_near = swap ? near0 : near1;
                     if (sp < RS_STACK) RS_PUSH(((unsigned long long)__float_as_uint(second_near) << 32) | (unsigned long long)(uint32_t)second);
+                    else (void)RS_IN_BOUNDS(false);
 #if RS_TUNE_STREAM_PREFETCH
                     // the walk is bound by the latency of its dependent node fetches (ncu: long_scoreboard 56 % of the
                     // stall samples at 8 warps per scheduler): start the fetch of the postponed child now
@@ -1428,7 +1491,7 @@ __global__ void __launch_bounds__(RS_SHADE_STAGED(TIER) ? RS_TUNE_SHADE_BLOCK : 
     };
 #endif
     auto stage_item = [&](int buf, uint2 entry) {  // entry = (path index, output slot reserved by extend)
-        const uint32_t i = entry.x;
+        const uint32_t i = RS_IN_BOUNDS(entry.x < ws.capacity) ? entry.x : 0u;
         outq[buf * 32] = entry.y;
         if constexpr (GENERIC) pidx[buf * 32] = i;
         uint4* s = stage + buf * (RS_SHADE_STAGE * 32);
@@ -1503,7 +1566,7 @@ __global__ void __launch_bounds__(RS_SHADE_STAGED(TIER) ? RS_TUNE_SHADE_BLOCK : 
         PathRec p;
         HitA ha;
         RngCtx rng;
-        rng.key = fp.key;
+        rng.key = &fp.rk;
         rng.pixel = 0;
         rng.sample = 0;
         rng.depth = (uint32_t)bounce + 1;
@@ -1520,8 +1583,9 @@ __global__ void __launch_bounds__(RS_SHADE_STAGED(TIER) ? RS_TUNE_SHADE_BLOCK : 
                 }
             } else {
                 load_path(fp, ws, in, i, p);
-                ha = ws.hit[i];
+                ha = ws.hit[RS_IN_BOUNDS(i < ws.capacity) ? i : 0u];
             }
+            (void)RS_IN_BOUNDS(p.slot < ws.capacity && (cls == 0 || (ha.root >= 0 && ha.root < S.n_roots)));
             rng.pixel = p.pixel;
             rng.sample = p.sample;
         }
@@ -1685,7 +1749,7 @@ __global__ void __launch_bounds__(RS_SHADE_STAGED(TIER) ? RS_TUNE_SHADE_BLOCK : 
                 // No material of the reference both emits and scatters (DiffuseLight never scatters,
                 // material/light.rs; nothing else overrides `emitted`), so a path adds radiance exactly
                 // once — when it ends on a light or leaves the scene: a plain 128-bit store, no RMW.
-                ws.contrib[p.slot] = make_float4(p.T.x * add.x, p.T.y * add.y, p.T.z * add.z, 0.f);
+                if (RS_IN_BOUNDS(p.slot < ws.capacity)) ws.contrib[p.slot] = make_float4(p.T.x * add.x, p.T.y * add.y, p.T.z * add.z, 0.f);
             }
             if (has_dbg) {
                 if (dbg.kind) dbg.kind[p.pixel] = kind;
@@ -1756,7 +1820,7 @@ __global__ void __launch_bounds__(RS_BLOCK) probe_primary_kernel(const __grid_co
             continue;
         }
         RngCtx rng;
-        rng.key = fp.key; rng.pixel = p.pixel; rng.sample = p.sample; rng.depth = 1;
+        rng.key = &fp.rk; rng.pixel = p.pixel; rng.sample = p.sample; rng.depth = 1;
         HitRec h;
         const int2 src = S.root_kind[ha.root] == ROOT_GENERIC ? ws.hit_src[i] : make_int2(0, 0);
         rebuild_hit<true, true>(S, p.ray, ha, src, true, h);
@@ -2026,6 +2090,17 @@ void launch_finalize_peers(const PeerAccums& peers, const unsigned char* mask, f
     if (end <= begin) return;
     finalize_peers_kernel<<<grid_for(end - begin), RS_BLOCK, 0, s>>>(peers, mask, out, begin, end, 1.0f / (float)n_samples, gamma);
 }
+unsigned long long read_violations() {
+#if RS_CHECKED
+    unsigned long long v = 0, zero = 0;
+    cudaMemcpyFromSymbol(&v, rs_violations, sizeof(v));  // (synchronises with the default stream; checked builds only)
+    cudaMemcpyToSymbol(rs_violations, &zero, sizeof(zero));
+    return v;
+#else
+    return 0ull;
+#endif
+}
+
 void launch_signal(uint32_t* counter, cudaStream_t s) { signal_kernel<<<1, 1, 0, s>>>(counter); }
 void launch_wait_counter(const uint32_t* counter, uint32_t expect, cudaStream_t s) { wait_counter_kernel<<<1, 32, 0, s>>>(counter, expect); }
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s) {

@@ -81,6 +81,7 @@ struct FrameParams {
     int stratum_row_begin;
     uint32_t flags;
     uint2 key;
+    PhiloxKeys rk;  // the ten Philox round keys of `key` (rt_math.cuh)
     // wave
     uint32_t pixel0;     // first pixel of the wave
     uint32_t n_pixels;   // P
@@ -122,6 +123,7 @@ struct PeerAccums {
 };
 void launch_finalize_peers(const PeerAccums& peers, const unsigned char* mask, float4* out, int64_t begin, int64_t end, int n_samples, int gamma,
                            cudaStream_t s);
+unsigned long long read_violations();  // RS_CHECKED builds: failed bounds checks since the last call (0 otherwise)
 void launch_signal(uint32_t* counter, cudaStream_t s);
 void launch_wait_counter(const uint32_t* counter, uint32_t expect, cudaStream_t s);
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s);

@@ -10,6 +10,22 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// RS_CHECKED=1 (make VARIANT=_chk TUNE=-DRS_CHECKED=1): the library's own memcheck.  Every indexed store / gather of the
+// wave state and every stack push goes through RS_IN_BOUNDS; a failed check is counted on the device, the access is
+// skipped, and the render call that follows returns RS_ERR_CUDA with the count (compute-sanitizer is not available on the
+// GPU pool this was developed on).  In the default build the macro is the constant `true`: no code.
+#ifndef RS_CHECKED
+#define RS_CHECKED 0
+#endif
+#if RS_CHECKED && defined(RS_DEFINE_VIOLATIONS)
+namespace rsd { __device__ unsigned long long rs_violations = 0ull; }
+#define RS_IN_BOUNDS(cond) ((cond) ? true : (atomicAdd(&rsd::rs_violations, 1ull), false))
+#elif RS_CHECKED
+#define RS_IN_BOUNDS(cond) (cond)  // (translation units without device entry points)
+#else
+#define RS_IN_BOUNDS(cond) true
+#endif
+
 namespace rsd {
 
 #define RS_PI 3.14159265358979323846
@@ -80,7 +96,26 @@ __device__ __forceinline__ V3 onb_local(const ONB& o, V3 a) {
 // ---------------------------------------------------------------------------------------------
 enum Purpose : uint32_t { P_PIXEL = 0, P_LENS = 1, P_SCATTER = 2, P_MIXED = 3, P_LIGHT = 4, P_BRDF = 5, P_MEDIUM = 6 };
 
-__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+// The ten round keys key + r * (0x9E3779B9, 0xBB67AE85) depend on the frame's seed alone, so the host computes them
+// (FrameParams::rk, make_frame) and a round reads its key straight from the kernel-parameter constant bank as an operand
+// of the XOR: two additions per round less than bumping the key in registers (3.6 % of the bounce-0 extend's
+// instructions went there; RS_TUNE_PHILOX_RK=0 builds that form for A/B).  Same integers either way.
+#ifndef RS_TUNE_PHILOX_RK
+#define RS_TUNE_PHILOX_RK 1
+#endif
+struct PhiloxKeys {
+    uint2 rk[10];
+};
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, const PhiloxKeys& K) {
+#if RS_TUNE_PHILOX_RK
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ K.rk[r].x, lo1, hi0 ^ c.w ^ K.rk[r].y, lo0);
+    }
+#else
+    uint2 k = K.rk[0];
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
         uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
@@ -89,17 +124,18 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
         k.x += 0x9E3779B9u;
         k.y += 0xBB67AE85u;
     }
+#endif
     return c;
 }
 
 __device__ __forceinline__ double u01(uint32_t w) { return (double)(w >> 8) * (1.0 / 16777216.0); }
 
 struct RngCtx {
-    uint2 key;
+    const PhiloxKeys* key;  // FrameParams::rk of the launch (kernel-parameter space)
     uint32_t pixel, sample, depth;
 };
 __device__ __forceinline__ uint4 rng_words(const RngCtx& r, uint32_t purpose, uint32_t call) {
-    return philox4x32_10(make_uint4(r.pixel, r.sample, r.depth, purpose | (call << 8)), r.key);
+    return philox4x32_10(make_uint4(r.pixel, r.sample, r.depth, purpose | (call << 8)), *r.key);
 }
 // rejection loops: iteration k reads word pair (k & 1) of call base + (k >> 1)
 __device__ __forceinline__ void rng_pair(const RngCtx& r, uint32_t purpose, uint32_t base, uint32_t k, double& a, double& b) {

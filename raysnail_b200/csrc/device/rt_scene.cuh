@@ -420,21 +420,43 @@ static __device__ __noinline__ bool hit_quadric(const rs_node& n, const Ray& ray
     return true;
 }
 
-// One triangle: 80 bytes read as five 128-bit ld.global.nc — p0.xyz, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2
-// (triangle_mesh.rs:51-56) and, in the spare word, the world object the triangle is (its root id).
-#define RS_TRI_STRIDE 5  // double2 per triangle
+// One triangle: p0.xyz, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56) and, in the word after them,
+// the world object the triangle is (its root id).  Default: 80-byte records read as five 128-bit ld.global.nc.
+// RS_TUNE_TRI256=1: 96-byte records, 32-byte aligned, read as three 256-bit loads (sm_100 LDG.E.256) — MEASURED
+// 0.9 % SLOWER on the 1 M-triangle mesh (profiles/r02b_ab_tri256.txt: 1267-1276 vs 1283-1284 M samples/s; the node
+// loads gain from 256-bit requests, the triangle records lose more to their 20 % larger footprint), kept as an option.
+#ifndef RS_TUNE_TRI256
+#define RS_TUNE_TRI256 0
+#endif
+#define RS_TRI_STRIDE (RS_TUNE_TRI256 ? 6 : 5)  // double2 per triangle
+#define RS_TRI_DOUBLES (2 * RS_TRI_STRIDE)
 struct TriGeom {
     double p0x, p0y, p0z, a, b, c, d, e, f;
     int root;
 };
 __device__ __forceinline__ TriGeom load_triangle(const double2* tri_geom, int tri) {
     const double2* g = tri_geom + (size_t)RS_TRI_STRIDE * (size_t)tri;
-    const double2 q0 = __ldg(g), q1 = __ldg(g + 1), q2 = __ldg(g + 2), q3 = __ldg(g + 3), q4 = __ldg(g + 4);
     TriGeom T;
+#if RS_TUNE_TRI256
+    uint32_t w[24];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        asm("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+            : "=r"(w[8 * k]), "=r"(w[8 * k + 1]), "=r"(w[8 * k + 2]), "=r"(w[8 * k + 3]), "=r"(w[8 * k + 4]), "=r"(w[8 * k + 5]), "=r"(w[8 * k + 6]), "=r"(w[8 * k + 7])
+            : "l"(g + 2 * k));
+#define RS_TRI_D(i) __hiloint2double((int)w[2 * (i) + 1], (int)w[2 * (i)])
+    T.p0x = RS_TRI_D(0); T.p0y = RS_TRI_D(1); T.p0z = RS_TRI_D(2);
+    T.a = RS_TRI_D(3); T.b = RS_TRI_D(4); T.c = RS_TRI_D(5);
+    T.d = RS_TRI_D(6); T.e = RS_TRI_D(7); T.f = RS_TRI_D(8);
+    T.root = (int)w[18];
+#undef RS_TRI_D
+#else
+    const double2 q0 = __ldg(g), q1 = __ldg(g + 1), q2 = __ldg(g + 2), q3 = __ldg(g + 3), q4 = __ldg(g + 4);
     T.p0x = q0.x; T.p0y = q0.y; T.p0z = q1.x;
     T.a = q1.y; T.b = q2.x; T.c = q2.y;
     T.d = q3.x; T.e = q3.y; T.f = q4.x;
     T.root = __double2loint(q4.y);
+#endif
     return T;
 }
 
@@ -843,7 +865,7 @@ static __device__ __noinline__ bool eval_object(const rs_node* nodes, const Xfor
             e.mat = n.material;
             e.src = pc;
             e.flavor = FLAVOR_LEAF;
-            stack[sp++] = e;
+            if (RS_IN_BOUNDS(sp < RS_EVAL_STACK)) stack[sp++] = e;  // (rs_upload_scene rejects programs that need more operands)
         } else if (op == OP_JMISS) {
             if (!stack[sp - 1].hit) pc += aux;
         } else if (op == OP_DIFF) {  // difference.rs:57-107
@@ -937,7 +959,7 @@ static __device__ __noinline__ bool eval_object(const rs_node* nodes, const Xfor
                     }
                 }
             }
-            stack[sp++] = res;
+            if (RS_IN_BOUNDS(sp < RS_EVAL_STACK)) stack[sp++] = res;
         }
     }
     out = stack[0];
