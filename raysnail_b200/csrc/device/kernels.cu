@@ -516,8 +516,25 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
 // together.
 // WIDE = false: binary tree of 64-byte nodes (the default: fewest instructions per ray on
 // these cache-resident scenes); WIDE = true: the 4-wide QBVH of 128-byte nodes.
+// `sstack` (binary tree only): the TOP RS_TUNE_SSTACK entries of the traversal stack live in shared memory, laid out
+// [entry][thread] so that a lane owns its banks (a warp's push or pop is conflict-free whatever depth each lane is at);
+// deeper entries spill to the local-memory array, which short walks never touch.  nullptr = the whole stack in local memory.
+// MEASURED SLOWER in this kernel (profiles/r02d_ab_sstack.txt, two runs each: headline 3.49 vs 3.67 G samples/s, quadric.sdl
+// 1.065 vs 1.133, csg.sdl 1.74 vs 1.83, Cornell 2.10 vs 2.16, example.sdl 4.42 vs 4.54, mesh equal): the walk is
+// issue-bound and the spill bookkeeping (`lo`, two compares per push / pop) costs more issue slots than the LDL / STL it
+// replaces cost L1 bandwidth — a warp's local-memory stack entries of one depth share a 128-byte line, so the lanes of a
+// coherent warp hit one line.  Off by default (RS_TUNE_SSTACK_MODES = 0); extend_stream_kernel, whose lanes sit at
+// unrelated depths, keeps its shared-memory stack (there it was 22 % of all L1 sector accesses).
+#ifndef RS_TUNE_SSTACK
+#define RS_TUNE_SSTACK 8  // entries per thread in shared memory (power of two; 0 = local memory only)
+#endif
+#ifndef RS_TUNE_SSTACK_MODES
+#define RS_TUNE_SSTACK_MODES 0  // bit m: extend_kernel<MODE = m> keeps its stack top in shared memory (0xf = all tiers)
+#endif
+#define RS_SSTACK_MODE(MODE) (((RS_TUNE_SSTACK_MODES) >> (MODE)) & 1)
 template <int MODE, bool WIDE, bool STAGE = false>
-__device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, Closest& best, const Staged st = Staged{0, 0}) {
+__device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, const RngCtx& rng, Closest& best, const Staged st = Staged{0, 0},
+                                            unsigned long long* const sstack = nullptr) {
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     best.t = inf;
     best.root = -1;
@@ -577,11 +594,34 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
     // most stacked entries are leaves, and a leaf costs an f64 object test
     unsigned long long stack[RS_STACK];
     int sp = 0;
-    stack[sp++] = (unsigned long long)(uint32_t)RS_BVH_SENTINEL;  // key 0: never dropped
     int node = S.bvh_root;  // may itself be a leaf (single object)
+    constexpr bool SST = !WIDE && RS_TUNE_SSTACK > 0;
+    const bool use_s = SST && sstack != nullptr;  // (uniform per kernel: folded after inlining)
+    int lo = 0;  // entries [lo, sp) are in shared memory (slot = index mod RS_TUNE_SSTACK), [0, lo) in local memory
+#define RS_SSLOT(k) sstack[((k) & ((RS_TUNE_SSTACK > 0 ? RS_TUNE_SSTACK : 1) - 1)) * RS_BLOCK]
+    if (use_s) RS_SSLOT(0) = (unsigned long long)(uint32_t)RS_BVH_SENTINEL;  // key 0: never dropped
+    else stack[0] = (unsigned long long)(uint32_t)RS_BVH_SENTINEL;
+    sp = 1;
+#define RS_PUSH2(e)                                                                        \
+    do {                                                                                   \
+        if (use_s) {                                                                       \
+            if (sp - lo == RS_TUNE_SSTACK) { stack[lo] = RS_SSLOT(lo); ++lo; }             \
+            RS_SSLOT(sp) = (e);                                                            \
+        } else {                                                                           \
+            stack[sp] = (e);                                                               \
+        }                                                                                  \
+        ++sp;                                                                              \
+    } while (false)
 #define RS_POP()                                                                   \
     do {                                                                           \
-        const unsigned long long e_ = stack[--sp];                                 \
+        unsigned long long e_;                                                     \
+        --sp;                                                                      \
+        if (use_s) {                                                               \
+            e_ = RS_SSLOT(sp);                                                     \
+            if (sp == lo && lo > 0) { --lo; RS_SSLOT(lo) = stack[lo]; }            \
+        } else {                                                                   \
+            e_ = stack[sp];                                                        \
+        }                                                                          \
         node = (int)(uint32_t)e_;                                                  \
         if (!(__uint_as_float((uint32_t)(e_ >> 32) & ~3u) > tmax_f)) break;        \
     } while (true)
@@ -626,7 +666,7 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
                 const bool swap = near1 < near0;
                 const int second = swap ? ch.x : ch.y;
                 const float second_near = swap ? near0 : near1;
-                if (sp < RS_STACK) stack[sp++] = ((unsigned long long)__float_as_uint(second_near) << 32) | (unsigned long long)(uint32_t)second;
+                if (sp < RS_STACK) RS_PUSH2(((unsigned long long)__float_as_uint(second_near) << 32) | (unsigned long long)(uint32_t)second);
                 else (void)RS_IN_BOUNDS(false);  // a dropped push would lose a subtree: upload bounds the depth so that it cannot happen
                 node = swap ? ch.y : ch.x;
             } else if (h0) {
@@ -689,6 +729,8 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
         RS_POP();
     }
 #undef RS_POP
+#undef RS_PUSH2
+#undef RS_SSLOT
 }
 
 template <int MODE>
@@ -734,6 +776,12 @@ __global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE 
     extend_kernel(const __grid_constant__ DScene S, const __grid_constant__ FrameParams fp, const __grid_constant__ WaveState ws, const int bounce,
                   const int miss_in_extend) {
     Staged st{0, 0};
+    // the hot end of every thread's traversal stack (see closest_hit)
+    unsigned long long* sstack = nullptr;
+    if constexpr (!WIDE && RS_TUNE_SSTACK > 0 && RS_SSTACK_MODE(MODE)) {
+        __shared__ unsigned long long s_stack[(RS_TUNE_SSTACK > 0 ? RS_TUNE_SSTACK : 1) * (STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK)];
+        sstack = s_stack + threadIdx.x;
+    }
     if constexpr (STAGE) {
         extern __shared__ __align__(128) unsigned char stage_smem[];
         __shared__ __align__(8) unsigned long long stage_bar;
@@ -813,7 +861,7 @@ __global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE 
             rng.depth = (uint32_t)bounce + 1;
             if constexpr (RS_TUNE_RESERVE && MODE < 2) rng_of_lane = rng;
             Closest best;
-            closest_hit<MODE, WIDE, STAGE>(S, ray, rng, best, st);
+            closest_hit<MODE, WIDE, STAGE>(S, ray, rng, best, st, sstack);
 #if RS_TUNE_COST_DUMP
             if (ws.dbg_cost) ws.dbg_cost[i] = make_int2(best.n_nodes, best.n_leaves);
 #endif
