@@ -407,3 +407,57 @@ def test_rs_multi_render_equals_the_one_device_image(renderer, devices):
         np.testing.assert_allclose(m.render(cam, p1), renderer.render(cam, p1), rtol=2e-6, atol=1e-7)
     finally:
         m.close()
+
+
+def test_reuploads_keep_or_rebuild_the_tree_correctly():
+    """rs_upload_scene keeps the SAH tree (and its device copy) while the objects' bounds and ids are unchanged.
+    One context sees: scene A, A again (tree kept), A with a sphere moved (same count: must rebuild), a scene with
+    other kinds at the same bounds (tree kept, leaf references must be re-encoded), a far-away camera (boxes
+    re-padded) and A once more — every image must equal the one a fresh context renders, bit for bit."""
+    from raysnail_b200 import Renderer
+
+    def spheres(shift, as_boxes=False):
+        s = Scene()
+        s.add(s.sphere((0, -1000, 0), 1000.0, s.lambertian(s.solid(0.5, 0.5, 0.5))))
+        light = s.sphere((0, 12, 0), 3.0, s.diffuse_light(s.solid(1, 1, 1), 5.0))
+        s.add(light)
+        s.add_light(light)
+        for k in range(40):
+            c = (-6.0 + 0.62 * (k % 20), 0.3 + 0.7 * (k // 20), -2.0 + 0.21 * k + (shift if k == 17 else 0.0))
+            m = s.lambertian(s.solid(0.2 + 0.02 * k, 0.9 - 0.02 * k, 0.4))
+            # a box with the bounds of the sphere: same tree members, another leaf kind
+            s.add(s.box((c[0] - 0.3, c[1] - 0.3, c[2] - 0.3), (c[0] + 0.3, c[1] + 0.3, c[2] + 0.3), m) if as_boxes else s.sphere(c, 0.3, m))
+        s.set_camera((0, 3, 12), (0, 0.5, 0), fov=40.0)
+        return s
+
+    params = make_params(samples=16)
+
+    def fresh(scene, cam):
+        r = Renderer(0)
+        try:
+            r.upload(scene)
+            return r.render(cam, params)
+        finally:
+            r.close()
+
+    a, moved, boxes = spheres(0.0), spheres(0.37), spheres(0.0, as_boxes=True)
+    r = Renderer(0)
+    try:
+        for label, scene in (("A", a), ("A again", a), ("moved", moved), ("A back", a), ("boxes at the same bounds", boxes), ("A after boxes", a)):
+            cam = scene.camera(96, 64)
+            r.upload(scene)
+            assert np.array_equal(r.render(cam, params), fresh(scene, cam)), label
+        # a camera far outside the scene extent: the f32 boxes are re-padded for its origin, then A is uploaded again
+        far = CameraBuilder().look_from((0.0, 900.0, 4000.0)).look_at((0.0, 0.5, 0.0)).fov(0.5).width(96).height(64).build()
+        img_far = r.render(far, params)
+        r.upload(a)
+        assert np.array_equal(r.render(far, params), img_far)
+        rf = Renderer(0)
+        try:
+            rf.upload(a)
+            assert np.array_equal(rf.render(far, params), img_far)
+        finally:
+            rf.close()
+        assert np.array_equal(r.render(a.camera(96, 64), params), fresh(a, a.camera(96, 64)))
+    finally:
+        r.close()
