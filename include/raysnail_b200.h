@@ -244,7 +244,7 @@ const char* rs_last_error(const rs_ctx* ctx);
  * n-1 internal ones, so the tail of each persistent kernel overlaps with another wave's work (the image
  * is bit-identical: accumulation stays in wave order); 1 = every kernel on the caller's stream. */
 #define RS_OPT_WAVE_STREAMS 2
-/* RS_OPT_LIST_MAX: n in 0..64 (default 12) = worlds of at most n objects that hold boxes, rects or expression
+/* RS_OPT_LIST_MAX: n in 0..64 (default 12, 24 for worlds that hold expression trees) = worlds of at most n objects that hold boxes, rects or expression
  * trees are searched by walking the object list (every lane of a warp tests the same object at the same time)
  * instead of the tree; 0 = always the tree.  Identical hits either way.  Set before rs_upload_scene. */
 #define RS_OPT_LIST_MAX 3

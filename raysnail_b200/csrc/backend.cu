@@ -100,10 +100,12 @@ struct rs_ctx {
     struct ListEntry { double box[6]; int root; bool noclip; };
     std::vector<ListEntry> list_host;  // the world objects with a proper bbox, ascending ids
     bool use_list = false;             // small worlds: the kernels walk the object list instead of the tree (RS_OPT_LIST_MAX)
-    int list_max = 12;
+    bool list_trees_uniform = false;   // the expression trees on the list all have the same program shape (closest_hit's skip-ahead walk)
+    int list_max = 12;       // RS_OPT_LIST_MAX; -1 = not set: 12, or 24 for worlds that hold expression trees
+    bool list_max_set = false;
     int bvh_root = 0;
     int bvh_width = 2;       // RS_OPT_BVH_WIDTH: 2 = binary 64-byte nodes (default), 4 = QBVH 128-byte nodes
-    int extend_mode = 3;     // 0 static spheres only, 1 + triangles, 2 + flat roots (rect / box), 3 everything
+    int extend_mode = 3;     // 0 static spheres only, 1 + triangles, 2 + flat roots (rect / box), 3 everything, 4 = 3 with the skip-ahead list walk
     int shade_generic = 2;  // shade tier: 0 = lean, 1 = + flat roots (no expression trees), 2 = everything
     bool uses_time = false;  // some sphere moves: rays carry their shutter time
     double scene_omax = 0.0, padded_omax = -1.0;
@@ -419,6 +421,15 @@ int upload_bvh(rs_ctx* ctx, double omax) {
         if (rcl != RS_OK) return rcl;
         ctx->scene.root_list = ctx->d_root_list.as<float4>();
         ctx->scene.n_list = (int)(list.size() / 2);
+        // (the list is sorted: objects tested regardless of distance, spheres, flat objects, expression trees)
+        int lock = 0;
+        for (const auto& e : ctx->list_host) lock += ctx->root_kind_host[e.root] != ROOT_GENERIC ? 1 : 0;
+        bool sorted = true;
+        for (size_t i = 0; i < ctx->list_host.size(); ++i) sorted = sorted && ((ctx->root_kind_host[ctx->list_host[i].root] != ROOT_GENERIC) == ((int)i < lock));
+        // lanes may evaluate DIFFERENT trees side by side only when the trees run the same instruction sequence
+        // (measured: sdl/quadric.sdl +14 %; with trees of different shapes the lanes diverge inside the evaluator
+        // and lockstep is faster: sdl/csg.sdl -15 %, sdl/transforms.sdl -13 %, profiles/r02e_ab_listskip.txt)
+        ctx->scene.n_list_lockstep = (sorted && ctx->list_trees_uniform) ? lock : ctx->scene.n_list;
     }
     if (ctx->tree_dev_valid && ctx->tree_dev_omax >= omax) {
         // same tree, same leaf references, boxes already padded for origins at least this far out (a wider pad is
@@ -966,6 +977,7 @@ int rs_set_option(rs_ctx* ctx, int option, int value) {
     if (option == RS_OPT_LIST_MAX && value >= 0 && value <= 64) {
         if (ctx->list_max != value) ctx->has_scene = false;
         ctx->list_max = value;
+        ctx->list_max_set = true;
         return RS_OK;
     }
     if (option == RS_OPT_WAVE_STREAMS && value >= 1 && value <= rs_ctx::kMaxSets) {
@@ -1156,10 +1168,16 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     }
     stage("root tables");
     // small worlds are searched as one list (RS_OPT_LIST_MAX); otherwise only the loose objects are
-    if (const char* e = std::getenv("RAYSNAIL_B200_LIST_MAX")) ctx->list_max = std::atoi(e);
-    bool flat_or_tree = !loose.empty();
-    for (const BuildPrim& p : prims) flat_or_tree |= root_kind[p.root] == ROOT_FLAT || root_kind[p.root] == ROOT_GENERIC;
-    ctx->use_list = flat_or_tree && ctx->bvh_width == 2 && (int)(prims.size() + loose.size()) <= ctx->list_max;
+    if (const char* e = std::getenv("RAYSNAIL_B200_LIST_MAX")) { ctx->list_max = std::atoi(e); ctx->list_max_set = true; }
+    bool flat_or_tree = !loose.empty(), any_generic = false;
+    for (const BuildPrim& p : prims) {
+        flat_or_tree |= root_kind[p.root] == ROOT_FLAT || root_kind[p.root] == ROOT_GENERIC;
+        any_generic |= root_kind[p.root] == ROOT_GENERIC;
+    }
+    // default: 12 objects; 24 when the world holds expression trees (a leaf that every lane reaches at another time costs
+    // a tree evaluation per lane; sdl/declares.sdl, 17 objects: 423 -> 471 M samples/s as a list, profiles/r02e_ab_listskip2.txt)
+    const int list_limit = ctx->list_max_set ? ctx->list_max : (any_generic ? 24 : 12);
+    ctx->use_list = flat_or_tree && ctx->bvh_width == 2 && (int)(prims.size() + loose.size()) <= list_limit;
     ctx->list_host.clear();
     auto list_add = [&](const BuildPrim& p, bool noclip) {
         rs_ctx::ListEntry e;
@@ -1224,6 +1242,39 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     stage(ctx->bvh_reused ? "tree (kept)" : "tree (built)");
     // (binary tree: depth <= 24 SAH levels + log2(n) median levels, one push per level: fits)
     ctx->scene_omax = omax;
+    // object programs of the expression-tree roots
+    ProgramBuilder pb{nodes, xf};
+    std::vector<int2> root_prog(std::max(s->n_roots, 1), make_int2(0, 0));
+    for (int i = 0; i < s->n_roots; ++i) {
+        if (root_kind[i] != ROOT_GENERIC) continue;
+        const int first = (int)pb.prog.size();
+        const int depth = pb.emit(s->roots[i], -1, false);
+        if (depth > RS_EVAL_STACK) return fail(ctx, RS_ERR_UNSUPPORTED, "object tree needs more than RS_EVAL_STACK operands");
+        root_prog[i] = make_int2(first, (int)pb.prog.size() - first);
+    }
+    if (pb.nested_medium) return fail(ctx, RS_ERR_UNSUPPORTED, "a ConstantMedium inside the boundary of another ConstantMedium is not supported");
+    {
+        // do the expression trees on the object list share one program shape (same operations, same primitive kinds,
+        // same skip distances)?  Then closest_hit lets every lane walk to its own next tree (upload_bvh).
+        int first_root = -1, n_trees = 0;
+        bool uniform = true;
+        for (const auto& e : ctx->list_host) {
+            if (root_kind[e.root] != ROOT_GENERIC) continue;
+            ++n_trees;
+            if (first_root < 0) { first_root = e.root; continue; }
+            const int2 a = root_prog[first_root], b = root_prog[e.root];
+            if (a.y != b.y) { uniform = false; break; }
+            for (int k = 0; k < a.y && uniform; ++k) {
+                const ObjInstr &ia = pb.prog[a.x + k], &ib = pb.prog[b.x + k];
+                uniform = ia.op == ib.op && (ia.xf >= 0) == (ib.xf >= 0);
+                if (uniform && ia.op == OP_LEAF) uniform = nodes[ia.node].type == nodes[ib.node].type;
+                if (uniform && (ia.op == OP_JMISS || ia.op == OP_MED_MID)) uniform = ia.aux == ib.aux;
+            }
+            if (!uniform) break;
+        }
+        ctx->list_trees_uniform = uniform && n_trees >= 2;
+        if (const char* e = std::getenv("RAYSNAIL_B200_LIST_SKIP")) ctx->list_trees_uniform = std::atoi(e) != 0;
+    }
     // which kernel specialisations this scene needs
     bool any_tri = false, any_flat = false, any_tree = RS_TUNE_QUADRIC_FLAT ? false : any_quadric_root;
     auto needs = [&](int root) {
@@ -1234,6 +1285,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     for (const BuildPrim& p : prims) needs(p.root);
     for (const auto& e : ctx->list_host) needs(e.root);
     ctx->extend_mode = any_tree ? 3 : (any_flat ? 2 : (any_tri ? 1 : 0));
+    // 4 = 3 + the skip-ahead walk over uniformly shaped trees on the object list (its own kernel: compiled into the
+    // generic one the extra code costs the other scenes 4-8 % in spills, profiles/r02e_ab_listskip2.txt)
+    if (ctx->extend_mode == 3 && ctx->list_trees_uniform && ctx->bvh_width == 2) ctx->extend_mode = 4;
     ctx->uses_time = false;
     for (const rs_node& n : nodes)
         if (n.type == RS_NODE_SPHERE && (n.p[4] != 0.0 || n.p[5] != 0.0 || n.p[6] != 0.0)) ctx->uses_time = true;
@@ -1274,17 +1328,6 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid = std::min(ctx->shade_grid, ctx->sm_count * v); }
     if (const char* e = std::getenv("RAYSNAIL_B200_SHADE_LAMBERT_BLOCKS_PER_SM")) { int v = std::atoi(e); if (v > 0) ctx->shade_grid_lambert = std::min(ctx->shade_grid_lambert, ctx->sm_count * v); }
 
-    // object programs of the expression-tree roots
-    ProgramBuilder pb{nodes, xf};
-    std::vector<int2> root_prog(std::max(s->n_roots, 1), make_int2(0, 0));
-    for (int i = 0; i < s->n_roots; ++i) {
-        if (root_kind[i] != ROOT_GENERIC) continue;
-        const int first = (int)pb.prog.size();
-        const int depth = pb.emit(s->roots[i], -1, false);
-        if (depth > RS_EVAL_STACK) return fail(ctx, RS_ERR_UNSUPPORTED, "object tree needs more than RS_EVAL_STACK operands");
-        root_prog[i] = make_int2(first, (int)pb.prog.size() - first);
-    }
-    if (pb.nested_medium) return fail(ctx, RS_ERR_UNSUPPORTED, "a ConstantMedium inside the boundary of another ConstantMedium is not supported");
 
     // triangles: p0, (a,b,c) = p0 - p1, (d,e,f) = p0 - p2 (triangle_mesh.rs:51-56)
     // RS_TRI_DOUBLES per record (load_triangle); word 9 names the world object the triangle is

@@ -509,7 +509,7 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
 #ifndef RS_TUNE_EXTEND_TRI
 #define RS_TUNE_EXTEND_TRI RS_TUNE_EXTEND_LEAN
 #endif
-#define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) == 3 ? RS_TUNE_EXTEND_GENERIC : ((MODE) == 2 ? RS_TUNE_EXTEND_FLAT : ((MODE) == 1 ? RS_TUNE_EXTEND_TRI : RS_TUNE_EXTEND_LEAN)))
+#define RS_EXTEND_MIN_BLOCKS(MODE) ((MODE) >= 3 ? RS_TUNE_EXTEND_GENERIC : ((MODE) == 2 ? RS_TUNE_EXTEND_FLAT : ((MODE) == 1 ? RS_TUNE_EXTEND_TRI : RS_TUNE_EXTEND_LEAN)))
 
 // while-while traversal: every lane first walks inner nodes until it holds a leaf (or is done),
 // the warp reconverges, then the lanes holding leaves run the (expensive, f64) object test
@@ -525,6 +525,9 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
 // replaces cost L1 bandwidth — a warp's local-memory stack entries of one depth share a 128-byte line, so the lanes of a
 // coherent warp hit one line.  Off by default (RS_TUNE_SSTACK_MODES = 0); extend_stream_kernel, whose lanes sit at
 // unrelated depths, keeps its shared-memory stack (there it was 22 % of all L1 sector accesses).
+#ifndef RS_TUNE_LIST_SKIP
+#define RS_TUNE_LIST_SKIP 1  // object list: lanes skip ahead to their own next expression tree (0 = all lanes walk in lockstep)
+#endif
 #ifndef RS_TUNE_SSTACK
 #define RS_TUNE_SSTACK 8  // entries per thread in shared memory (power of two; 0 = local memory only)
 #endif
@@ -571,7 +574,8 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
     //    sphere, box, expression tree — serialise: 12 of 32 lanes per instruction on bounce 1 of quadric.sdl).
     // Same conservative f32 slab test as a tree node; the tie rule (lower id wins) is order-independent.
     if constexpr (MODE >= 2) {
-        for (int k = 0; k < S.n_list; ++k) {
+        const int n_lock = MODE == 4 ? S.n_list_lockstep : S.n_list;
+        for (int k = 0; k < n_lock; ++k) {
             const float4 lo = __ldg(S.root_list + 2 * k), hi = __ldg(S.root_list + 2 * k + 1);
             const float x0 = fmaf(lo.x, idx, -oodx), x1 = fmaf(hi.x, idx, -oodx);
             const float y0 = fmaf(lo.y, idy, -oody), y1 = fmaf(hi.y, idy, -oody);
@@ -583,6 +587,37 @@ __device__ __forceinline__ void closest_hit(const DScene& S, const Ray& ray, con
                 ++best.n_leaves;
 #endif
                 test_root<MODE>(S, __float_as_int(lo.w), ray, inv_d, rng, best);
+                tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
+            }
+        }
+        // The expression trees at the end of the list all run ONE piece of code (eval_object), so here every lane
+        // skips ahead to ITS next tree whose box it enters and the warp evaluates 32 different trees together: the
+        // rounds a warp needs are the most trees any one of its rays enters, not the trees its rays enter between them
+        // (bounce >= 1 of sdl/quadric.sdl: four TfFacade(Intersection(quadric, box)), a ray enters one or two).
+        if constexpr (MODE == 4) {
+            int k = n_lock;
+            while (true) {
+                int ref = 0;
+                bool found = false;
+                while (k < S.n_list) {
+                    const float4 lo = __ldg(S.root_list + 2 * k), hi = __ldg(S.root_list + 2 * k + 1);
+                    ++k;
+                    const float x0 = fmaf(lo.x, idx, -oodx), x1 = fmaf(hi.x, idx, -oodx);
+                    const float y0 = fmaf(lo.y, idy, -oody), y1 = fmaf(hi.y, idy, -oody);
+                    const float z0 = fmaf(lo.z, idz, -oodz), z1 = fmaf(hi.z, idz, -oodz);
+                    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin_f));
+                    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), hi.w != 0.f ? FLT_MAX : tmax_f));
+                    if (tn <= tf * slack) {
+                        ref = __float_as_int(lo.w);
+                        found = true;
+                        break;
+                    }
+                }
+                if (!found) break;
+#if RS_TUNE_COST_DUMP
+                ++best.n_leaves;
+#endif
+                test_root<MODE>(S, ref, ray, inv_d, rng, best);
                 tmax_f = best.t < (double)FLT_MAX ? up(__double2float_ru(best.t)) : FLT_MAX;
             }
         }
@@ -910,13 +945,19 @@ __global__ void __launch_bounds__(STAGE ? RS_TUNE_STAGE_BLOCK : RS_BLOCK, STAGE 
                 if (RS_IN_BOUNDS(i < ws.capacity)) ws.hit[i] = h;
             }
             if constexpr (FIRST) {
+                if (RS_CHECKED && (fp.flags & 0x80000000u) && i < 32u) {  // (checked builds: the negative control, see render_into)
+                    PathRec q;
+                    q.ray = ray;
+                    q.T = make_float3(1.f, 1.f, 1.f);
+                    q.slot = i;
+                    store_path(ws, in, ws.capacity + i, q);
+                }
                 if (cls >= 0) {  // the path goes on to shade: now it needs its record (and a zeroed contribution)
                     PathRec p;
                     p.ray = ray;
                     p.T = make_float3(1.f, 1.f, 1.f);
                     p.slot = i;
                     store_path(ws, in, i, p);
-                    if (RS_CHECKED && (fp.flags & 0x80000000u) && i < 32u) store_path(ws, in, ws.capacity + i, p);  // (checked builds: the negative control)
                     if (RS_IN_BOUNDS(i < ws.capacity)) ws.contrib[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             }
@@ -2041,14 +2082,14 @@ static const void* extend_first_fn_for(int mode, int stage) {
     if (stage) return mode == 0 ? (const void*)extend_kernel<0, false, true, true> : (const void*)extend_kernel<1, false, true, true>;
 #endif
     return mode == 0 ? (const void*)extend_kernel<0, false, true> : (mode == 1 ? (const void*)extend_kernel<1, false, true>
-                     : (mode == 2 ? (const void*)extend_kernel<2, false, true> : (const void*)extend_kernel<3, false, true>));
+                     : (mode == 2 ? (const void*)extend_kernel<2, false, true> : (mode == 3 ? (const void*)extend_kernel<3, false, true> : (const void*)extend_kernel<4, false, true>)));
 }
 static const void* extend_fn_for(int mode, int wide, int stage) {
 #if RS_TUNE_STAGE_TREE
     if (stage) return mode == 0 ? (const void*)extend_kernel<0, false, false, true> : (const void*)extend_kernel<1, false, false, true>;
 #endif
     if (wide) return mode == 0 ? extend_fn<0, true>() : (mode == 1 ? extend_fn<1, true>() : (mode == 2 ? extend_fn<2, true>() : extend_fn<3, true>()));
-    return mode == 0 ? extend_fn<0, false>() : (mode == 1 ? extend_fn<1, false>() : (mode == 2 ? extend_fn<2, false>() : extend_fn<3, false>()));
+    return mode == 0 ? extend_fn<0, false>() : (mode == 1 ? extend_fn<1, false>() : (mode == 2 ? extend_fn<2, false>() : (mode == 3 ? extend_fn<3, false>() : extend_fn<4, false>())));
 }
 // stage_bytes > 0: the staged kernels (lean modes, binary tree), with that much dynamic shared memory
 void launch_extend_first(const DScene& S, const FrameParams& fp, const WaveState& ws, int mode, int grid, int stage_bytes, cudaStream_t s) {

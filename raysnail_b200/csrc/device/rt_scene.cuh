@@ -96,6 +96,7 @@ struct DScene {
     const float4* root_list;     // objects searched as a list before the tree: (lo.xyz, bits of the leaf ref), (hi.xyz, 1 = never dropped by distance)
     int any_gate;                // some root is gated by its reference bbox (aabb_hit_f64 needs 1 / direction)
     int n_list;                  // unbounded objects; in small worlds every object (then bvh_root is the sentinel: no tree)
+    int n_list_lockstep;         // entries [0, n_list_lockstep) are spheres / flat objects, the expression trees follow (closest_hit)
     const int* root_node;        // node index or ~triangle
     const int* root_kind;        // RootKind
     const double4* root_sphere;  // ROOT_SPHERE: (cx, cy, cz, r)
