@@ -245,11 +245,52 @@ __device__ __forceinline__ void rect_axes(int kind, int& a, int& b, int& c) {
     else { a = 1; b = 2; c = 0; }
 }
 
-// rect.rs:102-120, the distance only (what the closest-hit search of extend needs)
+// ~20-bit reciprocal (MUFU.RCP64H): one instruction where an IEEE division is ~35; for conservative pre-tests only
+__device__ __forceinline__ double rcp_rough(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    return r;
+}
+#ifndef RS_TUNE_RECT_QUICK
+#define RS_TUNE_RECT_QUICK 0  // MEASURED 15-20 % SLOWER on every scene with boxes (profiles/r02f_ab_rectquick.txt), see rect_t
+#endif
+
+// rect.rs:102-120, the distance only (what the closest-hit search of extend needs).
+// A box is six of these and a ray hits two of them at most, so most calls end in `return false` — and the reference's
+// first step is an f64 division.  The rejects that can be decided WITHOUT it come first (RS_TUNE_RECT_QUICK):
+//  - numerator and denominator of opposite sign: the quotient is negative (or -0), below any lower limit > 0 — exact;
+//  - the plane distance taken with a 20-bit reciprocal lies outside [lo, hi), or puts the hit point outside the
+//    rectangle, by more than 2^-16 relative — 16 times the error of the estimate, so the exact test would refuse as well.
+// Every condition is written so that a NaN or an infinity falls through; whatever is not refused runs the reference's
+// own sequence (divide, then compare) unchanged, and an accepted hit is therefore the reference's bit for bit.
+// Parity-green (75 GPU tests) but SLOWER, in extend and in shade alike: quadric.sdl 1.08 vs 1.30 G samples/s, csg.sdl
+// 1.49 vs 1.83, Cornell 1.83 vs 2.16, example.sdl 4.08 vs 4.53 — the ~14 extra f64 operations and compares per face and
+// the registers they hold (spill stores 456 -> 604 B in the generic extend) cost more than the division they avoid on
+// four faces of six.  Off by default; the division stays.
 __device__ __forceinline__ bool rect_t(int kind, double k, double a0, double a1, double b0, double b1, const Ray& ray, double lo, double hi, double& t1) {
     int ax0, ax1, ax2;
     rect_axes(kind, ax0, ax1, ax2);
     double dk = comp(ray.d, ax2);
+#if RS_TUNE_RECT_QUICK
+    {
+        const double n = k - comp(ray.o, ax2);
+        const double big = 1e300, eps = 1.52587890625e-05;  // 2^-16
+        if (lo > 0.0 && fabs(n) < big && fabs(dk) < big && ((n < 0.0 && dk > 0.0) || (n > 0.0 && dk < 0.0))) return false;
+        if (fabs(dk) > 1e-300 && fabs(dk) < big && fabs(n) < big) {
+            const double te = n * rcp_rough(dk);  // |te - n / dk| <= 2^-20 |te|
+            if (fabs(te) < big) {
+                const double slack = fabs(te) * eps;
+                if (te + slack < lo || te - slack >= hi) return false;
+                const double pa = te * comp(ray.d, ax0), pb = te * comp(ray.d, ax1);
+                const double ea = pa + comp(ray.o, ax0), eb = pb + comp(ray.o, ax1);
+                // (2^-40 of the origin covers the one-ulp difference between this sum and the reference's fused one)
+                const double tiny = 9.094947017729282e-13;  // 2^-40
+                const double sa = fma(fabs(pa), eps, fabs(comp(ray.o, ax0)) * tiny), sb = fma(fabs(pb), eps, fabs(comp(ray.o, ax1)) * tiny);
+                if (ea + sa < a0 || ea - sa > a1 || eb + sb < b0 || eb - sb > b1) return false;
+            }
+        }
+    }
+#endif
     t1 = (k - comp(ray.o, ax2)) / dk;
     if (!in_range(t1, lo, hi)) return false;
     double a = fma(t1, comp(ray.d, ax0), comp(ray.o, ax0));
