@@ -55,8 +55,13 @@ typedef enum rs_node_type {
     RS_NODE_TRANSFORM = 6,    /* src/hittable/transform/tf_facade.rs child0; xforms[first..first+n) */
     RS_NODE_MEDIUM = 7,       /* src/hittable/medium/constant.rs   child0 = boundary; p[0]=density;
                                  material = the Isotropic material                                  */
-    RS_NODE_RAYMARCHER = 8    /* src/hittable/geometry/raymarching.rs  the power-8 Mandelbulb about the
+    RS_NODE_RAYMARCHER = 8,   /* src/hittable/geometry/raymarching.rs  the power-8 Mandelbulb about the
                                  origin; p[0] = iterations (RayMarcher::new: 100)                  */
+    RS_NODE_BVH = 9           /* src/hittable/collection/bvh.rs:173-192 — a `BVH` used as ONE object (a world
+                                 member, under a TfFacade, as a medium boundary): child0 = left, child1 = right
+                                 (-1 = None), p[0..5] = the node's bbox (min xyz, max xyz), p[6] = 1 when the
+                                 bbox is Some.  Its `contains` is `unimplemented!()` in the reference, so a BVH
+                                 is refused as a CSG operand (RS_ERR_UNSUPPORTED)                     */
 } rs_node_type;
 
 /* rect_axis: which AARect constructor built it (src/hittable/geometry/rect.rs:56-78) */

@@ -70,6 +70,8 @@ int rs_host_obj_quadric(rs_host_scene* s, const double q[10], int mat);
 int rs_host_obj_raymarcher(rs_host_scene* s, int mat); /* RayMarcher::new (raymarching.rs:35-40) */
 int rs_host_obj_difference(rs_host_scene* s, int plus, int minus, int mat);
 int rs_host_obj_intersection(rs_host_scene* s, int o1, int o2, int mat);
+/* `BVH::new(list, time_range)` used as ONE object (bvh.rs:47-112, 173-192); the scene's time range as set so far */
+int rs_host_obj_bvh(rs_host_scene* s, int32_t n, const int32_t* objs);
 /* ops[i]: 0 translate(v) 1 rotate_x(v[0] rad) 2 rotate_y 3 rotate_z 4 scale(v); args = n*3 doubles */
 int rs_host_obj_transform(rs_host_scene* s, int child, int32_t n_ops, const int32_t* ops, const double* args);
 int rs_host_obj_medium(rs_host_scene* s, int boundary, float r, float g, float b, double density);

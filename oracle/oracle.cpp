@@ -1078,6 +1078,29 @@ struct IntersectionObj : Hittable {  // csg/intersection.rs
     const Material* material(bool& ok) const override { ok = false; return nullptr; }
 };
 
+struct BvhObj : Hittable {  // collection/bvh.rs:173-208 — a BVH used as one object
+    bool has_box = false;
+    AABB box;
+    const Hittable *left = nullptr, *right = nullptr;
+    bool hit(const Ray& ray, const Range& limit, const Rng& rng, HitRecord& out) const override {  // :174-190
+        if (!has_box || !box.hit(ray, limit)) return false;
+        HitRecord hl, hr;
+        // The reference searches the right child over start..left.t1 and prefers its hit (:181-189).  Canonical form, as
+        // for the objects of the world (header): both children over the node's own limit, the right one wins when strictly
+        // closer — the same winner, and what a Box member reports (which faces count, box.rs:125-150) does not depend on
+        // its sibling.
+        const bool a = left && left->hit(ray, limit, rng, hl);
+        const bool b = right && right->hit(ray, limit, rng, hr);
+        if (b && (!a || hr.t1 < hl.t1)) out = hr;
+        else if (a) out = hl;
+        return a || b;
+    }
+    bool contains(const Vec3&) const override { return false; }  // :194-200 unimplemented!(): refused at upload as a CSG operand
+    AABB bbox(const Range&) const override { return box; }
+    Vec3 random(const Vec3&, const Rng&) const override { return Vec3(1.0, 0.0, 0.0); }  // :206-208
+    const Material* material(bool& ok) const override { ok = false; return nullptr; }
+};
+
 struct TransformObj : Hittable {  // transform/tf_facade.rs + transform.rs:133-157
     const Hittable* object;
     std::vector<rs_xform> stack;
@@ -1334,6 +1357,15 @@ bool Scene::build(const rs_scene_desc& d, bool use_desc_bbox) {
                 p->density = n.p[0]; p->neg_inv_density = -1.0 / n.p[0]; out = std::move(p); break;
             }
             case RS_NODE_RAYMARCHER: { auto p = std::make_unique<RayMarcherObj>(); p->iterations = (int)n.p[0]; out = std::move(p); break; }
+            case RS_NODE_BVH: {
+                auto p = std::make_unique<BvhObj>();
+                p->has_box = n.p[6] != 0.0;
+                p->box = {Vec3(n.p[0], n.p[1], n.p[2]), Vec3(n.p[3], n.p[4], n.p[5])};
+                if (n.child0 >= i || n.child1 >= i) return false;
+                p->left = n.child0 >= 0 ? child(n.child0) : nullptr;
+                p->right = n.child1 >= 0 ? child(n.child1) : nullptr;
+                out = std::move(p); break;
+            }
             default: return false;
         }
         out->mat = mat(n.material);

@@ -38,7 +38,7 @@ HOST_SYMBOLS = [
     "rs_host_mat_metal", "rs_host_mat_diffuse_metal", "rs_host_mat_dielectric",
     "rs_host_mat_diffuse_light", "rs_host_mat_isotropic", "rs_host_mat_blinn_phong",
     "rs_host_mat_mixed", "rs_host_mat_set_phong", "rs_host_obj_sphere", "rs_host_obj_box",
-    "rs_host_obj_rect", "rs_host_obj_quadric", "rs_host_obj_raymarcher", "rs_host_obj_difference", "rs_host_obj_intersection",
+    "rs_host_obj_rect", "rs_host_obj_quadric", "rs_host_obj_raymarcher", "rs_host_obj_difference", "rs_host_obj_intersection", "rs_host_obj_bvh",
     "rs_host_obj_transform", "rs_host_obj_medium", "rs_host_world_add", "rs_host_world_add_light",
     "rs_host_world_add_mesh", "rs_host_world_add_obj_file", "rs_host_world_set_background",
     "rs_host_world_set_time_range", "rs_host_scene_set_camera", "rs_host_seed_random_u32",
@@ -189,6 +189,7 @@ def load() -> C.CDLL:
     proto("rs_host_obj_raymarcher", C.c_int, vp, C.c_int)
     proto("rs_host_obj_difference", C.c_int, vp, C.c_int, C.c_int, C.c_int)
     proto("rs_host_obj_intersection", C.c_int, vp, C.c_int, C.c_int, C.c_int)
+    proto("rs_host_obj_bvh", C.c_int, vp, C.c_int32, C.POINTER(C.c_int32))
     proto("rs_host_obj_transform", C.c_int, vp, C.c_int, i32, P(i32), P(f64))
     proto("rs_host_obj_medium", C.c_int, vp, C.c_int, f32, f32, f32, f64)
     proto("rs_host_world_add", C.c_int, vp, C.c_int)

@@ -146,6 +146,11 @@ class Scene:
     def intersection(self, o1, o2, mat=-1):
         return self._ck(self._lib.rs_host_obj_intersection(self._h, o1, o2, mat), "obj_intersection")
 
+    def bvh(self, members):
+        """`BVH::new(list)` used as ONE object (bvh.rs:173-192): a world member, under a transform, a medium boundary."""
+        n = len(members)
+        return self._ck(self._lib.rs_host_obj_bvh(self._h, n, (C.c_int32 * max(n, 1))(*[int(m) for m in members])), "obj_bvh")
+
     def transform(self, child, ops):
         """ops: list of ("translate", v3) | ("rotate_x", rad) | ("rotate_y", rad) | ("rotate_z", rad) | ("scale", v3)"""
         codes = {"translate": 0, "rotate_x": 1, "rotate_y": 2, "rotate_z": 3, "scale": 4}

@@ -239,6 +239,18 @@ bool geom_bound(const std::vector<rs_node>& nodes, const std::vector<XformPre>& 
         }
         return true;
     }
+    case RS_NODE_BVH: {  // every hit is a hit of a member
+        bool any = false;
+        for (int c : {n.child0, n.child1}) {
+            if (c < 0) continue;
+            double l1[3], h1[3];
+            if (!geom_bound(nodes, xf, c, l1, h1)) return false;
+            for (int a = 0; a < 3; ++a) { lo[a] = any ? std::min(lo[a], l1[a]) : l1[a]; hi[a] = any ? std::max(hi[a], h1[a]) : h1[a]; }
+            any = true;
+        }
+        if (!any) for (int a = 0; a < 3; ++a) { lo[a] = 0.0; hi[a] = 0.0; }
+        return true;
+    }
     case RS_NODE_RAYMARCHER:
         // a reported point is within one search step (0.05) of a point that has not escaped |v|^2 <= 8
         // after >= 1 iteration, the first of which is the point itself (raymarching.rs:59-76, 202-241)
@@ -554,6 +566,7 @@ int tree_depth(const rs_scene_desc* s, int ni) {
         case RS_NODE_INTERSECTION: return 1 + std::max(tree_depth(s, n.child0), tree_depth(s, n.child1));
         case RS_NODE_TRANSFORM:
         case RS_NODE_MEDIUM: return 1 + tree_depth(s, n.child0);
+        case RS_NODE_BVH: return 1 + std::max(n.child0 >= 0 ? tree_depth(s, n.child0) : 0, n.child1 >= 0 ? tree_depth(s, n.child1) : 0);
         default: return 1;
     }
 }
@@ -579,6 +592,7 @@ struct ProgramBuilder {
     std::vector<CsgInfo> csg;
     int max_stack = 0;
     bool nested_medium = false;
+    bool bvh_in_csg = false;  // BVH::contains is unimplemented!() in the reference (bvh.rs:194-200)
 
     // (parent chain `outer`, TfFacade `inner` below it): inv = inner.inv o outer.inv, fwd = outer.fwd o inner.fwd
     int compose(int outer, int inner) {
@@ -609,6 +623,7 @@ struct ProgramBuilder {
             cprog.push_back(make_int2((int)(((uint32_t)(n.type == RS_NODE_INTERSECTION ? RS_C_AND : RS_C_ANDNOT)) << 28), -1));
             return;
         }
+        if (n.type == RS_NODE_BVH) bvh_in_csg = true;
         if (primitive(n.type) && n.type != RS_NODE_RECT) cprog.push_back(make_int2(ni | (RS_C_LEAF << 28), cur));
         else cprog.push_back(make_int2((int)((uint32_t)RS_C_FALSE << 28), -1));  // rect, medium (hit.rs default / unimplemented)
     }
@@ -645,6 +660,18 @@ struct ProgramBuilder {
                 prog.push_back(ObjInstr{OP_MED_END, ni, cur, 0});
                 prog[mid].aux = (int)(prog.size() - 1 - mid);
                 return d0;
+            }
+            case RS_NODE_BVH: {  // bvh.rs:173-192
+                const size_t begin = prog.size();
+                prog.push_back(ObjInstr{OP_BVH_BEGIN, ni, cur, 0});
+                int d0 = 1, d1 = 1;
+                if (n.child0 >= 0) d0 = emit(n.child0, cur, in_medium);
+                else prog.push_back(ObjInstr{OP_MISS, ni, cur, 0});
+                if (n.child1 >= 0) d1 = emit(n.child1, cur, in_medium);
+                else prog.push_back(ObjInstr{OP_MISS, ni, cur, 0});
+                prog.push_back(ObjInstr{OP_BVH_END, ni, cur, 0});
+                prog[begin].aux = (int)(prog.size() - 1 - begin);  // pc += aux, then ++pc: the instruction after OP_BVH_END
+                return std::max(d0, 1 + d1);
             }
             default:
                 prog.push_back(ObjInstr{OP_LEAF, ni, cur, 0});
@@ -1033,7 +1060,9 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     std::vector<XformPre> xf;
     for (int i = 0; i < s->n_nodes; ++i) {
         rs_node& n = nodes[i];
-        if (n.type < RS_NODE_SPHERE || n.type > RS_NODE_RAYMARCHER) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad node type");
+        if (n.type < RS_NODE_SPHERE || n.type > RS_NODE_BVH) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad node type");
+        if (n.type == RS_NODE_BVH && (n.child0 >= i || n.child1 >= i || n.child0 < -1 || n.child1 < -1))
+            return fail(ctx, RS_ERR_INVALID_ARGUMENT, "the children of a BVH node must precede it (or be -1)");
         if (n.material >= s->n_materials) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "node material out of range");
         bool two = n.type == RS_NODE_DIFFERENCE || n.type == RS_NODE_INTERSECTION, one = n.type == RS_NODE_TRANSFORM || n.type == RS_NODE_MEDIUM;
         if ((two || one) && (n.child0 < 0 || n.child0 >= i)) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "child0 must precede its parent");
@@ -1253,6 +1282,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
         root_prog[i] = make_int2(first, (int)pb.prog.size() - first);
     }
     if (pb.nested_medium) return fail(ctx, RS_ERR_UNSUPPORTED, "a ConstantMedium inside the boundary of another ConstantMedium is not supported");
+    if (pb.bvh_in_csg) return fail(ctx, RS_ERR_UNSUPPORTED, "a BVH cannot be a CSG operand: BVH::contains is unimplemented!() in the reference (bvh.rs:194-200)");
     {
         // do the expression trees on the object list share one program shape (same operations, same primitive kinds,
         // same skip distances)?  Then closest_hit lets every lane walk to its own next tree (upload_bvh).

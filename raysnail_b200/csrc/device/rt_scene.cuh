@@ -749,6 +749,9 @@ enum ObjOp : int {
     OP_MED_BEGIN = 4,  // ConstantMedium (constant.rs:42-80): the boundary is hit over (-inf, +inf) ...
     OP_MED_MID = 5,    // ... then again from t1 + 0.0001 (the boundary's program follows twice); aux = skip when the first search misses
     OP_MED_END = 6,    // node = the medium, xf = its space: free-flight sample, push the result
+    OP_BVH_BEGIN = 7,  // node = a BVH used as an object (bvh.rs:173-192), xf = its space: AABB::hit on its bbox; on a miss push a miss and skip `aux` instructions (past its OP_BVH_END)
+    OP_BVH_END = 9,    // pop right, pop left, push the closer one (right only when strictly closer: bvh.rs:181-189)
+    OP_MISS = 10,      // push a miss (a child that is None)
 };
 enum ObjFlavor : int {
     FLAVOR_LEAF = 0,       // HitRecord::new of the primitive at `src` (hit.rs:32-53)
@@ -960,6 +963,30 @@ static __device__ __noinline__ bool eval_object(const rs_node* nodes, const Xfor
                 if (res.hit && res.mat < 0) res.mat = n.material;
             }
             stack[sp - 1] = res;
+        } else if (op == OP_BVH_BEGIN) {  // bvh.rs:174-177
+            const rs_node& n = nodes[ni];
+            if (xi != cur_xi) {
+                r = xi >= 0 ? xf_ray(xf[xi].inv, ray) : ray;
+                cur_xi = xi;
+            }
+            const V3 inv = v3(1.0 / r.d.x, 1.0 / r.d.y, 1.0 / r.d.z);
+            if (n.p[6] == 0.0 || !aabb_hit_f64(n.p, r, inv, lo, hi)) {
+                ObjHit e;
+                e.hit = false; e.t1 = 0.0; e.t2 = 0.0; e.mat = -1; e.src = pc; e.flavor = FLAVOR_LEAF;
+                if (RS_IN_BOUNDS(sp < RS_EVAL_STACK)) stack[sp++] = e;
+                pc += aux;
+            }
+        } else if (op == OP_BVH_END) {
+            // bvh.rs:181-189 searches the right child over start..left.t1 and prefers its hit.  Here both children are
+            // searched over the node's own limits and the right one wins when strictly closer — the same winner, and (as
+            // for the objects of the world) what a Box member reports does not depend on its sibling
+            const ObjHit hr = stack[--sp];
+            const ObjHit hl = stack[sp - 1];
+            if (hr.hit && (!hl.hit || hr.t1 < hl.t1)) stack[sp - 1] = hr;
+        } else if (op == OP_MISS) {
+            ObjHit e;
+            e.hit = false; e.t1 = 0.0; e.t2 = 0.0; e.mat = -1; e.src = pc; e.flavor = FLAVOR_LEAF;
+            if (RS_IN_BOUNDS(sp < RS_EVAL_STACK)) stack[sp++] = e;
         } else if (op == OP_MED_BEGIN) {  // constant.rs:45
             lo0 = lo; hi0 = hi;
             lo = -inf; hi = inf;

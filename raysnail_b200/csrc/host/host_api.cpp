@@ -255,6 +255,13 @@ int rs_host_obj_difference(rs_host_scene* s, int plus, int minus, int mat) {
 int rs_host_obj_intersection(rs_host_scene* s, int o1, int o2, int mat) {
     return guarded([&] { return add_obj(s, std::make_shared<Intersection>(obj_of(s, o1), obj_of(s, o2), mat_of(s, mat))); });
 }
+int rs_host_obj_bvh(rs_host_scene* s, int32_t n, const int32_t* objs) {
+    return guarded([&] {
+        std::vector<HittablePtr> members;
+        for (int i = 0; i < n; ++i) members.push_back(obj_of(s, objs[i]));
+        return add_obj(s, BVH::build(std::move(members), s->time_range));
+    });
+}
 int rs_host_obj_transform(rs_host_scene* s, int child, int32_t n_ops, const int32_t* ops, const double* args) {
     return guarded([&] {
         TransformStack st;

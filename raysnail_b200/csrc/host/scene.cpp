@@ -431,6 +431,51 @@ int Intersection::flatten(FlatScene& fs) const {
     });
 }
 
+// bvh.rs:47-112
+std::shared_ptr<BVH> BVH::build(std::vector<HittablePtr> objects, const TimeRange& tr) {
+    if (objects.empty()) return std::make_shared<BVH>();  // Self::default(): no bbox, never hit
+    for (const auto& o : objects)
+        if (!o) throw std::invalid_argument("BVH: null object");
+    return build_range(objects, 0, objects.size(), tr);
+}
+std::shared_ptr<BVH> BVH::build_range(std::vector<HittablePtr>& objects, size_t begin, size_t end, const TimeRange& tr) {
+    auto node = std::make_shared<BVH>();
+    const size_t count = end - begin;
+    node->has_bbox = true;
+    if (count == 1) {
+        node->left = objects[begin];
+        node->box = node->left->bbox(tr);
+    } else if (count == 2) {
+        node->left = objects[begin];
+        node->right = objects[begin + 1];
+        node->box = node->left->bbox(tr) | node->right->bbox(tr);
+    } else {
+        const int axis = (int)((begin + count) & 1);
+        const TimeRange zero{0.0, 0.0};  // cmp_geometry_by compares the boxes at time 0..0 (bvh.rs:29-30)
+        auto key = [&](const HittablePtr& o) { const AABB b = o->bbox(zero); return axis == 0 ? b.min.x : b.min.y; };
+        std::stable_sort(objects.begin() + (long)begin, objects.begin() + (long)end, [&](const HittablePtr& a, const HittablePtr& b) { return key(a) < key(b); });
+        const size_t mid = begin + count / 2;
+        auto l = build_range(objects, begin, mid, tr), r = build_range(objects, mid, end, tr);
+        node->box = l->box | r->box;
+        node->left = l;
+        node->right = r;
+    }
+    return node;
+}
+AABB BVH::bbox(const TimeRange&) const { return box; }
+int BVH::flatten(FlatScene& fs) const {
+    return cached(fs.node_cache, this, [&] {
+        const int a = left ? left->flatten(fs) : -1, b = right ? right->flatten(fs) : -1;
+        if ((left && a < 0) || (right && b < 0)) throw std::invalid_argument("triangles cannot be members of a nested BVH");
+        rs_node n = blank_node(RS_NODE_BVH);
+        n.child0 = a; n.child1 = b;
+        n.p[0] = box.min.x; n.p[1] = box.min.y; n.p[2] = box.min.z;
+        n.p[3] = box.max.x; n.p[4] = box.max.y; n.p[5] = box.max.z;
+        n.p[6] = has_bbox ? 1.0 : 0.0;
+        return push_node(fs, n);
+    });
+}
+
 // tf_facade.rs:59-88
 AABB TfFacade::bbox(const TimeRange& tr) const {
     AABB bb = object->bbox(tr);

@@ -358,6 +358,24 @@ struct TriangleMesh {  // triangle_mesh.rs:152-276
                                     double rotation_angle, int axis, MaterialPtr material);
 };
 
+// collection/bvh.rs — a BVH used as ONE object (bvh.rs:173-192 as a `Hittable`): a world member, the object of a
+// TfFacade, the boundary of a ConstantMedium.  (`World::new` builds its own tree over the world list; that one is
+// rs_upload_scene's business.)  `BVH::build` follows `BVH::new` / `new_internal` (bvh.rs:47-112): one object -> a node
+// with a left child only, two -> both children, more -> stable sort by the bbox minimum on an axis, split in the
+// middle.  The reference draws that axis with `Random::range(0..2)` (bvh.rs:91); here it is (start + count) & 1 — any
+// axis gives a valid tree, and the tree travels explicitly in the scene description, so oracle and GPU walk the same one.
+struct BVH : Hittable {
+    bool has_bbox = false;
+    AABB box;
+    HittablePtr left, right;
+    static std::shared_ptr<BVH> build(std::vector<HittablePtr> objects, const TimeRange& tr);
+    AABB bbox(const TimeRange& tr) const override;
+    int flatten(FlatScene& fs) const override;
+
+private:
+    static std::shared_ptr<BVH> build_range(std::vector<HittablePtr>& objects, size_t begin, size_t end, const TimeRange& tr);
+};
+
 struct HittableList {  // collection/list.rs
     std::vector<HittablePtr> objects;
     template <class G>

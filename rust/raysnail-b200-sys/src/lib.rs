@@ -31,6 +31,7 @@ pub const RS_NODE_INTERSECTION: i32 = 5;
 pub const RS_NODE_TRANSFORM: i32 = 6;
 pub const RS_NODE_MEDIUM: i32 = 7;
 pub const RS_NODE_RAYMARCHER: i32 = 8;
+pub const RS_NODE_BVH: i32 = 9;
 
 pub const RS_RECT_XY: i32 = 0;
 pub const RS_RECT_XZ: i32 = 1;

@@ -118,6 +118,12 @@ def random_world(seed, n_objects, uniform_trees=False):
                 obj = s.sphere(cell, u(0.4, 1.0), mat, speed=(u(-0.5, 0.5), u(0.0, 0.8), u(-0.5, 0.5)))
             elif pick < 0.65:
                 obj = s.transform(s.medium(primitive(-1, allow_rect=False), colour(), u(0.3, 2.0)), place)
+            elif pick < 0.75:
+                # a BVH as one object (bvh.rs:173-192): a few primitives, sometimes a nested group, under the cell's transform
+                members = [primitive(material(), centre=(u(-1.0, 1.0), u(-0.8, 0.8), u(-1.0, 1.0))) for _ in range(int(rng.integers(1, 6)))]
+                if rng.random() < 0.4:
+                    members.append(s.bvh([primitive(material(), centre=(u(-1.0, 1.0), u(-0.8, 0.8), u(-1.0, 1.0))) for _ in range(int(rng.integers(1, 4)))]))
+                obj = s.transform(s.bvh(members), (transform_ops(0.3) if rng.random() < 0.5 else []) + place)
             else:
                 obj = s.transform(solid(int(rng.integers(1, 4)), mat), transform_ops(0.3) + place)
         s.add(obj)

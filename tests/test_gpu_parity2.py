@@ -461,3 +461,64 @@ def test_reuploads_keep_or_rebuild_the_tree_correctly():
         assert np.array_equal(r.render(a.camera(96, 64), params), fresh(a, a.camera(96, 64)))
     finally:
         r.close()
+
+
+def bvh_scene():
+    """A `BVH` as ONE object (bvh.rs:173-192): bare, under a TfFacade, nested in another BVH with a CSG member, and as the
+    boundary of a ConstantMedium."""
+    s = Scene()
+    s.add(s.sphere((0, -1000, 0), 1000.0, s.lambertian(s.checker(s.solid(0.2, 0.3, 0.1), s.solid(0.9, 0.9, 0.9), 2.0))))
+    light = s.sphere((2, 14, 5), 3.0, s.diffuse_light(s.solid(1, 1, 1), 6.0))
+    s.add(light)
+    s.add_light(light)
+
+    def cluster(x0, z0, seed):
+        rng = np.random.default_rng(seed)
+        out = []
+        for k in range(7):
+            c = (x0 + float(rng.uniform(-1.5, 1.5)), float(rng.uniform(0.3, 2.2)), z0 + float(rng.uniform(-1.0, 1.0)))
+            m = [s.lambertian(s.solid(0.2 + 0.1 * k, 0.7 - 0.05 * k, 0.5)), s.metal(s.solid(0.8, 0.7, 0.6)), s.dielectric((1, 1, 1), 1.5)][k % 3]
+            out.append(s.sphere(c, 0.35, m) if k % 2 else s.box((c[0] - 0.3, c[1] - 0.3, c[2] - 0.3), (c[0] + 0.3, c[1] + 0.3, c[2] + 0.3), m))
+        return out
+
+    s.add(s.bvh(cluster(-4.0, 0.0, 1)))                                                                  # bare
+    s.add(s.transform(s.bvh(cluster(0.0, 0.0, 2)), [("rotate_y", 0.5), ("scale", (1.0, 1.2, 1.0)), ("translate", (0.0, 0.0, -1.0))]))
+    csg = s.difference(s.box((3.2, 0.2, -0.6), (4.4, 1.4, 0.6), s.lambertian(s.solid(0.7, 0.3, 0.3))), s.sphere((3.8, 0.8, 0.6), 0.5), -1)
+    s.add(s.bvh([s.bvh(cluster(4.0, 2.0, 3)[:3]), csg, s.sphere((5.2, 0.5, 0.0), 0.5, s.blinn_phong(0.5, 20.0, s.solid(0.3, 0.4, 0.8)))]))  # nested + CSG member
+    s.add(s.transform(s.medium(s.bvh([s.sphere((0, 0, 0), 0.8), s.box((0.5, -0.5, -0.5), (1.6, 0.5, 0.5))]), (0.9, 0.9, 0.95), 1.5),
+                      [("translate", (-1.0, 0.9, 3.0))]))                                               # medium boundary
+    s.add(s.bvh([s.sphere((-6.5, 0.6, 2.0), 0.6, s.lambertian(s.solid(0.9, 0.8, 0.2)))]))                # one member: left child only
+    s.set_camera((0.5, 4.0, 11.0), (0.0, 0.8, 0.0), fov=42.0)
+    return s
+
+
+def test_a_bvh_as_one_world_object(renderer):
+    scene = bvh_scene()
+    renderer.upload(scene)
+    oracle = OracleWorld(scene)
+    cam = scene.camera(W, H)
+    for flags, sample in ((RS_FLAG_PIXEL_CENTRE, 0), (0, 5)):
+        params = make_params(samples=9, flags=flags)
+        g, o = renderer.debug_primary(cam, params, sample), oracle.debug_primary(cam, params, sample)
+        assert np.array_equal(g["obj_id"], o["obj_id"])
+        hit = o["obj_id"] >= 0
+        assert set(np.unique(o["obj_id"][hit])) >= {0, 2, 3, 4, 5, 6}
+        assert _rel_err(g["t"][hit], o["t"][hit]).max() < REL
+        assert np.abs(g["normal"][hit] - o["normal"][hit]).max() < REL
+        for key in ("front", "material"):
+            assert np.array_equal(g[key][hit], o[key][hit]), key
+    check_scatter(renderer.debug_scatter(cam, make_params(samples=9), 2), oracle.debug_scatter(cam, make_params(samples=9), 2), "bvh")
+    small = scene.camera(64, 40)
+    gi = renderer.render(small, make_params(samples=256))
+    oi, _ = oracle.render(small, make_params(samples=256))
+    rmse = float(np.sqrt(np.mean((gi[..., :3] - oi[..., :3]) ** 2))) / float(np.sqrt(np.mean(oi[..., :3] ** 2)))
+    assert rmse < 0.01, rmse
+    # BVH::contains is unimplemented!() in the reference (bvh.rs:194-200): a BVH as a CSG operand is refused
+    bad = Scene()
+    light = bad.sphere((0, 10, 0), 2.0, bad.diffuse_light(bad.solid(1, 1, 1), 5.0))
+    bad.add(light)
+    bad.add_light(light)
+    bad.add(bad.intersection(bad.box((-1, -1, -1), (1, 1, 1)), bad.bvh([bad.sphere((0, 0, 0), 1.2)]), bad.lambertian(bad.solid(0.5, 0.5, 0.5))))
+    with pytest.raises(Exception, match="BVH"):
+        renderer.upload(bad)
+    renderer.upload(scene)

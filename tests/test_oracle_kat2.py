@@ -367,3 +367,88 @@ def test_mixed_settings_forward_to_material_1_recursively():
     assert len(mixed) == 2
     for m in mixed:
         assert (m.phong_factor, m.phong_exponent) == (2.0, 7)
+
+
+# ---------------------------------------------------------------------------------------------
+# a BVH used as one object (bvh.rs:173-192)
+# ---------------------------------------------------------------------------------------------
+def _bvh_members(s, mats):
+    """five solids scattered over x / y so that both sort axes of BVH::new matter"""
+    return [s.sphere((-2.0, 0.5, 0.0), 0.5, mats[0]), s.box((-1.2, 0.0, -0.4), (-0.4, 0.8, 0.4), mats[1]), s.sphere((0.3, 1.4, 0.2), 0.45, mats[2]),
+            s.box((1.0, 0.0, -0.3), (1.6, 1.6, 0.3), mats[3]), s.sphere((2.3, 0.4, -0.1), 0.4, mats[4])]
+
+
+def _bvh_world(grouped, transform=None):
+    s = Scene()
+    s.add(s.sphere((0, -1000, 0), 1000.0, s.lambertian(s.solid(0.5, 0.5, 0.5))))
+    light = s.sphere((0, 12, 3), 3.0, s.diffuse_light(s.solid(1, 1, 1), 5.0))
+    s.add(light)
+    s.add_light(light)
+    mats = [s.lambertian(s.solid(0.1 + 0.15 * k, 0.8 - 0.1 * k, 0.3)) for k in range(5)]
+    members = _bvh_members(s, mats)
+    if grouped:
+        obj = s.bvh(members)
+        s.add(s.transform(obj, transform) if transform else obj)
+    else:
+        for m in members:
+            s.add(s.transform(m, transform) if transform else m)
+    s.set_camera((0.5, 2.0, 7.0), (0.0, 0.6, 0.0), fov=45.0)
+    return s
+
+
+@pytest.mark.parametrize("transform", [None, [("rotate_y", 0.7), ("scale", (1.0, 1.3, 0.8)), ("translate", (0.2, 0.1, -0.5))]], ids=["bare", "tf_facade"])
+def test_a_bvh_as_one_object_finds_the_hits_of_its_members(transform):
+    """BVH::hit returns the closest member hit (bvh.rs:173-192): the same surfaces as the members
+    added to the world one by one — same t, normal, side and material wherever either is hit; one object id instead of five."""
+    cam_params = make_params(samples=1, flags=RS_FLAG_PIXEL_CENTRE)
+    g, f = _bvh_world(True, transform), _bvh_world(False, transform)
+    a = OracleWorld(g).debug_primary(g.camera(160, 100), cam_params, 0)
+    b = OracleWorld(f).debug_primary(f.camera(160, 100), cam_params, 0)
+    assert np.array_equal(a["obj_id"] >= 2, b["obj_id"] >= 2)
+    grp = a["obj_id"] == 2
+    assert grp.sum() > 800 and len(np.unique(b["obj_id"][grp])) == 5
+    assert np.array_equal(a["t"][grp], b["t"][grp])
+    assert np.array_equal(a["normal"][grp], b["normal"][grp])
+    assert np.array_equal(a["front"][grp], b["front"][grp])
+    # (material ids are handed out in flatten order, which differs between the two worlds: the pairing must be a bijection)
+    pairs = set(zip(a["material"][grp].tolist(), b["material"][grp].tolist()))
+    assert len(pairs) == 5 and len({p[0] for p in pairs}) == 5 and len({p[1] for p in pairs}) == 5
+
+
+def test_bvh_node_layout_follows_bvh_new():
+    """bvh.rs:47-112: one object -> left only; two -> both; more -> sorted by the bbox minimum, split in the middle; every
+    node's bbox is the union of its children's."""
+    s = Scene()
+    mats = [s.lambertian(s.solid(0.5, 0.5, 0.5))] * 5
+    s.add(s.bvh(_bvh_members(s, mats)))
+    light = s.sphere((0, 12, 3), 3.0, s.diffuse_light(s.solid(1, 1, 1), 5.0))
+    s.add(light)
+    s.add_light(light)
+    d = s.desc.contents
+    nodes = [d.nodes[i] for i in range(d.n_nodes)]
+    bvh = [n for n in nodes if n.type == 9]
+    assert len(bvh) == 5  # 5 -> (2, 3), 3 -> (1, 2): the root, its pair, its triple, the triple's single and the triple's pair
+    root = nodes[d.roots[0]]
+    assert root.type == 9 and root.p[6] == 1.0
+
+    def leaves(n):
+        if n.type != 9:
+            return 1
+        return sum(leaves(nodes[c]) for c in (n.child0, n.child1) if c >= 0)
+
+    def box_of(n):
+        if n.type == 9:
+            return np.array(n.p[:6])
+        if n.type == 0:
+            c, r = np.array(n.p[:3]), n.p[3]
+            return np.concatenate([c - r, c + r])
+        return np.array(n.p[:6])
+
+    assert leaves(root) == 5 and leaves(nodes[root.child0]) == 2 and leaves(nodes[root.child1]) == 3
+    for n in bvh:
+        kids = [box_of(nodes[c]) for c in (n.child0, n.child1) if c >= 0]
+        lo = np.min([k[:3] for k in kids], axis=0)
+        hi = np.max([k[3:] for k in kids], axis=0)
+        assert np.allclose(n.p[:3], lo, atol=2e-4) and np.allclose(n.p[3:6], hi, atol=2e-4)  # (Box::bbox pads by 0.0001, box.rs)
+    single = [n for n in bvh if n.child1 < 0]
+    assert len(single) == 1 and single[0].child0 >= 0
