@@ -387,9 +387,12 @@ def run_gpu(args):
             return
         renderer.upload(scene)                       # host scene buffers -> HBM (incl. BVH build)
         d_mask.copy_(host_mask, non_blocking=True)   # pixel mask from pinned host memory
+        # a mask that masks nothing is passed as NULL, as rs_render / rs_multi_render do with their host masks
+        # (memchr; backend.cu): the unmasked path generates the camera rays inside the first extend
+        mask_ptr = d_mask.data_ptr() if not bool(host_mask.all()) else None
         accum.zero_()
-        renderer.render_accumulate(cam, params, d_mask.data_ptr(), accum.data_ptr(), stream)
-        combine(d_mask.data_ptr())
+        renderer.render_accumulate(cam, params, mask_ptr, accum.data_ptr(), stream)
+        combine(mask_ptr)
         if rank == 0:
             host_img.copy_(out, non_blocking=True)   # the image the caller gets back
         torch.cuda.synchronize()
