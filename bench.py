@@ -171,7 +171,7 @@ def scene_bytes(desc):
             d.n_materials * C.sizeof(_abi.RsMaterial) + d.n_textures * C.sizeof(_abi.RsTexture) + d.n_texel_bytes + d.n_perlin_perm * 4 + d.n_perlin_values * 8)
 
 
-DEFAULT_WAVE_PATHS = 1 << 25  # csrc/backend.cu render_into: paths in flight per wave when rs_render_params.max_wave_paths is 0
+DEFAULT_WAVE_PATHS = 1 << 26  # csrc/backend.cu render_into: paths in flight per wave when rs_render_params.max_wave_paths is 0
 
 
 def load_bench_scene(name):
@@ -452,7 +452,7 @@ def run_gpu(args):
                        else f"{args.scene} {width}x{height} {q * q} spp depth 8 (not the headline workload)",
                        "parallelism": f"strata-rows x{world_size}",
                        "combine": ("none (single GPU: finalize only)" if world_size == 1 else
-                                   ("fused reduce+finalize kernel over NVLink peer memory" if args.reduce == "peer" else "ncclReduce + finalize")), "l2": "path/ray/hit buffers of one wave (> 6 GB at 32 Mi paths) exceed the 126 MB L2; no flush needed",
+                                   ("fused reduce+finalize kernel over NVLink peer memory" if args.reduce == "peer" else "ncclReduce + finalize")), "l2": "path/ray/hit buffers of one wave (> 12 GB at 64 Mi paths) exceed the 126 MB L2; no flush needed",
                        "wave_paths": args.wave or DEFAULT_WAVE_PATHS, "wave_streams": args.wave_streams},
             "mrays_per_s": n_segments / (ms_total / args.steps / 1e3) / 1e6,
             "segments_per_sample": n_segments / max(n_samples, 1.0),

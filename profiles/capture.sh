@@ -8,7 +8,7 @@ set -x
 python bench.py --steps 3 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv \
     python bench.py --steps 1 --warmup 1 --sqrt-spp 4 --no-cpu > gpurun_out/${TAG}_launches.log 2>&1
-# at 16 spp the frame is ONE wave of 1920x1080x16 = 33 177 600 paths (32 Mi paths per wave is the default)
+# at 16 spp the frame is ONE wave of 1920x1080x16 = 33 177 600 paths (64 Mi paths per wave is the default)
 # one wave = 8 bounces x (extend, shade<Lambertian>, shade<rest>) = 24 matching launches (bounce 0 = the extend
 # that generates the camera rays itself): skip the first wave, capture bounce 0 and bounce 1 of the second one
 ncu --set full --import-source on --clock-control none -k regex:"shade_kernel|extend_kernel" --launch-skip 24 --launch-count 6 \
