@@ -1120,9 +1120,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     root_kind.resize(s->n_roots);
     root_sphere.resize((size_t)s->n_roots * 4);
     root_gate.resize(s->n_roots);
-    prims.clear();
-    loose.clear();
-    prims.reserve(s->n_roots);
+    loose.clear();  // (`prims` is overwritten whole below: clearing it first would make the resize zero-fill 80 MB per million objects)
     bool any_quadric_root = false;
     double omax = 1.0;
     {
@@ -1134,6 +1132,8 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
             std::vector<BuildPrim>&my = sc.part[chunk], &my_loose = sc.part_loose[chunk];
             my.clear();
             my_loose.clear();
+            bool my_anyq = false;  // (chunk-local, stored once at the end: the shared arrays would bounce one cache line between the threads)
+            double my_om = 1.0;
             for (size_t ii = begin; ii < end; ++ii) {
                 const int i = (int)ii;
                 int r = s->roots[i];
@@ -1153,7 +1153,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
                         const rs_node& inner = n.type == RS_NODE_TRANSFORM ? nodes[n.child0] : n;
                         // (a quadric root takes the same inline route, but only the generic-tier kernels hold its code)
                         root_kind[i] = (inner.type == RS_NODE_BOX || inner.type == RS_NODE_RECT || inner.type == RS_NODE_QUADRIC) ? ROOT_FLAT : ROOT_GENERIC;
-                        anyq[chunk] |= inner.type == RS_NODE_QUADRIC;
+                        my_anyq |= inner.type == RS_NODE_QUADRIC;
                         // spheres / boxes / rects always lie inside their reference bbox; everything
                         // else is clipped by it the way the reference's BVH leaf clips it
                         root_gate[i] = !(n.type == RS_NODE_SPHERE || n.type == RS_NODE_BOX || n.type == RS_NODE_RECT);
@@ -1188,9 +1188,11 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
                             p.c[a] = 0.5 * (p.lo[a] + p.hi[a]);
                         }
                 }
-                for (int a = 0; a < 3; ++a) om[chunk] = std::max(om[chunk], std::max(std::fabs(p.lo[a]), std::fabs(p.hi[a])));
+                for (int a = 0; a < 3; ++a) my_om = std::max(my_om, std::max(std::fabs(p.lo[a]), std::fabs(p.hi[a])));
                 (bounded ? my : my_loose).push_back(p);
             }
+            anyq[chunk] = my_anyq;
+            om[chunk] = my_om;
         });
         size_t off[kMaxChunks + 1] = {0};
         for (int c = 0; c < chunks; ++c) {
