@@ -191,3 +191,80 @@ def test_random_worlds_match_the_oracle(seed, n_objects, uniform, bvh_width):
         assert rmse < 0.01, f"seed {seed}: relative RMSE {rmse}"
     finally:
         r.close()
+
+
+def random_lean_world(seed, n_spheres, n_tris):
+    """Static spheres and a random triangle soup only — the lean tier: batch extend on bounce 0, the streaming extend kernel
+    from bounce 1 on when triangles are present, the staged shade kernels.  Some triangles are axis-parallel (a bbox with no
+    thickness: never hit, triangle_mesh.rs:43-45 / aabb.rs:33) and some are slivers."""
+    rng = np.random.default_rng(seed)
+    s = Scene()
+    u = lambda a, b: float(rng.uniform(a, b))  # noqa: E731
+    mats = [s.lambertian(s.solid(u(0.1, 0.9), u(0.1, 0.9), u(0.1, 0.9))), s.metal(s.solid(0.8, 0.8, 0.7)), s.dielectric((1, 1, 1), 1.5),
+            s.blinn_phong(0.4, 30.0, s.solid(0.3, 0.5, 0.8)), s.diffuse_metal(40.0, s.solid(0.9, 0.6, 0.3)),
+            s.lambertian(s.checker(s.solid(0.1, 0.1, 0.1), s.solid(0.9, 0.9, 0.9), 4.0))]
+    s.add(s.sphere((0.0, -1000.5, 0.0), 1000.0, mats[5]))
+    lights = [s.sphere((u(-6, 6), u(8, 12), u(-6, 6)), u(1.0, 2.0), s.diffuse_light(s.solid(1, 1, 1), u(4.0, 9.0)))]
+    if seed % 2:
+        lights.append(s.rect("xz", 11.0, (-2.0, 2.0), (-2.0, 2.0), s.diffuse_light(s.solid(1.0, 0.9, 0.8), 5.0)))
+    for l in lights:
+        s.add(l)
+        s.add_light(l)
+    for _ in range(n_spheres):
+        s.add(s.sphere((u(-5, 5), u(0.0, 3.0), u(-5, 5)), u(0.15, 0.7), mats[int(rng.integers(0, 5))]))
+    if n_tris:
+        centres = rng.uniform([-5, 0.0, -5], [5, 3.5, 5], size=(n_tris, 3))
+        tri = centres[:, None, :] + rng.normal(0.0, 0.45, size=(n_tris, 3, 3))
+        tri[::17, :, 1] = tri[::17, :1, 1]            # axis-parallel: all three vertices at one height
+        tri[5::23, 2] = tri[5::23, 1] + 1e-3 * (tri[5::23, 2] - tri[5::23, 1])  # slivers
+        pos = tri.reshape(-1, 3).astype(np.float32)
+        idx = np.arange(3 * n_tris, dtype=np.uint32)
+        for k in range(3):  # three materials: three meshes
+            sel = np.arange(k, n_tris, 3)
+            s.add_mesh(pos, idx.reshape(-1, 3)[sel].reshape(-1), mat=mats[[0, 1, 3][k]])
+    s.set_camera((u(-2, 2), u(3.0, 5.0), 13.0), (0.0, 1.0, 0.0), fov=45.0, aperture=[0.0, 0.08][seed % 2], focus=13.0)
+    return s
+
+
+LEAN_CASES = [(201, 40, 0), (202, 10, 300), (203, 200, 2000), (204, 0, 5000), (205, 3, 40), (206, 600, 600)]
+
+
+@pytest.mark.parametrize("seed,n_spheres,n_tris", LEAN_CASES)
+@pytest.mark.parametrize("bvh_width", [2, 4])
+def test_random_lean_worlds_match_the_oracle(seed, n_spheres, n_tris, bvh_width):
+    from raysnail_b200 import Renderer
+    scene = random_lean_world(seed, n_spheres, n_tris)
+    oracle = OracleWorld(scene)
+    cam = scene.camera(W, H)
+    r = Renderer(0)
+    try:
+        r.set_bvh_width(bvh_width)
+        r.upload(scene)
+        for flags, sample in ((RS_FLAG_PIXEL_CENTRE, 0), (0, 2)):
+            params = make_params(samples=4, flags=flags)
+            g, o = r.debug_primary(cam, params, sample), oracle.debug_primary(cam, params, sample)
+            mism = np.flatnonzero(g["obj_id"] != o["obj_id"])
+            assert mism.size == 0, f"seed {seed}: {mism.size} ids differ at {mism[:5]}: gpu {g['obj_id'][mism[:5]]} oracle {o['obj_id'][mism[:5]]}"
+            hit = o["obj_id"] >= 0
+            assert _rel_err(g["t"][hit], o["t"][hit]).max() < REL
+            assert np.abs(g["normal"][hit] - o["normal"][hit]).max() < REL * max(1.0, np.abs(o["normal"][hit]).max())
+            for key in ("front", "material"):
+                assert np.array_equal(g[key][hit], o[key][hit]), key
+        params = make_params(samples=4)
+        g, o = r.debug_scatter(cam, params, 1), oracle.debug_scatter(cam, params, 1)
+        assert np.array_equal(g["kind"], o["kind"])
+        sc = (o["kind"] >= 2) & ~np.isnan(o["next"]).any(axis=1)
+        assert np.abs(g["next"][sc] - o["next"][sc]).max() < REL * max(1.0, np.abs(o["next"][sc]).max())
+        assert _rel_err(g["weight"][sc], o["weight"][sc], floor=1e-6).max() < 1e-4
+        # the whole wavefront, every bounce (the streaming extend kernel on the meshes): a converged image
+        small = scene.camera(64, 40)
+        gi = r.render(small, make_params(samples=64))
+        oi, _ = oracle.render(small, make_params(samples=64))
+        fin = np.isfinite(oi).all(axis=-1) & np.isfinite(gi).all(axis=-1)
+        assert fin.mean() > 0.995
+        rmse = float(np.sqrt(np.mean((gi[fin][:, :3] - oi[fin][:, :3]) ** 2))) / max(float(np.sqrt(np.mean(oi[fin][:, :3] ** 2))), 1e-3)
+        assert rmse < 0.01, f"seed {seed}: relative RMSE {rmse}"
+        st = r.stats()
+        assert st.n_samples == 64 * 40 * 64
+    finally:
+        r.close()
