@@ -389,6 +389,29 @@ int rs_multi_render(rs_multi* m, const rs_camera* cam, const rs_render_params* p
 int rs_signal(rs_ctx* ctx, uint32_t* d_counter, void* stream);
 int rs_wait_counter(rs_ctx* ctx, const uint32_t* d_counter, uint32_t expect, void* stream);
 
+/* ---- the redo-map step without any allocation -------------------------------------------------------
+ * No counterpart in the reference (its passes loop works on host Vecs, src/bin/raysnail.rs:404-423); this
+ * is the library's own addition for callers that cannot let it allocate device memory: hosts whose own
+ * pool already owns the whole card, per-frame loops where the device-wide stall of a cudaMalloc is not
+ * acceptable, and multi-GPU code sitting between rs_signal and rs_wait_counter, where a cudaMalloc waits
+ * for peer devices that may be spinning and never returns.
+ *
+ * One call = what rs_render_passes does after combine_pixels: noise = calc_noise(d_pixels) (exactly
+ * rs_noise_map, same `quirk`), d_redo_mask[i] = noise[i] >= noise_threshold ? 1 : 0, *d_redo_count = number
+ * of ones.  All three pointers are DEVICE pointers the caller owns (W*H float4 in; W*H bytes and one
+ * uint64 out).  The noise map in between is kept in a fixed array inside the library, RS_STATIC_MAX_PIXELS
+ * floats = 16 MiB, present on every GPU the library is loaded on for the life of the process.
+ *   - width*height > RS_STATIC_MAX_PIXELS is refused with RS_ERR_UNSUPPORTED (rs_last_error says by how much);
+ *   - the call allocates and frees nothing on the device, and does not synchronise: work is queued on `stream`;
+ *   - the first call on each device looks the array's address up (one-time set-up that may also load the
+ *     library's device code): make that first call outside of any stream capture;
+ *   - the array is shared by every context, stream and thread on that GPU and keeps what the last call wrote:
+ *     two calls whose kernels can run at the same time on one GPU (different streams, different contexts)
+ *     overwrite each other's noise map.  Order them on one stream, or with events. */
+#define RS_STATIC_MAX_PIXELS 4194304 /* 4 Mi pixels (2048 x 2048; a 1920 x 1080 frame is 2 073 600) */
+int rs_redo_map_static(rs_ctx* ctx, const float* d_pixels, uint8_t* d_redo_mask, uint64_t* d_redo_count,
+                       int32_t width, int32_t height, int32_t quirk, float noise_threshold, void* stream);
+
 int rs_get_stats(const rs_ctx* ctx, rs_stats* out);
 
 #ifdef __cplusplus

@@ -27,7 +27,7 @@ CORE_SYMBOLS = [
     "rs_device_alloc", "rs_device_free", "rs_ipc_export", "rs_ipc_open", "rs_ipc_close", "rs_finalize_peers",
     "rs_render_passes", "rs_pass_seed", "rs_philox4x32_10", "rs_philox_uniform",
     "rs_create_multi", "rs_destroy_multi", "rs_multi_last_error", "rs_multi_device_count", "rs_multi_set_option",
-    "rs_multi_upload_scene", "rs_multi_render", "rs_signal", "rs_wait_counter",
+    "rs_multi_upload_scene", "rs_multi_render", "rs_signal", "rs_wait_counter", "rs_redo_map_static",
 ]
 # every symbol include/raysnail_b200_host.h declares
 HOST_SYMBOLS = [
@@ -136,6 +136,7 @@ def load() -> C.CDLL:
     proto("rs_combine_passes", C.c_int, vp, vp, vp, vp, C.c_int64, f32, vp)
     proto("rs_noise_map", C.c_int, vp, vp, vp, i32, i32, i32, vp)
     proto("rs_quantize_rgb8", C.c_int, vp, vp, vp, C.c_int64, vp)
+    proto("rs_redo_map_static", C.c_int, vp, vp, vp, vp, i32, i32, i32, f32, vp)
     proto("rs_debug_primary", C.c_int, vp, P(RsCamera), P(RsRenderParams), i32, vp, vp, vp, vp, vp, vp, vp)
     proto("rs_debug_scatter", C.c_int, vp, P(RsCamera), P(RsRenderParams), i32, vp, vp, vp, vp)
     proto("rs_get_stats", C.c_int, vp, P(RsStats))

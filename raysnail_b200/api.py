@@ -389,6 +389,15 @@ class Renderer:
     def noise_map(self, d_pixels, d_noise, width, height, quirk=True, stream: int = 0):
         self._ck(self._lib.rs_noise_map(self._ctx, d_pixels, d_noise, width, height, int(quirk), stream), "rs_noise_map")
 
+    def redo_map_static(self, d_pixels, d_redo_mask, d_redo_count, width, height, quirk=True, threshold: float = 0.01, stream: int = 0):
+        """rs_redo_map_static: noise map -> redo mask + count, for hosts that cannot let the library allocate on the
+        device (their own pool owns the card, or a cudaMalloc would stall or dead-lock what is running).  The three
+        arguments are device addresses the caller owns; the noise map in between sits in a fixed 16 MiB array inside
+        the library (at most RS_STATIC_MAX_PIXELS = 4 Mi pixels; larger frames raise).  Calls that overlap on one GPU
+        share that array and corrupt each other: keep them on one stream."""
+        self._ck(self._lib.rs_redo_map_static(self._ctx, d_pixels, d_redo_mask, d_redo_count, int(width), int(height), int(quirk),
+                                              float(threshold), stream), "rs_redo_map_static")
+
     def quantize_rgb8(self, d_pixels, d_rgb, n_pixels, stream: int = 0):
         self._ck(self._lib.rs_quantize_rgb8(self._ctx, d_pixels, d_rgb, n_pixels, stream), "rs_quantize_rgb8")
 

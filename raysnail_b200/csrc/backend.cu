@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -2090,3 +2091,65 @@ int rs_get_stats(const rs_ctx* ctx, rs_stats* out) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------
+// rs_redo_map_static — the redo-map step of the passes loop for callers that must not allocate.
+//
+// Who that is: a host that has handed the whole card to its own memory pool and leaves the CUDA heap nothing to
+// give; a per-frame loop in which a cudaMalloc would stall every stream of the process (cudaMalloc synchronises
+// the device); and, in this very library, code that runs between rs_signal and rs_wait_counter on several GPUs —
+// with peer access on, cudaMalloc waits for the peer devices, and a peer that is already spinning in a wait
+// kernel never answers (see the note in rs_multi_render).  rs_render_passes keeps the intermediate noise map in a
+// cudaMalloc'ed context buffer; here it lives in the fixed array below, which belongs to the loaded library, not
+// to a context: every GPU that loads the library carries these 16 MiB until the process exits.
+//
+// `rs_static_noise` as written in HOST code is only a handle for the runtime, not an address a kernel can use;
+// the address on a given GPU comes from cudaGetSymbolAddress, asked once per device with that device current.
+// ------------------------------------------------------------------------------------------------------------
+static_assert(RS_STATIC_MAX_PIXELS == (1 << 22), "the header states 4 Mi pixels");
+static __device__ __align__(256) float rs_static_noise[RS_STATIC_MAX_PIXELS];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mutex;
+float* g_static_noise_ptr[kStaticMaxDevices] = {};  // device address of rs_static_noise on device k; nullptr = not asked yet
+
+// set-up, once per device (the caller has made `device` current).  The first use of the array on a device may load the
+// library's code onto it, which is why that first call belongs before any stream capture.
+int static_noise_address(rs_ctx* ctx, int device, float** out) {
+    if (device < 0 || device >= kStaticMaxDevices) return fail(ctx, RS_ERR_UNSUPPORTED, "rs_redo_map_static: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_noise_ptr[device]) {
+        float* p = nullptr;
+        CK(cudaGetSymbolAddress((void**)&p, rs_static_noise));
+        if (!p) return fail(ctx, RS_ERR_CUDA, "cudaGetSymbolAddress(rs_static_noise) returned a null address");
+        g_static_noise_ptr[device] = p;
+    }
+    *out = g_static_noise_ptr[device];
+    return RS_OK;
+}
+}  // namespace
+
+extern "C" int rs_redo_map_static(rs_ctx* ctx, const float* d_pixels, uint8_t* d_redo_mask, uint64_t* d_redo_count, int32_t width,
+                                  int32_t height, int32_t quirk, float noise_threshold, void* stream) {
+    if (!ctx || !d_pixels || !d_redo_mask || !d_redo_count || width <= 0 || height <= 0)
+        return fail(ctx, RS_ERR_INVALID_ARGUMENT, "bad rs_redo_map_static arguments");
+    const int64_t np = (int64_t)width * height;
+    if (np > (int64_t)RS_STATIC_MAX_PIXELS)
+        return fail(ctx, RS_ERR_UNSUPPORTED, "rs_redo_map_static: " + std::to_string(width) + " x " + std::to_string(height) + " = " +
+                                                 std::to_string(np) + " pixels exceed the fixed scratch of RS_STATIC_MAX_PIXELS = " +
+                                                 std::to_string((long long)RS_STATIC_MAX_PIXELS) +
+                                                 " pixels; use rs_noise_map with a buffer of your own or rs_render_passes");
+    CK(cudaSetDevice(ctx->device));
+    float* d_noise = nullptr;
+    const int rc = static_noise_address(ctx, ctx->device, &d_noise);
+    if (rc != RS_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the count is summed with atomics, so it has to start from zero; the noise map needs no clearing: its first
+    // width*height entries are all rewritten by the first kernel before the second one reads them
+    CK(cudaMemsetAsync(d_redo_count, 0, sizeof(uint64_t), st));
+    launch_noise(reinterpret_cast<const float4*>(d_pixels), d_noise, width, height, quirk, st);
+    launch_redo_mask(d_noise, d_redo_mask, np, noise_threshold, reinterpret_cast<unsigned long long*>(d_redo_count), st);
+    CK(cudaGetLastError());
+    return RS_OK;
+}

@@ -71,6 +71,7 @@ pub const RS_OPT_WAVE_STREAMS: c_int = 2;
 pub const RS_OPT_LIST_MAX: c_int = 3;
 pub const RS_IPC_HANDLE_BYTES: usize = 64;
 pub const RS_MAX_PEERS: usize = 16;
+pub const RS_STATIC_MAX_PIXELS: usize = 4194304;
 
 #[repr(C)]
 #[derive(Clone, Copy, Debug)]
@@ -233,6 +234,9 @@ extern "C" {
     pub fn rs_finalize_peers(ctx: *mut rs_ctx, d_accums: *const *const f32, n_peers: i32, d_pixel_mask: *const u8, d_out_rgba: *mut f32, pixel_begin: i64, pixel_end: i64, n_samples: i32, gamma: i32, stream: *mut c_void) -> c_int;
     pub fn rs_combine_passes(ctx: *mut rs_ctx, d_old: *const f32, d_new: *const f32, d_out: *mut f32, n_pixels: i64, pass: f32, stream: *mut c_void) -> c_int;
     pub fn rs_noise_map(ctx: *mut rs_ctx, d_pixels: *const f32, d_noise: *mut f32, width: i32, height: i32, quirk: i32, stream: *mut c_void) -> c_int;
+    /// No counterpart in the reference: the redo map computed without any device allocation (fixed 16 MiB scratch
+    /// inside the library, at most RS_STATIC_MAX_PIXELS pixels; calls that overlap on one GPU race on it).
+    pub fn rs_redo_map_static(ctx: *mut rs_ctx, d_pixels: *const f32, d_redo_mask: *mut u8, d_redo_count: *mut u64, width: i32, height: i32, quirk: i32, noise_threshold: f32, stream: *mut c_void) -> c_int;
     pub fn rs_quantize_rgb8(ctx: *mut rs_ctx, d_pixels: *const f32, d_rgb: *mut u8, n_pixels: i64, stream: *mut c_void) -> c_int;
     pub fn rs_debug_primary(ctx: *mut rs_ctx, cam: *const rs_camera, params: *const rs_render_params, sample_index: i32, obj_id: *mut i32, t: *mut f64, normal3: *mut f64, point3: *mut f64, front: *mut i32, material: *mut i32, ray_od6: *mut f64) -> c_int;
     pub fn rs_debug_scatter(ctx: *mut rs_ctx, cam: *const rs_camera, params: *const rs_render_params, sample_index: i32, kind: *mut i32, next_od6: *mut f64, weight3: *mut f64, emitted3: *mut f64) -> c_int;
