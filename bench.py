@@ -171,6 +171,32 @@ def scene_bytes(desc):
             d.n_materials * C.sizeof(_abi.RsMaterial) + d.n_textures * C.sizeof(_abi.RsTexture) + d.n_texel_bytes + d.n_perlin_perm * 4 + d.n_perlin_values * 8)
 
 
+E2E_WARM = ("warm: the world is unchanged between steps, so rs_upload_scene re-uploads the scene tables but keeps the SAH tree "
+            "and its device copy (tree cache); wave buffers already allocated")
+E2E_COLD = ("cold: a fresh context per step — rs_create + rs_upload_scene (SAH build from nothing, tree upload) + rs_render with "
+            "host mask and host image, wave buffers allocated inside the timed region; the first frame a caller sees")
+
+
+def e2e_cold(device, scene, cam, params, host_mask_ptr, host_img_ptr, samples_per_step, bvh_width=2, wave_streams=4, reps=2):
+    """First-frame e2e: nothing cached.  Every repetition creates its own context, so neither the tree cache nor the
+    wave buffers of an earlier call can help; wall clock around create + upload + render + destroy."""
+    from raysnail_b200 import Renderer
+    times = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        r = Renderer(device)
+        try:
+            r.set_bvh_width(bvh_width)
+            r.set_wave_streams(wave_streams)
+            r.upload(scene)
+            r.render_to_ptr(cam, params, host_mask_ptr, host_img_ptr)
+        finally:
+            r.close()
+        times.append(time.perf_counter() - t0)
+    dt = min(times)  # (the first repetition may also pay one-time driver work that is no property of the frame)
+    return {"value": samples_per_step / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "ms_per_step_all": [t * 1e3 for t in times], "kind": E2E_COLD}
+
+
 DEFAULT_WAVE_PATHS = 1 << 26  # csrc/backend.cu render_into: paths in flight per wave when rs_render_params.max_wave_paths is 0
 
 
@@ -273,7 +299,8 @@ def measure_config(renderer, dev, label, scene_name, width, height, q, steps, wo
             e2e_step()
         dt = (time.perf_counter() - t0) / steps
         e2e = {"value": width * height * q * q / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "h2d_bytes_per_step": int(scene_bytes(scene.desc) + height * width),
-               "d2h_bytes_per_step": height * width * 16}
+               "d2h_bytes_per_step": height * width * 16, "kind": E2E_WARM,
+               "cold": e2e_cold(dev.index, scene, cam, p_all, host_mask.data_ptr(), host_img.data_ptr(), width * height * q * q, reps=1)}
     if peer is not None:
         barrier()
         peer.close()
@@ -380,8 +407,10 @@ def run_gpu(args):
 
     def e2e_step():
         if world_size == 1:
-            # the reference-facing call itself: rs_upload_scene (host scene buffers -> HBM, BVH build) +
-            # rs_render with a HOST pixel mask and a HOST output image (the C ABI's shot_to_target)
+            # the reference-facing call itself: rs_upload_scene (host scene buffers -> HBM) + rs_render with a HOST
+            # pixel mask and a HOST output image (the C ABI's shot_to_target).  WARM: the world does not change between
+            # steps, so the upload keeps the SAH tree (tree cache, filled by the untimed first call) and the all-ones
+            # mask is recognised as "no mask"; the cold first frame is measured separately (e2e_cold)
             renderer.upload(scene)
             renderer.render_to_ptr(cam, params, host_mask.data_ptr(), host_img.data_ptr())
             return
@@ -409,6 +438,10 @@ def run_gpu(args):
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
     total_samples_per_step = float(width * height * q * q)
     e2e_value = total_samples_per_step * e2e_steps / (float(e2e_ms.item()) / 1e3)
+    cold = None
+    if world_size == 1:
+        p_cold = make_params(sqrt_spp=q, depth=depth, max_wave_paths=args.wave)
+        cold = e2e_cold(local_rank, scene, cam, p_cold, host_mask.data_ptr(), host_img.data_ptr(), total_samples_per_step, args.bvh_width, args.wave_streams)
 
     # the other BASELINE.json configs, outside the timed headline region (all ranks take part; N = 1: C1, C3a, C3b, C4, C5
     # at 256 spp; N > 1: C5 at its full 4096 spp)
@@ -425,6 +458,50 @@ def run_gpu(args):
                 others.append({"workload": label, "error": f"{type(exc).__name__}: {exc}"})
         if rank == 0:
             others_clocks = osampler.stop()
+
+    # ---- N > 1: is the N-GPU image the one-GPU image, and what does the ONE-call C ABI (rs_multi_render) deliver? ----
+    image_check, multi_call = None, None
+    if world_size > 1:
+        cpu_group = dist.new_group(backend="gloo")  # the idle ranks wait on the host: an NCCL barrier would spin on their GPUs
+        step(params)
+        barrier()
+        if rank == 0:
+            sharded = out.clone()
+            # the whole frame on rank 0's GPU alone, same seed: every pixel is the same set of per-sample values, summed in
+            # N groups instead of one, so the images may differ by the f32 rounding of that grouping only
+            accum1 = torch.zeros((height, width, 4), dtype=torch.float32, device=dev)
+            out1 = torch.empty_like(accum1)
+            renderer.render_accumulate(cam, make_params(sqrt_spp=q, depth=depth, max_wave_paths=args.wave), None, accum1.data_ptr(), stream)
+            renderer.finalize(accum1.data_ptr(), None, out1.data_ptr(), width, height, q * q, True, stream)
+            torch.cuda.synchronize()
+            diff = (sharded - out1).abs()
+            image_check = {"vs": "the whole frame rendered on rank 0's GPU alone (same Philox key)", "max_abs_diff": float(diff.max().item()),
+                           "mean_abs_diff": float(diff.mean().item()), "mean_value": float(out1[..., :3].mean().item()),
+                           "ok": bool(torch.allclose(sharded, out1, rtol=2e-5, atol=2e-6))}
+            del accum1, out1, diff
+            # rs_create_multi / rs_multi_render: what a single-process host (the Rust crate) binds — host scene in, host image
+            # out, all N devices behind one call, no torch.distributed anywhere on the path
+            try:
+                from raysnail_b200 import MultiRenderer
+                mr = MultiRenderer(list(range(world_size)))
+                try:
+                    mr.upload(scene)
+                    p_all = make_params(sqrt_spp=q, depth=depth, max_wave_paths=args.wave)
+                    mr.render_to_ptr(cam, p_all, None, host_img.data_ptr())
+                    m_steps = max(1, min(args.steps, 3))
+                    t0 = time.perf_counter()
+                    for _ in range(m_steps):
+                        mr.render_to_ptr(cam, p_all, None, host_img.data_ptr())
+                    dt = (time.perf_counter() - t0) / m_steps
+                    same = bool(torch.allclose(host_img, sharded.cpu(), rtol=2e-5, atol=2e-6))
+                    multi_call = {"call": "rs_multi_render (one process, one host thread per device, host image out)", "value": total_samples_per_step / dt,
+                                  "unit": UNIT, "ms_per_step": dt * 1e3, "steps": m_steps, "devices": world_size, "image_equals_torchrun_image": same,
+                                  "timing": "host wall clock around the call (it returns after the image is in host memory)"}
+                finally:
+                    mr.close()
+            except Exception as exc:
+                multi_call = {"error": f"{type(exc).__name__}: {exc}"}
+        dist.barrier(group=cpu_group)
 
     if rank == 0:
         value = total_samples_per_step * args.steps / (ms_total / 1e3)
@@ -451,12 +528,13 @@ def run_gpu(args):
             "config": {"workload": WORKLOAD if (args.scene, width, height, q) == ("rtow_final", WIDTH, HEIGHT, SQRT_SPP)
                        else f"{args.scene} {width}x{height} {q * q} spp depth 8 (not the headline workload)",
                        "parallelism": f"strata-rows x{world_size}",
+                       "oracle": "port, canonical rules (C++ restatement of the Rust reference with the tie / range rules of DESIGN.md §2; parity unpinned)",
                        "combine": ("none (single GPU: finalize only)" if world_size == 1 else
                                    ("fused reduce+finalize kernel over NVLink peer memory" if args.reduce == "peer" else "ncclReduce + finalize")), "l2": "path/ray/hit buffers of one wave (> 12 GB at 64 Mi paths) exceed the 126 MB L2; no flush needed",
                        "wave_paths": args.wave or DEFAULT_WAVE_PATHS, "wave_streams": args.wave_streams},
             "mrays_per_s": n_segments / (ms_total / args.steps / 1e3) / 1e6,
             "segments_per_sample": n_segments / max(n_samples, 1.0),
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "kind": E2E_WARM, "cold": cold},
             "gpu_launches": int(n_launches * args.steps),
             "roofline": {"bound": "hbm", "kernel": dom + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(dom)[0],
@@ -468,6 +546,10 @@ def run_gpu(args):
                          "kernel_ms_per_step": shares},
             "clocks": clocks,
         }
+        if image_check is not None:
+            line["image_check"] = image_check
+        if multi_call is not None:
+            line["multi_call"] = multi_call
         if others:
             line["other_configs"] = others
             line["other_configs_clocks"] = others_clocks

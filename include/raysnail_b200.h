@@ -253,6 +253,15 @@ const char* rs_last_error(const rs_ctx* ctx);
  * trees are searched by walking the object list (every lane of a warp tests the same object at the same time)
  * instead of the tree; 0 = always the tree.  Identical hits either way.  Set before rs_upload_scene. */
 #define RS_OPT_LIST_MAX 3
+/* RS_OPT_WAIT_BUDGET_MS: n >= 0 (default 600000 = 10 min) = how long the wait kernels of rs_wait_counter and
+ * rs_multi_render poll for their peers before they give up; 0 = for ever.  A peer whose host failed between two
+ * launches never signals: with a budget, rs_multi_render then returns an error, re-bases its counters and the next
+ * call works again; a wait queued by rs_wait_counter raises a flag of its context and lets the stream go on (what was
+ * queued behind it then runs on incomplete data): ask rs_wait_check.  Choose it well above the longest frame a device renders. */
+#define RS_OPT_WAIT_BUDGET_MS 4
+/* RS_OPT_INJECT_FAULT (rs_multi_set_option only; for tests): the next rs_multi_render fails on purpose on its last
+ * device — 1 = before anything is signalled, 2 = between its two signals — to exercise the recovery path. */
+#define RS_OPT_INJECT_FAULT 100
 int rs_set_option(rs_ctx* ctx, int option, int value);
 
 /* ---- scene: replaces `World::new` (world.rs:40-53) + `BVH::new` (bvh.rs:47-112) -----------*/
@@ -388,6 +397,11 @@ int rs_multi_render(rs_multi* m, const rs_camera* cam, const rs_render_params* p
  * rs_wait_counter: work queued on `stream` after this call starts once counter >= expect (wrap-safe). */
 int rs_signal(rs_ctx* ctx, uint32_t* d_counter, void* stream);
 int rs_wait_counter(rs_ctx* ctx, const uint32_t* d_counter, uint32_t expect, void* stream);
+/* Synchronises `stream` and reports whether a wait queued by rs_wait_counter on this context has given up since the last
+ * check (RS_OPT_WAIT_BUDGET_MS): RS_OK = every wait was satisfied; RS_ERR_CUDA = a peer never signalled and the frame
+ * behind that wait is not valid (rs_last_error says so).  Clears the flag.  The multi-process caller's counterpart of the
+ * check rs_multi_render makes by itself. */
+int rs_wait_check(rs_ctx* ctx, void* stream);
 
 /* ---- the redo-map step without any allocation -------------------------------------------------------
  * No counterpart in the reference (its passes loop works on host Vecs, src/bin/raysnail.rs:404-423); this

@@ -27,7 +27,7 @@ CORE_SYMBOLS = [
     "rs_device_alloc", "rs_device_free", "rs_ipc_export", "rs_ipc_open", "rs_ipc_close", "rs_finalize_peers",
     "rs_render_passes", "rs_pass_seed", "rs_philox4x32_10", "rs_philox_uniform",
     "rs_create_multi", "rs_destroy_multi", "rs_multi_last_error", "rs_multi_device_count", "rs_multi_set_option",
-    "rs_multi_upload_scene", "rs_multi_render", "rs_signal", "rs_wait_counter", "rs_redo_map_static",
+    "rs_multi_upload_scene", "rs_multi_render", "rs_signal", "rs_wait_counter", "rs_wait_check", "rs_redo_map_static",
 ]
 # every symbol include/raysnail_b200_host.h declares
 HOST_SYMBOLS = [
@@ -157,6 +157,7 @@ def load() -> C.CDLL:
     proto("rs_multi_render", C.c_int, vp, P(RsCamera), P(RsRenderParams), vp, vp, P(RsStats))
     proto("rs_signal", C.c_int, vp, vp, vp)
     proto("rs_wait_counter", C.c_int, vp, vp, C.c_uint32, vp)
+    proto("rs_wait_check", C.c_int, vp, vp)
     proto("rs_philox4x32_10", C.c_int, vp, vp, vp)
     proto("rs_philox_uniform", C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp)
 

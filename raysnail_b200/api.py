@@ -307,8 +307,12 @@ class Renderer:
             self.upload(self._scene)
 
     def set_wave_streams(self, n: int):
-        """RS_OPT_WAVE_STREAMS: 2 = consecutive waves overlap on two streams (default), 1 = one stream."""
+        """RS_OPT_WAVE_STREAMS: n in 1..4 (default 4) = consecutive waves rotate over n streams, 1 = one stream."""
         self._ck(self._lib.rs_set_option(self._ctx, 2, int(n)), "rs_set_option")
+
+    def set_wait_budget_ms(self, ms: int):
+        """RS_OPT_WAIT_BUDGET_MS: how long rs_wait_counter's kernel polls before it gives up (0 = for ever; default 10 min)."""
+        self._ck(self._lib.rs_set_option(self._ctx, 4, int(ms)), "rs_set_option")
 
     def upload(self, scene: Scene):
         self._ck(self._lib.rs_upload_scene(self._ctx, scene.desc), "rs_upload_scene")
@@ -371,6 +375,10 @@ class Renderer:
     def wait_counter(self, d_counter: int, expect: int, stream: int = 0):
         """rs_wait_counter: work queued on `stream` after this starts once the counter has reached `expect`."""
         self._ck(self._lib.rs_wait_counter(self._ctx, int(d_counter), int(expect) & 0xffffffff, stream), "rs_wait_counter")
+
+    def wait_check(self, stream: int = 0):
+        """rs_wait_check: synchronise `stream`; raises if a wait of this context gave up (a peer never signalled)."""
+        self._ck(self._lib.rs_wait_check(self._ctx, stream), "rs_wait_check")
 
     def render_passes(self, cam: RsCamera, params: RsRenderParams, n_passes: int, redo_mode: int = 0, threshold: float = 0.01,
                       want_rgb8: bool = False):

@@ -122,8 +122,10 @@ struct rs_ctx {
     static constexpr int kMaxSets = 4;
     WaveSet wset[kMaxSets];
     DevBuf d_stats;
+    DevBuf d_wait_flag;  // one uint32, zeroed at rs_create: raised by a wait kernel of rs_wait_counter that ran out of budget (rs_wait_check)
     uint32_t capacity = 0;
     WaveState ws{}, ws_aux[kMaxSets - 1] = {};
+    int wait_budget_ms = 600000;  // RS_OPT_WAIT_BUDGET_MS: how long a wait kernel polls before it gives up (0 = for ever)
     int wave_streams = 4;  // (r02: 2 -> 4 streams and 8 M -> 32 M paths per wave: the tail of every launch — a few very long rays —
                            //  overlaps the next wave's kernels; +33 % on the 1 M-triangle mesh, +6 % on the headline scene)
     cudaStream_t aux_stream[kMaxSets - 1] = {};
@@ -418,6 +420,10 @@ int leaf_ref(const rs_ctx* ctx, int root) {
 
 int upload_bvh(rs_ctx* ctx, double omax) {
     const double k = 1.0 / 2097152.0;  // 2^-21
+    // a kept device tree may be padded for a larger origin than this call asks for; padded_omax below reports THAT value,
+    // so the object list has to be padded for it too (otherwise a camera between the two values would find the list boxes
+    // too tight and prepare_camera, trusting padded_omax, would not re-pad them)
+    if (ctx->tree_dev_valid && ctx->tree_dev_omax >= omax) omax = ctx->tree_dev_omax;
     {
         // small worlds: the object list the kernels walk instead of a tree (same outward padding as the node boxes)
         std::vector<float4> list;
@@ -791,19 +797,54 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
     const uint32_t s_total = (uint32_t)(p->stratum_row_end - p->stratum_row_begin) * (uint32_t)p->sqrt_spp;
     ctx->stats = rs_stats{};
     ctx->stats_final = false;
-    if (s_total == 0 || np == 0) return RS_OK;
+    if (s_total == 0 || np == 0) {  // nothing to render (a device beyond the strata rows): the zeroed counters above ARE the result;
+        ctx->stats_final = true;    // the device-side ones hold an earlier frame's values, or do not exist yet on a fresh context
+        return RS_OK;
+    }
     // default: 64 Mi paths per wave (272 B of wave state per path: 18 GB per wave set, 73 of the 180 GB for the four sets).
     // 32 -> 64 Mi: +0.9 % on the headline scene, +4.6 % on the 1 M-triangle mesh; 128 Mi another +0.4 / +1.5 % for twice
     // the memory (profiles/r02h_ab_wave.txt, r02h_ab_wave2.txt)
     uint32_t cap = p->max_wave_paths > 0 ? (uint32_t)p->max_wave_paths : (1u << 26);
     cap = std::max(cap, 1024u);
-    const uint32_t P = std::min(np, cap);
-    const uint32_t K = std::max(1u, std::min(s_total, cap / P));
-    const uint32_t n_waves = ((np + P - 1) / P) * ((s_total + K - 1) / K);
-    // kernel timing needs the kernels back to back on one stream
-    const int n_sets = timing ? 1 : (int)std::min<uint32_t>((uint32_t)ctx->wave_streams, n_waves);
+    uint32_t P, K, n_waves;
+    int n_sets;
+    auto partition = [&] {
+        P = std::min(np, cap);
+        K = std::max(1u, std::min(s_total, cap / P));
+        n_waves = ((np + P - 1) / P) * ((s_total + K - 1) / K);
+        // kernel timing needs the kernels back to back on one stream
+        n_sets = timing ? 1 : (int)std::min<uint32_t>((uint32_t)ctx->wave_streams, n_waves);
+    };
+    partition();
+    if (p->max_wave_paths <= 0) {
+        // The default is sized for an otherwise empty 180 GB card.  Where less is free — a smaller device, several contexts
+        // or ranks on one GPU, a host application with its own buffers — halve the wave until the sets that still have to
+        // grow fit into 80 % of what is free now (the image does not depend on the wave size beyond the rounding of the
+        // per-wave sums); 1 Mi paths (1.1 GB for four sets) is the floor, below it the allocation may simply fail.
+        constexpr size_t kBytesPerPath = 272;
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+            auto missing = [&] {
+                size_t need = 0;
+                for (int k = 0; k < n_sets; ++k)
+                    if (ctx->wset[k].capacity < P * K) need += (size_t)P * K * kBytesPerPath;
+                return need;
+            };
+            while (cap > (1u << 20) && missing() > free_b / 5 * 4) {
+                cap >>= 1;
+                partition();
+            }
+        } else {
+            cudaGetLastError();
+        }
+    }
     int rc = ensure_wave(ctx, P * K, n_sets);
-    if (rc != RS_OK) return rc;
+    if (rc != RS_OK) {
+        if (ctx->error.find("out of memory") != std::string::npos)
+            return fail(ctx, RS_ERR_OUT_OF_MEMORY, "wave buffers (" + std::to_string(n_sets) + " sets of " + std::to_string((uint64_t)P * K) +
+                                                       " paths, 272 B each) do not fit: lower rs_render_params.max_wave_paths or RS_OPT_WAVE_STREAMS");
+        return rc;
+    }
     rc = prepare_camera(ctx, cam);
     if (rc != RS_OK) return rc;
     FrameParams fp = make_frame(cam, p);
@@ -929,6 +970,7 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
 }
 
 int fetch_device_stats(rs_ctx* ctx, cudaStream_t stream) {
+    if (ctx->stats_final) return RS_OK;  // an empty render: nothing was counted on the device
     DeviceStats ds;
     CK(cudaMemcpyAsync(&ds, ctx->ws.stats, sizeof(ds), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
@@ -986,6 +1028,12 @@ int rs_create(rs_ctx** out, int device) {
     ctx->sm_count = prop.multiProcessorCount;
     ctx->extend_grid = ctx->sm_count * extend_blocks_per_sm(3, 0, 0);
     ctx->shade_grid = ctx->sm_count * shade_blocks_per_sm(2, 0);
+    // allocated here, not at the first rs_wait_counter: by then peers may already be spinning, and cudaMalloc can wait for them
+    if (ctx->d_wait_flag.ensure(256) != cudaSuccess || cudaMemset(ctx->d_wait_flag.p, 0, 256) != cudaSuccess) {
+        const std::string why = std::string("rs_create: ") + cudaGetErrorString(cudaGetLastError());
+        delete ctx;
+        return fail(nullptr, RS_ERR_CUDA, why);
+    }
     *out = ctx;
     return RS_OK;
 }
@@ -1020,6 +1068,10 @@ int rs_set_option(rs_ctx* ctx, int option, int value) {
     }
     if (option == RS_OPT_WAVE_STREAMS && value >= 1 && value <= rs_ctx::kMaxSets) {
         ctx->wave_streams = value;
+        return RS_OK;
+    }
+    if (option == RS_OPT_WAIT_BUDGET_MS && value >= 0) {
+        ctx->wait_budget_ms = value;
         return RS_OK;
     }
     return fail(ctx, RS_ERR_INVALID_ARGUMENT, "unknown option or value");
@@ -1210,7 +1262,7 @@ int rs_upload_scene(rs_ctx* ctx, const rs_scene_desc* s) {
     }
     stage("root tables");
     // small worlds are searched as one list (RS_OPT_LIST_MAX); otherwise only the loose objects are
-    if (const char* e = std::getenv("RAYSNAIL_B200_LIST_MAX")) { ctx->list_max = std::atoi(e); ctx->list_max_set = true; }
+    if (const char* e = std::getenv("RAYSNAIL_B200_LIST_MAX")) { ctx->list_max = std::min(std::max(std::atoi(e), 0), 64); ctx->list_max_set = true; }  // same range as RS_OPT_LIST_MAX
     bool flat_or_tree = !loose.empty(), any_generic = false;
     for (const BuildPrim& p : prims) {
         flat_or_tree |= root_kind[p.root] == ROOT_FLAT || root_kind[p.root] == ROOT_GENERIC;
@@ -1845,8 +1897,9 @@ struct rs_multi {
     std::vector<int> device;
     std::vector<cudaStream_t> stream;
     std::vector<DevBuf> accum, mask;
-    DevBuf out0, counters;  // device 0: the image; [0] = accumulators complete, [1] = slices written
-    uint32_t epoch = 0;
+    DevBuf out0, counters;  // device 0: the image; [0] = accumulators complete, [1] = slices written, [2] = a wait kernel gave up
+    uint32_t epoch = 0;     // frames completed since the counters were last zeroed: the counters stand at n * epoch between calls
+    int inject_fault = 0;   // RS_OPT_INJECT_FAULT (tests): 1 = the last device fails in phase 1, 2 = between its two signals; one shot
     std::string error;
 };
 
@@ -1868,6 +1921,19 @@ int for_each_device(rs_multi* m, F f) {
     for (int k = 0; k < n; ++k)
         if (rc[k] != RS_OK) return multi_fail(m, rc[k], "device " + std::to_string(m->device[k]) + ": " + rs_last_error(m->ctx[k]));
     return RS_OK;
+}
+// After a frame that failed part-way: some devices may have signalled and others not, so the counters no longer
+// stand at n * epoch and the next frame's waits would never be satisfied.  Let every stream drain (wait kernels give
+// up after the budget), then start counting from zero again.  Keeps m->error (the reason of the failure).
+void multi_rebase(rs_multi* m) {
+    for (size_t k = 0; k < m->ctx.size(); ++k) {
+        cudaSetDevice(m->device[k]);
+        if (m->stream[k]) cudaStreamSynchronize(m->stream[k]);
+        cudaGetLastError();
+    }
+    cudaSetDevice(m->device[0]);
+    if (m->counters.p) cudaMemset(m->counters.p, 0, 4 * sizeof(uint32_t));
+    m->epoch = 0;
 }
 }  // namespace
 
@@ -1929,7 +1995,7 @@ int rs_create_multi(rs_multi** out, const int32_t* device_ids, int32_t n) {
         }
     }
     cudaSetDevice(m->device[0]);
-    if (m->counters.ensure(2 * sizeof(uint32_t)) != cudaSuccess || cudaMemset(m->counters.p, 0, 2 * sizeof(uint32_t)) != cudaSuccess) {
+    if (m->counters.ensure(4 * sizeof(uint32_t)) != cudaSuccess || cudaMemset(m->counters.p, 0, 4 * sizeof(uint32_t)) != cudaSuccess) {
         rs_destroy_multi(m);
         return multi_fail(nullptr, RS_ERR_CUDA, "counter allocation failed");
     }
@@ -1959,6 +2025,11 @@ int rs_multi_device_count(const rs_multi* m) { return m ? (int)m->ctx.size() : 0
 
 int rs_multi_set_option(rs_multi* m, int option, int value) {
     if (!m) return RS_ERR_INVALID_ARGUMENT;
+    if (option == RS_OPT_INJECT_FAULT) {
+        if (value < 0 || value > 2) return multi_fail(m, RS_ERR_INVALID_ARGUMENT, "RS_OPT_INJECT_FAULT: 0, 1 or 2");
+        m->inject_fault = value;
+        return RS_OK;
+    }
     for (size_t k = 0; k < m->ctx.size(); ++k) {
         if (option == RS_OPT_WAVE_STREAMS) {  // contexts that share a device keep their single stream (rs_create_multi)
             int same = 0;
@@ -1995,9 +2066,15 @@ int rs_multi_render(rs_multi* m, const rs_camera* cam, const rs_render_params* p
     }
     cudaSetDevice(m->device[0]);
     if (m->out0.ensure(np * sizeof(float4)) != cudaSuccess) return multi_fail(m, RS_ERR_OUT_OF_MEMORY, "image allocation failed");
-    const uint32_t expect = (uint32_t)n * ++m->epoch;
+    // the counters stand at n * epoch; this frame brings them to n * (epoch + 1).  epoch itself moves only once the frame
+    // is through: a frame that fails part-way re-bases the counters (multi_rebase) instead of leaving them short
+    const uint32_t expect = (uint32_t)n * (m->epoch + 1);
     uint32_t* const arrived = m->counters.as<uint32_t>();
     uint32_t* const written = arrived + 1;
+    uint32_t* const gave_up = arrived + 2;
+    const unsigned long long budget_ns = (unsigned long long)m->ctx[0]->wait_budget_ms * 1000000ull;
+    const int fault = m->inject_fault;
+    m->inject_fault = 0;
     PeerAccums pa;
     std::memset(&pa, 0, sizeof(pa));
     pa.n = n;
@@ -2020,9 +2097,13 @@ int rs_multi_render(rs_multi* m, const rs_camera* cam, const rs_render_params* p
         pk.stratum_row_begin = rows0 + (int)(((int64_t)rows * k) / n);
         pk.stratum_row_end = rows0 + (int)(((int64_t)rows * (k + 1)) / n);
         pk.flags &= ~RS_FLAG_KERNEL_TIMING;
+        if (fault == 1 && k == n - 1) return fail(ctx, RS_ERR_CUDA, "injected fault in phase 1 (RS_OPT_INJECT_FAULT)");
         return render_into(ctx, cam, &pk, d_mask, m->accum[k].as<float4>(), st, false);
     });
-    if (rc != RS_OK) return rc;
+    if (rc != RS_OK) {  // nobody has signalled yet: drain the renders that were queued and leave the counters where they were
+        multi_rebase(m);
+        return rc;
+    }
     // Phase 2, every device: arrive, wait for all accumulators, reduce + finalize this device's slice of the pixels
     // into device 0's image, arrive again; device 0 waits for all slices and copies the image out.
     rc = for_each_device(m, [&](int k) -> int {
@@ -2031,20 +2112,31 @@ int rs_multi_render(rs_multi* m, const rs_camera* cam, const rs_render_params* p
         CK(cudaSetDevice(m->device[k]));
         const unsigned char* d_mask = pixel_mask ? m->mask[k].as<unsigned char>() : nullptr;
         launch_signal(arrived, st);
-        launch_wait_counter(arrived, expect, st);
+        launch_wait_counter(arrived, expect, st, budget_ns, gave_up);
+        if (fault == 2 && k == n - 1) return fail(ctx, RS_ERR_CUDA, "injected fault between the two signals (RS_OPT_INJECT_FAULT)");
         const int64_t per = ((((int64_t)np + n - 1) / n) + 15) / 16 * 16;
         const int64_t b = std::min<int64_t>((int64_t)np, k * per), e = std::min<int64_t>((int64_t)np, (k + 1) * per);
         launch_finalize_peers(pa, d_mask, m->out0.as<float4>(), b, e, n_total, p->gamma, st);
         launch_signal(written, st);
         CK(cudaGetLastError());
         if (k == 0) {
-            launch_wait_counter(written, expect, st);
+            launch_wait_counter(written, expect, st, budget_ns, gave_up);
             CK(cudaMemcpyAsync(out_rgba, m->out0.p, np * sizeof(float4), cudaMemcpyDeviceToHost, st));
         }
         CK(cudaStreamSynchronize(st));
         return fetch_device_stats(ctx, st);
     });
-    if (rc != RS_OK) return rc;
+    if (rc == RS_OK) {  // every stream has drained: did a wait kernel run out of patience?
+        uint32_t flag = 0;
+        cudaSetDevice(m->device[0]);
+        if (cudaMemcpy(&flag, gave_up, sizeof(flag), cudaMemcpyDeviceToHost) != cudaSuccess) rc = multi_fail(m, RS_ERR_CUDA, "reading the wait flag failed");
+        else if (flag) rc = multi_fail(m, RS_ERR_CUDA, "a device waited longer than RS_OPT_WAIT_BUDGET_MS for its peers");
+    }
+    if (rc != RS_OK) {
+        multi_rebase(m);
+        return rc;
+    }
+    ++m->epoch;
     if (stats_sum) {
         *stats_sum = rs_stats{};
         for (int k = 0; k < n; ++k) {
@@ -2070,9 +2162,20 @@ int rs_signal(rs_ctx* ctx, uint32_t* d_counter, void* stream) {
 int rs_wait_counter(rs_ctx* ctx, const uint32_t* d_counter, uint32_t expect, void* stream) {
     if (!ctx || !d_counter) return fail(ctx, RS_ERR_INVALID_ARGUMENT, "null counter");
     CK(cudaSetDevice(ctx->device));
-    launch_wait_counter(d_counter, expect, (cudaStream_t)stream);
+    launch_wait_counter(d_counter, expect, (cudaStream_t)stream, (unsigned long long)ctx->wait_budget_ms * 1000000ull, ctx->d_wait_flag.as<uint32_t>());
     CK(cudaGetLastError());
     return RS_OK;
+}
+int rs_wait_check(rs_ctx* ctx, void* stream) {
+    if (!ctx) return RS_ERR_INVALID_ARGUMENT;
+    CK(cudaSetDevice(ctx->device));
+    uint32_t flag = 0;
+    CK(cudaMemcpyAsync(&flag, ctx->d_wait_flag.p, sizeof(flag), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CK(cudaStreamSynchronize((cudaStream_t)stream));
+    if (!flag) return RS_OK;
+    CK(cudaMemsetAsync(ctx->d_wait_flag.p, 0, sizeof(flag), (cudaStream_t)stream));
+    return fail(ctx, RS_ERR_CUDA, "a wait kernel gave up after RS_OPT_WAIT_BUDGET_MS = " + std::to_string(ctx->wait_budget_ms) +
+                                      " ms: a peer never signalled; what was queued behind that wait ran on incomplete data");
 }
 
 int rs_get_stats(const rs_ctx* ctx, rs_stats* out) {

@@ -1989,12 +1989,25 @@ __global__ void signal_kernel(uint32_t* counter) {
 // the stream then see what the signalling devices wrote.  (The poll sits in its own one-warp kernel rather than
 // at the top of the reduce kernel: a whole grid of spinning blocks could keep co-resident work — another
 // context's render on the same device — from ever running.)
-__global__ void wait_counter_kernel(const uint32_t* counter, uint32_t expect) {
+// budget_ns > 0 bounds the poll (RS_OPT_WAIT_BUDGET_MS): a peer that never signals — its host failed between two
+// launches — must not hang this device for good.  When the budget runs out the kernel raises *gave_up and ends; the
+// kernels queued behind it then run on incomplete data, and the host, which checks the flag once the stream has
+// drained (rs_multi_render, rs_wait_check), reports the frame as failed.
+__global__ void wait_counter_kernel(const uint32_t* counter, uint32_t expect, unsigned long long budget_ns, uint32_t* gave_up) {
     if (threadIdx.x == 0) {
         uint32_t v;
+        unsigned long long t0 = 0, now;
+        if (budget_ns) asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t0));
         while (true) {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(counter) : "memory");
             if ((int32_t)(v - expect) >= 0) break;
+            if (budget_ns) {
+                asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(now));
+                if (now - t0 > budget_ns) {
+                    if (gave_up) asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(gave_up), "r"(1u) : "memory");
+                    break;
+                }
+            }
             __nanosleep(500);
         }
     }
@@ -2191,7 +2204,9 @@ unsigned long long read_violations() {
 }
 
 void launch_signal(uint32_t* counter, cudaStream_t s) { signal_kernel<<<1, 1, 0, s>>>(counter); }
-void launch_wait_counter(const uint32_t* counter, uint32_t expect, cudaStream_t s) { wait_counter_kernel<<<1, 32, 0, s>>>(counter, expect); }
+void launch_wait_counter(const uint32_t* counter, uint32_t expect, cudaStream_t s, unsigned long long budget_ns, uint32_t* gave_up) {
+    wait_counter_kernel<<<1, 32, 0, s>>>(counter, expect, budget_ns, gave_up);
+}
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s) {
     combine_kernel<<<grid_for(n), RS_BLOCK, 0, s>>>(old_px, new_px, out, n, pass);
 }

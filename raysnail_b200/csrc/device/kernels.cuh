@@ -125,7 +125,8 @@ void launch_finalize_peers(const PeerAccums& peers, const unsigned char* mask, f
                            cudaStream_t s);
 unsigned long long read_violations();  // RS_CHECKED builds: failed bounds checks since the last call (0 otherwise)
 void launch_signal(uint32_t* counter, cudaStream_t s);
-void launch_wait_counter(const uint32_t* counter, uint32_t expect, cudaStream_t s);
+// budget_ns: 0 = poll without limit; otherwise give up after that long and set *gave_up
+void launch_wait_counter(const uint32_t* counter, uint32_t expect, cudaStream_t s, unsigned long long budget_ns = 0, uint32_t* gave_up = nullptr);
 void launch_combine(const float4* old_px, const float4* new_px, float4* out, int64_t n, float pass, cudaStream_t s);
 void launch_noise(const float4* px, float* noise, int w, int h, int quirk, cudaStream_t s);
 void launch_quantize(const float4* px, unsigned char* rgb, int64_t n, cudaStream_t s);

@@ -90,19 +90,29 @@ class PeerImage:
         rank's pixel slice into rank 0's image -> signal(written) -> wait(written == world), so work queued
         afterwards sees the complete image (rank 0) and may reuse the accumulator (every rank).  The ranks order
         themselves on the devices; there is no host barrier (the two of round 1 are gone)."""
-        self.epoch += 1
-        expect = self.world * self.epoch
+        # the counters stand at world * epoch; epoch moves only after BOTH signals of this rank are queued, so a call that
+        # raises before its first signal leaves the count intact (a failure between the two signals cannot be repaired
+        # from one process: the peers' waits then end through RS_OPT_WAIT_BUDGET_MS, loudly, instead of spinning for ever)
+        expect = self.world * (self.epoch + 1)
         arrived, written = self.counters_on_rank0, self.counters_on_rank0 + 4
         self.r.signal(arrived, stream)
         self.r.wait_counter(arrived, expect, stream)
         b, e = pixel_slice(self.rank, self.world, self.n_pixels)
         self.r.finalize_peers(self.peer_accums, d_mask, self.out_on_rank0, b, e, n_samples, gamma, stream)
         self.r.signal(written, stream)
+        self.epoch += 1
         # every rank: nobody reads this rank's accumulator any more (it may be cleared for the next frame), and
         # on rank 0 the image is complete
         self.r.wait_counter(written, expect, stream)
 
     def close(self):
+        # rank 0 owns the counters and the image the other ranks' kernels poll and write: nobody frees anything before
+        # every rank has drained its stream and said so
+        import torch
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        if dist.is_initialized() and self.world > 1:
+            dist.barrier()
         for p in self._opened:
             self.r.ipc_close(p)
         self._opened = []

@@ -69,6 +69,8 @@ pub const RS_RNG_MEDIUM: u32 = 6;
 pub const RS_OPT_BVH_WIDTH: c_int = 1;
 pub const RS_OPT_WAVE_STREAMS: c_int = 2;
 pub const RS_OPT_LIST_MAX: c_int = 3;
+pub const RS_OPT_WAIT_BUDGET_MS: c_int = 4;
+pub const RS_OPT_INJECT_FAULT: c_int = 100;
 pub const RS_IPC_HANDLE_BYTES: usize = 64;
 pub const RS_MAX_PEERS: usize = 16;
 pub const RS_STATIC_MAX_PIXELS: usize = 4194304;
@@ -254,6 +256,7 @@ extern "C" {
     pub fn rs_multi_render(m: *mut rs_multi, cam: *const rs_camera, params: *const rs_render_params, pixel_mask: *const u8, out_rgba: *mut f32, stats_sum: *mut rs_stats) -> c_int;
     pub fn rs_signal(ctx: *mut rs_ctx, d_counter: *mut u32, stream: *mut c_void) -> c_int;
     pub fn rs_wait_counter(ctx: *mut rs_ctx, d_counter: *const u32, expect: u32, stream: *mut c_void) -> c_int;
+    pub fn rs_wait_check(ctx: *mut rs_ctx, stream: *mut c_void) -> c_int;
 }
 
 /// Compares `size_of` of every `#[repr(C)]` struct with what the loaded library was compiled

@@ -265,6 +265,10 @@ def test_device_alloc_and_ipc_export(renderer):
     ("rtow_final", (1920, 1080), 2),   # BASELINE.json config 2 frame (headline), one 8.29 M-path wave
     ("cornell", (3840, 2160), 1),      # config 5 frame
     ("mesh_blinn", (2048, 2048), 1),   # config 4 frame (the fixture mesh, not the 1 M-triangle one)
+    ("example", (800, 500), 2),        # config 1 frame (sdl/example.sdl)
+    ("quadric", (1920, 1080), 6),      # config 3a frame: 74.6 M paths = two default waves (64 Mi) on two streams, skip-ahead list walk
+    ("csg", (1920, 1080), 2),          # config 3b frame
+    ("declares", (1920, 1080), 1),     # sdl/declares.sdl at the C3 frame
 ])
 def test_full_size_frames_on_sampled_pixels(renderer, name, size, sqrt_spp):
     """BASELINE.json's frame sizes are far too big for the CPU oracle, so the full frame is checked

@@ -409,6 +409,85 @@ def test_rs_multi_render_equals_the_one_device_image(renderer, devices):
         m.close()
 
 
+def test_rs_multi_render_recovers_after_a_failed_frame(renderer):
+    """A frame that fails part-way (here: on purpose, RS_OPT_INJECT_FAULT) leaves some devices' arrival signals out.
+    The call has to come back with an error — the peers' wait kernels give up after RS_OPT_WAIT_BUDGET_MS instead of
+    spinning for ever — and re-base its counters, so that the NEXT frame is complete and correct again.  Two contexts
+    on device 0, so that a one-GPU box runs it."""
+    from raysnail_b200 import MultiRenderer, RaysnailError
+    RS_OPT_WAIT_BUDGET_MS, RS_OPT_INJECT_FAULT = 4, 100
+    scene = load_scene("cornell")
+    cam = scene.camera(96, 72)
+    params = make_params(sqrt_spp=4, depth=6)
+    renderer.upload(scene)
+    ref = renderer.render(cam, params)
+    m = MultiRenderer((0, 0))
+    try:
+        m.upload(scene)
+        m.set_option(RS_OPT_WAIT_BUDGET_MS, 1500)
+        np.testing.assert_allclose(m.render(cam, params), ref, rtol=2e-6, atol=1e-7)
+        for fault in (1, 2, 2, 1):  # 1 = before anything is signalled, 2 = between the two signals of one device
+            m.set_option(RS_OPT_INJECT_FAULT, fault)
+            with pytest.raises(RaysnailError, match="injected fault"):
+                m.render(cam, params)
+            for _ in range(2):
+                np.testing.assert_allclose(m.render(cam, params), ref, rtol=2e-6, atol=1e-7)
+                assert m.stats.n_samples == 96 * 72 * 16
+    finally:
+        m.close()
+
+
+def test_rs_multi_first_frame_with_more_devices_than_strata_rows(renderer):
+    """sqrt_spp = 1 on two FRESH contexts: the second one has no strata row, never sets up its wave state, and its
+    counters must read zero (not fail, not repeat an earlier frame's)."""
+    from raysnail_b200 import MultiRenderer
+    scene = load_scene("cornell")
+    cam = scene.camera(80, 60)
+    p1 = make_params(sqrt_spp=1, depth=4)
+    renderer.upload(scene)
+    ref = renderer.render(cam, p1)
+    m = MultiRenderer((0, 0))
+    try:
+        m.upload(scene)
+        np.testing.assert_allclose(m.render(cam, p1), ref, rtol=2e-6, atol=1e-7)
+        assert m.stats.n_samples == 80 * 60
+        p4 = make_params(sqrt_spp=4, depth=4)
+        m.render(cam, p4)
+        assert m.stats.n_samples == 80 * 60 * 16
+        m.render(cam, p1)  # after a full frame: the idle context must not report that frame's counters again
+        assert m.stats.n_samples == 80 * 60
+    finally:
+        m.close()
+
+
+def test_a_wait_without_a_signal_ends_after_its_budget():
+    """rs_wait_counter on a counter nobody signals: with RS_OPT_WAIT_BUDGET_MS the kernel stops polling, the stream
+    drains, and rs_wait_check reports it (once); a satisfied wait reports nothing."""
+    import time
+    import torch
+    from raysnail_b200 import RaysnailError, Renderer
+    r = Renderer(0)
+    try:
+        r.set_wait_budget_ms(300)
+        c = r.device_alloc(256)
+        r.signal(c)
+        r.wait_counter(c, 1)
+        r.wait_check()  # satisfied
+        t0 = time.time()
+        r.wait_counter(c, 2)  # nobody will bring the counter to 2
+        with pytest.raises(RaysnailError, match="gave up"):
+            r.wait_check()
+        assert 0.25 < time.time() - t0 < 30.0
+        r.wait_check()  # the flag was cleared
+        r.signal(c)
+        r.wait_counter(c, 2)
+        r.wait_check()
+        torch.cuda.synchronize()
+        r.device_free(c)
+    finally:
+        r.close()
+
+
 def test_reuploads_keep_or_rebuild_the_tree_correctly():
     """rs_upload_scene keeps the SAH tree (and its device copy) while the objects' bounds and ids are unchanged.
     One context sees: scene A, A again (tree kept), A with a sphere moved (same count: must rebuild), a scene with
