@@ -463,6 +463,7 @@ def run_gpu(args):
     image_check, multi_call = None, None
     if world_size > 1:
         cpu_group = dist.new_group(backend="gloo")  # the idle ranks wait on the host: an NCCL barrier would spin on their GPUs
+        renderer.upload(scene)  # (the other configs above left their own scene in the context)
         step(params)
         barrier()
         if rank == 0:
@@ -493,9 +494,14 @@ def run_gpu(args):
                     for _ in range(m_steps):
                         mr.render_to_ptr(cam, p_all, None, host_img.data_ptr())
                     dt = (time.perf_counter() - t0) / m_steps
-                    same = bool(torch.allclose(host_img, sharded.cpu(), rtol=2e-5, atol=2e-6))
+                    got, want = host_img.clone(), sharded.cpu()
+                    same = bool(torch.allclose(got, want, rtol=2e-5, atol=2e-6))
+                    d = (got - want).abs()
+                    bad = d > (2e-6 + 2e-5 * want.abs())
+                    diag = {"max_abs_diff": float(d.max().item()), "pixels_off": int(bad.any(dim=-1).sum().item()), "nan": int(torch.isnan(got).sum().item()),
+                            "first_off": [int(v) for v in bad.any(dim=-1).nonzero()[0].tolist()] if bool(bad.any()) else None}
                     multi_call = {"call": "rs_multi_render (one process, one host thread per device, host image out)", "value": total_samples_per_step / dt,
-                                  "unit": UNIT, "ms_per_step": dt * 1e3, "steps": m_steps, "devices": world_size, "image_equals_torchrun_image": same,
+                                  "unit": UNIT, "ms_per_step": dt * 1e3, "steps": m_steps, "devices": world_size, "image_equals_torchrun_image": same, "image_diff": diag,
                                   "timing": "host wall clock around the call (it returns after the image is in host memory)"}
                 finally:
                     mr.close()

@@ -576,7 +576,20 @@ int tree_depth(const rs_scene_desc* s, int ni) {
         case RS_NODE_INTERSECTION: return 1 + std::max(tree_depth(s, n.child0), tree_depth(s, n.child1));
         case RS_NODE_TRANSFORM:
         case RS_NODE_MEDIUM: return 1 + tree_depth(s, n.child0);
-        case RS_NODE_BVH: return 1 + std::max(n.child0 >= 0 ? tree_depth(s, n.child0) : 0, n.child1 >= 0 ? tree_depth(s, n.child1) : 0);
+        case RS_NODE_BVH: {  // one level for the whole BVH object, however deep its own tree is (ProgramBuilder::emit keeps one running result)
+            int d = 0;
+            std::vector<int> st{ni};
+            while (!st.empty()) {
+                const rs_node& b = s->nodes[st.back()];
+                st.pop_back();
+                for (int c : {b.child0, b.child1}) {
+                    if (c < 0) continue;
+                    if (s->nodes[c].type == RS_NODE_BVH) st.push_back(c);
+                    else d = std::max(d, tree_depth(s, c));
+                }
+            }
+            return 1 + d;
+        }
         default: return 1;
     }
 }
@@ -672,16 +685,43 @@ struct ProgramBuilder {
                 return d0;
             }
             case RS_NODE_BVH: {  // bvh.rs:173-192
+                // "The closer of my two children" is associative, and ties go to the left child, so a BVH object returns the
+                // closest of its members with ties to the first one in left-to-right order — whatever the shape of the tree.
+                // The program therefore keeps ONE running result for the whole BVH object instead of one operand per level
+                // (a balanced tree over the 400 boxes of the reference's all_feature scene, examples/common/scene.rs:361,
+                // would need 10 operands that way):
+                //     BVH_BEGIN top        bbox gate of the object; on a miss: push a miss, jump to the end
+                //     MISS                 the running result
+                //     BVH_GATE inner ...   bbox gate of an inner node: on a miss skip its subtree (nothing is pushed)
+                //     <member> BVH_END     the member's own program, then: keep the closer of (running result, member)
+                // Every gate the reference applies is still applied, in the reference's order.
                 const size_t begin = prog.size();
                 prog.push_back(ObjInstr{OP_BVH_BEGIN, ni, cur, 0});
-                int d0 = 1, d1 = 1;
-                if (n.child0 >= 0) d0 = emit(n.child0, cur, in_medium);
-                else prog.push_back(ObjInstr{OP_MISS, ni, cur, 0});
-                if (n.child1 >= 0) d1 = emit(n.child1, cur, in_medium);
-                else prog.push_back(ObjInstr{OP_MISS, ni, cur, 0});
-                prog.push_back(ObjInstr{OP_BVH_END, ni, cur, 0});
-                prog[begin].aux = (int)(prog.size() - 1 - begin);  // pc += aux, then ++pc: the instruction after OP_BVH_END
-                return std::max(d0, 1 + d1);
+                prog.push_back(ObjInstr{OP_MISS, ni, cur, 0});
+                int depth = 0;
+                struct Frame { int node; size_t gate; int next; };  // explicit stack: a degenerate tree may be as deep as it has nodes
+                std::vector<Frame> st;
+                st.push_back(Frame{ni, (size_t)-1, 0});
+                while (!st.empty()) {
+                    Frame& f = st.back();
+                    if (f.next == 2) {
+                        if (f.gate != (size_t)-1) prog[f.gate].aux = (int)(prog.size() - 1 - f.gate);  // pc += aux, then ++pc
+                        st.pop_back();
+                        continue;
+                    }
+                    const rs_node& b = nodes[f.node];
+                    const int c = f.next++ == 0 ? b.child0 : b.child1;
+                    if (c < 0) continue;  // a child that is None contributes nothing
+                    if (nodes[c].type == RS_NODE_BVH) {
+                        prog.push_back(ObjInstr{OP_BVH_GATE, c, cur, 0});
+                        st.push_back(Frame{c, prog.size() - 1, 0});  // (invalidates f)
+                    } else {
+                        depth = std::max(depth, emit(c, cur, in_medium));
+                        prog.push_back(ObjInstr{OP_BVH_END, ni, cur, 0});
+                    }
+                }
+                prog[begin].aux = (int)(prog.size() - 1 - begin);  // on a miss of the top gate: past the last instruction
+                return 1 + std::max(depth, 1);
             }
             default:
                 prog.push_back(ObjInstr{OP_LEAF, ni, cur, 0});

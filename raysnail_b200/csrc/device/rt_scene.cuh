@@ -751,6 +751,7 @@ enum ObjOp : int {
     OP_MED_END = 6,    // node = the medium, xf = its space: free-flight sample, push the result
     OP_BVH_BEGIN = 7,  // node = a BVH used as an object (bvh.rs:173-192), xf = its space: AABB::hit on its bbox; on a miss push a miss and skip `aux` instructions (past its OP_BVH_END)
     OP_BVH_END = 9,    // pop right, pop left, push the closer one (right only when strictly closer: bvh.rs:181-189)
+    OP_BVH_GATE = 11,  // node = a BVH node INSIDE a BVH object: AABB::hit on its bbox; on a miss skip `aux` instructions (its whole subtree), push nothing
     OP_MISS = 10,      // push a miss (a child that is None)
 };
 enum ObjFlavor : int {
@@ -976,6 +977,14 @@ static __device__ __noinline__ bool eval_object(const rs_node* nodes, const Xfor
                 if (RS_IN_BOUNDS(sp < RS_EVAL_STACK)) stack[sp++] = e;
                 pc += aux;
             }
+        } else if (op == OP_BVH_GATE) {  // bvh.rs:174-177 for the nodes below the top of a BVH object (see ProgramBuilder::emit)
+            const rs_node& n = nodes[ni];
+            if (xi != cur_xi) {
+                r = xi >= 0 ? xf_ray(xf[xi].inv, ray) : ray;
+                cur_xi = xi;
+            }
+            const V3 inv = v3(1.0 / r.d.x, 1.0 / r.d.y, 1.0 / r.d.z);
+            if (n.p[6] == 0.0 || !aabb_hit_f64(n.p, r, inv, lo, hi)) pc += aux;
         } else if (op == OP_BVH_END) {
             // bvh.rs:181-189 searches the right child over start..left.t1 and prefers its hit.  Here both children are
             // searched over the node's own limits and the right one wins when strictly closer — the same winner, and (as

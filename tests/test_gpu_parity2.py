@@ -571,6 +571,66 @@ def bvh_scene():
     return s
 
 
+def test_a_bvh_of_400_members_as_one_world_object(renderer):
+    """The reference's all_feature scene adds `BVH::new` over 400 boxes as ONE world object
+    (examples/common/scene.rs:361, bvh.rs:173-192).  A balanced tree over 400 members is 9-10 levels deep; the object
+    program keeps one running result per BVH object, so its depth does not count against RS_MAX_TREE_DEPTH.  The same
+    400 boxes (a few spheres and one CSG member among them) added to the world one by one must give the same hits."""
+    rng = np.random.default_rng(400)
+
+    def build(as_one_object):
+        s = Scene()
+        s.add(s.sphere((0, -1000, 0), 1000.0, s.lambertian(s.solid(0.5, 0.5, 0.5))))
+        light = s.sphere((0, 30, 10), 8.0, s.diffuse_light(s.solid(1, 1, 1), 5.0))
+        s.add(light)
+        s.add_light(light)
+        r = np.random.default_rng(7)
+        members = []
+        for i in range(20):
+            for j in range(20):
+                x0, z0, hgt = -10.0 + i, -10.0 + j, float(r.uniform(0.1, 1.6))
+                m = s.lambertian(s.solid(float(r.uniform(0.2, 0.9)), float(r.uniform(0.2, 0.9)), float(r.uniform(0.2, 0.9))))
+                if (i * 20 + j) % 37 == 5:
+                    members.append(s.sphere((x0 + 0.5, hgt, z0 + 0.5), 0.45, s.metal(s.solid(0.8, 0.8, 0.7))))
+                elif (i, j) == (9, 12):
+                    members.append(s.difference(s.box((x0, 0.0, z0), (x0 + 0.9, 1.5, z0 + 0.9), m), s.sphere((x0 + 0.45, 1.5, z0 + 0.45), 0.4), -1))
+                else:
+                    members.append(s.box((x0, 0.0, z0), (x0 + 0.9, hgt, z0 + 0.9), m))
+        if as_one_object:
+            s.add(s.bvh(members))
+        else:
+            for m in members:
+                s.add(m)
+        s.set_camera((3.0, 9.0, 16.0), (0.0, 0.5, 0.0), fov=48.0)
+        return s
+
+    one, flat = build(True), build(False)
+    cam = one.camera(W, H)
+    params = make_params(samples=9, flags=RS_FLAG_PIXEL_CENTRE)
+    renderer.upload(flat)
+    f = renderer.debug_primary(cam, params, 0)
+    renderer.upload(one)  # refused before round 3: "object tree deeper than RS_MAX_TREE_DEPTH"
+    g = renderer.debug_primary(cam, params, 0)
+    o = OracleWorld(one).debug_primary(cam, params, 0)
+    assert np.array_equal(g["obj_id"], o["obj_id"])
+    hit = o["obj_id"] >= 0
+    assert (o["obj_id"] == 2).mean() > 0.2  # the BVH object fills a good part of the frame
+    assert _rel_err(g["t"][hit], o["t"][hit]).max() < REL
+    assert np.abs(g["normal"][hit] - o["normal"][hit]).max() < REL
+    for key in ("front", "material"):
+        assert np.array_equal(g[key][hit], o[key][hit]), key
+    # one object or 400: the same surfaces are hit at the same distances (ids differ by construction)
+    assert np.array_equal(f["obj_id"] >= 2, g["obj_id"] == 2)
+    assert _rel_err(g["t"][hit], f["t"][hit]).max() < REL
+    assert np.abs(g["normal"][hit] - f["normal"][hit]).max() < REL  # (material indices are per scene and not comparable)
+    check_scatter(renderer.debug_scatter(cam, make_params(samples=9), 4), OracleWorld(one).debug_scatter(cam, make_params(samples=9), 4), "bvh400")
+    small = one.camera(64, 40)
+    gi = renderer.render(small, make_params(samples=64))
+    oi, _ = OracleWorld(one).render(small, make_params(samples=64))
+    rmse = float(np.sqrt(np.mean((gi[..., :3] - oi[..., :3]) ** 2))) / float(np.sqrt(np.mean(oi[..., :3] ** 2)))
+    assert rmse < 0.01, rmse
+
+
 def test_a_bvh_as_one_world_object(renderer):
     scene = bvh_scene()
     renderer.upload(scene)
