@@ -862,20 +862,23 @@ int render_into(rs_ctx* ctx, const rs_camera* cam, const rs_render_params* p, co
         // grow fit into 80 % of what is free now (the image does not depend on the wave size beyond the rounding of the
         // per-wave sums); 1 Mi paths (1.1 GB for four sets) is the floor, below it the allocation may simply fail.
         constexpr size_t kBytesPerPath = 272;
+        auto missing = [&] {
+            size_t need = 0;
+            for (int k = 0; k < n_sets; ++k)
+                if (ctx->wset[k].capacity < P * K) need += (size_t)P * K * kBytesPerPath;
+            return need;
+        };
         size_t free_b = 0, total_b = 0;
-        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
-            auto missing = [&] {
-                size_t need = 0;
-                for (int k = 0; k < n_sets; ++k)
-                    if (ctx->wset[k].capacity < P * K) need += (size_t)P * K * kBytesPerPath;
-                return need;
-            };
-            while (cap > (1u << 20) && missing() > free_b / 5 * 4) {
-                cap >>= 1;
-                partition();
+        // (the query is not free — tens of microseconds to a millisecond — so frames whose buffers exist never make it)
+        if (missing() > 0) {
+            if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+                while (cap > (1u << 20) && missing() > free_b / 5 * 4) {
+                    cap >>= 1;
+                    partition();
+                }
+            } else {
+                cudaGetLastError();
             }
-        } else {
-            cudaGetLastError();
         }
     }
     int rc = ensure_wave(ctx, P * K, n_sets);
